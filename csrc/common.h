@@ -1,0 +1,29 @@
+// Host-side helpers shared by all translation units: error plumbing for the C ABI.
+#pragma once
+#include <cuda_runtime.h>
+#include <stdarg.h>
+#include <stdio.h>
+
+#include "../include/dmlp_b200.h"
+
+namespace dmlp {
+
+// Stores a formatted message in the calling thread's error slot and returns `code`.
+int set_error(int code, const char* fmt, ...) __attribute__((format(printf, 2, 3)));
+
+#define DMLP_CUDA_CHECK(expr)                                                              \
+  do {                                                                                     \
+    cudaError_t _e = (expr);                                                               \
+    if (_e != cudaSuccess)                                                                 \
+      return ::dmlp::set_error(DMLP_ERR_CUDA, "%s failed: %s (%s:%d)", #expr,              \
+                               cudaGetErrorString(_e), __FILE__, __LINE__);                \
+  } while (0)
+
+#define DMLP_REQUIRE(cond, ...)                                          \
+  do {                                                                   \
+    if (!(cond)) return ::dmlp::set_error(DMLP_ERR_INVALID, __VA_ARGS__); \
+  } while (0)
+
+inline cudaStream_t as_stream(void* s) { return reinterpret_cast<cudaStream_t>(s); }
+
+}  // namespace dmlp

@@ -1,0 +1,391 @@
+// tcgen05 / TMEM / TMA GEMM with fused MLP epilogues (sm_100a only).
+//
+// One CTA computes a 128 x block_n output tile:
+//   warp 0      : TMA producer  (cp.async.bulk.tensor, 128B swizzle, mbarrier complete_tx)
+//   warp 1      : TMEM allocator + single-thread tcgen05.mma issuer (accumulator in TMEM)
+//   warps 2..5  : epilogue (tcgen05.ld -> bias / ReLU / ReLU-mask / column-sum -> global)
+// The smem ring has `stages` slots, each holding one 128-byte-wide K slab of A and B
+// (32 tf32 or 64 bf16 elements of K). block_n is a *runtime* value: the instruction
+// descriptor, the TMEM column count and the smem carve-up are all computed at launch.
+//
+// Provides (reference DSML/client/client.go): forward GEMM+bias+ReLU (:112-141),
+// dgrad + ReLU mask (:178-189), wgrad (:167-176, :191-199), bias-gradient column sums
+// (:173-175, :197-199).
+#include "common.h"
+#include "ptx_sm100.cuh"
+
+namespace dmlp {
+
+struct GemmParams {
+  int M, N, K;
+  int block_n;
+  int num_k_blocks;
+  int stages;
+  uint32_t tmem_cols;
+  uint32_t a_stage_bytes, b_stage_bytes;
+  uint32_t idesc;
+  float* out_f32;
+  long long ld_out;
+  __nv_bfloat16* out_bf16;
+  long long ld_out_bf16;
+  const float* bias;
+  const void* mask;
+  long long ld_mask;
+  int mask_is_bf16;
+  float* colsum;
+  int relu;
+  int accumulate;
+};
+
+constexpr int kMaxStages = 8;
+constexpr int kGemmThreads = 192;
+
+template <int EB, bool A_MN, bool B_MN>
+__global__ void __launch_bounds__(kGemmThreads, 1)
+gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA,
+                    const __grid_constant__ CUtensorMap tmB, const GemmParams p) {
+  constexpr int BM = 128;
+  constexpr int KS = 128 / EB;            // K elements per pipeline stage (one 128 B swizzle row)
+  constexpr int UK = 32 / EB;             // K elements per tcgen05.mma
+  constexpr int ATOM_MN = 128 / EB;       // MN elements in one MN-major swizzle atom
+  constexpr uint32_t MN_ATOM_COL_BYTES = KS * 128;  // one MN-atom column of a stage (KS k-rows)
+
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) &
+                                             ~static_cast<uintptr_t>(1023));
+  uint8_t* smem_a = smem;
+  uint8_t* smem_b = smem + static_cast<size_t>(p.stages) * p.a_stage_bytes;
+
+  __shared__ __align__(8) uint64_t full_bar[kMaxStages];
+  __shared__ __align__(8) uint64_t empty_bar[kMaxStages];
+  __shared__ __align__(8) uint64_t tmem_full_bar;
+  __shared__ uint32_t tmem_base_slot;
+
+  const int warp = threadIdx.x >> 5;
+  const int lane = threadIdx.x & 31;
+  const int m0 = blockIdx.y * BM;
+  const int n0 = blockIdx.x * p.block_n;
+
+  if (warp == 0 && lane == 0) {
+    tma_prefetch_desc(&tmA);
+    tma_prefetch_desc(&tmB);
+    for (int s = 0; s < p.stages; ++s) {
+      mbar_init(&full_bar[s], 1);
+      mbar_init(&empty_bar[s], 1);
+    }
+    mbar_init(&tmem_full_bar, 1);
+    fence_mbar_init();
+  }
+  if (warp == 1) {
+    tmem_alloc(&tmem_base_slot, p.tmem_cols);
+    tmem_relinquish();
+  }
+  tc_fence_before_sync();
+  __syncthreads();
+  tc_fence_after_sync();
+  const uint32_t tmem_base = tmem_base_slot;
+
+  if (warp == 0) {
+    // ------------------------------------------------------------ TMA producer
+    if (lane == 0) {
+      const uint32_t stage_bytes = p.a_stage_bytes + p.b_stage_bytes;
+      for (int kb = 0; kb < p.num_k_blocks; ++kb) {
+        const int s = kb % p.stages;
+        const uint32_t ph = (kb / p.stages) & 1;
+        mbar_wait(&empty_bar[s], ph ^ 1);
+        mbar_arrive_expect_tx(&full_bar[s], stage_bytes);
+        uint8_t* a_dst = smem_a + static_cast<size_t>(s) * p.a_stage_bytes;
+        uint8_t* b_dst = smem_b + static_cast<size_t>(s) * p.b_stage_bytes;
+        const int k0 = kb * KS;
+        if constexpr (!A_MN) {
+          tma_load_2d(a_dst, &tmA, &full_bar[s], k0, m0);
+        } else {
+#pragma unroll
+          for (int j = 0; j < BM / ATOM_MN; ++j)
+            tma_load_2d(a_dst + j * MN_ATOM_COL_BYTES, &tmA, &full_bar[s], m0 + j * ATOM_MN, k0);
+        }
+        if constexpr (!B_MN) {
+          tma_load_2d(b_dst, &tmB, &full_bar[s], k0, n0);
+        } else {
+          const int n_atoms = (p.block_n + ATOM_MN - 1) / ATOM_MN;
+          for (int j = 0; j < n_atoms; ++j)
+            tma_load_2d(b_dst + j * MN_ATOM_COL_BYTES, &tmB, &full_bar[s], n0 + j * ATOM_MN, k0);
+        }
+      }
+    }
+  } else if (warp == 1) {
+    // ------------------------------------------------------------ MMA issuer (one thread)
+    if (lane == 0) {
+      for (int kb = 0; kb < p.num_k_blocks; ++kb) {
+        const int s = kb % p.stages;
+        const uint32_t ph = (kb / p.stages) & 1;
+        mbar_wait(&full_bar[s], ph);
+        tc_fence_after_sync();
+        const uint32_t a_addr = smem_u32(smem_a + static_cast<size_t>(s) * p.a_stage_bytes);
+        const uint32_t b_addr = smem_u32(smem_b + static_cast<size_t>(s) * p.b_stage_bytes);
+#pragma unroll
+        for (int k = 0; k < KS / UK; ++k) {
+          // K-major: step 32 B inside the 128 B swizzle row. MN-major: step UK k-rows of 128 B.
+          const uint64_t adesc = A_MN ? make_smem_desc(a_addr + k * UK * 128, MN_ATOM_COL_BYTES, 1024)
+                                      : make_smem_desc(a_addr + k * 32, 16, 1024);
+          const uint64_t bdesc = B_MN ? make_smem_desc(b_addr + k * UK * 128, MN_ATOM_COL_BYTES, 1024)
+                                      : make_smem_desc(b_addr + k * 32, 16, 1024);
+          tc_mma<EB>(tmem_base, adesc, bdesc, p.idesc, (kb | k) != 0 ? 1u : 0u);
+        }
+        tc_commit(&empty_bar[s]);  // frees the smem slot once these MMAs have read it
+        if (kb == p.num_k_blocks - 1) tc_commit(&tmem_full_bar);
+      }
+    }
+  } else {
+    // ------------------------------------------------------------ epilogue warps
+    const int q = warp & 3;  // TMEM lane quadrant this warp may access
+    const int row = q * 32 + lane;
+    const int m = m0 + row;
+    const bool m_ok = m < p.M;
+    mbar_wait(&tmem_full_bar, 0);
+    tc_fence_after_sync();
+    const uint32_t t_row = tmem_base + (static_cast<uint32_t>(q * 32) << 16);
+    for (int c = 0; c < p.block_n; c += 16) {
+      uint32_t r[16];
+      tmem_ld_x16(t_row + c, r);
+      tmem_ld_wait();
+      const int nb = n0 + c;
+      if (nb >= p.N) break;  // uniform across the CTA
+      float v[16];
+#pragma unroll
+      for (int j = 0; j < 16; ++j) v[j] = __uint_as_float(r[j]);
+      const bool full = (nb + 16 <= p.N);
+      if (p.bias != nullptr) {
+#pragma unroll
+        for (int j = 0; j < 16; ++j)
+          if (full || nb + j < p.N) v[j] += __ldg(p.bias + nb + j);
+      }
+      if (p.relu) {
+#pragma unroll
+        for (int j = 0; j < 16; ++j) v[j] = fmaxf(v[j], 0.f);
+      }
+      if (p.mask != nullptr && m_ok) {
+        if (p.mask_is_bf16) {
+          const __nv_bfloat16* mk =
+              reinterpret_cast<const __nv_bfloat16*>(p.mask) + static_cast<long long>(m) * p.ld_mask + nb;
+#pragma unroll
+          for (int j = 0; j < 16; ++j)
+            if (full || nb + j < p.N)
+              if (!(__bfloat162float(mk[j]) > 0.f)) v[j] = 0.f;
+        } else {
+          const float* mk = reinterpret_cast<const float*>(p.mask) + static_cast<long long>(m) * p.ld_mask + nb;
+#pragma unroll
+          for (int j = 0; j < 16; ++j)
+            if (full || nb + j < p.N)
+              if (!(mk[j] > 0.f)) v[j] = 0.f;
+        }
+      }
+      if (m_ok) {
+        if (p.out_f32 != nullptr) {
+          float* o = p.out_f32 + static_cast<long long>(m) * p.ld_out + nb;
+          const bool vec = full && ((reinterpret_cast<uintptr_t>(o) & 15) == 0);
+          if (p.accumulate) {
+#pragma unroll
+            for (int j = 0; j < 16; ++j)
+              if (full || nb + j < p.N) v[j] += o[j];
+          }
+          if (vec) {
+#pragma unroll
+            for (int j = 0; j < 16; j += 4)
+              *reinterpret_cast<float4*>(o + j) = make_float4(v[j], v[j + 1], v[j + 2], v[j + 3]);
+          } else {
+#pragma unroll
+            for (int j = 0; j < 16; ++j)
+              if (full || nb + j < p.N) o[j] = v[j];
+          }
+        }
+        if (p.out_bf16 != nullptr) {
+          __nv_bfloat16* o = p.out_bf16 + static_cast<long long>(m) * p.ld_out_bf16 + nb;
+          const bool vec = full && ((reinterpret_cast<uintptr_t>(o) & 15) == 0);
+          if (vec) {
+#pragma unroll
+            for (int j = 0; j < 16; j += 8) {
+              __nv_bfloat162 h0 = __floats2bfloat162_rn(v[j], v[j + 1]);
+              __nv_bfloat162 h1 = __floats2bfloat162_rn(v[j + 2], v[j + 3]);
+              __nv_bfloat162 h2 = __floats2bfloat162_rn(v[j + 4], v[j + 5]);
+              __nv_bfloat162 h3 = __floats2bfloat162_rn(v[j + 6], v[j + 7]);
+              uint4 pk;
+              pk.x = *reinterpret_cast<uint32_t*>(&h0);
+              pk.y = *reinterpret_cast<uint32_t*>(&h1);
+              pk.z = *reinterpret_cast<uint32_t*>(&h2);
+              pk.w = *reinterpret_cast<uint32_t*>(&h3);
+              *reinterpret_cast<uint4*>(o + j) = pk;
+            }
+          } else {
+#pragma unroll
+            for (int j = 0; j < 16; ++j)
+              if (full || nb + j < p.N) o[j] = __float2bfloat16_rn(v[j]);
+          }
+        }
+      }
+      if (p.colsum != nullptr) {
+        // Bias gradient: column sums over the rows of this tile (rows past M contribute zero).
+#pragma unroll
+        for (int j = 0; j < 16; ++j) {
+          float s = m_ok ? v[j] : 0.f;
+          s += __shfl_xor_sync(0xffffffffu, s, 16);
+          s += __shfl_xor_sync(0xffffffffu, s, 8);
+          s += __shfl_xor_sync(0xffffffffu, s, 4);
+          s += __shfl_xor_sync(0xffffffffu, s, 2);
+          s += __shfl_xor_sync(0xffffffffu, s, 1);
+          if (lane == j && nb + j < p.N) atomicAdd(p.colsum + nb + j, s);
+        }
+      }
+    }
+  }
+
+  tc_fence_before_sync();
+  __syncthreads();
+  if (warp == 1) {
+    tc_fence_after_sync();
+    tmem_dealloc(tmem_base, p.tmem_cols);
+  }
+}
+
+// ---------------------------------------------------------------------------- host side
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*,
+                                  const cuuint64_t*, const cuuint64_t*, const cuuint32_t*,
+                                  const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
+                                  CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+static EncodeTiledFn get_encode_fn() {
+  static EncodeTiledFn fn = nullptr;
+  if (fn == nullptr) {
+    void* p = nullptr;
+    cudaDriverEntryPointQueryResult qres;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &qres) ==
+            cudaSuccess &&
+        qres == cudaDriverEntryPointSuccess)
+      fn = reinterpret_cast<EncodeTiledFn>(p);
+  }
+  return fn;
+}
+
+// 2-D tensor map over a row-major [rows][ld] matrix (inner dimension `cols` contiguous).
+int make_tensor_map_2d(CUtensorMap* out, const void* base, int elem_bytes, bool is_bf16,
+                       uint64_t cols, uint64_t rows, uint64_t ld_elems, uint32_t box_cols,
+                       uint32_t box_rows, bool swizzle128) {
+  EncodeTiledFn fn = get_encode_fn();
+  if (fn == nullptr) return set_error(DMLP_ERR_CUDA, "cuTensorMapEncodeTiled is unavailable");
+  if ((reinterpret_cast<uintptr_t>(base) & 15) != 0)
+    return set_error(DMLP_ERR_INVALID, "TMA operand base %p is not 16-byte aligned", base);
+  if ((ld_elems * elem_bytes) % 16 != 0)
+    return set_error(DMLP_ERR_INVALID,
+                     "TMA operand leading dimension %llu elements is not a multiple of 16 bytes",
+                     (unsigned long long)ld_elems);
+  cuuint64_t gdim[2] = {cols, rows};
+  cuuint64_t gstride[1] = {ld_elems * static_cast<uint64_t>(elem_bytes)};
+  cuuint32_t box[2] = {box_cols, box_rows};
+  cuuint32_t estr[2] = {1, 1};
+  CUtensorMapDataType dt = is_bf16 ? CU_TENSOR_MAP_DATA_TYPE_BFLOAT16 : CU_TENSOR_MAP_DATA_TYPE_FLOAT32;
+  CUresult r = fn(out, dt, 2, const_cast<void*>(base), gdim, gstride, box, estr,
+                  CU_TENSOR_MAP_INTERLEAVE_NONE,
+                  swizzle128 ? CU_TENSOR_MAP_SWIZZLE_128B : CU_TENSOR_MAP_SWIZZLE_NONE,
+                  CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS)
+    return set_error(DMLP_ERR_CUDA, "cuTensorMapEncodeTiled failed with CUresult %d", (int)r);
+  return DMLP_OK;
+}
+
+template <int EB, bool A_MN, bool B_MN>
+static int launch_gemm(const CUtensorMap& tmA, const CUtensorMap& tmB, const GemmParams& p,
+                       dim3 grid, size_t smem_bytes, cudaStream_t stream) {
+  auto kern = gemm_tcgen05_kernel<EB, A_MN, B_MN>;
+  static unsigned long long attr_mask = 0;  // devices on which the smem opt-in has been applied
+  int dev = 0;
+  DMLP_CUDA_CHECK(cudaGetDevice(&dev));
+  if (!(attr_mask & (1ull << dev))) {
+    DMLP_CUDA_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                         227 * 1024 - 2048));
+    attr_mask |= 1ull << dev;
+  }
+  kern<<<grid, kGemmThreads, smem_bytes, stream>>>(tmA, tmB, p);
+  DMLP_CUDA_CHECK(cudaGetLastError());
+  return DMLP_OK;
+}
+
+static int ceil_div(int a, int b) { return (a + b - 1) / b; }
+
+int choose_block_n(int M, int N) {
+  const int tiles_m = ceil_div(M, 128);
+  int bn = ((N + 15) / 16) * 16;
+  if (bn > 256) bn = 256;
+  // Small problems are latency bound: spread N over more CTAs (down to the N=16 MMA minimum).
+  while (bn > 16 && (bn / 2) % 16 == 0 && tiles_m * ceil_div(N, bn) < 148) bn /= 2;
+  return bn;
+}
+
+}  // namespace dmlp
+
+using namespace dmlp;
+
+extern "C" int dmlp_gemm(const dmlp_gemm_desc_t* d, void* stream) {
+  DMLP_REQUIRE(d != nullptr, "dmlp_gemm: null descriptor");
+  DMLP_REQUIRE(d->dtype == DMLP_F32 || d->dtype == DMLP_BF16, "dmlp_gemm: dtype must be F32 (tf32) or BF16");
+  DMLP_REQUIRE(d->M > 0 && d->N > 0 && d->K > 0, "dmlp_gemm: empty problem %dx%dx%d", d->M, d->N, d->K);
+  DMLP_REQUIRE(d->A_dev && d->B_dev, "dmlp_gemm: null operand");
+  DMLP_REQUIRE(d->out_f32_dev || d->out_bf16_dev || d->colsum_dev, "dmlp_gemm: no output requested");
+  const bool bf16 = d->dtype == DMLP_BF16;
+  const int EB = bf16 ? 2 : 4;
+  const int KS = 128 / EB;
+  const int ATOM = 128 / EB;
+  int bn = d->block_n > 0 ? d->block_n : choose_block_n(d->M, d->N);
+  DMLP_REQUIRE(bn % 16 == 0 && bn >= 16 && bn <= 256, "dmlp_gemm: block_n %d must be a multiple of 16 in [16,256]", bn);
+
+  CUtensorMap tmA, tmB;
+  int rc;
+  if (d->a_major == 0)
+    rc = make_tensor_map_2d(&tmA, d->A_dev, EB, bf16, d->K, d->M, d->lda, KS, 128, true);
+  else
+    rc = make_tensor_map_2d(&tmA, d->A_dev, EB, bf16, d->M, d->K, d->lda, ATOM, KS, true);
+  if (rc) return rc;
+  if (d->b_major == 0)
+    rc = make_tensor_map_2d(&tmB, d->B_dev, EB, bf16, d->K, d->N, d->ldb, KS, bn, true);
+  else
+    rc = make_tensor_map_2d(&tmB, d->B_dev, EB, bf16, d->N, d->K, d->ldb, ATOM, KS, true);
+  if (rc) return rc;
+
+  GemmParams p{};
+  p.M = d->M; p.N = d->N; p.K = d->K;
+  p.block_n = bn;
+  p.num_k_blocks = ceil_div(d->K, KS);
+  p.a_stage_bytes = 128 * 128;
+  p.b_stage_bytes = d->b_major == 0 ? bn * 128 : ceil_div(bn, ATOM) * KS * 128;
+  const size_t stage_bytes = p.a_stage_bytes + p.b_stage_bytes;
+  const size_t budget = 200 * 1024;
+  int stages = static_cast<int>(budget / stage_bytes);
+  if (stages > kMaxStages) stages = kMaxStages;
+  if (stages > p.num_k_blocks) stages = p.num_k_blocks;
+  if (stages < 1) stages = 1;
+  p.stages = stages;
+  uint32_t cols = 32;
+  while (cols < static_cast<uint32_t>(bn)) cols <<= 1;
+  p.tmem_cols = cols;
+  p.idesc = make_instr_desc(EB, d->a_major != 0, d->b_major != 0, bn);
+  p.out_f32 = d->out_f32_dev; p.ld_out = d->ld_out;
+  p.out_bf16 = reinterpret_cast<__nv_bfloat16*>(d->out_bf16_dev); p.ld_out_bf16 = d->ld_out_bf16;
+  p.bias = d->bias_dev;
+  p.mask = d->mask_dev; p.ld_mask = d->ld_mask; p.mask_is_bf16 = d->mask_dtype == DMLP_BF16;
+  p.colsum = d->colsum_dev;
+  p.relu = d->relu; p.accumulate = d->accumulate;
+
+  dim3 grid(ceil_div(d->N, bn), ceil_div(d->M, 128));
+  const size_t smem = stages * stage_bytes + 1024;
+  cudaStream_t st = as_stream(stream);
+  const int key = (bf16 ? 4 : 0) | (d->a_major ? 2 : 0) | (d->b_major ? 1 : 0);
+  switch (key) {
+    case 0: return launch_gemm<4, false, false>(tmA, tmB, p, grid, smem, st);
+    case 1: return launch_gemm<4, false, true>(tmA, tmB, p, grid, smem, st);
+    case 2: return launch_gemm<4, true, false>(tmA, tmB, p, grid, smem, st);
+    case 3: return launch_gemm<4, true, true>(tmA, tmB, p, grid, smem, st);
+    case 4: return launch_gemm<2, false, false>(tmA, tmB, p, grid, smem, st);
+    case 5: return launch_gemm<2, false, true>(tmA, tmB, p, grid, smem, st);
+    case 6: return launch_gemm<2, true, false>(tmA, tmB, p, grid, smem, st);
+    default: return launch_gemm<2, true, true>(tmA, tmB, p, grid, smem, st);
+  }
+}

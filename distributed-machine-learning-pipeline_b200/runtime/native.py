@@ -1,0 +1,98 @@
+"""ctypes binding of ``libdmlp_b200.so`` (the C ABI declared in ``include/dmlp_b200.h``).
+
+The library is built in-tree by ``build_native.py`` and loaded from ``_native/``. On a machine
+with a GPU a missing library is a hard error (no silent eager fallback): ``lib()`` raises.
+ctypes releases the GIL for the duration of every call, so gRPC handler threads can block in
+native waits without stalling the interpreter.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+import threading
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+_SO_PATH = os.path.join(os.path.dirname(_HERE), "_native", "libdmlp_b200.so")
+
+OK, ERR_INVALID, ERR_CUDA, ERR_NOT_FOUND, ERR_TIMEOUT, ERR_ABORTED, ERR_UNSUPPORTED = range(7)
+F32, BF16, U8, I32, F16 = range(5)
+SUM, PROD, MIN, MAX, AVG = range(5)
+MAX_RANKS = 8
+
+DTYPE_SIZE = {F32: 4, BF16: 2, U8: 1, I32: 4, F16: 2}
+
+
+class NativeError(RuntimeError):
+    def __init__(self, code: int, msg: str):
+        super().__init__(f"dmlp native error {code}: {msg}")
+        self.code = code
+        self.message = msg
+
+
+class GemmDesc(C.Structure):
+    _fields_ = [
+        ("dtype", C.c_int), ("a_major", C.c_int), ("b_major", C.c_int),
+        ("M", C.c_int), ("N", C.c_int), ("K", C.c_int),
+        ("A", C.c_void_p), ("lda", C.c_int64),
+        ("B", C.c_void_p), ("ldb", C.c_int64),
+        ("out_f32", C.c_void_p), ("ld_out", C.c_int64),
+        ("out_bf16", C.c_void_p), ("ld_out_bf16", C.c_int64),
+        ("bias", C.c_void_p), ("relu", C.c_int),
+        ("mask", C.c_void_p), ("mask_dtype", C.c_int), ("ld_mask", C.c_int64),
+        ("colsum", C.c_void_p), ("accumulate", C.c_int), ("block_n", C.c_int),
+    ]
+
+
+_lib = None
+_lock = threading.Lock()
+
+
+def so_path() -> str:
+    return _SO_PATH
+
+
+def available() -> bool:
+    return os.path.exists(_SO_PATH)
+
+
+def _declare(lib) -> None:
+    vp, i32, i64, sz, f32 = C.c_void_p, C.c_int, C.c_int64, C.c_size_t, C.c_float
+    lib.dmlp_last_error.restype = C.c_char_p
+    lib.dmlp_build_info.restype = C.c_char_p
+    sigs = {
+        "dmlp_gemm": [C.POINTER(GemmDesc), vp],
+        "dmlp_softmax_ce": [vp, i64, vp, i32, i32, f32, vp, vp, vp, vp, vp, vp],
+        "dmlp_sgd": [vp, vp, sz, vp, f32, vp, vp],
+        "dmlp_fill_u32": [vp, C.c_uint32, sz, vp],
+        "dmlp_cast_f32_to_bf16": [vp, vp, sz, vp],
+    }
+    for name, args in sigs.items():
+        fn = getattr(lib, name)
+        fn.argtypes = args
+        fn.restype = C.c_int
+    # Optional symbols (declared by the modules that use them) are looked up lazily.
+
+
+def lib():
+    """Returns the loaded library, loading it on first use."""
+    global _lib
+    if _lib is None:
+        with _lock:
+            if _lib is None:
+                if not os.path.exists(_SO_PATH):
+                    raise NativeError(ERR_UNSUPPORTED,
+                                      f"{_SO_PATH} is missing; run `python build_native.py` (needs nvcc)")
+                l = C.CDLL(_SO_PATH, mode=C.RTLD_GLOBAL)
+                _declare(l)
+                _lib = l
+    return _lib
+
+
+def check(rc: int) -> None:
+    if rc != 0:
+        msg = lib().dmlp_last_error().decode("utf-8", "replace")
+        raise NativeError(rc, msg)
+
+
+def build_info() -> str:
+    return lib().dmlp_build_info().decode()

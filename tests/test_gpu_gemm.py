@@ -1,0 +1,107 @@
+"""Numerics of the tcgen05 GEMM kernels against plain PyTorch references (GPU only).
+
+Two references per case: (a) the same product computed in fp64 on inputs truncated to the
+precision the tensor core consumes (tf32: 10-bit mantissa, truncated) — this pins layout /
+descriptor correctness tightly; (b) the plain fp32 product, with the tolerance tf32/bf16 allows.
+"""
+import pytest
+import torch
+
+pytestmark = pytest.mark.gpu
+
+
+def _trunc_tf32(t: torch.Tensor) -> torch.Tensor:
+    return (t.contiguous().view(torch.int32) & ~0x1FFF).view(torch.float32)
+
+
+def _operand_ref(t: torch.Tensor) -> torch.Tensor:
+    return _trunc_tf32(t).double() if t.dtype == torch.float32 else t.double()
+
+
+def _rand(shape, dtype, ld=None):
+    rows, cols = shape
+    ld = ld or cols
+    buf = torch.randn(rows, ld, device="cuda", dtype=torch.float32).to(dtype)
+    return buf[:, :cols]
+
+
+CASES = [
+    # (M(batch), K(in), N(out)) — reference shapes, north-star small, ragged, multi-tile
+    (64, 784, 128), (64, 128, 64), (64, 64, 16), (64, 128, 16),
+    (128, 256, 256), (200, 100, 72), (512, 1024, 384), (1024, 512, 1024),
+]
+
+
+@pytest.mark.parametrize("dtype", [torch.float32, torch.bfloat16])
+@pytest.mark.parametrize("M,K,N", CASES)
+def test_forward_bias_relu(dtype, M, K, N):
+    from dmlp_b200.ops import kernels as k
+    torch.manual_seed(0)
+    ldk = (K + 7) // 8 * 8
+    ldn = (N + 7) // 8 * 8
+    x = _rand((M, K), dtype, ldk)
+    w = _rand((K, N), dtype, ldn) * 0.1
+    b = torch.randn(N, device="cuda")
+    out = torch.full((M, N), float("nan"), device="cuda")
+    out16 = torch.zeros((M, N), device="cuda", dtype=torch.bfloat16)
+    k.linear_forward(x, w, b, True, out=out, out_bf16=out16)
+    torch.cuda.synchronize()
+    ref = torch.relu(_operand_ref(x) @ _operand_ref(w) + b.double())
+    err = (out.double() - ref).abs().max().item()
+    assert err < 2e-3 * max(1.0, ref.abs().max().item()), f"max err {err}"
+    assert (out16.double() - ref).abs().max().item() < 2e-2 * max(1.0, ref.abs().max().item())
+
+
+@pytest.mark.parametrize("dtype", [torch.float32, torch.bfloat16])
+@pytest.mark.parametrize("M,K,N", CASES)
+def test_dgrad_mask_colsum(dtype, M, K, N):
+    """dX[M, K_in] = dZ[M, N_out] · W[K_in, N_out]ᵀ, masked; colsum = column sums of the result."""
+    from dmlp_b200.ops import kernels as k
+    torch.manual_seed(1)
+    ldn = (N + 7) // 8 * 8
+    dz = _rand((M, N), dtype, ldn)
+    w = _rand((K, N), dtype, ldn) * 0.1
+    h = torch.relu(torch.randn(M, K, device="cuda"))
+    out = torch.full((M, K), float("nan"), device="cuda")
+    cs = torch.zeros(K, device="cuda")
+    k.linear_dgrad(dz, w, h, out=out, colsum=cs)
+    torch.cuda.synchronize()
+    ref = (_operand_ref(dz) @ _operand_ref(w).T) * (h > 0)
+    scale = max(1.0, ref.abs().max().item())
+    assert (out.double() - ref).abs().max().item() < 2e-3 * scale
+    assert (cs.double() - ref.sum(0)).abs().max().item() < 2e-3 * scale * (M ** 0.5)
+
+
+@pytest.mark.parametrize("dtype", [torch.float32, torch.bfloat16])
+@pytest.mark.parametrize("B,M,N", CASES)
+def test_wgrad(dtype, B, M, N):
+    """dW[M_in, N_out] = act[B, M_in]ᵀ · dZ[B, N_out] (both operands MN-major)."""
+    from dmlp_b200.ops import kernels as k
+    torch.manual_seed(2)
+    ldm = (M + 7) // 8 * 8
+    ldn = (N + 7) // 8 * 8
+    act = _rand((B, M), dtype, ldm)
+    dz = _rand((B, N), dtype, ldn)
+    out = torch.full((M, N), float("nan"), device="cuda")
+    k.linear_wgrad(act, dz, out)
+    torch.cuda.synchronize()
+    ref = _operand_ref(act).T @ _operand_ref(dz)
+    scale = max(1.0, ref.abs().max().item())
+    assert (out.double() - ref).abs().max().item() < 2e-3 * scale
+    # accumulate mode adds on top
+    k.linear_wgrad(act, dz, out, accumulate=True)
+    torch.cuda.synchronize()
+    assert (out.double() - 2 * ref).abs().max().item() < 4e-3 * scale
+
+
+@pytest.mark.parametrize("bn", [16, 32, 64, 128, 256])
+def test_forward_explicit_block_n(bn):
+    from dmlp_b200.ops import kernels as k
+    torch.manual_seed(3)
+    x = _rand((300, 160), torch.float32)
+    w = _rand((160, 512), torch.float32)
+    out = torch.empty(300, 512, device="cuda")
+    k.linear_forward(x, w, None, False, out=out, block_n=bn)
+    torch.cuda.synchronize()
+    ref = _operand_ref(x) @ _operand_ref(w)
+    assert (out.double() - ref).abs().max().item() < 1e-3 * ref.abs().max().item()
