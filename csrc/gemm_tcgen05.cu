@@ -49,6 +49,10 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA,
   constexpr int UK = 32 / EB;             // K elements per tcgen05.mma
   constexpr int ATOM_MN = 128 / EB;       // MN elements in one MN-major swizzle atom
   constexpr uint32_t MN_ATOM_COL_BYTES = KS * 128;  // one MN-atom column of a stage (KS k-rows)
+  // MN-major swizzle flavour: 16-bit types use SWIZZLE_128B (8 K-rows per atom, 1024 B); 32-bit
+  // types must use SWIZZLE_128B_BASE32B (32 B chunks, 4 K-rows per atom, 512 B).
+  constexpr uint32_t MN_SBO = (EB == 4) ? 512 : 1024;
+  constexpr uint32_t MN_LAYOUT = (EB == 4) ? 1 : 2;
 
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) &
@@ -126,9 +130,9 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA,
 #pragma unroll
         for (int k = 0; k < KS / UK; ++k) {
           // K-major: step 32 B inside the 128 B swizzle row. MN-major: step UK k-rows of 128 B.
-          const uint64_t adesc = A_MN ? make_smem_desc(a_addr + k * UK * 128, MN_ATOM_COL_BYTES, 1024)
+          const uint64_t adesc = A_MN ? make_smem_desc(a_addr + k * UK * 128, MN_ATOM_COL_BYTES, MN_SBO, MN_LAYOUT)
                                       : make_smem_desc(a_addr + k * 32, 16, 1024);
-          const uint64_t bdesc = B_MN ? make_smem_desc(b_addr + k * UK * 128, MN_ATOM_COL_BYTES, 1024)
+          const uint64_t bdesc = B_MN ? make_smem_desc(b_addr + k * UK * 128, MN_ATOM_COL_BYTES, MN_SBO, MN_LAYOUT)
                                       : make_smem_desc(b_addr + k * 32, 16, 1024);
           tc_mma<EB>(tmem_base, adesc, bdesc, p.idesc, (kb | k) != 0 ? 1u : 0u);
         }
@@ -269,7 +273,7 @@ static EncodeTiledFn get_encode_fn() {
 // 2-D tensor map over a row-major [rows][ld] matrix (inner dimension `cols` contiguous).
 int make_tensor_map_2d(CUtensorMap* out, const void* base, int elem_bytes, bool is_bf16,
                        uint64_t cols, uint64_t rows, uint64_t ld_elems, uint32_t box_cols,
-                       uint32_t box_rows, bool swizzle128) {
+                       uint32_t box_rows, int swizzle /*0 none, 1 128B, 2 128B with 32B atoms*/) {
   EncodeTiledFn fn = get_encode_fn();
   if (fn == nullptr) return set_error(DMLP_ERR_CUDA, "cuTensorMapEncodeTiled is unavailable");
   if ((reinterpret_cast<uintptr_t>(base) & 15) != 0)
@@ -285,7 +289,9 @@ int make_tensor_map_2d(CUtensorMap* out, const void* base, int elem_bytes, bool 
   CUtensorMapDataType dt = is_bf16 ? CU_TENSOR_MAP_DATA_TYPE_BFLOAT16 : CU_TENSOR_MAP_DATA_TYPE_FLOAT32;
   CUresult r = fn(out, dt, 2, const_cast<void*>(base), gdim, gstride, box, estr,
                   CU_TENSOR_MAP_INTERLEAVE_NONE,
-                  swizzle128 ? CU_TENSOR_MAP_SWIZZLE_128B : CU_TENSOR_MAP_SWIZZLE_NONE,
+                  swizzle == 1 ? CU_TENSOR_MAP_SWIZZLE_128B
+                  : swizzle == 2 ? CU_TENSOR_MAP_SWIZZLE_128B_ATOM_32B
+                                 : CU_TENSOR_MAP_SWIZZLE_NONE,
                   CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
   if (r != CUDA_SUCCESS)
     return set_error(DMLP_ERR_CUDA, "cuTensorMapEncodeTiled failed with CUresult %d", (int)r);
@@ -339,15 +345,16 @@ extern "C" int dmlp_gemm(const dmlp_gemm_desc_t* d, void* stream) {
 
   CUtensorMap tmA, tmB;
   int rc;
+  const int mn_swz = bf16 ? 1 : 2;  // fp32 MN-major operands need the 32B-atom swizzle
   if (d->a_major == 0)
-    rc = make_tensor_map_2d(&tmA, d->A_dev, EB, bf16, d->K, d->M, d->lda, KS, 128, true);
+    rc = make_tensor_map_2d(&tmA, d->A_dev, EB, bf16, d->K, d->M, d->lda, KS, 128, 1);
   else
-    rc = make_tensor_map_2d(&tmA, d->A_dev, EB, bf16, d->M, d->K, d->lda, ATOM, KS, true);
+    rc = make_tensor_map_2d(&tmA, d->A_dev, EB, bf16, d->M, d->K, d->lda, ATOM, KS, mn_swz);
   if (rc) return rc;
   if (d->b_major == 0)
-    rc = make_tensor_map_2d(&tmB, d->B_dev, EB, bf16, d->K, d->N, d->ldb, KS, bn, true);
+    rc = make_tensor_map_2d(&tmB, d->B_dev, EB, bf16, d->K, d->N, d->ldb, KS, bn, 1);
   else
-    rc = make_tensor_map_2d(&tmB, d->B_dev, EB, bf16, d->N, d->K, d->ldb, ATOM, KS, true);
+    rc = make_tensor_map_2d(&tmB, d->B_dev, EB, bf16, d->N, d->K, d->ldb, ATOM, KS, mn_swz);
   if (rc) return rc;
 
   GemmParams p{};

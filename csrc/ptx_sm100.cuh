@@ -182,14 +182,16 @@ __device__ __forceinline__ void tmem_ld_wait() {
 //  K-major  tile: rows 128 B apart, 8-row groups `sbo` bytes apart (dense TMA box: 1024).
 //  MN-major tile: 128 B of MN contiguous x 8 K-rows per atom; K-atoms `sbo` bytes apart,
 //                 MN-atoms `lbo` bytes apart.
+//  32-bit MN-major operands only exist in the SWIZZLE_128B_BASE32B flavour (layout_type 1):
+//                 32 B chunks swizzled over 4 K-rows, so K-atoms are 4 rows (512 B dense).
 __device__ __forceinline__ uint64_t make_smem_desc(uint32_t saddr, uint32_t lbo_bytes,
-                                                   uint32_t sbo_bytes) {
+                                                   uint32_t sbo_bytes, uint32_t layout_type = 2) {
   uint64_t d = 0;
   d |= static_cast<uint64_t>((saddr & 0x3FFFFu) >> 4);
   d |= static_cast<uint64_t>((lbo_bytes >> 4) & 0x3FFFu) << 16;
   d |= static_cast<uint64_t>((sbo_bytes >> 4) & 0x3FFFu) << 32;
   d |= 1ull << 46;  // descriptor version (Blackwell)
-  d |= 2ull << 61;  // SWIZZLE_128B
+  d |= static_cast<uint64_t>(layout_type) << 61;  // 2 = SWIZZLE_128B, 1 = SWIZZLE_128B_BASE32B
   return d;
 }
 

@@ -13,7 +13,7 @@ ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 sys.path.insert(0, ROOT)
 
 SHAPES = [(64, 784, 128), (64, 128, 64), (64, 64, 16), (128, 32, 16), (128, 64, 32), (128, 256, 256),
-          (200, 100, 72), (512, 1024, 384), (4096, 4096, 4096)]
+          (200, 104, 72), (512, 1024, 384), (4096, 4096, 4096)]
 
 
 def trunc(t):
