@@ -26,4 +26,18 @@ int set_error(int code, const char* fmt, ...) __attribute__((format(printf, 2, 3
 
 inline cudaStream_t as_stream(void* s) { return reinterpret_cast<cudaStream_t>(s); }
 
+// Selects a device for the current scope and restores the caller's device afterwards, so the
+// library never changes the current device behind PyTorch's back.
+struct DeviceGuard {
+  int prev = -1;
+  bool ok = true;
+  explicit DeviceGuard(int dev) {
+    if (cudaGetDevice(&prev) != cudaSuccess) prev = -1;
+    if (prev != dev) ok = cudaSetDevice(dev) == cudaSuccess;
+  }
+  ~DeviceGuard() {
+    if (prev >= 0) cudaSetDevice(prev);
+  }
+};
+
 }  // namespace dmlp

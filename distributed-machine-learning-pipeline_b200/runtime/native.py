@@ -43,6 +43,31 @@ class GemmDesc(C.Structure):
     ]
 
 
+class DeviceInfo(C.Structure):
+    _fields_ = [
+        ("name", C.c_char * 128), ("uuid", C.c_char * 48),
+        ("sm_count", C.c_int), ("cc_major", C.c_int), ("cc_minor", C.c_int), ("clock_khz", C.c_int),
+        ("multicast_supported", C.c_int), ("smem_per_block_optin", C.c_int),
+        ("total_mem", C.c_size_t), ("l2_bytes", C.c_size_t),
+    ]
+
+
+ALGO_AUTO, ALGO_ONESHOT, ALGO_TWOSHOT, ALGO_RING, ALGO_NVLS = range(5)
+ALGO_BY_NAME = {"auto": ALGO_AUTO, "oneshot": ALGO_ONESHOT, "twoshot": ALGO_TWOSHOT, "ring": ALGO_RING,
+                "nvls": ALGO_NVLS}
+ALGO_NAMES = {v: k for k, v in ALGO_BY_NAME.items()}
+
+
+class AllReduceDesc(C.Structure):
+    _fields_ = [
+        ("algo", C.c_int), ("dtype", C.c_int), ("op", C.c_int), ("fuse_sgd", C.c_int),
+        ("skip_end_barrier", C.c_int), ("scale", C.c_float), ("count", C.c_size_t),
+        ("inp", C.c_void_p * MAX_RANKS), ("out", C.c_void_p * MAX_RANKS),
+        ("out_bf16", C.c_void_p * MAX_RANKS), ("lr", C.c_void_p * MAX_RANKS),
+        ("streams", C.c_void_p * MAX_RANKS),
+    ]
+
+
 _lib = None
 _lock = threading.Lock()
 
@@ -65,6 +90,46 @@ def _declare(lib) -> None:
         "dmlp_sgd": [vp, vp, sz, vp, f32, vp, vp],
         "dmlp_fill_u32": [vp, C.c_uint32, sz, vp],
         "dmlp_cast_f32_to_bf16": [vp, vp, sz, vp],
+        "dmlp_device_count": [C.POINTER(i32)],
+        "dmlp_device_info": [i32, C.POINTER(DeviceInfo)],
+        "dmlp_peer_matrix": [i32, C.POINTER(i32), C.POINTER(i32), C.POINTER(i32), C.POINTER(i32)],
+        "dmlp_enable_peer_access": [i32, C.POINTER(i32)],
+        "dmlp_malloc": [i32, sz, C.POINTER(vp)],
+        "dmlp_free": [i32, vp],
+        "dmlp_host_alloc": [sz, C.POINTER(vp)],
+        "dmlp_host_free": [vp],
+        "dmlp_memcpy_h2d": [i32, vp, vp, sz, vp],
+        "dmlp_memcpy_d2h": [i32, vp, vp, sz, vp],
+        "dmlp_memcpy_d2d": [i32, vp, vp, sz, vp],
+        "dmlp_memset": [i32, vp, i32, sz, vp],
+        "dmlp_stream_create": [i32, C.POINTER(vp)],
+        "dmlp_stream_destroy": [i32, vp],
+        "dmlp_stream_sync": [i32, vp],
+        "dmlp_stream_query": [i32, vp, C.POINTER(i32)],
+        "dmlp_stream_wait_event": [i32, vp, vp],
+        "dmlp_device_sync": [i32],
+        "dmlp_event_create": [i32, i32, C.POINTER(vp)],
+        "dmlp_event_destroy": [vp],
+        "dmlp_event_record": [i32, vp, vp],
+        "dmlp_event_query": [vp, C.POINTER(i32)],
+        "dmlp_event_sync": [vp],
+        "dmlp_event_elapsed_ms": [vp, vp, C.POINTER(f32)],
+        "dmlp_ipc_get_handle": [i32, vp, C.c_char_p],
+        "dmlp_ipc_open_handle": [i32, C.c_char_p, C.POINTER(vp)],
+        "dmlp_ipc_close_handle": [i32, vp],
+        "dmlp_comm_create": [i32, i32, C.POINTER(i32), C.POINTER(i32), sz, sz, C.POINTER(vp)],
+        "dmlp_comm_destroy": [vp],
+        "dmlp_comm_export": [vp, i32, C.c_char_p],
+        "dmlp_comm_import": [vp, i32, C.c_char_p],
+        "dmlp_comm_arena_ptr": [vp, i32, i32, C.POINTER(vp), C.POINTER(sz)],
+        "dmlp_comm_set_timeout_ms": [vp, C.c_uint64],
+        "dmlp_comm_abort": [vp],
+        "dmlp_comm_status": [vp, C.POINTER(C.c_uint32)],
+        "dmlp_comm_inject_dead_ranks": [vp, C.c_uint32],
+        "dmlp_allreduce": [vp, i32, C.POINTER(AllReduceDesc), vp],
+        "dmlp_allreduce_pick_algo": [i32, sz],
+        "dmlp_p2p_copy": [i32, vp, vp, sz, vp],
+        "dmlp_reduce_n": [i32, vp, C.POINTER(vp), i32, sz, i32, i32, vp],
     }
     for name, args in sigs.items():
         fn = getattr(lib, name)

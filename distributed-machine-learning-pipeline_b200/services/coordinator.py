@@ -1,0 +1,646 @@
+"""GPUCoordinator service: communicator registry, collectives, group ops, health monitor.
+
+Contract kept from the reference (``DSML/gpu_coordinator_service/gpu_coordinator_server.go``):
+  * ``CommInit``       ranks follow ``device_addresses`` order; any unreachable/invalid device fails
+                       the whole call with ``Internal`` (commId is still consumed); ``numDevices``
+                       alone (no addresses) binds that many local GPUs as an extension (:121-192)
+  * ``Memcpy``         H2D bound ``0x1000 <= addr <= 0x2000`` → ``InvalidArgument`` (:199-201);
+                       D2H of unknown device/address → ``Internal`` (:221-230)
+  * ``GroupStart/End`` unknown communicator → ``NotFound`` (:242-270)
+  * ``AllReduceRing``  ``NotFound`` / ``FailedPrecondition`` on a FAILED communicator / immediate
+                       SUCCESS for fewer than two devices / status SUCCESS afterwards (:272-376)
+  * ``NaiveAllReduce`` gather → reduce → broadcast to 0x2000 with ``latencyMs`` sleeps, returning
+                       ``totalTimeMs`` and ``2·n·dataSize`` (:611-717)
+  * health monitor     every ``health_interval`` s each device is probed (2 s timeout); a device
+                       that does not answer is dropped and the communicator turns FAILED, sticky
+                       (:54-119). ``CommFinalize`` (unimplemented in the reference) is provided.
+
+What differs on purpose (SURVEY §3.2 lists the reference defects): the reduction really crosses
+devices; ``op`` and ``memAddrs`` are honoured; the coordinator's ``Memcpy`` writes the *device's*
+memory (one source of truth) instead of a private host map; ``count`` is bytes and the element
+type comes from gRPC metadata ``dmlp-dtype`` (default ``f32`` when ``count % 4 == 0`` else ``u8``).
+
+Execution paths for collectives:
+  native    all devices are in-process CUDA backends → one fused kernel per rank over peer memory
+            (``runtime.comm.Communicator``); metadata ``dmlp-algo`` picks ring/oneshot/twoshot/auto
+  portable  anything else (sim devices, remote devices) → the ring schedule is driven through the
+            device RPC contract (BeginSend/BeginReceive/StreamSend/GetStreamStatus/Memcpy)
+"""
+from __future__ import annotations
+
+import logging
+import threading
+import time
+from dataclasses import dataclass, field
+from typing import Callable, Dict, List, Optional, Tuple
+
+import grpc
+import numpy as np
+
+from ..proto import gpu_sim as pb
+from ..proto import rpc
+from .device import GPUDeviceService
+
+log = logging.getLogger("dmlp.coordinator")
+
+DEFAULT_ADDR = 0x1000
+RECV_ADDR = 0x2000
+COORD_MIN_ADDR, COORD_MAX_ADDR = 0x1000, 0x2000  # inclusive upper bound, as in the reference (:199)
+
+_NP_DTYPES = {"u8": np.uint8, "i32": np.int32, "f32": np.float32, "bf16": None}
+_NP_OPS = {pb.SUM: np.add, pb.PROD: np.multiply, pb.MIN: np.minimum, pb.MAX: np.maximum}
+
+# In-process registry: listening address -> device service. A coordinator living in the same
+# process as the device servers (the normal B200 deployment: one daemon owns all 8 GPUs) finds the
+# devices here and drives the GPUs directly; gRPC to them is then only used for health probes.
+LOCAL_DEVICES: Dict[str, GPUDeviceService] = {}
+_LOCAL_LOCK = threading.Lock()
+
+
+def register_local_device(addr: str, svc: GPUDeviceService) -> None:
+    with _LOCAL_LOCK:
+        LOCAL_DEVICES[addr] = svc
+        host, _, port = addr.rpartition(":")
+        for alias in ("localhost", "127.0.0.1", "[::1]", "[::]", "0.0.0.0"):
+            LOCAL_DEVICES[f"{alias}:{port}"] = svc
+
+
+def unregister_local_device(addr: str) -> None:
+    with _LOCAL_LOCK:
+        svc = LOCAL_DEVICES.pop(addr, None)
+        if svc is not None:
+            for k in [k for k, v in LOCAL_DEVICES.items() if v is svc]:
+                LOCAL_DEVICES.pop(k, None)
+
+
+@dataclass
+class DeviceInfo:
+    rank: int
+    device_id: int
+    addr: str
+    stub: rpc.DeviceStub
+    channel: grpc.Channel
+    local: Optional[GPUDeviceService] = None
+    last_health: float = field(default_factory=time.time)
+
+
+@dataclass
+class QueuedOp:
+    run: Callable[[], None]
+    name: str
+
+
+class Communicator:
+    def __init__(self, comm_id: int, devices: List[DeviceInfo]):
+        self.id = comm_id
+        self.devices = devices
+        self.status = pb.IN_PROGRESS
+        self.mu = threading.Lock()
+        self.group_active = False
+        self.queue: List[QueuedOp] = []
+        self.native = None  # runtime.comm.Communicator when every device is an in-process CUDA backend
+        self.finalized = False
+        self.failure_reason = ""
+
+
+class GPUCoordinatorService:
+    def __init__(self, health_interval: float = 5.0, probe_timeout: float = 2.0,
+                 watchdog_ms: int = 10000, start_monitor: bool = True):
+        self.mu = threading.Lock()
+        self.next_comm_id = 0
+        self.communicators: Dict[int, Communicator] = {}
+        self.health_interval = health_interval
+        self.probe_timeout = probe_timeout
+        self.watchdog_ms = watchdog_ms
+        # Staging for Memcpy to devices this coordinator has never seen in a communicator
+        # (the reference always stores on the coordinator; kept only as that fallback).
+        self.host_memory: Dict[int, Dict[int, bytes]] = {}
+        self._stop = threading.Event()
+        self._monitor: Optional[threading.Thread] = None
+        if start_monitor:
+            self._monitor = threading.Thread(target=self._health_loop, name="dmlp-health", daemon=True)
+            self._monitor.start()
+
+    # ------------------------------------------------------------------ lifecycle
+    def Stop(self) -> None:
+        """Ends the health monitor (reference ``Stop()``, :65-67) and releases native communicators."""
+        self._stop.set()
+        if self._monitor is not None:
+            self._monitor.join(timeout=self.probe_timeout + 1)
+        with self.mu:
+            comms = list(self.communicators.values())
+        for c in comms:
+            self._release(c)
+
+    def _release(self, comm: Communicator) -> None:
+        if comm.native is not None:
+            try:
+                comm.native.abort()
+                comm.native.destroy()
+            except Exception as e:  # pragma: no cover
+                log.warning("releasing native communicator %d: %s", comm.id, e)
+            comm.native = None
+        for d in comm.devices:
+            try:
+                d.channel.close()
+            except Exception:
+                pass
+
+    # ------------------------------------------------------------------ health monitor (:69-119)
+    def _health_loop(self) -> None:
+        while not self._stop.wait(self.health_interval):
+            self.check_all_communicator_health()
+
+    def check_all_communicator_health(self) -> None:
+        with self.mu:
+            comms = list(self.communicators.values())
+        for comm in comms:
+            self._check_communicator_health(comm)
+
+    def _check_communicator_health(self, comm: Communicator) -> None:
+        with comm.mu:
+            if comm.status == pb.FAILED:
+                return
+            devices = list(comm.devices)
+            native = comm.native
+        alive, failed = [], []
+        for d in devices:  # network probes run without holding any lock
+            try:
+                d.stub.GetDeviceMetadata(pb.GetDeviceMetadataRequest(), timeout=self.probe_timeout)
+                d.last_health = time.time()
+                alive.append(d)
+            except grpc.RpcError as e:
+                log.warning("Device %d at %s unreachable: %s", d.device_id, d.addr, e.code())
+                failed.append(d)
+        reason = ""
+        if native is not None:  # CUDA-level heartbeat: a watchdog that fired inside a collective kernel
+            st = native.status()
+            if st["code"] != 0:
+                reason = (f"collective watchdog: rank {st['rank']} waited for rank {st['peer']} "
+                          f"({st['phase_name']})")
+        if failed or reason:
+            with comm.mu:
+                comm.devices = alive if failed else comm.devices
+                comm.status = pb.FAILED
+                comm.failure_reason = reason or f"lost devices {[d.device_id for d in failed]}"
+            log.warning("Communicator %d lost devices; marking as FAILED (%s)", comm.id, comm.failure_reason)
+            if native is not None:
+                native.abort()  # release any kernel still spinning on the dead peer
+
+    # ------------------------------------------------------------------ helpers
+    def _get(self, comm_id: int, context) -> Communicator:
+        with self.mu:
+            comm = self.communicators.get(comm_id)
+        if comm is None:
+            context.abort(grpc.StatusCode.NOT_FOUND, "Communicator not found")
+        return comm
+
+    def _find_device(self, device_id: int) -> Optional[DeviceInfo]:
+        with self.mu:
+            comms = list(self.communicators.values())
+        for c in comms:
+            for d in c.devices:
+                if d.device_id == device_id:
+                    return d
+        return None
+
+    @staticmethod
+    def _metadata(context) -> Dict[str, str]:
+        try:
+            return {k.lower(): v for k, v in (context.invocation_metadata() or ())}
+        except Exception:
+            return {}
+
+    # ------------------------------------------------------------------ CommInit (:121-192)
+    def CommInit(self, request, context):
+        with self.mu:
+            comm_id = self.next_comm_id
+            self.next_comm_id += 1
+        addrs = list(request.device_addresses)
+        devices: List[DeviceInfo] = []
+        errors: List[str] = []
+        if not addrs and request.numDevices > 0 and self._metadata(context).get("dmlp-bind-local") == "1":
+            # opt-in extension (metadata dmlp-bind-local=1): no addresses → bind the first numDevices
+            # in-process devices. Without the opt-in an empty list is a valid 0-device communicator,
+            # which the reference's TestCoordinatorAllReduceRing relies on (:259).
+            seen, picked = set(), []
+            for a, svc in sorted(LOCAL_DEVICES.items()):
+                if id(svc) not in seen and a.startswith("127.0.0.1"):
+                    seen.add(id(svc))
+                    picked.append(a)
+            if len(picked) >= request.numDevices:
+                addrs = picked[:request.numDevices]
+        for i, addr in enumerate(addrs):
+            try:
+                channel = rpc.insecure_channel(addr)
+                stub = rpc.DeviceStub(channel)
+                md = stub.GetDeviceMetadata(pb.GetDeviceMetadataRequest(), timeout=self.probe_timeout)
+            except (grpc.RpcError, ValueError, Exception) as e:  # bad address formats raise at call time
+                errors.append(f"GetDeviceMetadata failed for {addr}: {getattr(e, 'code', lambda: e)()}")
+                continue
+            with _LOCAL_LOCK:
+                local = LOCAL_DEVICES.get(addr)
+            devices.append(DeviceInfo(rank=i, device_id=md.metadata.deviceId.value, addr=addr, stub=stub,
+                                      channel=channel, local=local))
+        if errors:
+            for d in devices:
+                d.channel.close()
+            context.abort(grpc.StatusCode.INTERNAL, f"CommInit encountered errors: {errors}")
+        comm = Communicator(comm_id, devices)
+        self._setup_native(comm)
+        peers = {d.rank: d.local for d in devices if d.local is not None}
+        for d in devices:
+            if d.local is not None:
+                d.local.set_peers(d.rank, peers)
+        with self.mu:
+            self.communicators[comm_id] = comm
+        # The reference answers with hard-coded 0x1000/0x2000 bounds (:178-185); kept for parity.
+        metas = [pb.DeviceMetadata(deviceId=pb.DeviceId(value=d.device_id),
+                                   minMemAddr=pb.MemAddr(value=COORD_MIN_ADDR),
+                                   maxMemAddr=pb.MemAddr(value=COORD_MAX_ADDR)) for d in devices]
+        return pb.CommInitResponse(success=True, commId=comm_id, devices=metas)
+
+    def _setup_native(self, comm: Communicator) -> None:
+        """All devices in-process and CUDA-backed → build the peer-memory communicator."""
+        devs = comm.devices
+        if len(devs) < 2 or not all(d.local is not None and d.local.backend.kind == "cuda" for d in devs):
+            return
+        try:
+            from ..runtime.comm import Communicator as NativeComm
+            ordinals = [d.local.backend.ordinal for d in devs]
+            comm.native = NativeComm.local(ordinals, staging_bytes=16 << 20)
+            comm.native.set_timeout_ms(self.watchdog_ms)
+        except Exception as e:
+            log.error("native communicator unavailable, using the portable path: %s", e)
+            comm.native = None
+
+    # ------------------------------------------------------------------ Memcpy (:194-240)
+    def Memcpy(self, request, context):
+        which = request.WhichOneof("either")
+        if which == "hostToDevice":
+            h2d = request.hostToDevice
+            did, addr = h2d.dstDeviceId.value, h2d.dstMemAddr.value
+            if addr < COORD_MIN_ADDR or addr > COORD_MAX_ADDR:
+                context.abort(grpc.StatusCode.INVALID_ARGUMENT, "Memory address out of bounds")
+            dev = self._find_device(did)
+            if dev is None:
+                with self.mu:
+                    self.host_memory.setdefault(did, {})[addr] = bytes(h2d.hostSrcData)
+            else:
+                self._dev_write(dev, addr, h2d.hostSrcData, context)
+            return pb.MemcpyResponse(hostToDevice=pb.MemcpyHostToDeviceResponse(success=True))
+        if which == "deviceToHost":
+            d2h = request.deviceToHost
+            did, addr = d2h.srcDeviceId.value, d2h.srcMemAddr.value
+            dev = self._find_device(did)
+            if dev is None:
+                with self.mu:
+                    mem = self.host_memory.get(did)
+                    if mem is None:
+                        context.abort(grpc.StatusCode.INTERNAL, f"No memory initialized for device {did}")
+                    data = mem.get(addr)
+                if data is None:
+                    context.abort(grpc.StatusCode.INTERNAL, f"DeviceToHost: no data at address 0x{addr:x}")
+                return pb.MemcpyResponse(deviceToHost=pb.MemcpyDeviceToHostResponse(dstData=data))
+            data = self._dev_read(dev, addr, d2h.numBytes, context)
+            return pb.MemcpyResponse(deviceToHost=pb.MemcpyDeviceToHostResponse(dstData=data))
+        context.abort(grpc.StatusCode.INVALID_ARGUMENT,
+                      "Invalid Memcpy request: must specify hostToDevice or deviceToHost")
+
+    def _dev_write(self, dev: DeviceInfo, addr: int, data: bytes, context=None) -> None:
+        req = pb.MemcpyRequest(hostToDevice=pb.MemcpyHostToDeviceRequest(
+            hostSrcData=data, dstDeviceId=pb.DeviceId(value=dev.device_id), dstMemAddr=pb.MemAddr(value=addr)))
+        try:
+            if dev.local is not None and not dev.local.backend.dead:
+                dev.local.backend.check_addr(addr)
+                dev.local.backend.write(addr, data)
+            else:
+                dev.stub.Memcpy(req, timeout=60)
+        except grpc.RpcError as e:
+            if context is not None:
+                context.abort(e.code(), e.details())
+            raise
+        except ValueError as e:
+            if context is not None:
+                context.abort(grpc.StatusCode.INVALID_ARGUMENT, str(e))
+            raise
+
+    def _dev_read(self, dev: DeviceInfo, addr: int, nbytes: int = 0, context=None) -> bytes:
+        req = pb.MemcpyRequest(deviceToHost=pb.MemcpyDeviceToHostRequest(
+            srcDeviceId=pb.DeviceId(value=dev.device_id), srcMemAddr=pb.MemAddr(value=addr), numBytes=nbytes))
+        try:
+            if dev.local is not None and not dev.local.backend.dead:
+                dev.local.backend.check_addr(addr)
+                return dev.local.backend.read(addr, nbytes)
+            return dev.stub.Memcpy(req, timeout=60).deviceToHost.dstData
+        except grpc.RpcError as e:
+            if context is not None:
+                context.abort(e.code(), e.details())
+            raise
+        except KeyError as e:
+            if context is not None:
+                context.abort(grpc.StatusCode.INTERNAL, f"DeviceToHost: {e.args[0] if e.args else e}")
+            raise
+        except ValueError as e:
+            if context is not None:
+                context.abort(grpc.StatusCode.INVALID_ARGUMENT, str(e))
+            raise
+
+    # ------------------------------------------------------------------ group ops (:242-270)
+    def GroupStart(self, request, context):
+        comm = self._get(request.commId, context)
+        with comm.mu:
+            comm.group_active = True
+        return pb.GroupStartResponse(success=True)
+
+    def GroupEnd(self, request, context):
+        """Ops issued since GroupStart were queued; they are launched back to back here (one fused
+        submission), the way ncclGroupEnd flushes a group. The reference only flips a flag."""
+        comm = self._get(request.commId, context)
+        with comm.mu:
+            comm.group_active = False
+            queued, comm.queue = comm.queue, []
+        for op in queued:
+            try:
+                op.run()
+            except Exception as e:
+                with comm.mu:
+                    comm.status = pb.FAILED
+                    comm.failure_reason = f"{op.name}: {e}"
+                context.abort(grpc.StatusCode.UNKNOWN, f"{op.name} failed at GroupEnd: {e}")
+        if queued:
+            with comm.mu:
+                if comm.status != pb.FAILED:
+                    comm.status = pb.SUCCESS
+        return pb.GroupEndResponse(success=True)
+
+    # ------------------------------------------------------------------ AllReduceRing (:272-376)
+    def AllReduceRing(self, request, context):
+        comm = self._get(request.commId, context)
+        with comm.mu:
+            if comm.status == pb.FAILED:
+                context.abort(grpc.StatusCode.FAILED_PRECONDITION, "Communicator is in FAILED state")
+            devices = list(comm.devices)
+            grouped = comm.group_active
+        n = len(devices)
+        if n < 2:
+            with comm.mu:
+                comm.status = pb.SUCCESS
+            return pb.AllReduceRingResponse(success=True)
+        md = self._metadata(context)
+        count = int(request.count)
+        dtype = md.get("dmlp-dtype") or ("f32" if count % 4 == 0 else "u8")
+        if dtype not in _NP_DTYPES:
+            context.abort(grpc.StatusCode.INVALID_ARGUMENT, f"unknown dmlp-dtype {dtype!r}")
+        algo = md.get("dmlp-algo", "auto")
+        addrs = {d.rank: DEFAULT_ADDR for d in devices}
+        for rank, ma in request.memAddrs.items():
+            if rank in addrs:
+                addrs[rank] = ma.value
+        op = request.op
+
+        def run():
+            if comm.native is not None and len(comm.native.local_devs) == n:
+                self._allreduce_native(comm, devices, addrs, count, dtype, op, algo, md)
+            else:
+                self._allreduce_portable(comm, devices, addrs, count, dtype, op)
+
+        if grouped:
+            with comm.mu:
+                comm.queue.append(QueuedOp(run, "AllReduceRing"))
+            return pb.AllReduceRingResponse(success=True)
+        try:
+            run()
+        except grpc.RpcError as e:
+            with comm.mu:
+                comm.status = pb.FAILED
+                comm.failure_reason = f"AllReduceRing: {e.code()}"
+            context.abort(grpc.StatusCode.UNKNOWN, f"AllReduceRing failed: {e.code().name}: {e.details()}")
+        except Exception as e:
+            with comm.mu:
+                comm.status = pb.FAILED
+                comm.failure_reason = f"AllReduceRing: {e}"
+            context.abort(grpc.StatusCode.UNKNOWN, f"AllReduceRing failed: {e}")
+        with comm.mu:
+            comm.status = pb.SUCCESS
+        return pb.AllReduceRingResponse(success=True)
+
+    # -- native path: one kernel per rank over peer memory -------------------------------------
+    def _allreduce_native(self, comm, devices, addrs, count, dtype, op, algo, md) -> None:
+        from ..runtime import native
+        ndt = {"u8": native.U8, "i32": native.I32, "f32": native.F32, "bf16": native.BF16}[dtype]
+        esz = native.DTYPE_SIZE[ndt]
+        if count % esz:
+            raise ValueError(f"count {count} is not a multiple of the {dtype} element size")
+        ptrs = []
+        for d in devices:
+            be = d.local.backend
+            be.check_addr(addrs[d.rank])
+            be.ensure(addrs[d.rank], count)
+            ptrs.append(be.pointer(addrs[d.rank]))
+        kwargs = {}
+        if "dmlp-sgd-lr" in md:
+            # Fused gradient average + SGD: weights at dmlp-sgd-weights (default 0x2000) are updated
+            # in the same kernel; nothing elementwise runs afterwards (client.go:254-267 on device).
+            waddr = int(md.get("dmlp-sgd-weights", hex(RECV_ADDR)), 0)
+            outs, lrs = [], []
+            for d in devices:
+                be = d.local.backend
+                be.check_addr(waddr)
+                be.ensure(waddr, count)
+                outs.append(be.pointer(waddr))
+                lrs.append(be.scalar_f32("lr", float(md["dmlp-sgd-lr"])))
+            kwargs = dict(fuse_sgd=True, lr=lrs, scale=1.0 / len(devices))
+        else:
+            outs = ptrs
+        comm.native.allreduce(ptrs, outs, count // esz, dtype=ndt, op=int(op),
+                              algo=native.ALGO_BY_NAME.get(algo, native.ALGO_AUTO), **kwargs)
+        comm.native.sync()
+        comm.native.check()  # raises CommFailure when a watchdog fired (dead peer mid-collective)
+
+    # -- portable path: ring schedule driven through the device RPC contract -------------------
+    def _transfer(self, dst: DeviceInfo, payload: bytes, recv_addr: int, src_rank: int) -> None:
+        """One P2P hop delivered through BeginSend/BeginReceive/StreamSend/GetStreamStatus on the
+        receiving device (the reference drives the same five calls, :427-516)."""
+        n = len(payload)
+        s = dst.stub.BeginSend(pb.BeginSendRequest(sendBuffAddr=pb.MemAddr(value=DEFAULT_ADDR), numBytes=n,
+                                                   dstRank=pb.Rank(value=dst.rank)), timeout=30)
+        r = dst.stub.BeginReceive(pb.BeginReceiveRequest(streamId=s.streamId, recvBuffAddr=pb.MemAddr(value=recv_addr),
+                                                         numBytes=n, srcRank=pb.Rank(value=src_rank)), timeout=30)
+        if not r.initiated:
+            raise RuntimeError(f"rank {dst.rank}: BeginReceive not initiated")
+        chunk = 2 << 20
+        it = (pb.DataChunk(data=payload[o:o + chunk], streamId=s.streamId.value) for o in range(0, max(n, 1), chunk))
+        dst.stub.StreamSend(it, timeout=60)
+        while True:
+            st = dst.stub.GetStreamStatus(pb.GetStreamStatusRequest(streamId=s.streamId), timeout=30).status
+            if st == pb.SUCCESS:
+                return
+            if st == pb.FAILED:
+                raise RuntimeError(f"rank {dst.rank}: stream failed")
+            time.sleep(0.001)
+
+    def _allreduce_portable(self, comm, devices, addrs, count, dtype, op) -> None:
+        n = len(devices)
+        np_dt = _NP_DTYPES[dtype]
+        if np_dt is None:
+            raise ValueError("bf16 needs the cuda backend")
+        esz = np.dtype(np_dt).itemsize
+        if count % esz:
+            raise ValueError(f"count {count} is not a multiple of the {dtype} element size")
+        nelem = count // esz
+        # Local working copies (zero-extended like the reference's padding branch, :300-334).
+        bufs, tails = [], []
+        for d in devices:
+            try:
+                raw = self._dev_read(d, addrs[d.rank])
+            except KeyError:
+                raw = b""
+            tails.append(raw[count:])  # bytes past `count` are not part of the collective: kept as is
+            arr = np.zeros(nelem, dtype=np_dt)
+            have = min(len(raw) // esz, nelem)
+            arr[:have] = np.frombuffer(raw[:have * esz], dtype=np_dt)
+            bufs.append(arr)
+        seg = -(-nelem // n)
+        red = _NP_OPS[op]
+        bounds = [(min(s * seg, nelem), min((s + 1) * seg, nelem)) for s in range(n)]
+
+        def hop(step_send_seg):
+            # every rank r sends segment step_send_seg(r) to rank r+1 through the device contract
+            staged = {}
+            for r, d in enumerate(devices):
+                lo, hi = bounds[step_send_seg(r)]
+                dst = devices[(r + 1) % n]
+                self._transfer(dst, bufs[r][lo:hi].tobytes(), RECV_ADDR, r)
+                raw = self._dev_read(dst, RECV_ADDR, (hi - lo) * esz)
+                staged[(r + 1) % n] = (step_send_seg(r), np.frombuffer(raw, dtype=np_dt))
+            return staged
+
+        for step in range(n - 1):  # reduce-scatter
+            staged = hop(lambda r: (r - step) % n)
+            for r, (s, data) in staged.items():
+                lo, hi = bounds[s]
+                with np.errstate(over="ignore"):
+                    bufs[r][lo:hi] = red(bufs[r][lo:hi], data)
+        for step in range(n - 1):  # all-gather (send index shifted by one; the reference reuses the
+            staged = hop(lambda r: (r + 1 - step) % n)  # scatter schedule here, SURVEY §3.2 defect 2)
+            for r, (s, data) in staged.items():
+                lo, hi = bounds[s]
+                bufs[r][lo:hi] = data
+        for d, arr, tail in zip(devices, bufs, tails):
+            self._dev_write(d, addrs[d.rank], arr.tobytes() + tail)
+
+    # ------------------------------------------------------------------ status / destroy / finalize
+    def GetCommStatus(self, request, context):
+        comm = self._get(request.commId, context)
+        if comm.native is not None:
+            st = comm.native.status()
+            if st["code"] != 0:
+                with comm.mu:
+                    comm.status = pb.FAILED
+        with comm.mu:
+            return pb.GetCommStatusResponse(status=comm.status)
+
+    def CommDestroy(self, request, context):
+        with self.mu:
+            comm = self.communicators.pop(request.commId, None)
+        if comm is None:
+            context.abort(grpc.StatusCode.NOT_FOUND, "Communicator not found")
+        self._release(comm)
+        log.info("Communicator %d destroyed", comm.id)
+        return pb.CommDestroyResponse(success=True)
+
+    def CommFinalize(self, request, context):
+        """Flushes queued group work and waits for the devices to go idle; the communicator stays
+        registered until CommDestroy (NCCL's finalize/destroy split)."""
+        comm = self._get(request.commId, context)
+        with comm.mu:
+            queued, comm.queue = comm.queue, []
+        for op in queued:
+            op.run()
+        if comm.native is not None:
+            comm.native.sync()
+        with comm.mu:
+            comm.finalized = True
+        return pb.CommFinalizeResponse(success=True)
+
+    # ------------------------------------------------------------------ NaiveAllReduce (:611-717)
+    def NaiveAllReduce(self, request, context):
+        comm = self._get(request.commId, context)
+        with comm.mu:
+            if comm.status == pb.FAILED:
+                context.abort(grpc.StatusCode.FAILED_PRECONDITION, "Communicator is in FAILED state")
+            devices = list(comm.devices)
+        if not devices:
+            context.abort(grpc.StatusCode.INTERNAL, "No devices available in the communicator")
+        size, latency = int(request.dataSize), request.latencyMs / 1000.0
+        ones = b"\x01" * size
+        try:
+            for d in devices:  # untimed initialisation
+                time.sleep(latency)
+                self._dev_write(d, DEFAULT_ADDR, ones)
+        except Exception as e:
+            context.abort(grpc.StatusCode.INTERNAL, f"Failed to initialize data: {e}")
+        native_ok = comm.native is not None or (
+            len(devices) == 1 and devices[0].local is not None and devices[0].local.backend.kind == "cuda")
+        t0 = time.perf_counter()
+        moved = 0
+        try:
+            if native_ok and all(d.local is not None for d in devices):
+                moved = self._naive_native(devices, size, latency)
+            else:
+                gathered = []
+                for d in devices:
+                    time.sleep(latency)
+                    gathered.append(np.frombuffer(self._dev_read(d, DEFAULT_ADDR, size), dtype=np.uint8))
+                    moved += size
+                acc = np.zeros(size, dtype=np.uint8)
+                for g in gathered:
+                    acc = acc + g  # uint8 wrap-around like the reference (:681-686)
+                out = acc.tobytes()
+                for d in devices:
+                    time.sleep(latency)
+                    self._dev_write(d, RECV_ADDR, out)
+                    moved += size
+        except grpc.RpcError as e:
+            context.abort(grpc.StatusCode.INTERNAL, f"NaiveAllReduce failed: {e.code().name}: {e.details()}")
+        except Exception as e:
+            context.abort(grpc.StatusCode.INTERNAL, f"NaiveAllReduce failed: {e}")
+        ms = int((time.perf_counter() - t0) * 1000)
+        log.info("Naive AllReduce completed: DataSize=%d, Latency=%dms, TotalTime=%dms, TotalDataTransferred=%d bytes",
+                 size, request.latencyMs, ms, moved)
+        return pb.NaiveAllReduceResponse(success=True, totalTimeMs=ms, totalDataTransferred=moved)
+
+    def _naive_native(self, devices: List[DeviceInfo], size: int, latency: float) -> int:
+        """Comparison mode on GPUs: serial P2P gathers to rank 0, one reduce kernel, serial P2P
+        broadcasts to 0x2000. No overlap on purpose — it is the baseline the ring is compared to."""
+        import ctypes as C
+        from ..runtime import native
+        root = devices[0].local.backend
+        moved = 0
+        stage = []
+        for d in devices:
+            time.sleep(latency)
+            be = d.local.backend
+            buf = root.scratch(f"naive-{d.rank}", size)
+            native.check(native.lib().dmlp_p2p_copy(be.ordinal, buf, be.pointer(DEFAULT_ADDR), size, None))
+            native.check(native.lib().dmlp_device_sync(be.ordinal))
+            stage.append(buf)
+            moved += size
+        root.check_addr(RECV_ADDR)
+        root.ensure(RECV_ADDR, size)
+        arr = (C.c_void_p * len(stage))(*stage)
+        native.check(native.lib().dmlp_reduce_n(root.ordinal, root.pointer(RECV_ADDR), arr, len(stage), size,
+                                                native.U8, native.SUM, None))
+        native.check(native.lib().dmlp_device_sync(root.ordinal))
+        for d in devices:
+            time.sleep(latency)
+            be = d.local.backend
+            be.check_addr(RECV_ADDR)
+            be.ensure(RECV_ADDR, size)
+            if be is not root:
+                native.check(native.lib().dmlp_p2p_copy(root.ordinal, be.pointer(RECV_ADDR), root.pointer(RECV_ADDR),
+                                                        size, None))
+                native.check(native.lib().dmlp_device_sync(root.ordinal))
+            moved += size
+        return moved

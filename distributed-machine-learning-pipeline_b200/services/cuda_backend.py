@@ -1,0 +1,176 @@
+"""CUDA device backend: the reference's per-device ``map[uint64][]byte``
+(``DSML/gpu_device_service/gpu_device_server.go:26-49``) kept in real GPU memory.
+
+Each address owns one device allocation made by the native runtime. In a single process every
+allocation is addressable from every peer GPU once peer access is enabled (UVA), so collectives
+and the P2P copy kernel take these pointers as they are. Host<->device copies are
+``cudaMemcpy`` through the runtime (C3/K10 in SURVEY.md); device<->device transfers use the
+hand-written ``p2p_copy`` kernel on the device's copy stream and report completion via an event.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import struct
+import threading
+from typing import Callable, Dict, Tuple
+
+from ..runtime import native
+from .backend import DeviceBackend, MissingBufferError
+
+
+class CudaBackend(DeviceBackend):
+    kind = "cuda"
+
+    def __init__(self, device_id: int, mem_size: int, ordinal: int):
+        super().__init__(device_id, mem_size)
+        self.ordinal = int(ordinal)
+        self._lib = native.lib()
+        self._lock = threading.RLock()
+        self._bufs: Dict[int, Tuple[int, int, int]] = {}  # addr -> (ptr, size, capacity)
+        self._scratch: Dict[str, Tuple[int, int]] = {}
+        self._scalars: Dict[str, int] = {}
+        s = C.c_void_p()
+        native.check(self._lib.dmlp_stream_create(self.ordinal, C.byref(s)))
+        self.copy_stream = s.value
+        info = native.DeviceInfo()
+        native.check(self._lib.dmlp_device_info(self.ordinal, C.byref(info)))
+        self._info = {"cuda-ordinal": str(self.ordinal), "uuid": info.uuid.decode(), "name": info.name.decode(),
+                      "sm-count": str(info.sm_count), "multicast": str(int(info.multicast_supported)),
+                      "interconnect": "nvlink5-nvswitch"}
+
+    def info(self) -> Dict[str, str]:
+        d = super().info()
+        d.update(self._info)
+        return d
+
+    # ------------------------------------------------------------------ allocation table
+    def _alloc(self, nbytes: int) -> int:
+        p = C.c_void_p()
+        native.check(self._lib.dmlp_malloc(self.ordinal, max(nbytes, 16), C.byref(p)))
+        return p.value
+
+    def _reserve(self, addr: int, nbytes: int, keep: bool) -> int:
+        """Returns a pointer with capacity >= nbytes for ``addr`` (growing keeps old contents if asked)."""
+        ent = self._bufs.get(addr)
+        if ent is not None and ent[2] >= nbytes:
+            self._bufs[addr] = (ent[0], nbytes if not keep else max(ent[1], nbytes), ent[2])
+            return ent[0]
+        cap = max(256, (nbytes + 255) // 256 * 256)
+        ptr = self._alloc(cap)
+        if ent is not None:
+            if keep and ent[1] > 0:
+                native.check(self._lib.dmlp_memcpy_d2d(self.ordinal, ptr, ent[0], ent[1], None))
+            native.check(self._lib.dmlp_free(self.ordinal, ent[0]))
+        size = nbytes if not keep or ent is None else max(ent[1], nbytes)
+        self._bufs[addr] = (ptr, size, cap)
+        return ptr
+
+    def write(self, addr: int, data: bytes) -> None:
+        with self._lock:
+            n = len(data)
+            ptr = self._reserve(addr, n, keep=False)
+            self._bufs[addr] = (ptr, n, self._bufs[addr][2])
+            if n:
+                native.check(self._lib.dmlp_memcpy_h2d(self.ordinal, ptr, bytes(data), n, None))
+
+    def read(self, addr: int, nbytes: int = 0) -> bytes:
+        with self._lock:
+            ent = self._bufs.get(addr)
+            if ent is None:
+                raise MissingBufferError(f"no data at address 0x{addr:x}")
+            n = ent[1] if nbytes <= 0 or nbytes >= ent[1] else nbytes
+            buf = C.create_string_buffer(n)
+            if n:
+                native.check(self._lib.dmlp_memcpy_d2h(self.ordinal, buf, ent[0], n, None))
+            return buf.raw
+
+    def has(self, addr: int) -> bool:
+        with self._lock:
+            return addr in self._bufs
+
+    def size(self, addr: int) -> int:
+        with self._lock:
+            ent = self._bufs.get(addr)
+            if ent is None:
+                raise MissingBufferError(f"no data at address 0x{addr:x}")
+            return ent[1]
+
+    def ensure(self, addr: int, nbytes: int) -> None:
+        with self._lock:
+            ent = self._bufs.get(addr)
+            if ent is None or ent[1] < nbytes:
+                self._reserve(addr, nbytes, keep=True)  # fresh memory is zeroed by the runtime
+
+    def pointer(self, addr: int) -> int:
+        with self._lock:
+            ent = self._bufs.get(addr)
+            if ent is None:
+                raise MissingBufferError(f"no data at address 0x{addr:x}")
+            return ent[0]
+
+    # ------------------------------------------------------------------ helpers for collectives
+    def scratch(self, name: str, nbytes: int) -> int:
+        with self._lock:
+            ent = self._scratch.get(name)
+            if ent is None or ent[1] < nbytes:
+                if ent is not None:
+                    native.check(self._lib.dmlp_free(self.ordinal, ent[0]))
+                ent = (self._alloc(nbytes), nbytes)
+                self._scratch[name] = ent
+            return ent[0]
+
+    def scalar_f32(self, name: str, value: float) -> int:
+        """Device-resident fp32 scalar (e.g. the learning rate read by the fused SGD kernels)."""
+        with self._lock:
+            ptr = self._scalars.get(name)
+            if ptr is None:
+                ptr = self._alloc(16)
+                self._scalars[name] = ptr
+            native.check(self._lib.dmlp_memcpy_h2d(self.ordinal, ptr, struct.pack("<f", value), 4, None))
+            return ptr
+
+    def p2p_copy_to(self, dst: "CudaBackend", send_addr: int, recv_addr: int, nbytes: int) -> Callable[[], bool]:
+        """Pushes ``nbytes`` from this device's buffer to ``dst``'s buffer with the P2P kernel.
+        Returns a poll function (True once the copy's event has completed)."""
+        with self._lock:
+            ent = self._bufs.get(send_addr)
+            if ent is None:
+                raise MissingBufferError(f"no data at address 0x{send_addr:x}")
+            if ent[1] < nbytes:
+                raise MissingBufferError(f"send buffer 0x{send_addr:x} holds {ent[1]} bytes, need {nbytes}")
+            src_ptr = ent[0]
+        dst.check_addr(recv_addr)
+        with dst._lock:
+            dptr = dst._reserve(recv_addr, nbytes, keep=False)
+            dst._bufs[recv_addr] = (dptr, nbytes, dst._bufs[recv_addr][2])
+        if dst.ordinal != self.ordinal:
+            devs = (C.c_int * 2)(self.ordinal, dst.ordinal)
+            native.check(self._lib.dmlp_enable_peer_access(2, devs))
+        native.check(self._lib.dmlp_p2p_copy(self.ordinal, dptr, src_ptr, nbytes, self.copy_stream))
+        ev = C.c_void_p()
+        native.check(self._lib.dmlp_event_create(self.ordinal, 0, C.byref(ev)))
+        native.check(self._lib.dmlp_event_record(self.ordinal, ev, self.copy_stream))
+
+        def poll() -> bool:
+            busy = C.c_int(1)
+            native.check(self._lib.dmlp_event_query(ev, C.byref(busy)))
+            if not busy.value:
+                self._lib.dmlp_event_destroy(ev)
+            return not busy.value
+
+        return poll
+
+    def close(self) -> None:
+        with self._lock:
+            for ptr, _, _ in self._bufs.values():
+                self._lib.dmlp_free(self.ordinal, ptr)
+            for ptr, _ in self._scratch.values():
+                self._lib.dmlp_free(self.ordinal, ptr)
+            for ptr in self._scalars.values():
+                self._lib.dmlp_free(self.ordinal, ptr)
+            self._bufs.clear()
+            self._scratch.clear()
+            self._scalars.clear()
+            if self.copy_stream:
+                self._lib.dmlp_stream_destroy(self.ordinal, self.copy_stream)
+                self.copy_stream = None

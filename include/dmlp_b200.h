@@ -95,6 +95,119 @@ int dmlp_sgd(float* w_dev, const float* g_dev, size_t n, const float* lr_dev, fl
 int dmlp_fill_u32(void* dst_dev, uint32_t value, size_t n_words, void* stream);
 int dmlp_cast_f32_to_bf16(const float* src_dev, void* dst_bf16_dev, size_t n, void* stream);
 
+/* ------------------------------------------------------------------ devices, memory, streams
+ * The real-GPU counterpart of the reference's simulated device memory
+ * (DSML/gpu_device_service/gpu_device_server.go:26-49) and of CommInit's per-device connection
+ * set-up (DSML/gpu_coordinator_service/gpu_coordinator_server.go:131-164). */
+typedef struct {
+  char name[128];
+  char uuid[48];
+  int sm_count;
+  int cc_major, cc_minor;
+  int clock_khz;
+  int multicast_supported; /* NVLS: cuMulticast* usable on this device */
+  int smem_per_block_optin;
+  size_t total_mem;
+  size_t l2_bytes;
+} dmlp_device_info_t;
+
+int dmlp_device_count(int* n);
+int dmlp_device_info(int dev, dmlp_device_info_t* out);
+/* n x n matrices (row-major): peer access possible, native atomics, performance rank. */
+int dmlp_peer_matrix(int n, const int* devs, int* access, int* atomics, int* perf_rank);
+int dmlp_enable_peer_access(int n, const int* devs);
+
+int dmlp_malloc(int dev, size_t bytes, void** ptr_dev); /* zero-initialised */
+int dmlp_free(int dev, void* ptr_dev);
+int dmlp_host_alloc(size_t bytes, void** ptr_host);    /* pinned, portable, mapped */
+int dmlp_host_free(void* ptr_host);
+/* stream == NULL: synchronous copy. Reference Memcpy H2D/D2H: gpu_device_server.go:195-230. */
+int dmlp_memcpy_h2d(int dev, void* dst_dev, const void* src_host, size_t bytes, void* stream);
+int dmlp_memcpy_d2h(int dev, void* dst_host, const void* src_dev, size_t bytes, void* stream);
+int dmlp_memcpy_d2d(int dev, void* dst_dev, const void* src_dev, size_t bytes, void* stream);
+int dmlp_memset(int dev, void* dst_dev, int value, size_t bytes, void* stream);
+
+int dmlp_stream_create(int dev, void** stream);
+int dmlp_stream_destroy(int dev, void* stream);
+int dmlp_stream_sync(int dev, void* stream);
+int dmlp_stream_query(int dev, void* stream, int* busy);
+int dmlp_stream_wait_event(int dev, void* stream, void* event);
+int dmlp_device_sync(int dev);
+int dmlp_event_create(int dev, int timing, void** event);
+int dmlp_event_destroy(void* event);
+int dmlp_event_record(int dev, void* event, void* stream);
+int dmlp_event_query(void* event, int* busy); /* GetStreamStatus: gpu_device_server.go:183-193 */
+int dmlp_event_sync(void* event);
+int dmlp_event_elapsed_ms(void* start, void* stop, float* ms);
+
+/* CUDA IPC: lets one-process-per-GPU jobs map each other's buffers. */
+int dmlp_ipc_get_handle(int dev, void* ptr_dev, unsigned char out[64]);
+int dmlp_ipc_open_handle(int dev, const unsigned char in[64], void** ptr_dev);
+int dmlp_ipc_close_handle(int dev, void* ptr_dev);
+
+/* ------------------------------------------------------------------ communicator + collectives
+ * Reference: communicator registry and CommInit (gpu_coordinator_server.go:25-52,121-192), ring
+ * all-reduce (:272-566), naive all-reduce (:611-717), device failure handling (:91-119).
+ *
+ * A communicator spans `world` ranks; `nlocal` of them are driven by the calling process
+ * (all of them in the single-process coordinator; exactly one under torchrun). Each rank owns a
+ * peer-visible segment: [signal pad][ring staging][arena]. Other processes' segments are mapped
+ * with dmlp_comm_export / dmlp_comm_import. If every rank is local and on the SAME device the
+ * communicator is "emulated": collectives run as one cooperative launch with gridDim.y = world.
+ */
+typedef struct dmlp_comm_opaque* dmlp_comm_t;
+
+int dmlp_comm_create(int world, int nlocal, const int* local_ranks, const int* local_devs,
+                     size_t staging_bytes, size_t arena_bytes, dmlp_comm_t* out);
+int dmlp_comm_destroy(dmlp_comm_t comm);
+int dmlp_comm_export(dmlp_comm_t comm, int local_idx, unsigned char out[64]);
+int dmlp_comm_import(dmlp_comm_t comm, int rank, const unsigned char in[64]);
+/* Base of rank `rank`'s arena as addressable from local rank `local_idx`. */
+int dmlp_comm_arena_ptr(dmlp_comm_t comm, int local_idx, int rank, void** ptr_dev, size_t* bytes);
+int dmlp_comm_set_timeout_ms(dmlp_comm_t comm, uint64_t ms); /* in-kernel watchdog, default 10 s */
+int dmlp_comm_abort(dmlp_comm_t comm);                       /* releases every spinning kernel */
+/* out = {failure code, reporting rank, awaited peer, phase, abort flag}; code 0 = healthy. */
+int dmlp_comm_status(dmlp_comm_t comm, uint32_t out[5]);
+int dmlp_comm_inject_dead_ranks(dmlp_comm_t comm, uint32_t rank_mask); /* fault injection */
+
+typedef enum {
+  DMLP_ALGO_AUTO = 0,
+  DMLP_ALGO_ONESHOT = 1,
+  DMLP_ALGO_TWOSHOT = 2,
+  DMLP_ALGO_RING = 3,
+  DMLP_ALGO_NVLS = 4
+} dmlp_algo_t;
+
+typedef struct {
+  int algo;  /* dmlp_algo_t */
+  int dtype; /* dmlp_dtype_t */
+  int op;    /* dmlp_op_t */
+  int fuse_sgd;         /* out (weights) -= lr * scale * sum(in) instead of out = reduce(in); f32 SUM */
+  int skip_end_barrier; /* one-shot only: caller double-buffers `in`, drop the trailing rendezvous */
+  float scale;          /* 0 is read as 1; AVG multiplies by 1/world on top */
+  size_t count;         /* elements */
+  /* Per-rank buffers as addressable from the launching GPU, 16-byte aligned. one-shot needs every
+   * in[]; two-shot every in[] and out[]; ring only the caller's own in/out (it moves data through
+   * the communicator's staging). */
+  const void* in[DMLP_MAX_RANKS];
+  void* out[DMLP_MAX_RANKS];
+  void* out_bf16[DMLP_MAX_RANKS];  /* optional bf16 shadow of the updated weights (fuse_sgd) */
+  const float* lr[DMLP_MAX_RANKS]; /* device scalar per rank (fuse_sgd) */
+  void* streams[DMLP_MAX_RANKS];   /* local_idx < 0: per-local-rank streams (NULL = `stream` arg) */
+} dmlp_allreduce_desc_t;
+
+/* Launches the all-reduce for local rank `local_idx` (or for every local rank when < 0) and
+ * returns immediately. Failures of peers surface through dmlp_comm_status. */
+int dmlp_allreduce(dmlp_comm_t comm, int local_idx, const dmlp_allreduce_desc_t* desc, void* stream);
+int dmlp_allreduce_pick_algo(int world, size_t bytes);
+
+/* P2P push copy kernel (StreamSend on real GPUs, gpu_device_server.go:112-181): launched on
+ * src_dev, dst may be peer memory. */
+int dmlp_p2p_copy(int src_dev, void* dst_dev, const void* src_dev_ptr, size_t bytes, void* stream);
+/* dst = reduce(srcs[0..n)) on one device (root step of NaiveAllReduce, :681-686). */
+int dmlp_reduce_n(int dev, void* dst_dev, const void* const* srcs_dev, int n, size_t count, int dtype,
+                  int op, void* stream);
+
 #ifdef __cplusplus
 }
 #endif
