@@ -1,0 +1,46 @@
+// A GEMM launch prepared once (TMA descriptors encoded, tile/stage configuration chosen) and
+// replayed every step: the native trainer builds its plans at set-up so the per-step path is
+// kernel launches only (and is then captured into a CUDA graph).
+#pragma once
+#include <cuda.h>
+#include <cuda_bf16.h>
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include "../include/dmlp_b200.h"
+
+namespace dmlp {
+
+struct GemmParams {
+  int M, N, K;
+  int block_n;
+  int num_k_blocks;
+  int stages;
+  uint32_t tmem_cols;
+  uint32_t a_stage_bytes, b_stage_bytes;
+  uint32_t idesc;
+  float* out_f32;
+  long long ld_out;
+  __nv_bfloat16* out_bf16;
+  long long ld_out_bf16;
+  const float* bias;
+  const void* mask;
+  long long ld_mask;
+  int mask_is_bf16;
+  float* colsum;
+  int relu;
+  int accumulate;
+};
+
+struct GemmPlan {
+  CUtensorMap tmA, tmB;
+  GemmParams p;
+  int grid_x, grid_y;
+  size_t smem;
+  int key;  // kernel instantiation: (bf16 << 2) | (a_mn << 1) | b_mn
+};
+
+int gemm_plan_create(const dmlp_gemm_desc_t* desc, GemmPlan* plan);
+int gemm_plan_run(const GemmPlan* plan, cudaStream_t stream);
+
+}  // namespace dmlp

@@ -12,30 +12,11 @@
 // dgrad + ReLU mask (:178-189), wgrad (:167-176, :191-199), bias-gradient column sums
 // (:173-175, :197-199).
 #include "common.h"
+#include "gemm_plan.h"
 #include "ptx_sm100.cuh"
 
 namespace dmlp {
 
-struct GemmParams {
-  int M, N, K;
-  int block_n;
-  int num_k_blocks;
-  int stages;
-  uint32_t tmem_cols;
-  uint32_t a_stage_bytes, b_stage_bytes;
-  uint32_t idesc;
-  float* out_f32;
-  long long ld_out;
-  __nv_bfloat16* out_bf16;
-  long long ld_out_bf16;
-  const float* bias;
-  const void* mask;
-  long long ld_mask;
-  int mask_is_bf16;
-  float* colsum;
-  int relu;
-  int accumulate;
-};
 
 constexpr int kMaxStages = 8;
 constexpr int kGemmThreads = 192;
@@ -330,8 +311,8 @@ int choose_block_n(int M, int N) {
 
 using namespace dmlp;
 
-extern "C" int dmlp_gemm(const dmlp_gemm_desc_t* d, void* stream) {
-  DMLP_REQUIRE(d != nullptr, "dmlp_gemm: null descriptor");
+int dmlp::gemm_plan_create(const dmlp_gemm_desc_t* d, GemmPlan* plan) {
+  DMLP_REQUIRE(d != nullptr && plan != nullptr, "dmlp_gemm: null descriptor");
   DMLP_REQUIRE(d->dtype == DMLP_F32 || d->dtype == DMLP_BF16, "dmlp_gemm: dtype must be F32 (tf32) or BF16");
   DMLP_REQUIRE(d->M > 0 && d->N > 0 && d->K > 0, "dmlp_gemm: empty problem %dx%dx%d", d->M, d->N, d->K);
   DMLP_REQUIRE(d->A_dev && d->B_dev, "dmlp_gemm: null operand");
@@ -343,21 +324,21 @@ extern "C" int dmlp_gemm(const dmlp_gemm_desc_t* d, void* stream) {
   int bn = d->block_n > 0 ? d->block_n : choose_block_n(d->M, d->N);
   DMLP_REQUIRE(bn % 16 == 0 && bn >= 16 && bn <= 256, "dmlp_gemm: block_n %d must be a multiple of 16 in [16,256]", bn);
 
-  CUtensorMap tmA, tmB;
   int rc;
   const int mn_swz = bf16 ? 1 : 2;  // fp32 MN-major operands need the 32B-atom swizzle
   if (d->a_major == 0)
-    rc = make_tensor_map_2d(&tmA, d->A_dev, EB, bf16, d->K, d->M, d->lda, KS, 128, 1);
+    rc = make_tensor_map_2d(&plan->tmA, d->A_dev, EB, bf16, d->K, d->M, d->lda, KS, 128, 1);
   else
-    rc = make_tensor_map_2d(&tmA, d->A_dev, EB, bf16, d->M, d->K, d->lda, ATOM, KS, mn_swz);
+    rc = make_tensor_map_2d(&plan->tmA, d->A_dev, EB, bf16, d->M, d->K, d->lda, ATOM, KS, mn_swz);
   if (rc) return rc;
   if (d->b_major == 0)
-    rc = make_tensor_map_2d(&tmB, d->B_dev, EB, bf16, d->K, d->N, d->ldb, KS, bn, 1);
+    rc = make_tensor_map_2d(&plan->tmB, d->B_dev, EB, bf16, d->K, d->N, d->ldb, KS, bn, 1);
   else
-    rc = make_tensor_map_2d(&tmB, d->B_dev, EB, bf16, d->N, d->K, d->ldb, ATOM, KS, mn_swz);
+    rc = make_tensor_map_2d(&plan->tmB, d->B_dev, EB, bf16, d->N, d->K, d->ldb, ATOM, KS, mn_swz);
   if (rc) return rc;
 
-  GemmParams p{};
+  GemmParams& p = plan->p;
+  p = GemmParams{};
   p.M = d->M; p.N = d->N; p.K = d->K;
   p.block_n = bn;
   p.num_k_blocks = ceil_div(d->K, KS);
@@ -381,18 +362,30 @@ extern "C" int dmlp_gemm(const dmlp_gemm_desc_t* d, void* stream) {
   p.colsum = d->colsum_dev;
   p.relu = d->relu; p.accumulate = d->accumulate;
 
-  dim3 grid(ceil_div(d->N, bn), ceil_div(d->M, 128));
-  const size_t smem = stages * stage_bytes + 1024;
-  cudaStream_t st = as_stream(stream);
-  const int key = (bf16 ? 4 : 0) | (d->a_major ? 2 : 0) | (d->b_major ? 1 : 0);
-  switch (key) {
-    case 0: return launch_gemm<4, false, false>(tmA, tmB, p, grid, smem, st);
-    case 1: return launch_gemm<4, false, true>(tmA, tmB, p, grid, smem, st);
-    case 2: return launch_gemm<4, true, false>(tmA, tmB, p, grid, smem, st);
-    case 3: return launch_gemm<4, true, true>(tmA, tmB, p, grid, smem, st);
-    case 4: return launch_gemm<2, false, false>(tmA, tmB, p, grid, smem, st);
-    case 5: return launch_gemm<2, false, true>(tmA, tmB, p, grid, smem, st);
-    case 6: return launch_gemm<2, true, false>(tmA, tmB, p, grid, smem, st);
-    default: return launch_gemm<2, true, true>(tmA, tmB, p, grid, smem, st);
+  plan->grid_x = ceil_div(d->N, bn);
+  plan->grid_y = ceil_div(d->M, 128);
+  plan->smem = stages * stage_bytes + 1024;
+  plan->key = (bf16 ? 4 : 0) | (d->a_major ? 2 : 0) | (d->b_major ? 1 : 0);
+  return DMLP_OK;
+}
+
+int dmlp::gemm_plan_run(const GemmPlan* plan, cudaStream_t st) {
+  const dim3 grid(plan->grid_x, plan->grid_y);
+  switch (plan->key) {
+    case 0: return launch_gemm<4, false, false>(plan->tmA, plan->tmB, plan->p, grid, plan->smem, st);
+    case 1: return launch_gemm<4, false, true>(plan->tmA, plan->tmB, plan->p, grid, plan->smem, st);
+    case 2: return launch_gemm<4, true, false>(plan->tmA, plan->tmB, plan->p, grid, plan->smem, st);
+    case 3: return launch_gemm<4, true, true>(plan->tmA, plan->tmB, plan->p, grid, plan->smem, st);
+    case 4: return launch_gemm<2, false, false>(plan->tmA, plan->tmB, plan->p, grid, plan->smem, st);
+    case 5: return launch_gemm<2, false, true>(plan->tmA, plan->tmB, plan->p, grid, plan->smem, st);
+    case 6: return launch_gemm<2, true, false>(plan->tmA, plan->tmB, plan->p, grid, plan->smem, st);
+    default: return launch_gemm<2, true, true>(plan->tmA, plan->tmB, plan->p, grid, plan->smem, st);
   }
+}
+
+extern "C" int dmlp_gemm(const dmlp_gemm_desc_t* d, void* stream) {
+  GemmPlan plan;
+  int rc = gemm_plan_create(d, &plan);
+  if (rc) return rc;
+  return gemm_plan_run(&plan, as_stream(stream));
 }

@@ -1,0 +1,596 @@
+// Native data-parallel MLP trainer: owns the device buffers, pre-encodes every TMA descriptor,
+// captures the whole training step into CUDA graphs and runs the input pipeline and the step loop
+// without returning to Python.
+//
+// Replaces the reference's training loop (DSML/client/client.go:516-659): per batch it ran
+// forwardPass / backwardPass on the CPU, pushed the gradient to every "device" over gRPC, called
+// AllReduceRing, read the gradient back, applied SGD on the CPU and re-uploaded the weights
+// (8 client RPCs + ~60 coordinator RPCs per batch). Here one step is:
+//   H2D(x, y) on a copy stream  ->  graph { fwd GEMMs (+bias+ReLU), fused softmax-CE, dgrad/wgrad
+//   GEMMs (+ReLU mask, +bias-gradient), all-reduce fused with average+SGD over peer memory }
+//   -> D2H(loss, correct).
+// Gradients are double-buffered by step parity, so the one-shot all-reduce needs a single
+// rendezvous per step; with `overlap` on, each layer's bucket is reduced on a second stream while
+// backward continues (layer-by-layer overlap).
+#include "common.h"
+#include "gemm_plan.h"
+
+#include <string.h>
+
+#include <new>
+#include <vector>
+
+namespace dmlp {
+
+constexpr int kMaxLayers = DMLP_MAX_LAYERS;
+
+static size_t align_up(size_t v, size_t a) { return (v + a - 1) / a * a; }
+
+struct ParamLayout {
+  int L = 0;
+  int in[kMaxLayers], out[kMaxLayers], out_pad[kMaxLayers];
+  size_t w_off[kMaxLayers], b_off[kMaxLayers];  // in floats
+  size_t total = 0;                              // floats, multiple of 64
+};
+
+static void make_layout(const dmlp_trainer_config_t& c, ParamLayout* lay) {
+  lay->L = c.num_layers;
+  size_t cur = 0;
+  for (int l = 0; l < c.num_layers; ++l) {
+    lay->in[l] = c.dims[l];
+    lay->out[l] = c.dims[l + 1];
+    lay->out_pad[l] = static_cast<int>(align_up(c.dims[l + 1], 16));
+    lay->w_off[l] = cur;
+    cur = align_up(cur + static_cast<size_t>(lay->in[l]) * lay->out_pad[l], 64);
+    lay->b_off[l] = cur;
+    cur = align_up(cur + lay->out_pad[l], 64);
+  }
+  lay->total = cur;
+}
+
+struct Trainer {
+  dmlp_trainer_config_t cfg;
+  ParamLayout lay;
+  int dev = 0;
+  dmlp_comm_t comm = nullptr;
+  int local_idx = 0, rank = 0, world = 1;
+  bool bf16 = false;
+  // peer-visible (arena) or private buffers
+  float* params = nullptr;
+  __nv_bfloat16* shadow = nullptr;
+  float* grads[2] = {nullptr, nullptr};
+  float* peer_params[DMLP_MAX_RANKS];
+  void* peer_shadow[DMLP_MAX_RANKS];
+  float* peer_grads[2][DMLP_MAX_RANKS];
+  bool owns_params = false;
+  // private buffers
+  float* x[2] = {nullptr, nullptr};
+  __nv_bfloat16* x16 = nullptr;
+  int* labels[2] = {nullptr, nullptr};
+  float* act[kMaxLayers];            // fp32 activations (tf32 mode) / logits (always, last layer)
+  __nv_bfloat16* act16[kMaxLayers];  // bf16 activations (bf16 mode)
+  float* dz[kMaxLayers];
+  __nv_bfloat16* dz16[kMaxLayers];
+  float* metrics_dev[2] = {nullptr, nullptr};  // {loss_sum, correct(int bits)}
+  float* metrics_host = nullptr;               // pinned [2][2]
+  float* lr_dev = nullptr;
+  float* lr_host = nullptr;                    // pinned staging for lr updates
+  cudaStream_t s_main = nullptr, s_comm = nullptr, s_copy = nullptr;
+  cudaEvent_t ev_h2d[2], ev_done[2], ev_fork, ev_join, ev_bucket[kMaxLayers];
+  bool launched[2] = {false, false};
+  cudaGraph_t graph[2] = {nullptr, nullptr};
+  cudaGraphExec_t gexec[2] = {nullptr, nullptr};
+  GemmPlan fwd[2][kMaxLayers], wgrad[2][kMaxLayers], dgrad[kMaxLayers], fwd_eval[kMaxLayers];
+  int kernels_per_step = 0;
+  unsigned long long steps_done = 0;
+  std::vector<void*> owned;
+};
+
+static int dev_alloc(Trainer* t, size_t bytes, void** out) {
+  int rc = dmlp_malloc(t->dev, bytes, out);
+  if (rc == DMLP_OK) t->owned.push_back(*out);
+  return rc;
+}
+
+#define TRY(expr)        \
+  do {                   \
+    int _rc = (expr);    \
+    if (_rc) return _rc; \
+  } while (0)
+
+// Builds every GEMM plan (TMA descriptors included) for both input parities.
+static int build_plans(Trainer* t) {
+  const ParamLayout& L = t->lay;
+  const int B = t->cfg.batch;
+  const int dt = t->bf16 ? DMLP_BF16 : DMLP_F32;
+  for (int par = 0; par < 2; ++par) {
+    for (int l = 0; l < L.L; ++l) {
+      const bool last = l == L.L - 1;
+      dmlp_gemm_desc_t d;
+      // ---- forward: act[l] = f(in_l . W_l + b_l)
+      memset(&d, 0, sizeof(d));
+      d.dtype = dt; d.a_major = 0; d.b_major = 1;
+      d.M = B; d.N = L.out_pad[l]; d.K = L.in[l];
+      if (l == 0) { d.A_dev = t->bf16 ? static_cast<void*>(t->x16) : static_cast<void*>(t->x[par]); d.lda = L.in[0]; }
+      else { d.A_dev = t->bf16 ? static_cast<void*>(t->act16[l - 1]) : static_cast<void*>(t->act[l - 1]); d.lda = L.out_pad[l - 1]; }
+      d.B_dev = t->bf16 ? static_cast<void*>(t->shadow + L.w_off[l]) : static_cast<void*>(t->params + L.w_off[l]);
+      d.ldb = L.out_pad[l];
+      d.bias_dev = t->params + L.b_off[l];
+      d.relu = last ? 0 : 1;
+      if (last || !t->bf16) { d.out_f32_dev = t->act[l]; d.ld_out = L.out_pad[l]; }
+      if (!last && t->bf16) { d.out_bf16_dev = t->act16[l]; d.ld_out_bf16 = L.out_pad[l]; }
+      TRY(gemm_plan_create(&d, &t->fwd[par][l]));
+      // ---- wgrad: dW_l = in_l^T . dZ_l  -> grads[par]
+      memset(&d, 0, sizeof(d));
+      d.dtype = dt; d.a_major = 1; d.b_major = 1;
+      d.M = L.in[l]; d.N = L.out_pad[l]; d.K = B;
+      if (l == 0) { d.A_dev = t->bf16 ? static_cast<void*>(t->x16) : static_cast<void*>(t->x[par]); d.lda = L.in[0]; }
+      else { d.A_dev = t->bf16 ? static_cast<void*>(t->act16[l - 1]) : static_cast<void*>(t->act[l - 1]); d.lda = L.out_pad[l - 1]; }
+      d.B_dev = t->bf16 ? static_cast<void*>(t->dz16[l]) : static_cast<void*>(t->dz[l]);
+      d.ldb = L.out_pad[l];
+      d.out_f32_dev = t->grads[par] + L.w_off[l];
+      d.ld_out = L.out_pad[l];
+      TRY(gemm_plan_create(&d, &t->wgrad[par][l]));
+    }
+  }
+  for (int l = 1; l < L.L; ++l) {
+    // ---- dgrad: dZ_{l-1} = (dZ_l . W_l^T) * (act_{l-1} > 0); column sums -> db_{l-1} (set per parity at launch)
+    dmlp_gemm_desc_t d;
+    memset(&d, 0, sizeof(d));
+    d.dtype = dt; d.a_major = 0; d.b_major = 0;
+    d.M = B; d.N = L.in[l]; d.K = L.out_pad[l];
+    d.A_dev = t->bf16 ? static_cast<void*>(t->dz16[l]) : static_cast<void*>(t->dz[l]);
+    d.lda = L.out_pad[l];
+    d.B_dev = t->bf16 ? static_cast<void*>(t->shadow + L.w_off[l]) : static_cast<void*>(t->params + L.w_off[l]);
+    d.ldb = L.out_pad[l];
+    if (t->bf16) { d.out_bf16_dev = t->dz16[l - 1]; d.ld_out_bf16 = L.out_pad[l - 1]; d.mask_dev = t->act16[l - 1]; d.mask_dtype = DMLP_BF16; }
+    else { d.out_f32_dev = t->dz[l - 1]; d.ld_out = L.out_pad[l - 1]; d.mask_dev = t->act[l - 1]; d.mask_dtype = DMLP_F32; }
+    d.ld_mask = L.out_pad[l - 1];
+    d.colsum_dev = t->grads[0] + L.b_off[l - 1];  // patched per parity in enqueue_step
+    TRY(gemm_plan_create(&d, &t->dgrad[l]));
+  }
+  return DMLP_OK;
+}
+
+static int enqueue_allreduce(Trainer* t, int par, size_t off, size_t count, cudaStream_t st) {
+  if (t->comm == nullptr) {
+    return dmlp_sgd(t->params + off, t->grads[par] + off, count, t->lr_dev, 1.f,
+                    t->bf16 ? static_cast<void*>(t->shadow + off) : nullptr, st);
+  }
+  dmlp_allreduce_desc_t d;
+  memset(&d, 0, sizeof(d));
+  d.algo = t->cfg.allreduce_algo;
+  d.dtype = DMLP_F32;
+  d.op = DMLP_SUM;
+  d.fuse_sgd = 1;
+  d.skip_end_barrier = 1;  // gradients are double-buffered by step parity
+  d.scale = 1.f / static_cast<float>(t->world);
+  d.count = count;
+  for (int r = 0; r < t->world; ++r) {
+    d.in[r] = t->peer_grads[par][r] ? t->peer_grads[par][r] + off : nullptr;
+    d.out[r] = t->peer_params[r] ? t->peer_params[r] + off : nullptr;
+    d.out_bf16[r] = (t->bf16 && t->peer_shadow[r]) ? static_cast<void*>(static_cast<__nv_bfloat16*>(t->peer_shadow[r]) + off) : nullptr;
+  }
+  d.lr[t->rank] = t->lr_dev;
+  return dmlp_allreduce(t->comm, t->local_idx, &d, st);
+}
+
+// Enqueues one full training step for input parity `par` on the trainer's streams.
+static int enqueue_step(Trainer* t, int par, bool count_kernels) {
+  const ParamLayout& L = t->lay;
+  const int B = t->cfg.batch;
+  cudaStream_t S = t->s_main;
+  int nk = 0;
+  DMLP_CUDA_CHECK(cudaMemsetAsync(t->metrics_dev[par], 0, 8, S));
+  for (int l = 0; l < L.L; ++l)
+    DMLP_CUDA_CHECK(cudaMemsetAsync(t->grads[par] + L.b_off[l], 0, sizeof(float) * L.out_pad[l], S));
+  if (t->bf16) { TRY(dmlp_cast_f32_to_bf16(t->x[par], t->x16, static_cast<size_t>(B) * L.in[0], S)); ++nk; }
+  for (int l = 0; l < L.L; ++l) { TRY(gemm_plan_run(&t->fwd[par][l], S)); ++nk; }
+  const int last = L.L - 1;
+  TRY(dmlp_softmax_ce(t->act[last], L.out_pad[last], t->labels[par], B, L.out[last], 1.f / B,
+                      t->bf16 ? nullptr : t->dz[last], t->bf16 ? static_cast<void*>(t->dz16[last]) : nullptr,
+                      t->metrics_dev[par], reinterpret_cast<int32_t*>(t->metrics_dev[par] + 1),
+                      t->grads[par] + L.b_off[last], S));
+  ++nk;
+  const bool overlap = t->cfg.overlap != 0 && t->comm != nullptr;
+  for (int l = last; l >= 0; --l) {
+    if (l > 0) {  // dgrad first: it reads W_l, which the bucket's fused SGD is about to overwrite
+      GemmPlan pl = t->dgrad[l];
+      pl.p.colsum = t->grads[par] + L.b_off[l - 1];
+      TRY(gemm_plan_run(&pl, S));
+      ++nk;
+    }
+    TRY(gemm_plan_run(&t->wgrad[par][l], S));
+    ++nk;
+    if (overlap) {
+      const size_t lo = L.w_off[l];
+      const size_t hi = (l + 1 < L.L) ? L.w_off[l + 1] : L.total;
+      DMLP_CUDA_CHECK(cudaEventRecord(t->ev_bucket[l], S));
+      DMLP_CUDA_CHECK(cudaStreamWaitEvent(t->s_comm, t->ev_bucket[l], 0));
+      TRY(enqueue_allreduce(t, par, lo, hi - lo, t->s_comm));
+      ++nk;
+    }
+  }
+  if (overlap) {
+    DMLP_CUDA_CHECK(cudaEventRecord(t->ev_join, t->s_comm));
+    DMLP_CUDA_CHECK(cudaStreamWaitEvent(S, t->ev_join, 0));
+  } else {
+    TRY(enqueue_allreduce(t, par, 0, L.total, S));
+    ++nk;
+  }
+  DMLP_CUDA_CHECK(cudaMemcpyAsync(t->metrics_host + 2 * par, t->metrics_dev[par], 8, cudaMemcpyDeviceToHost, S));
+  if (count_kernels) t->kernels_per_step = nk;
+  return DMLP_OK;
+}
+
+static int capture_graphs(Trainer* t) {
+  for (int par = 0; par < 2; ++par) {
+    DMLP_CUDA_CHECK(cudaStreamBeginCapture(t->s_main, cudaStreamCaptureModeRelaxed));
+    int rc = enqueue_step(t, par, false);
+    cudaGraph_t g = nullptr;
+    cudaError_t e = cudaStreamEndCapture(t->s_main, &g);
+    if (rc) { if (g) cudaGraphDestroy(g); return rc; }
+    if (e != cudaSuccess) return set_error(DMLP_ERR_CUDA, "cudaStreamEndCapture: %s", cudaGetErrorString(e));
+    t->graph[par] = g;
+    DMLP_CUDA_CHECK(cudaGraphInstantiate(&t->gexec[par], g, 0));
+  }
+  return DMLP_OK;
+}
+
+}  // namespace dmlp
+
+using namespace dmlp;
+
+extern "C" int dmlp_trainer_param_count(const dmlp_trainer_config_t* cfg, size_t* floats) {
+  DMLP_REQUIRE(cfg && floats && cfg->num_layers >= 1 && cfg->num_layers <= kMaxLayers, "bad trainer config");
+  ParamLayout lay;
+  make_layout(*cfg, &lay);
+  *floats = lay.total;
+  return DMLP_OK;
+}
+
+// Bytes of communicator arena the trainer needs: params + 2 gradient buffers (+ bf16 shadow).
+extern "C" int dmlp_trainer_arena_bytes(const dmlp_trainer_config_t* cfg, size_t* bytes) {
+  size_t n = 0;
+  TRY(dmlp_trainer_param_count(cfg, &n));
+  size_t b = 3 * align_up(n * 4, 256);
+  if (cfg->dtype == DMLP_BF16) b += align_up(n * 2, 256);
+  *bytes = b;
+  return DMLP_OK;
+}
+
+extern "C" int dmlp_trainer_layout(const dmlp_trainer_config_t* cfg, int layer, size_t* w_off, size_t* b_off,
+                                   int* ld) {
+  DMLP_REQUIRE(cfg && layer >= 0 && layer < cfg->num_layers, "bad layer index");
+  ParamLayout lay;
+  make_layout(*cfg, &lay);
+  if (w_off) *w_off = lay.w_off[layer];
+  if (b_off) *b_off = lay.b_off[layer];
+  if (ld) *ld = lay.out_pad[layer];
+  return DMLP_OK;
+}
+
+extern "C" int dmlp_trainer_destroy(dmlp_trainer_t h) {
+  Trainer* t = reinterpret_cast<Trainer*>(h);
+  if (!t) return DMLP_OK;
+  DeviceGuard g(t->dev);
+  cudaDeviceSynchronize();
+  for (int p = 0; p < 2; ++p) {
+    if (t->gexec[p]) cudaGraphExecDestroy(t->gexec[p]);
+    if (t->graph[p]) cudaGraphDestroy(t->graph[p]);
+    if (t->ev_h2d[p]) cudaEventDestroy(t->ev_h2d[p]);
+    if (t->ev_done[p]) cudaEventDestroy(t->ev_done[p]);
+  }
+  if (t->ev_join) cudaEventDestroy(t->ev_join);
+  for (int l = 0; l < kMaxLayers; ++l)
+    if (t->ev_bucket[l]) cudaEventDestroy(t->ev_bucket[l]);
+  if (t->s_main) cudaStreamDestroy(t->s_main);
+  if (t->s_comm) cudaStreamDestroy(t->s_comm);
+  if (t->s_copy) cudaStreamDestroy(t->s_copy);
+  for (void* p : t->owned) cudaFree(p);
+  if (t->metrics_host) cudaFreeHost(t->metrics_host);
+  if (t->lr_host) cudaFreeHost(t->lr_host);
+  cudaGetLastError();
+  delete t;
+  return DMLP_OK;
+}
+
+extern "C" int dmlp_trainer_create(const dmlp_trainer_config_t* cfg, int device, dmlp_comm_t comm, int local_idx,
+                                   int rank, int world, size_t arena_offset, dmlp_trainer_t* out) {
+  DMLP_REQUIRE(cfg && out, "dmlp_trainer_create: null argument");
+  DMLP_REQUIRE(cfg->num_layers >= 1 && cfg->num_layers <= kMaxLayers, "num_layers %d not in [1,%d]", cfg->num_layers, kMaxLayers);
+  DMLP_REQUIRE(cfg->batch >= 1, "batch must be positive");
+  DMLP_REQUIRE(cfg->dtype == DMLP_F32 || cfg->dtype == DMLP_BF16, "dtype must be F32 (tf32 math) or BF16");
+  DMLP_REQUIRE(cfg->dims[0] % 8 == 0, "input width %d must be a multiple of 8 (TMA row pitch)", cfg->dims[0]);
+  for (int l = 1; l < cfg->num_layers; ++l)
+    DMLP_REQUIRE(cfg->dims[l] % 16 == 0, "hidden width %d must be a multiple of 16", cfg->dims[l]);
+  DMLP_REQUIRE(world >= 1 && world <= DMLP_MAX_RANKS && rank >= 0 && rank < world, "bad rank/world");
+  DMLP_REQUIRE((world == 1) || comm != nullptr, "world > 1 needs a communicator");
+  Trainer* t = new (std::nothrow) Trainer();
+  if (!t) return set_error(DMLP_ERR_CUDA, "out of host memory");
+  memset(t->ev_h2d, 0, sizeof(t->ev_h2d));
+  memset(t->ev_done, 0, sizeof(t->ev_done));
+  memset(t->ev_bucket, 0, sizeof(t->ev_bucket));
+  t->ev_fork = t->ev_join = nullptr;
+  memset(t->act, 0, sizeof(t->act));
+  memset(t->act16, 0, sizeof(t->act16));
+  memset(t->dz, 0, sizeof(t->dz));
+  memset(t->dz16, 0, sizeof(t->dz16));
+  memset(t->peer_params, 0, sizeof(t->peer_params));
+  memset(t->peer_shadow, 0, sizeof(t->peer_shadow));
+  memset(t->peer_grads, 0, sizeof(t->peer_grads));
+  t->cfg = *cfg;
+  t->dev = device;
+  t->comm = (world > 1) ? comm : nullptr;
+  t->local_idx = local_idx;
+  t->rank = rank;
+  t->world = world;
+  t->bf16 = cfg->dtype == DMLP_BF16;
+  make_layout(*cfg, &t->lay);
+  const ParamLayout& L = t->lay;
+  const int B = cfg->batch;
+  DeviceGuard guard(device);
+  int rc = DMLP_OK;
+  auto fail = [&](int code) { dmlp_trainer_destroy(reinterpret_cast<dmlp_trainer_t>(t)); return code; };
+#define TRYF(expr) do { rc = (expr); if (rc) return fail(rc); } while (0)
+#define CUF(expr) do { cudaError_t _e = (expr); if (_e != cudaSuccess) { set_error(DMLP_ERR_CUDA, "%s: %s", #expr, cudaGetErrorString(_e)); return fail(DMLP_ERR_CUDA); } } while (0)
+
+  const size_t pbytes = align_up(L.total * 4, 256);
+  const size_t sbytes = align_up(L.total * 2, 256);
+  if (t->comm) {
+    for (int r = 0; r < world; ++r) {
+      void* base = nullptr;
+      size_t cap = 0;
+      int e = dmlp_comm_arena_ptr(t->comm, local_idx, r, &base, &cap);
+      if (e != DMLP_OK) { if (r == rank) return fail(e); continue; }  // peers unmapped: ring still works
+      size_t need = arena_offset + 3 * pbytes + (t->bf16 ? sbytes : 0);
+      if (cap < need) { set_error(DMLP_ERR_INVALID, "communicator arena too small: %zu < %zu", cap, need); return fail(DMLP_ERR_INVALID); }
+      uint8_t* b = static_cast<uint8_t*>(base) + arena_offset;
+      t->peer_params[r] = reinterpret_cast<float*>(b);
+      t->peer_grads[0][r] = reinterpret_cast<float*>(b + pbytes);
+      t->peer_grads[1][r] = reinterpret_cast<float*>(b + 2 * pbytes);
+      if (t->bf16) t->peer_shadow[r] = b + 3 * pbytes;
+    }
+    t->params = t->peer_params[rank];
+    t->grads[0] = t->peer_grads[0][rank];
+    t->grads[1] = t->peer_grads[1][rank];
+    t->shadow = reinterpret_cast<__nv_bfloat16*>(t->peer_shadow[rank]);
+  } else {
+    void* p = nullptr;
+    TRYF(dev_alloc(t, pbytes, &p)); t->params = static_cast<float*>(p);
+    TRYF(dev_alloc(t, pbytes, &p)); t->grads[0] = static_cast<float*>(p);
+    TRYF(dev_alloc(t, pbytes, &p)); t->grads[1] = static_cast<float*>(p);
+    if (t->bf16) { TRYF(dev_alloc(t, sbytes, &p)); t->shadow = static_cast<__nv_bfloat16*>(p); }
+  }
+  void* p = nullptr;
+  for (int par = 0; par < 2; ++par) {
+    TRYF(dev_alloc(t, static_cast<size_t>(B) * L.in[0] * 4, &p)); t->x[par] = static_cast<float*>(p);
+    TRYF(dev_alloc(t, static_cast<size_t>(B) * 4, &p)); t->labels[par] = static_cast<int*>(p);
+    TRYF(dev_alloc(t, 16, &p)); t->metrics_dev[par] = static_cast<float*>(p);
+  }
+  if (t->bf16) { TRYF(dev_alloc(t, static_cast<size_t>(B) * L.in[0] * 2, &p)); t->x16 = static_cast<__nv_bfloat16*>(p); }
+  for (int l = 0; l < L.L; ++l) {
+    const size_t n = static_cast<size_t>(B) * L.out_pad[l];
+    const bool last = l == L.L - 1;
+    if (!t->bf16 || last) { TRYF(dev_alloc(t, n * 4, &p)); t->act[l] = static_cast<float*>(p); }
+    if (t->bf16 && !last) { TRYF(dev_alloc(t, n * 2, &p)); t->act16[l] = static_cast<__nv_bfloat16*>(p); }
+    if (t->bf16) { TRYF(dev_alloc(t, n * 2, &p)); t->dz16[l] = static_cast<__nv_bfloat16*>(p); }
+    else { TRYF(dev_alloc(t, n * 4, &p)); t->dz[l] = static_cast<float*>(p); }
+  }
+  TRYF(dev_alloc(t, 16, &p)); t->lr_dev = static_cast<float*>(p);
+  CUF(cudaHostAlloc(reinterpret_cast<void**>(&t->metrics_host), 64, cudaHostAllocPortable));
+  CUF(cudaHostAlloc(reinterpret_cast<void**>(&t->lr_host), 64, cudaHostAllocPortable));
+  memset(t->metrics_host, 0, 64);
+  t->lr_host[0] = cfg->lr;
+  CUF(cudaMemcpy(t->lr_dev, t->lr_host, 4, cudaMemcpyHostToDevice));
+  CUF(cudaStreamCreateWithFlags(&t->s_main, cudaStreamNonBlocking));
+  CUF(cudaStreamCreateWithFlags(&t->s_comm, cudaStreamNonBlocking));
+  CUF(cudaStreamCreateWithFlags(&t->s_copy, cudaStreamNonBlocking));
+  for (int par = 0; par < 2; ++par) {
+    CUF(cudaEventCreateWithFlags(&t->ev_h2d[par], cudaEventDisableTiming));
+    CUF(cudaEventCreateWithFlags(&t->ev_done[par], cudaEventDisableTiming));
+  }
+  CUF(cudaEventCreateWithFlags(&t->ev_join, cudaEventDisableTiming));
+  for (int l = 0; l < L.L; ++l) CUF(cudaEventCreateWithFlags(&t->ev_bucket[l], cudaEventDisableTiming));
+  TRYF(build_plans(t));
+  *out = reinterpret_cast<dmlp_trainer_t>(t);
+  return DMLP_OK;
+#undef TRYF
+#undef CUF
+}
+
+extern "C" int dmlp_trainer_params(dmlp_trainer_t h, float** params_dev, size_t* count) {
+  Trainer* t = reinterpret_cast<Trainer*>(h);
+  DMLP_REQUIRE(t, "null trainer");
+  if (params_dev) *params_dev = t->params;
+  if (count) *count = t->lay.total;
+  return DMLP_OK;
+}
+
+// Call after the parameters were (re)written from the host: refreshes the bf16 shadow.
+extern "C" int dmlp_trainer_params_updated(dmlp_trainer_t h) {
+  Trainer* t = reinterpret_cast<Trainer*>(h);
+  DMLP_REQUIRE(t, "null trainer");
+  DeviceGuard g(t->dev);
+  if (t->bf16) TRY(dmlp_cast_f32_to_bf16(t->params, t->shadow, t->lay.total, t->s_main));
+  DMLP_CUDA_CHECK(cudaStreamSynchronize(t->s_main));
+  return DMLP_OK;
+}
+
+extern "C" int dmlp_trainer_set_lr(dmlp_trainer_t h, float lr) {
+  Trainer* t = reinterpret_cast<Trainer*>(h);
+  DMLP_REQUIRE(t, "null trainer");
+  DeviceGuard g(t->dev);
+  DMLP_CUDA_CHECK(cudaStreamSynchronize(t->s_main));
+  t->lr_host[0] = lr;
+  DMLP_CUDA_CHECK(cudaMemcpyAsync(t->lr_dev, t->lr_host, 4, cudaMemcpyHostToDevice, t->s_main));
+  DMLP_CUDA_CHECK(cudaStreamSynchronize(t->s_main));
+  return DMLP_OK;
+}
+
+extern "C" int dmlp_trainer_kernels_per_step(dmlp_trainer_t h, int* n) {
+  Trainer* t = reinterpret_cast<Trainer*>(h);
+  DMLP_REQUIRE(t && n, "null argument");
+  *n = t->kernels_per_step;
+  return DMLP_OK;
+}
+
+// Runs `steps` training steps. Batch for step s is rows [(first_batch + s*batch_stride) mod
+// num_batches] * batch of x_host/y_host (pinned host memory gives true async copies). Per-step
+// {loss_sum, correct} pairs are written to metrics_out (2*steps floats; correct as float) if non-null.
+// lr_schedule (nullable, `steps` entries) is applied before each step.
+extern "C" int dmlp_trainer_run(dmlp_trainer_t h, const float* x_host, const int32_t* y_host, size_t num_batches,
+                                size_t first_batch, size_t batch_stride, int steps, const float* lr_schedule,
+                                float* metrics_out, int use_graph) {
+  Trainer* t = reinterpret_cast<Trainer*>(h);
+  DMLP_REQUIRE(t && x_host && y_host && num_batches > 0 && steps >= 0, "dmlp_trainer_run: bad arguments");
+  DeviceGuard g(t->dev);
+  const int B = t->cfg.batch;
+  const size_t xin = t->lay.in[0];
+  if (use_graph && t->gexec[0] == nullptr) {
+    // One eager warm-up pass per parity sets function attributes / loads modules outside capture.
+    // It must not change the model: run it with lr = 0.
+    // (Collectives stay matched across ranks: every rank performs the same two extra steps.)
+    float saved = t->lr_host[0];
+    t->lr_host[0] = 0.f;
+    DMLP_CUDA_CHECK(cudaMemcpy(t->lr_dev, t->lr_host, 4, cudaMemcpyHostToDevice));
+    for (int par = 0; par < 2; ++par) {
+      DMLP_CUDA_CHECK(cudaMemcpyAsync(t->x[par], x_host, sizeof(float) * B * xin, cudaMemcpyHostToDevice, t->s_main));
+      DMLP_CUDA_CHECK(cudaMemcpyAsync(t->labels[par], y_host, sizeof(int) * B, cudaMemcpyHostToDevice, t->s_main));
+      TRY(enqueue_step(t, par, true));
+    }
+    DMLP_CUDA_CHECK(cudaStreamSynchronize(t->s_main));
+    t->lr_host[0] = saved;
+    DMLP_CUDA_CHECK(cudaMemcpy(t->lr_dev, t->lr_host, 4, cudaMemcpyHostToDevice));
+    TRY(capture_graphs(t));
+  }
+  int pending[2] = {-1, -1};  // step index whose metrics sit in metrics_host[par]
+  for (int s = 0; s < steps; ++s) {
+    const int par = static_cast<int>((t->steps_done + s) & 1);
+    if (t->launched[par]) {
+      DMLP_CUDA_CHECK(cudaEventSynchronize(t->ev_done[par]));
+      if (pending[par] >= 0 && metrics_out) {
+        metrics_out[2 * pending[par]] = t->metrics_host[2 * par];
+        metrics_out[2 * pending[par] + 1] = static_cast<float>(reinterpret_cast<int*>(t->metrics_host)[2 * par + 1]);
+      }
+    }
+    const size_t bidx = (first_batch + static_cast<size_t>(s) * batch_stride) % num_batches;
+    DMLP_CUDA_CHECK(cudaMemcpyAsync(t->x[par], x_host + bidx * B * xin, sizeof(float) * B * xin,
+                                    cudaMemcpyHostToDevice, t->s_copy));
+    DMLP_CUDA_CHECK(cudaMemcpyAsync(t->labels[par], y_host + bidx * B, sizeof(int) * B, cudaMemcpyHostToDevice, t->s_copy));
+    DMLP_CUDA_CHECK(cudaEventRecord(t->ev_h2d[par], t->s_copy));
+    DMLP_CUDA_CHECK(cudaStreamWaitEvent(t->s_main, t->ev_h2d[par], 0));
+    if (lr_schedule && lr_schedule[s] != t->lr_host[0]) {
+      // lr_host is read by the async copy: wait for the previous update to land first
+      DMLP_CUDA_CHECK(cudaStreamSynchronize(t->s_main));
+      t->lr_host[0] = lr_schedule[s];
+      DMLP_CUDA_CHECK(cudaMemcpyAsync(t->lr_dev, t->lr_host, 4, cudaMemcpyHostToDevice, t->s_main));
+    }
+    if (use_graph) {
+      DMLP_CUDA_CHECK(cudaGraphLaunch(t->gexec[par], t->s_main));
+    } else {
+      TRY(enqueue_step(t, par, true));
+    }
+    DMLP_CUDA_CHECK(cudaEventRecord(t->ev_done[par], t->s_main));
+    t->launched[par] = true;
+    pending[par] = s;
+  }
+  DMLP_CUDA_CHECK(cudaStreamSynchronize(t->s_main));
+  for (int par = 0; par < 2; ++par) {
+    if (pending[par] >= 0 && metrics_out) {
+      metrics_out[2 * pending[par]] = t->metrics_host[2 * par];
+      metrics_out[2 * pending[par] + 1] = static_cast<float>(reinterpret_cast<int*>(t->metrics_host)[2 * par + 1]);
+    }
+  }
+  t->steps_done += steps;
+  if (t->comm) {
+    uint32_t st[5];
+    TRY(dmlp_comm_status(t->comm, st));
+    if (st[0] != 0)
+      return set_error(DMLP_ERR_TIMEOUT, "collective watchdog: rank %u waited for rank %u (phase %u)", st[1], st[2], st[3]);
+  }
+  return DMLP_OK;
+}
+
+// Device-resident variant used for kernel-only timing: inputs already sit in the trainer's two
+// input buffers (filled by dmlp_trainer_load_inputs); no H2D/D2H happens inside the loop.
+extern "C" int dmlp_trainer_load_inputs(dmlp_trainer_t h, int parity, const float* x_host, const int32_t* y_host) {
+  Trainer* t = reinterpret_cast<Trainer*>(h);
+  DMLP_REQUIRE(t && x_host && y_host && (parity == 0 || parity == 1), "bad arguments");
+  DeviceGuard g(t->dev);
+  DMLP_CUDA_CHECK(cudaMemcpy(t->x[parity], x_host, sizeof(float) * t->cfg.batch * t->lay.in[0], cudaMemcpyHostToDevice));
+  DMLP_CUDA_CHECK(cudaMemcpy(t->labels[parity], y_host, sizeof(int) * t->cfg.batch, cudaMemcpyHostToDevice));
+  return DMLP_OK;
+}
+
+extern "C" int dmlp_trainer_run_resident(dmlp_trainer_t h, int steps, int use_graph, void* start_event, void* stop_event) {
+  Trainer* t = reinterpret_cast<Trainer*>(h);
+  DMLP_REQUIRE(t && steps >= 0, "bad arguments");
+  DeviceGuard g(t->dev);
+  if (use_graph && t->gexec[0] == nullptr) {
+    float saved = t->lr_host[0];
+    t->lr_host[0] = 0.f;
+    DMLP_CUDA_CHECK(cudaMemcpy(t->lr_dev, t->lr_host, 4, cudaMemcpyHostToDevice));
+    for (int par = 0; par < 2; ++par) TRY(enqueue_step(t, par, true));
+    DMLP_CUDA_CHECK(cudaStreamSynchronize(t->s_main));
+    t->lr_host[0] = saved;
+    DMLP_CUDA_CHECK(cudaMemcpy(t->lr_dev, t->lr_host, 4, cudaMemcpyHostToDevice));
+    TRY(capture_graphs(t));
+  }
+  if (start_event) DMLP_CUDA_CHECK(cudaEventRecord(reinterpret_cast<cudaEvent_t>(start_event), t->s_main));
+  for (int s = 0; s < steps; ++s) {
+    const int par = static_cast<int>((t->steps_done + s) & 1);
+    if (use_graph) DMLP_CUDA_CHECK(cudaGraphLaunch(t->gexec[par], t->s_main));
+    else TRY(enqueue_step(t, par, true));
+  }
+  if (stop_event) DMLP_CUDA_CHECK(cudaEventRecord(reinterpret_cast<cudaEvent_t>(stop_event), t->s_main));
+  DMLP_CUDA_CHECK(cudaStreamSynchronize(t->s_main));
+  t->steps_done += steps;
+  return DMLP_OK;
+}
+
+// Forward-only evaluation over n_batches full batches (reference testModel, client.go:462-502).
+extern "C" int dmlp_trainer_eval(dmlp_trainer_t h, const float* x_host, const int32_t* y_host, size_t n_batches,
+                                 double* loss_sum, long long* correct) {
+  Trainer* t = reinterpret_cast<Trainer*>(h);
+  DMLP_REQUIRE(t && x_host && y_host, "bad arguments");
+  DeviceGuard g(t->dev);
+  const ParamLayout& L = t->lay;
+  const int B = t->cfg.batch;
+  const int last = L.L - 1;
+  double ls = 0;
+  long long cs = 0;
+  DMLP_CUDA_CHECK(cudaStreamSynchronize(t->s_main));
+  for (size_t b = 0; b < n_batches; ++b) {
+    cudaStream_t S = t->s_main;
+    DMLP_CUDA_CHECK(cudaMemcpyAsync(t->x[0], x_host + b * B * L.in[0], sizeof(float) * B * L.in[0], cudaMemcpyHostToDevice, S));
+    DMLP_CUDA_CHECK(cudaMemcpyAsync(t->labels[0], y_host + b * B, sizeof(int) * B, cudaMemcpyHostToDevice, S));
+    DMLP_CUDA_CHECK(cudaMemsetAsync(t->metrics_dev[0], 0, 8, S));
+    if (t->bf16) TRY(dmlp_cast_f32_to_bf16(t->x[0], t->x16, static_cast<size_t>(B) * L.in[0], S));
+    for (int l = 0; l < L.L; ++l) TRY(gemm_plan_run(&t->fwd[0][l], S));
+    TRY(dmlp_softmax_ce(t->act[last], L.out_pad[last], t->labels[0], B, L.out[last], 1.f / B, nullptr, nullptr,
+                        t->metrics_dev[0], reinterpret_cast<int32_t*>(t->metrics_dev[0] + 1), nullptr, S));
+    DMLP_CUDA_CHECK(cudaMemcpyAsync(t->metrics_host, t->metrics_dev[0], 8, cudaMemcpyDeviceToHost, S));
+    DMLP_CUDA_CHECK(cudaStreamSynchronize(S));
+    ls += t->metrics_host[0];
+    cs += reinterpret_cast<int*>(t->metrics_host)[1];
+  }
+  if (loss_sum) *loss_sum = ls;
+  if (correct) *correct = cs;
+  return DMLP_OK;
+}
+
+// Debug/test access to intermediate buffers: kind 0 = activation l (fp32), 1 = dZ l (fp32),
+// 2 = gradient buffer `l` (parity), 3 = logits.
+extern "C" int dmlp_trainer_buffer(dmlp_trainer_t h, int kind, int l, void** ptr) {
+  Trainer* t = reinterpret_cast<Trainer*>(h);
+  DMLP_REQUIRE(t && ptr, "bad arguments");
+  switch (kind) {
+    case 0: *ptr = t->act[l]; break;
+    case 1: *ptr = t->dz[l]; break;
+    case 2: *ptr = t->grads[l & 1]; break;
+    case 3: *ptr = t->act[t->lay.L - 1]; break;
+    default: return set_error(DMLP_ERR_INVALID, "unknown buffer kind %d", kind);
+  }
+  return DMLP_OK;
+}

@@ -1,0 +1,303 @@
+"""Data-parallel MLP trainer — the public training API.
+
+    from dmlp_b200.parallel.trainer import Trainer, TrainerConfig
+    t = Trainer(TrainerConfig(dims=(784, 128, 64, 10), batch=64), device=0)          # one GPU
+    t = Trainer(cfg, device=local_rank, process_group=True)                          # under torchrun
+    stats = t.fit(x_host, y_host, steps=1000)     # x float32 [N,784] (pinned for async copies), y int32 [N]
+
+Each ``fit`` call runs natively (``csrc/trainer.cu``): per step the batch is copied host→device on a
+copy stream, a captured CUDA graph runs forward / softmax-CE / backward / fused all-reduce+SGD, and
+{loss, correct} are copied back. Replaces the reference client's loop
+(``DSML/client/client.go:516-659``); log lines keep the reference wording.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import logging
+import time
+from dataclasses import dataclass, field
+from typing import Dict, List, Optional, Sequence, Tuple
+
+import numpy as np
+
+from ..models.layout import ParamLayout
+from ..runtime import native
+from ..runtime.comm import Communicator
+from . import schedule as sched
+
+log = logging.getLogger("dmlp.trainer")
+
+
+class _NativeCfg(C.Structure):
+    _fields_ = [("num_layers", C.c_int), ("dims", C.c_int * 9), ("batch", C.c_int), ("dtype", C.c_int),
+                ("lr", C.c_float), ("allreduce_algo", C.c_int), ("overlap", C.c_int)]
+
+
+@dataclass
+class TrainerConfig:
+    dims: Sequence[int] = (784, 128, 64, 10)   # north-star MLP (README shape); reference code: (784,128,10)
+    batch: int = 64                            # per GPU (reference batchSize, client.go:23)
+    lr: float = 0.01                           # reference learningRate (client.go:27)
+    precision: str = "tf32"                    # "tf32" (fp32 storage) | "bf16" (fp32 master + bf16 shadow)
+    allreduce: str = "auto"                    # auto | oneshot | twoshot | ring
+    overlap: bool = False                      # per-layer buckets reduced during backward
+    use_graph: bool = True
+    schedule: str = "constant"
+    seed: int = 0
+    watchdog_ms: int = 10000
+    staging_bytes: int = 8 << 20
+
+    def native(self) -> _NativeCfg:
+        c = _NativeCfg()
+        c.num_layers = len(self.dims) - 1
+        for i, d in enumerate(self.dims):
+            c.dims[i] = int(d)
+        c.batch, c.lr = int(self.batch), float(self.lr)
+        c.dtype = native.BF16 if self.precision == "bf16" else native.F32
+        c.allreduce_algo = native.ALGO_BY_NAME[self.allreduce]
+        c.overlap = int(self.overlap)
+        return c
+
+
+_declared = False
+
+
+def _declare(lib) -> None:
+    global _declared
+    if _declared:
+        return
+    vp, i32, sz = C.c_void_p, C.c_int, C.c_size_t
+    cfgp = C.POINTER(_NativeCfg)
+    sigs = {
+        "dmlp_trainer_param_count": [cfgp, C.POINTER(sz)],
+        "dmlp_trainer_arena_bytes": [cfgp, C.POINTER(sz)],
+        "dmlp_trainer_layout": [cfgp, i32, C.POINTER(sz), C.POINTER(sz), C.POINTER(i32)],
+        "dmlp_trainer_create": [cfgp, i32, vp, i32, i32, i32, sz, C.POINTER(vp)],
+        "dmlp_trainer_destroy": [vp],
+        "dmlp_trainer_params": [vp, C.POINTER(vp), C.POINTER(sz)],
+        "dmlp_trainer_params_updated": [vp],
+        "dmlp_trainer_set_lr": [vp, C.c_float],
+        "dmlp_trainer_kernels_per_step": [vp, C.POINTER(i32)],
+        "dmlp_trainer_run": [vp, vp, vp, sz, sz, sz, i32, vp, vp, i32],
+        "dmlp_trainer_load_inputs": [vp, i32, vp, vp],
+        "dmlp_trainer_run_resident": [vp, i32, i32, vp, vp],
+        "dmlp_trainer_eval": [vp, vp, vp, sz, C.POINTER(C.c_double), C.POINTER(C.c_longlong)],
+        "dmlp_trainer_buffer": [vp, i32, i32, C.POINTER(vp)],
+    }
+    for name, args in sigs.items():
+        fn = getattr(lib, name)
+        fn.argtypes, fn.restype = args, C.c_int
+    _declared = True
+
+
+class PinnedArray:
+    """NumPy array backed by pinned (page-locked) host memory from the native runtime."""
+
+    def __init__(self, shape, dtype):
+        self.dtype = np.dtype(dtype)
+        self.shape = tuple(shape)
+        nbytes = int(np.prod(self.shape)) * self.dtype.itemsize
+        p = C.c_void_p()
+        native.check(native.lib().dmlp_host_alloc(max(nbytes, 16), C.byref(p)))
+        self.ptr = p.value
+        buf = (C.c_char * max(nbytes, 16)).from_address(self.ptr)
+        self.array = np.frombuffer(buf, dtype=self.dtype, count=int(np.prod(self.shape))).reshape(self.shape)
+
+    def free(self):
+        if self.ptr:
+            self.array = None
+            native.lib().dmlp_host_free(self.ptr)
+            self.ptr = None
+
+
+def pin(arr: np.ndarray) -> PinnedArray:
+    out = PinnedArray(arr.shape, arr.dtype)
+    out.array[...] = arr
+    return out
+
+
+class Trainer:
+    def __init__(self, cfg: TrainerConfig, device: int = 0, process_group: bool = False,
+                 comm: Optional[Communicator] = None, local_idx: int = 0):
+        self.cfg = cfg
+        self.device = device
+        self.lib = native.lib()
+        _declare(self.lib)
+        self.layout = ParamLayout(cfg.dims)
+        ncfg = cfg.native()
+        self.rank, self.world = 0, 1
+        self._owns_comm = False
+        self.comm = comm
+        if process_group:
+            import torch.distributed as dist
+            self.rank, self.world = dist.get_rank(), dist.get_world_size()
+            if self.world > 1 and comm is None:
+                need = C.c_size_t()
+                native.check(self.lib.dmlp_trainer_arena_bytes(C.byref(ncfg), C.byref(need)))
+                self.comm = Communicator.from_process_group(device, staging_bytes=cfg.staging_bytes,
+                                                            arena_bytes=need.value)
+                self.comm.set_timeout_ms(cfg.watchdog_ms)
+                self._owns_comm = True
+        elif comm is not None:
+            self.rank, self.world = comm.local_ranks[local_idx], comm.world
+        h = C.c_void_p()
+        native.check(self.lib.dmlp_trainer_create(
+            C.byref(ncfg), device, self.comm._h if (self.comm is not None and self.world > 1) else None,
+            local_idx, self.rank, self.world, 0, C.byref(h)))
+        self._h = h
+        self.global_step = 0
+        self._pinned: Dict[int, Tuple[PinnedArray, PinnedArray]] = {}
+        self.set_params(self.layout.init_reference(cfg.seed))
+
+    # ------------------------------------------------------------------ parameters
+    def _param_ptr(self) -> Tuple[int, int]:
+        p, n = C.c_void_p(), C.c_size_t()
+        native.check(self.lib.dmlp_trainer_params(self._h, C.byref(p), C.byref(n)))
+        return p.value, n.value
+
+    def get_params(self) -> np.ndarray:
+        """Flat padded fp32 parameter buffer (see ``models.layout.ParamLayout``)."""
+        ptr, n = self._param_ptr()
+        out = np.empty(n, dtype=np.float32)
+        native.check(self.lib.dmlp_device_sync(self.device))
+        native.check(self.lib.dmlp_memcpy_d2h(self.device, out.ctypes.data, ptr, n * 4, None))
+        return out
+
+    def set_params(self, flat: np.ndarray) -> None:
+        ptr, n = self._param_ptr()
+        flat = np.ascontiguousarray(flat, dtype=np.float32)
+        assert flat.size == n, f"expected {n} floats, got {flat.size}"
+        native.check(self.lib.dmlp_memcpy_h2d(self.device, ptr, flat.ctypes.data, n * 4, None))
+        native.check(self.lib.dmlp_trainer_params_updated(self._h))
+
+    def weights(self) -> List[Tuple[np.ndarray, np.ndarray]]:
+        return [(w.copy(), b.copy()) for w, b in self.layout.views(self.get_params())]
+
+    def save_weights(self, path: str) -> None:
+        """Writes the reference client's weight blob (W1‖b1‖W2‖b2…, LE float32; client.go:204-218)."""
+        with open(path, "wb") as f:
+            f.write(self.layout.to_reference_bytes(self.get_params()))
+
+    def load_weights(self, path: str) -> None:
+        with open(path, "rb") as f:
+            self.set_params(self.layout.from_reference_bytes(f.read()))
+
+    def set_lr(self, lr: float) -> None:
+        native.check(self.lib.dmlp_trainer_set_lr(self._h, float(lr)))
+
+    @property
+    def kernels_per_step(self) -> int:
+        n = C.c_int()
+        native.check(self.lib.dmlp_trainer_kernels_per_step(self._h, C.byref(n)))
+        return n.value
+
+    # ------------------------------------------------------------------ training
+    def _host_ptrs(self, x, y) -> Tuple[int, int, int]:
+        """Accepts NumPy arrays or PinnedArray; returns (x_ptr, y_ptr, n_samples)."""
+        xa = x.array if isinstance(x, PinnedArray) else x
+        ya = y.array if isinstance(y, PinnedArray) else y
+        assert xa.dtype == np.float32 and ya.dtype == np.int32 and xa.flags["C_CONTIGUOUS"] and ya.flags["C_CONTIGUOUS"]
+        assert xa.shape[1] == self.cfg.dims[0] and xa.shape[0] == ya.shape[0]
+        xp = x.ptr if isinstance(x, PinnedArray) else xa.ctypes.data
+        yp = y.ptr if isinstance(y, PinnedArray) else ya.ctypes.data
+        return xp, yp, xa.shape[0]
+
+    def fit(self, x, y, steps: int, first_batch: Optional[int] = None, lr_schedule: Optional[sched.Schedule] = None,
+            return_metrics: bool = True) -> Dict[str, float]:
+        """Runs ``steps`` optimisation steps. Rank r consumes batches r, r+world, r+2·world, … of the
+        host dataset (sequential, no shuffle, partial last batch dropped — like the reference)."""
+        xp, yp, n = self._host_ptrs(x, y)
+        nb = n // self.cfg.batch
+        if nb == 0:
+            raise ValueError("dataset smaller than one batch")
+        first = self.global_step * self.world + self.rank if first_batch is None else first_batch
+        lrs = None
+        if lr_schedule is not None:
+            lrs = np.array([lr_schedule(self.global_step + s) for s in range(steps)], dtype=np.float32)
+        metrics = np.zeros(2 * steps, dtype=np.float32) if return_metrics else None
+        t0 = time.perf_counter()
+        native.check(self.lib.dmlp_trainer_run(
+            self._h, xp, yp, nb, first % nb, self.world, steps, lrs.ctypes.data if lrs is not None else None,
+            metrics.ctypes.data if metrics is not None else None, int(self.cfg.use_graph)))
+        dt = time.perf_counter() - t0
+        self.global_step += steps
+        out = {"steps": steps, "seconds": dt, "samples_per_s": steps * self.cfg.batch * self.world / dt if dt > 0 else 0.0}
+        if metrics is not None and steps:
+            m = metrics.reshape(steps, 2)
+            out["loss"] = float(m[:, 0].mean() / self.cfg.batch)
+            out["accuracy"] = float(m[:, 1].sum() / (steps * self.cfg.batch))
+            out["last_loss"] = float(m[-1, 0] / self.cfg.batch)
+            out["per_step_loss"] = (m[:, 0] / self.cfg.batch)
+        return out
+
+    def train_epochs(self, x, y, epochs: int, steps_per_epoch: Optional[int] = None,
+                     lr_schedule: Optional[sched.Schedule] = None) -> List[Dict[str, float]]:
+        """Epoch loop with the reference's per-epoch log line (client.go:650-652)."""
+        _, _, n = self._host_ptrs(x, y)
+        spe = steps_per_epoch or (n // (self.cfg.batch * self.world))
+        hist = []
+        if self.rank == 0:
+            log.info("Starting MLP training...")
+        for ep in range(1, epochs + 1):
+            st = self.fit(x, y, spe, lr_schedule=lr_schedule)
+            hist.append(st)
+            if self.rank == 0:
+                log.info("Epoch %d complete: Avg Loss: %.4f, Accuracy: %.2f%%", ep, st["loss"], 100 * st["accuracy"])
+        if self.rank == 0:
+            log.info("Training complete.")
+        return hist
+
+    def evaluate(self, x, y) -> Dict[str, float]:
+        """Forward-only pass over all full batches (reference ``testModel``, client.go:462-502)."""
+        xp, yp, n = self._host_ptrs(x, y)
+        nb = n // self.cfg.batch
+        loss, correct = C.c_double(), C.c_longlong()
+        native.check(self.lib.dmlp_trainer_eval(self._h, xp, yp, nb, C.byref(loss), C.byref(correct)))
+        tot = nb * self.cfg.batch
+        acc = correct.value / max(tot, 1)
+        if self.rank == 0:
+            log.info("Final Test Accuracy: %.2f%%", 100 * acc)
+        return {"loss": loss.value / max(tot, 1), "accuracy": acc, "samples": tot}
+
+    # ------------------------------------------------------------------ kernel-only timing helpers
+    def load_resident_inputs(self, x: np.ndarray, y: np.ndarray) -> None:
+        B = self.cfg.batch
+        for par in range(2):
+            xs = np.ascontiguousarray(x[par * B:(par + 1) * B], dtype=np.float32)
+            ys = np.ascontiguousarray(y[par * B:(par + 1) * B], dtype=np.int32)
+            native.check(self.lib.dmlp_trainer_load_inputs(self._h, par, xs.ctypes.data, ys.ctypes.data))
+
+    def run_resident(self, steps: int) -> float:
+        """Runs ``steps`` steps on the device-resident inputs; returns device milliseconds (CUDA events)."""
+        e0, e1 = C.c_void_p(), C.c_void_p()
+        native.check(self.lib.dmlp_event_create(self.device, 1, C.byref(e0)))
+        native.check(self.lib.dmlp_event_create(self.device, 1, C.byref(e1)))
+        native.check(self.lib.dmlp_trainer_run_resident(self._h, steps, int(self.cfg.use_graph), e0, e1))
+        ms = C.c_float()
+        native.check(self.lib.dmlp_event_elapsed_ms(e0, e1, C.byref(ms)))
+        self.lib.dmlp_event_destroy(e0)
+        self.lib.dmlp_event_destroy(e1)
+        self.global_step += steps
+        return ms.value
+
+    def debug_buffer(self, kind: int, index: int, count: int) -> np.ndarray:
+        p = C.c_void_p()
+        native.check(self.lib.dmlp_trainer_buffer(self._h, kind, index, C.byref(p)))
+        out = np.empty(count, dtype=np.float32)
+        native.check(self.lib.dmlp_device_sync(self.device))
+        native.check(self.lib.dmlp_memcpy_d2h(self.device, out.ctypes.data, p.value, count * 4, None))
+        return out
+
+    def close(self) -> None:
+        if getattr(self, "_h", None):
+            self.lib.dmlp_trainer_destroy(self._h)
+            self._h = None
+        if self._owns_comm and self.comm is not None:
+            self.comm.destroy()
+            self.comm = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass

@@ -208,6 +208,48 @@ int dmlp_p2p_copy(int src_dev, void* dst_dev, const void* src_dev_ptr, size_t by
 int dmlp_reduce_n(int dev, void* dst_dev, const void* const* srcs_dev, int n, size_t count, int dtype,
                   int op, void* stream);
 
+/* ------------------------------------------------------------------ native data-parallel MLP trainer
+ * Reference: the client's model, step and epoch loop (DSML/client/client.go:22-58 model/init,
+ * :112-202 forward/backward, :254-267 SGD, :462-502 eval, :516-659 training loop).
+ *
+ * Parameters live in one flat fp32 buffer, per layer W[in][out_pad] then b[out_pad] (out_pad = out
+ * rounded up to 16, padding kept at zero; every tensor starts on a 256-byte boundary). This is the
+ * reference's W1|b1|W2|b2(|W3|b3) order; the unpadded little-endian byte layout the reference
+ * uploads to MemAddr 0x2000 (client.go:60-66,204-218) is produced/consumed by the Python
+ * checkpoint helpers. With a communicator the buffer sits in the symmetric arena so peers can
+ * read gradients / write updated weights directly.
+ */
+#define DMLP_MAX_LAYERS 8
+typedef struct {
+  int num_layers;
+  int dims[DMLP_MAX_LAYERS + 1]; /* e.g. 784,128,64,10 */
+  int batch;                     /* per-GPU batch */
+  int dtype;                     /* DMLP_F32: tf32 tensor-core math, fp32 storage; DMLP_BF16 */
+  float lr;
+  int allreduce_algo;            /* dmlp_algo_t */
+  int overlap;                   /* 1: per-layer buckets reduced on a second stream during backward */
+} dmlp_trainer_config_t;
+typedef struct dmlp_trainer_opaque* dmlp_trainer_t;
+
+int dmlp_trainer_param_count(const dmlp_trainer_config_t* cfg, size_t* floats);
+int dmlp_trainer_arena_bytes(const dmlp_trainer_config_t* cfg, size_t* bytes);
+int dmlp_trainer_layout(const dmlp_trainer_config_t* cfg, int layer, size_t* w_off, size_t* b_off, int* ld);
+int dmlp_trainer_create(const dmlp_trainer_config_t* cfg, int device, dmlp_comm_t comm, int local_idx,
+                        int rank, int world, size_t arena_offset, dmlp_trainer_t* out);
+int dmlp_trainer_destroy(dmlp_trainer_t t);
+int dmlp_trainer_params(dmlp_trainer_t t, float** params_dev, size_t* count);
+int dmlp_trainer_params_updated(dmlp_trainer_t t);
+int dmlp_trainer_set_lr(dmlp_trainer_t t, float lr);
+int dmlp_trainer_kernels_per_step(dmlp_trainer_t t, int* n);
+int dmlp_trainer_run(dmlp_trainer_t t, const float* x_host, const int32_t* y_host, size_t num_batches,
+                     size_t first_batch, size_t batch_stride, int steps, const float* lr_schedule,
+                     float* metrics_out, int use_graph);
+int dmlp_trainer_load_inputs(dmlp_trainer_t t, int parity, const float* x_host, const int32_t* y_host);
+int dmlp_trainer_run_resident(dmlp_trainer_t t, int steps, int use_graph, void* start_event, void* stop_event);
+int dmlp_trainer_eval(dmlp_trainer_t t, const float* x_host, const int32_t* y_host, size_t n_batches,
+                      double* loss_sum, long long* correct);
+int dmlp_trainer_buffer(dmlp_trainer_t t, int kind, int index, void** ptr_dev);
+
 #ifdef __cplusplus
 }
 #endif
