@@ -436,12 +436,15 @@ extern "C" int dmlp_trainer_kernels_per_step(dmlp_trainer_t h, int* n) {
 }
 
 // Runs `steps` training steps. Batch for step s is rows [(first_batch + s*batch_stride) mod
-// num_batches] * batch of x_host/y_host (pinned host memory gives true async copies). Per-step
+// num_batches] * batch of x_host/y_host (pinned host memory gives true async copies; the pointers
+// may also name a device-resident dataset — the copy direction is inferred — which is how the
+// kernel-only timing streams inputs from a dataset larger than L2). start/stop events (nullable)
+// are recorded on the compute stream around the loop. Per-step
 // {loss_sum, correct} pairs are written to metrics_out (2*steps floats; correct as float) if non-null.
 // lr_schedule (nullable, `steps` entries) is applied before each step.
 extern "C" int dmlp_trainer_run(dmlp_trainer_t h, const float* x_host, const int32_t* y_host, size_t num_batches,
                                 size_t first_batch, size_t batch_stride, int steps, const float* lr_schedule,
-                                float* metrics_out, int use_graph) {
+                                float* metrics_out, int use_graph, void* start_event, void* stop_event) {
   Trainer* t = reinterpret_cast<Trainer*>(h);
   DMLP_REQUIRE(t && x_host && y_host && num_batches > 0 && steps >= 0, "dmlp_trainer_run: bad arguments");
   DeviceGuard g(t->dev);
@@ -455,8 +458,8 @@ extern "C" int dmlp_trainer_run(dmlp_trainer_t h, const float* x_host, const int
     t->lr_host[0] = 0.f;
     DMLP_CUDA_CHECK(cudaMemcpy(t->lr_dev, t->lr_host, 4, cudaMemcpyHostToDevice));
     for (int par = 0; par < 2; ++par) {
-      DMLP_CUDA_CHECK(cudaMemcpyAsync(t->x[par], x_host, sizeof(float) * B * xin, cudaMemcpyHostToDevice, t->s_main));
-      DMLP_CUDA_CHECK(cudaMemcpyAsync(t->labels[par], y_host, sizeof(int) * B, cudaMemcpyHostToDevice, t->s_main));
+      DMLP_CUDA_CHECK(cudaMemcpyAsync(t->x[par], x_host, sizeof(float) * B * xin, cudaMemcpyDefault, t->s_main));
+      DMLP_CUDA_CHECK(cudaMemcpyAsync(t->labels[par], y_host, sizeof(int) * B, cudaMemcpyDefault, t->s_main));
       TRY(enqueue_step(t, par, true));
     }
     DMLP_CUDA_CHECK(cudaStreamSynchronize(t->s_main));
@@ -465,6 +468,7 @@ extern "C" int dmlp_trainer_run(dmlp_trainer_t h, const float* x_host, const int
     TRY(capture_graphs(t));
   }
   int pending[2] = {-1, -1};  // step index whose metrics sit in metrics_host[par]
+  if (start_event) DMLP_CUDA_CHECK(cudaEventRecord(reinterpret_cast<cudaEvent_t>(start_event), t->s_main));
   for (int s = 0; s < steps; ++s) {
     const int par = static_cast<int>((t->steps_done + s) & 1);
     if (t->launched[par]) {
@@ -476,8 +480,8 @@ extern "C" int dmlp_trainer_run(dmlp_trainer_t h, const float* x_host, const int
     }
     const size_t bidx = (first_batch + static_cast<size_t>(s) * batch_stride) % num_batches;
     DMLP_CUDA_CHECK(cudaMemcpyAsync(t->x[par], x_host + bidx * B * xin, sizeof(float) * B * xin,
-                                    cudaMemcpyHostToDevice, t->s_copy));
-    DMLP_CUDA_CHECK(cudaMemcpyAsync(t->labels[par], y_host + bidx * B, sizeof(int) * B, cudaMemcpyHostToDevice, t->s_copy));
+                                    cudaMemcpyDefault, t->s_copy));
+    DMLP_CUDA_CHECK(cudaMemcpyAsync(t->labels[par], y_host + bidx * B, sizeof(int) * B, cudaMemcpyDefault, t->s_copy));
     DMLP_CUDA_CHECK(cudaEventRecord(t->ev_h2d[par], t->s_copy));
     DMLP_CUDA_CHECK(cudaStreamWaitEvent(t->s_main, t->ev_h2d[par], 0));
     if (lr_schedule && lr_schedule[s] != t->lr_host[0]) {
@@ -495,6 +499,7 @@ extern "C" int dmlp_trainer_run(dmlp_trainer_t h, const float* x_host, const int
     t->launched[par] = true;
     pending[par] = s;
   }
+  if (stop_event) DMLP_CUDA_CHECK(cudaEventRecord(reinterpret_cast<cudaEvent_t>(stop_event), t->s_main));
   DMLP_CUDA_CHECK(cudaStreamSynchronize(t->s_main));
   for (int par = 0; par < 2; ++par) {
     if (pending[par] >= 0 && metrics_out) {

@@ -78,7 +78,7 @@ def _declare(lib) -> None:
         "dmlp_trainer_params_updated": [vp],
         "dmlp_trainer_set_lr": [vp, C.c_float],
         "dmlp_trainer_kernels_per_step": [vp, C.POINTER(i32)],
-        "dmlp_trainer_run": [vp, vp, vp, sz, sz, sz, i32, vp, vp, i32],
+        "dmlp_trainer_run": [vp, vp, vp, sz, sz, sz, i32, vp, vp, i32, vp, vp],
         "dmlp_trainer_load_inputs": [vp, i32, vp, vp],
         "dmlp_trainer_run_resident": [vp, i32, i32, vp, vp],
         "dmlp_trainer_eval": [vp, vp, vp, sz, C.POINTER(C.c_double), C.POINTER(C.c_longlong)],
@@ -108,6 +108,29 @@ class PinnedArray:
             self.array = None
             native.lib().dmlp_host_free(self.ptr)
             self.ptr = None
+
+
+class DeviceDataset:
+    """A dataset resident in device memory (kernel-only timing: inputs stream from HBM, not PCIe)."""
+
+    def __init__(self, device: int, x: np.ndarray, y: np.ndarray):
+        self.device, self.n = device, x.shape[0]
+        self.shape_x = x.shape
+        lib = native.lib()
+        px, py = C.c_void_p(), C.c_void_p()
+        native.check(lib.dmlp_malloc(device, x.nbytes, C.byref(px)))
+        native.check(lib.dmlp_malloc(device, y.nbytes, C.byref(py)))
+        x = np.ascontiguousarray(x, dtype=np.float32)
+        y = np.ascontiguousarray(y, dtype=np.int32)
+        native.check(lib.dmlp_memcpy_h2d(device, px, x.ctypes.data, x.nbytes, None))
+        native.check(lib.dmlp_memcpy_h2d(device, py, y.ctypes.data, y.nbytes, None))
+        self.x_ptr, self.y_ptr, self.nbytes = px.value, py.value, x.nbytes + y.nbytes
+
+    def free(self):
+        if self.x_ptr:
+            native.lib().dmlp_free(self.device, self.x_ptr)
+            native.lib().dmlp_free(self.device, self.y_ptr)
+            self.x_ptr = self.y_ptr = None
 
 
 def pin(arr: np.ndarray) -> PinnedArray:
@@ -193,7 +216,10 @@ class Trainer:
 
     # ------------------------------------------------------------------ training
     def _host_ptrs(self, x, y) -> Tuple[int, int, int]:
-        """Accepts NumPy arrays or PinnedArray; returns (x_ptr, y_ptr, n_samples)."""
+        """Accepts NumPy arrays, PinnedArray or a DeviceDataset (as x; y ignored); returns (x_ptr, y_ptr, n)."""
+        if isinstance(x, DeviceDataset):
+            assert x.shape_x[1] == self.cfg.dims[0]
+            return x.x_ptr, x.y_ptr, x.n
         xa = x.array if isinstance(x, PinnedArray) else x
         ya = y.array if isinstance(y, PinnedArray) else y
         assert xa.dtype == np.float32 and ya.dtype == np.int32 and xa.flags["C_CONTIGUOUS"] and ya.flags["C_CONTIGUOUS"]
@@ -203,25 +229,39 @@ class Trainer:
         return xp, yp, xa.shape[0]
 
     def fit(self, x, y, steps: int, first_batch: Optional[int] = None, lr_schedule: Optional[sched.Schedule] = None,
-            return_metrics: bool = True) -> Dict[str, float]:
+            return_metrics: bool = True, device_timing: bool = False,
+            batch_stride: Optional[int] = None) -> Dict[str, float]:
         """Runs ``steps`` optimisation steps. Rank r consumes batches r, r+world, r+2·world, … of the
-        host dataset (sequential, no shuffle, partial last batch dropped — like the reference)."""
+        host dataset (sequential, no shuffle, partial last batch dropped — like the reference).
+        ``batch_stride=1`` walks a rank-private dataset densely instead."""
         xp, yp, n = self._host_ptrs(x, y)
         nb = n // self.cfg.batch
         if nb == 0:
             raise ValueError("dataset smaller than one batch")
-        first = self.global_step * self.world + self.rank if first_batch is None else first_batch
+        stride = self.world if batch_stride is None else int(batch_stride)
+        first = self.global_step * stride + (self.rank if batch_stride is None else 0) if first_batch is None else first_batch
         lrs = None
         if lr_schedule is not None:
             lrs = np.array([lr_schedule(self.global_step + s) for s in range(steps)], dtype=np.float32)
         metrics = np.zeros(2 * steps, dtype=np.float32) if return_metrics else None
+        e0 = e1 = None
+        if device_timing:
+            e0, e1 = C.c_void_p(), C.c_void_p()
+            native.check(self.lib.dmlp_event_create(self.device, 1, C.byref(e0)))
+            native.check(self.lib.dmlp_event_create(self.device, 1, C.byref(e1)))
         t0 = time.perf_counter()
         native.check(self.lib.dmlp_trainer_run(
-            self._h, xp, yp, nb, first % nb, self.world, steps, lrs.ctypes.data if lrs is not None else None,
-            metrics.ctypes.data if metrics is not None else None, int(self.cfg.use_graph)))
+            self._h, xp, yp, nb, first % nb, stride, steps, lrs.ctypes.data if lrs is not None else None,
+            metrics.ctypes.data if metrics is not None else None, int(self.cfg.use_graph), e0, e1))
         dt = time.perf_counter() - t0
         self.global_step += steps
         out = {"steps": steps, "seconds": dt, "samples_per_s": steps * self.cfg.batch * self.world / dt if dt > 0 else 0.0}
+        if device_timing:
+            ms = C.c_float()
+            native.check(self.lib.dmlp_event_elapsed_ms(e0, e1, C.byref(ms)))
+            out["device_ms"] = ms.value
+            self.lib.dmlp_event_destroy(e0)
+            self.lib.dmlp_event_destroy(e1)
         if metrics is not None and steps:
             m = metrics.reshape(steps, 2)
             out["loss"] = float(m[:, 0].mean() / self.cfg.batch)

@@ -243,7 +243,7 @@ int dmlp_trainer_set_lr(dmlp_trainer_t t, float lr);
 int dmlp_trainer_kernels_per_step(dmlp_trainer_t t, int* n);
 int dmlp_trainer_run(dmlp_trainer_t t, const float* x_host, const int32_t* y_host, size_t num_batches,
                      size_t first_batch, size_t batch_stride, int steps, const float* lr_schedule,
-                     float* metrics_out, int use_graph);
+                     float* metrics_out, int use_graph, void* start_event, void* stop_event);
 int dmlp_trainer_load_inputs(dmlp_trainer_t t, int parity, const float* x_host, const int32_t* y_host);
 int dmlp_trainer_run_resident(dmlp_trainer_t t, int steps, int use_graph, void* start_event, void* stop_event);
 int dmlp_trainer_eval(dmlp_trainer_t t, const float* x_host, const int32_t* y_host, size_t n_batches,

@@ -7,10 +7,10 @@ import pytest
 pytestmark = pytest.mark.gpu
 
 
-def _setup(dims=(784, 128, 64, 10), batch=64, precision="tf32", **kw):
+def _setup(dims=(784, 128, 64, 10), batch=64, precision="tf32", lr=0.05, **kw):
     from dmlp_b200.parallel.trainer import Trainer, TrainerConfig
     from dmlp_b200.utils.data import synthetic_mnist
-    cfg = TrainerConfig(dims=dims, batch=batch, lr=0.05, precision=precision, **kw)
+    cfg = TrainerConfig(dims=dims, batch=batch, lr=lr, precision=precision, **kw)
     t = Trainer(cfg, device=0)
     x, y = synthetic_mnist(batch * 40, seed=1, features=dims[0], num_classes=dims[-1])
     return t, x, y
@@ -41,7 +41,7 @@ def test_steps_match_oracle(dims, use_graph):
 
 
 def test_loss_decreases_and_eval_runs():
-    t, x, y = _setup()
+    t, x, y = _setup(lr=0.2)
     first = t.fit(x, y, 5)["loss"]
     hist = t.train_epochs(x, y, epochs=3)
     assert hist[-1]["loss"] < 0.5 * first
