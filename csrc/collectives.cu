@@ -891,3 +891,109 @@ extern "C" int dmlp_reduce_n(int dev, void* dst, const void* const* srcs, int n,
   DMLP_CUDA_CHECK(cudaGetLastError());
   return DMLP_OK;
 }
+
+// ------------------------------------------------------------------ allocation-free all-reduce
+// Some users of this library must not allocate device memory when they call it. Two we know of:
+// a serving process that gave all of the GPU's memory to its own tensor pool at start-up (a later
+// cudaMalloc can simply fail there), and a latency-critical loop that cannot afford cudaMalloc /
+// cudaFree because both synchronise the whole device and stall every stream. For them
+// dmlp_allreduce_sum_f32_noalloc runs the ring all-reduce kernel with its signal pads, sequence
+// state, watchdog words and staging slots carved out of the fixed array below instead of a
+// communicator's cudaMalloc'd segment. The array costs every GPU that loads this library
+// kNoAllocBytes (about 4.1 MiB) until the process exits, and its size bounds the message.
+namespace dmlp {
+
+constexpr size_t kNoAllocFlagBytes = 256;                // [0] abort word, [4..8) watchdog status
+constexpr size_t kNoAllocPadBytes = 8 * 1024;            // one signal pad (uses kPadWords * 4)
+constexpr size_t kNoAllocStateBytes = 1024;              // one rank's epochs + ring sequence numbers
+constexpr size_t kNoAllocSlotBytes = 256 * 1024;         // one ring staging slot; two per rank
+constexpr size_t kNoAllocCtrlBytes = kNoAllocFlagBytes + kMaxRanks * (kNoAllocPadBytes + kNoAllocStateBytes);
+constexpr size_t kNoAllocBytes = kNoAllocCtrlBytes + kMaxRanks * 2 * kNoAllocSlotBytes;
+constexpr size_t kNoAllocMaxFloatsPerRank = kNoAllocSlotBytes / sizeof(float);  // x world = largest count
+static_assert(kPadWords * 4 <= kNoAllocPadBytes, "signal pad does not fit its static slice");
+static_assert(kStateWords * 4 <= kNoAllocStateBytes, "rank state does not fit its static slice");
+static_assert(kNoAllocCtrlBytes % 256 == 0, "staging slices must stay 256-byte aligned");
+
+// Only device code may use this name as an address. On the host it is a stand-in symbol: the
+// launcher below asks the runtime for the real device address, once per device.
+static __device__ __align__(256) unsigned char g_noalloc_scratch[kNoAllocBytes];
+
+constexpr int kNoAllocMaxDevices = 64;
+static std::mutex g_noalloc_mu;
+static unsigned char* g_noalloc_dev_ptr[kNoAllocMaxDevices];
+
+// Device address of the scratch array on the CURRENT device (resolved on first use per device).
+static int noalloc_scratch_ptr(unsigned char** out) {
+  int dev = -1;
+  DMLP_CUDA_CHECK(cudaGetDevice(&dev));
+  if (dev < 0 || dev >= kNoAllocMaxDevices)
+    return set_error(DMLP_ERR_UNSUPPORTED, "device ordinal %d is outside the %d supported by the static scratch table",
+                     dev, kNoAllocMaxDevices);
+  std::lock_guard<std::mutex> lock(g_noalloc_mu);
+  if (g_noalloc_dev_ptr[dev] == nullptr) {
+    void* p = nullptr;
+    cudaError_t e = cudaGetSymbolAddress(&p, g_noalloc_scratch);
+    if (e != cudaSuccess || p == nullptr)
+      return set_error(DMLP_ERR_CUDA, "cudaGetSymbolAddress(static all-reduce scratch) failed on device %d: %s", dev,
+                       cudaGetErrorString(e));
+    g_noalloc_dev_ptr[dev] = static_cast<unsigned char*>(p);
+  }
+  *out = g_noalloc_dev_ptr[dev];
+  return DMLP_OK;
+}
+
+}  // namespace dmlp
+
+extern "C" int dmlp_allreduce_sum_f32_noalloc(int world, const float* const* in_dev, float* const* out_dev,
+                                              size_t count, void* stream) {
+  DMLP_REQUIRE(world >= 1 && world <= kMaxRanks, "dmlp_allreduce_sum_f32_noalloc: world %d not in [1,%d]", world, kMaxRanks);
+  DMLP_REQUIRE(in_dev != nullptr && out_dev != nullptr, "dmlp_allreduce_sum_f32_noalloc: null pointer table");
+  const size_t max_count = static_cast<size_t>(world) * kNoAllocMaxFloatsPerRank;
+  if (count > max_count)
+    return set_error(DMLP_ERR_INVALID,
+                     "dmlp_allreduce_sum_f32_noalloc: count %zu exceeds the static scratch capacity of %zu floats "
+                     "(%zu per rank x %d ranks); use dmlp_allreduce with a communicator for larger messages",
+                     count, max_count, kNoAllocMaxFloatsPerRank, world);
+  for (int r = 0; r < world; ++r) {
+    DMLP_REQUIRE(in_dev[r] != nullptr && out_dev[r] != nullptr, "dmlp_allreduce_sum_f32_noalloc: rank %d has a null buffer", r);
+    DMLP_REQUIRE(((reinterpret_cast<uintptr_t>(in_dev[r]) | reinterpret_cast<uintptr_t>(out_dev[r])) & 15) == 0,
+                 "dmlp_allreduce_sum_f32_noalloc: rank %d buffers must be 16-byte aligned", r);
+  }
+  if (count == 0) return DMLP_OK;
+  unsigned char* base = nullptr;
+  int rc = noalloc_scratch_ptr(&base);
+  if (rc) return rc;
+  cudaStream_t st = as_stream(stream);
+  // The array keeps whatever the previous call left behind. Flags, epochs, sequence numbers and
+  // the watchdog words must start from zero; staging slots are always written before they are read.
+  DMLP_CUDA_CHECK(cudaMemsetAsync(base, 0, kNoAllocCtrlBytes, st));
+
+  CollArgs a;
+  memset(&a, 0, sizeof(a));
+  a.world = world;
+  a.rank = world > 1 ? -1 : 0;  // every rank lives on this device: one launch, rank = blockIdx.y
+  a.op = DMLP_SUM;
+  a.scale = 1.f;
+  a.count = count;
+  a.staging_bytes = 2 * kNoAllocSlotBytes;
+  a.abort_flag = reinterpret_cast<uint32_t*>(base);
+  a.status = reinterpret_cast<uint32_t*>(base) + 4;
+  a.timeout_ns = 10ull * 1000 * 1000 * 1000;
+  unsigned char* pads = base + kNoAllocFlagBytes;
+  unsigned char* states = pads + kMaxRanks * kNoAllocPadBytes;
+  unsigned char* staging = base + kNoAllocCtrlBytes;
+  for (int r = 0; r < world; ++r) {
+    a.in[r] = in_dev[r];
+    a.out[r] = out_dev[r];
+    a.pad[r] = reinterpret_cast<uint32_t*>(pads + r * kNoAllocPadBytes);
+    a.state[r] = reinterpret_cast<uint32_t*>(states + r * kNoAllocStateBytes);
+    a.staging[r] = staging + static_cast<size_t>(r) * 2 * kNoAllocSlotBytes;
+  }
+  const size_t npack = (count * sizeof(float) + 15) / 16;
+  const size_t work = (npack + world - 1) / world;
+  int blocks = static_cast<int>((work + kCollThreads * 2 - 1) / (kCollThreads * 2));
+  if (blocks < 1) blocks = 1;
+  if (blocks > 16) blocks = 16;
+  if (world == 1) return launch_coll(allreduce_oneshot_kernel<float, false>, a, blocks, 1, st);
+  return launch_coll(allreduce_ring_kernel<float, false>, a, blocks, world, st);
+}

@@ -208,6 +208,30 @@ int dmlp_p2p_copy(int src_dev, void* dst_dev, const void* src_dev_ptr, size_t by
 int dmlp_reduce_n(int dev, void* dst_dev, const void* const* srcs_dev, int n, size_t count, int dtype,
                   int op, void* stream);
 
+/* ------------------------------------------------------------------ all-reduce without allocation
+ * (No counterpart in the reference: its coordinator allocates freely on the host.)
+ *
+ * out[r][i] = sum over ranks of in[r'][i] for `world` logical ranks whose buffers all live on the
+ * CURRENT device, using the ring kernel — but with every byte of working memory (signal pads,
+ * sequence state, watchdog words, staging slots) taken from a fixed array compiled into the
+ * library, so the call performs no cudaMalloc / cudaFree / cudaHostAlloc and creates no
+ * communicator. It exists for callers that must not allocate at call time: a process that has
+ * already handed the whole GPU to its own memory pool (a late cudaMalloc may fail), or a loop
+ * that cannot tolerate the device-wide synchronisation cudaMalloc and cudaFree imply.
+ *
+ *  - in_dev / out_dev are HOST arrays of `world` device pointers, 16-byte aligned; out may alias in.
+ *  - Limit: count <= world * 65536 floats (one 256 KiB staging slot per rank per step); larger
+ *    counts are rejected with DMLP_ERR_INVALID — use dmlp_allreduce for those. world <= 8.
+ *  - Cost: about 4.1 MiB of device memory on every GPU that loads the library, held until exit.
+ *  - The first call on each device looks up the array's device address; make that first call
+ *    outside of any stream capture. Later calls only enqueue a memset and one kernel on `stream`.
+ *  - All calls on a device share the one array (the control words are cleared at the start of
+ *    each call). Two calls whose GPU execution overlaps corrupt each other: keep them on one
+ *    stream or order them with events.
+ */
+int dmlp_allreduce_sum_f32_noalloc(int world, const float* const* in_dev, float* const* out_dev,
+                                   size_t count, void* stream);
+
 /* ------------------------------------------------------------------ native data-parallel MLP trainer
  * Reference: the client's model, step and epoch loop (DSML/client/client.go:22-58 model/init,
  * :112-202 forward/backward, :254-267 SGD, :462-502 eval, :516-659 training loop).
