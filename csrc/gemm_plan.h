@@ -30,6 +30,13 @@ struct GemmParams {
   float* colsum;
   int relu;
   int accumulate;
+  // fused softmax cross-entropy epilogue (last layer): non-null labels switch it on
+  const int* ce_labels;
+  int ce_classes;
+  float ce_scale;
+  float* ce_logits;
+  float* ce_loss_sum;
+  int* ce_correct;
 };
 
 struct GemmPlan {

@@ -45,6 +45,9 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA,
   __shared__ __align__(8) uint64_t empty_bar[kMaxStages];
   __shared__ __align__(8) uint64_t tmem_full_bar;
   __shared__ uint32_t tmem_base_slot;
+  __shared__ float s_part[4][256];  // per-epilogue-warp column partials
+  __shared__ float s_loss[4];
+  __shared__ int s_hit[4];
 
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
@@ -127,98 +130,210 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA,
     const int row = q * 32 + lane;
     const int m = m0 + row;
     const bool m_ok = m < p.M;
+    const int etid = (warp - 2) * 32 + lane;   // 0..127 among the epilogue threads
+    // A single M tile sees every row of the problem: its reductions (bias gradient, loss, hits) are
+    // final and can be stored; otherwise they are accumulated atomically into zeroed buffers.
+    const bool direct = gridDim.y == 1;
     mbar_wait(&tmem_full_bar, 0);
     tc_fence_after_sync();
     const uint32_t t_row = tmem_base + (static_cast<uint32_t>(q * 32) << 16);
-    for (int c = 0; c < p.block_n; c += 16) {
-      uint32_t r[16];
-      tmem_ld_x16(t_row + c, r);
-      tmem_ld_wait();
-      const int nb = n0 + c;
-      if (nb >= p.N) break;  // uniform across the CTA
-      float v[16];
+
+    if (p.ce_labels != nullptr) {
+      // ---- fused softmax cross-entropy (reference client.go:76-93,144-165,352-382): the whole logits
+      // row (block_n == N <= 32) sits in this thread's registers; logits never travel through memory.
+      float v[32];
 #pragma unroll
-      for (int j = 0; j < 16; ++j) v[j] = __uint_as_float(r[j]);
-      const bool full = (nb + 16 <= p.N);
-      if (p.bias != nullptr) {
+      for (int c = 0; c < 32; c += 16) {
+        if (c < p.block_n) {
+          uint32_t r[16];
+          tmem_ld_x16(t_row + c, r);
+          tmem_ld_wait();
 #pragma unroll
-        for (int j = 0; j < 16; ++j)
-          if (full || nb + j < p.N) v[j] += __ldg(p.bias + nb + j);
-      }
-      if (p.relu) {
-#pragma unroll
-        for (int j = 0; j < 16; ++j) v[j] = fmaxf(v[j], 0.f);
-      }
-      if (p.mask != nullptr && m_ok) {
-        if (p.mask_is_bf16) {
-          const __nv_bfloat16* mk =
-              reinterpret_cast<const __nv_bfloat16*>(p.mask) + static_cast<long long>(m) * p.ld_mask + nb;
-#pragma unroll
-          for (int j = 0; j < 16; ++j)
-            if (full || nb + j < p.N)
-              if (!(__bfloat162float(mk[j]) > 0.f)) v[j] = 0.f;
+          for (int j = 0; j < 16; ++j) {
+            float x = __uint_as_float(r[j]);
+            if (p.bias != nullptr && c + j < p.N) x += __ldg(p.bias + c + j);
+            v[c + j] = x;
+          }
         } else {
-          const float* mk = reinterpret_cast<const float*>(p.mask) + static_cast<long long>(m) * p.ld_mask + nb;
 #pragma unroll
-          for (int j = 0; j < 16; ++j)
-            if (full || nb + j < p.N)
-              if (!(mk[j] > 0.f)) v[j] = 0.f;
+          for (int j = 0; j < 16; ++j) v[c + j] = 0.f;
         }
       }
+      const int C = p.ce_classes;
+      if (p.ce_logits != nullptr && m_ok) {
+        float* lo = p.ce_logits + static_cast<long long>(m) * p.ld_out;
+#pragma unroll
+        for (int j = 0; j < 32; ++j)
+          if (j < p.N) lo[j] = v[j];
+      }
+      float mx = -INFINITY;
+      int arg = 0;
+#pragma unroll
+      for (int j = 0; j < 32; ++j)
+        if (j < C && v[j] > mx) { mx = v[j]; arg = j; }
+      float sum = 0.f;
+#pragma unroll
+      for (int j = 0; j < 32; ++j) {
+        v[j] = (j < C) ? __expf(v[j] - mx) : 0.f;
+        sum += v[j];
+      }
+      const float inv = 1.f / sum;
+      const int y = m_ok ? p.ce_labels[m] : -1;
+      float loss = 0.f;
+      int hit = 0;
+#pragma unroll
+      for (int j = 0; j < 32; ++j) {
+        const float pr = v[j] * inv;
+        if (j == y) loss = -__logf(pr + 1e-10f);
+        v[j] = (m_ok && j < C) ? (pr - (j == y ? 1.f : 0.f)) * p.ce_scale : 0.f;
+      }
+      if (m_ok && arg == y) hit = 1;
       if (m_ok) {
         if (p.out_f32 != nullptr) {
-          float* o = p.out_f32 + static_cast<long long>(m) * p.ld_out + nb;
-          const bool vec = full && ((reinterpret_cast<uintptr_t>(o) & 15) == 0);
-          if (p.accumulate) {
+          float* o = p.out_f32 + static_cast<long long>(m) * p.ld_out;
 #pragma unroll
-            for (int j = 0; j < 16; ++j)
-              if (full || nb + j < p.N) v[j] += o[j];
-          }
-          if (vec) {
-#pragma unroll
-            for (int j = 0; j < 16; j += 4)
-              *reinterpret_cast<float4*>(o + j) = make_float4(v[j], v[j + 1], v[j + 2], v[j + 3]);
-          } else {
-#pragma unroll
-            for (int j = 0; j < 16; ++j)
-              if (full || nb + j < p.N) o[j] = v[j];
-          }
+          for (int j = 0; j < 32; ++j)
+            if (j < p.N) o[j] = v[j];
         }
         if (p.out_bf16 != nullptr) {
-          __nv_bfloat16* o = p.out_bf16 + static_cast<long long>(m) * p.ld_out_bf16 + nb;
-          const bool vec = full && ((reinterpret_cast<uintptr_t>(o) & 15) == 0);
-          if (vec) {
+          __nv_bfloat16* o = p.out_bf16 + static_cast<long long>(m) * p.ld_out_bf16;
 #pragma unroll
-            for (int j = 0; j < 16; j += 8) {
-              __nv_bfloat162 h0 = __floats2bfloat162_rn(v[j], v[j + 1]);
-              __nv_bfloat162 h1 = __floats2bfloat162_rn(v[j + 2], v[j + 3]);
-              __nv_bfloat162 h2 = __floats2bfloat162_rn(v[j + 4], v[j + 5]);
-              __nv_bfloat162 h3 = __floats2bfloat162_rn(v[j + 6], v[j + 7]);
-              uint4 pk;
-              pk.x = *reinterpret_cast<uint32_t*>(&h0);
-              pk.y = *reinterpret_cast<uint32_t*>(&h1);
-              pk.z = *reinterpret_cast<uint32_t*>(&h2);
-              pk.w = *reinterpret_cast<uint32_t*>(&h3);
-              *reinterpret_cast<uint4*>(o + j) = pk;
-            }
-          } else {
+          for (int j = 0; j < 32; ++j)
+            if (j < p.N) o[j] = __float2bfloat16_rn(v[j]);
+        }
+      }
+      // reductions over the rows of this tile
+#pragma unroll
+      for (int j = 0; j < 32; ++j) {
+        float sj = v[j];
+        sj += __shfl_xor_sync(0xffffffffu, sj, 16);
+        sj += __shfl_xor_sync(0xffffffffu, sj, 8);
+        sj += __shfl_xor_sync(0xffffffffu, sj, 4);
+        sj += __shfl_xor_sync(0xffffffffu, sj, 2);
+        sj += __shfl_xor_sync(0xffffffffu, sj, 1);
+        if (lane == j) s_part[q][j] = sj;
+      }
+#pragma unroll
+      for (int o = 16; o > 0; o >>= 1) {
+        loss += __shfl_xor_sync(0xffffffffu, loss, o);
+        hit += __shfl_xor_sync(0xffffffffu, hit, o);
+      }
+      if (lane == 0) { s_loss[q] = loss; s_hit[q] = hit; }
+      asm volatile("bar.sync 1, 128;" ::: "memory");
+      if (etid < p.N && p.colsum != nullptr) {
+        const float t = s_part[0][etid] + s_part[1][etid] + s_part[2][etid] + s_part[3][etid];
+        if (direct) p.colsum[etid] = t; else atomicAdd(p.colsum + etid, t);
+      }
+      if (etid == 0) {
+        const float l = s_loss[0] + s_loss[1] + s_loss[2] + s_loss[3];
+        const int h = s_hit[0] + s_hit[1] + s_hit[2] + s_hit[3];
+        if (p.ce_loss_sum != nullptr) { if (direct) *p.ce_loss_sum = l; else atomicAdd(p.ce_loss_sum, l); }
+        if (p.ce_correct != nullptr) { if (direct) *p.ce_correct = h; else if (h) atomicAdd(p.ce_correct, h); }
+      }
+    } else {
+      int chunks_done = 0;
+      for (int c = 0; c < p.block_n; c += 16) {
+        uint32_t r[16];
+        tmem_ld_x16(t_row + c, r);
+        tmem_ld_wait();
+        const int nb = n0 + c;
+        if (nb >= p.N) break;  // uniform across the CTA
+        ++chunks_done;
+        float v[16];
+#pragma unroll
+        for (int j = 0; j < 16; ++j) v[j] = __uint_as_float(r[j]);
+        const bool full = (nb + 16 <= p.N);
+        if (p.bias != nullptr) {
+#pragma unroll
+          for (int j = 0; j < 16; ++j)
+            if (full || nb + j < p.N) v[j] += __ldg(p.bias + nb + j);
+        }
+        if (p.relu) {
+#pragma unroll
+          for (int j = 0; j < 16; ++j) v[j] = fmaxf(v[j], 0.f);
+        }
+        if (p.mask != nullptr && m_ok) {
+          if (p.mask_is_bf16) {
+            const __nv_bfloat16* mk =
+                reinterpret_cast<const __nv_bfloat16*>(p.mask) + static_cast<long long>(m) * p.ld_mask + nb;
 #pragma unroll
             for (int j = 0; j < 16; ++j)
-              if (full || nb + j < p.N) o[j] = __float2bfloat16_rn(v[j]);
+              if (full || nb + j < p.N)
+                if (!(__bfloat162float(mk[j]) > 0.f)) v[j] = 0.f;
+          } else {
+            const float* mk = reinterpret_cast<const float*>(p.mask) + static_cast<long long>(m) * p.ld_mask + nb;
+#pragma unroll
+            for (int j = 0; j < 16; ++j)
+              if (full || nb + j < p.N)
+                if (!(mk[j] > 0.f)) v[j] = 0.f;
+          }
+        }
+        if (m_ok) {
+          if (p.out_f32 != nullptr) {
+            float* o = p.out_f32 + static_cast<long long>(m) * p.ld_out + nb;
+            const bool vec = full && ((reinterpret_cast<uintptr_t>(o) & 15) == 0);
+            if (p.accumulate) {
+#pragma unroll
+              for (int j = 0; j < 16; ++j)
+                if (full || nb + j < p.N) v[j] += o[j];
+            }
+            if (vec) {
+#pragma unroll
+              for (int j = 0; j < 16; j += 4)
+                *reinterpret_cast<float4*>(o + j) = make_float4(v[j], v[j + 1], v[j + 2], v[j + 3]);
+            } else {
+#pragma unroll
+              for (int j = 0; j < 16; ++j)
+                if (full || nb + j < p.N) o[j] = v[j];
+            }
+          }
+          if (p.out_bf16 != nullptr) {
+            __nv_bfloat16* o = p.out_bf16 + static_cast<long long>(m) * p.ld_out_bf16 + nb;
+            const bool vec = full && ((reinterpret_cast<uintptr_t>(o) & 15) == 0);
+            if (vec) {
+#pragma unroll
+              for (int j = 0; j < 16; j += 8) {
+                __nv_bfloat162 h0 = __floats2bfloat162_rn(v[j], v[j + 1]);
+                __nv_bfloat162 h1 = __floats2bfloat162_rn(v[j + 2], v[j + 3]);
+                __nv_bfloat162 h2 = __floats2bfloat162_rn(v[j + 4], v[j + 5]);
+                __nv_bfloat162 h3 = __floats2bfloat162_rn(v[j + 6], v[j + 7]);
+                uint4 pk;
+                pk.x = *reinterpret_cast<uint32_t*>(&h0);
+                pk.y = *reinterpret_cast<uint32_t*>(&h1);
+                pk.z = *reinterpret_cast<uint32_t*>(&h2);
+                pk.w = *reinterpret_cast<uint32_t*>(&h3);
+                *reinterpret_cast<uint4*>(o + j) = pk;
+              }
+            } else {
+#pragma unroll
+              for (int j = 0; j < 16; ++j)
+                if (full || nb + j < p.N) o[j] = __float2bfloat16_rn(v[j]);
+            }
+          }
+        }
+        if (p.colsum != nullptr) {
+          // Bias gradient: column sums over this warp's 32 rows (rows past M contribute zero).
+#pragma unroll
+          for (int j = 0; j < 16; ++j) {
+            float sj = m_ok ? v[j] : 0.f;
+            sj += __shfl_xor_sync(0xffffffffu, sj, 16);
+            sj += __shfl_xor_sync(0xffffffffu, sj, 8);
+            sj += __shfl_xor_sync(0xffffffffu, sj, 4);
+            sj += __shfl_xor_sync(0xffffffffu, sj, 2);
+            sj += __shfl_xor_sync(0xffffffffu, sj, 1);
+            if (lane == j) s_part[q][c + j] = sj;
           }
         }
       }
       if (p.colsum != nullptr) {
-        // Bias gradient: column sums over the rows of this tile (rows past M contribute zero).
-#pragma unroll
-        for (int j = 0; j < 16; ++j) {
-          float s = m_ok ? v[j] : 0.f;
-          s += __shfl_xor_sync(0xffffffffu, s, 16);
-          s += __shfl_xor_sync(0xffffffffu, s, 8);
-          s += __shfl_xor_sync(0xffffffffu, s, 4);
-          s += __shfl_xor_sync(0xffffffffu, s, 2);
-          s += __shfl_xor_sync(0xffffffffu, s, 1);
-          if (lane == j && nb + j < p.N) atomicAdd(p.colsum + nb + j, s);
+        // combine the four warps' partials: one store (or one atomic) per column per CTA
+        asm volatile("bar.sync 1, 128;" ::: "memory");
+        for (int cidx = etid; cidx < chunks_done * 16; cidx += 128) {
+          const int n = n0 + cidx;
+          if (n < p.N) {
+            const float t = s_part[0][cidx] + s_part[1][cidx] + s_part[2][cidx] + s_part[3][cidx];
+            if (direct) p.colsum[n] = t; else atomicAdd(p.colsum + n, t);
+          }
         }
       }
     }
@@ -316,7 +431,7 @@ int dmlp::gemm_plan_create(const dmlp_gemm_desc_t* d, GemmPlan* plan) {
   DMLP_REQUIRE(d->dtype == DMLP_F32 || d->dtype == DMLP_BF16, "dmlp_gemm: dtype must be F32 (tf32) or BF16");
   DMLP_REQUIRE(d->M > 0 && d->N > 0 && d->K > 0, "dmlp_gemm: empty problem %dx%dx%d", d->M, d->N, d->K);
   DMLP_REQUIRE(d->A_dev && d->B_dev, "dmlp_gemm: null operand");
-  DMLP_REQUIRE(d->out_f32_dev || d->out_bf16_dev || d->colsum_dev, "dmlp_gemm: no output requested");
+  DMLP_REQUIRE(d->out_f32_dev || d->out_bf16_dev || d->colsum_dev || d->ce_labels_dev, "dmlp_gemm: no output requested");
   const bool bf16 = d->dtype == DMLP_BF16;
   const int EB = bf16 ? 2 : 4;
   const int KS = 128 / EB;
@@ -361,6 +476,14 @@ int dmlp::gemm_plan_create(const dmlp_gemm_desc_t* d, GemmPlan* plan) {
   p.mask = d->mask_dev; p.ld_mask = d->ld_mask; p.mask_is_bf16 = d->mask_dtype == DMLP_BF16;
   p.colsum = d->colsum_dev;
   p.relu = d->relu; p.accumulate = d->accumulate;
+  p.ce_labels = d->ce_labels_dev; p.ce_classes = d->ce_classes; p.ce_scale = d->ce_scale;
+  p.ce_logits = d->ce_logits_dev; p.ce_loss_sum = d->ce_loss_sum_dev; p.ce_correct = d->ce_correct_dev;
+  if (d->ce_labels_dev != nullptr) {
+    DMLP_REQUIRE(d->N <= 32 && d->ce_classes >= 1 && d->ce_classes <= d->N, "fused softmax-CE needs classes <= N <= 32 (got N=%d classes=%d)", d->N, d->ce_classes);
+    DMLP_REQUIRE(!d->relu && !d->mask_dev && !d->accumulate, "fused softmax-CE excludes relu/mask/accumulate");
+    bn = ((d->N + 15) / 16) * 16;  // one N tile holds the whole row
+    p.block_n = bn;
+  }
 
   plan->grid_x = ceil_div(d->N, bn);
   plan->grid_y = ceil_div(d->M, 128);

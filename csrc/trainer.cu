@@ -80,7 +80,11 @@ struct Trainer {
   bool launched[2] = {false, false};
   cudaGraph_t graph[2] = {nullptr, nullptr};
   cudaGraphExec_t gexec[2] = {nullptr, nullptr};
-  GemmPlan fwd[2][kMaxLayers], wgrad[2][kMaxLayers], dgrad[kMaxLayers], fwd_eval[kMaxLayers];
+  GemmPlan fwd[2][kMaxLayers], wgrad[2][kMaxLayers], dgrad[kMaxLayers], fwd_eval_last;
+  bool fused_ce = false;   // softmax-CE runs in the last forward GEMM's epilogue
+  bool direct = false;     // batch fits one M tile: reductions are stored, no zeroing needed
+  cudaStream_t s_aux = nullptr;  // wgrad branch (runs beside the dgrad chain)
+  cudaEvent_t ev_dz[kMaxLayers], ev_aux_done;
   int kernels_per_step = 0;
   unsigned long long steps_done = 0;
   std::vector<void*> owned;
@@ -119,6 +123,24 @@ static int build_plans(Trainer* t) {
       d.relu = last ? 0 : 1;
       if (last || !t->bf16) { d.out_f32_dev = t->act[l]; d.ld_out = L.out_pad[l]; }
       if (!last && t->bf16) { d.out_bf16_dev = t->act16[l]; d.ld_out_bf16 = L.out_pad[l]; }
+      if (last && t->fused_ce) {
+        // logits stay in TMEM/registers: the epilogue writes dlogits, db, loss and hit count
+        d.out_f32_dev = t->bf16 ? nullptr : t->dz[l];
+        d.ld_out = L.out_pad[l];
+        d.out_bf16_dev = t->bf16 ? static_cast<void*>(t->dz16[l]) : nullptr;
+        d.ld_out_bf16 = L.out_pad[l];
+        d.ce_labels_dev = t->labels[par];
+        d.ce_classes = L.out[l];
+        d.ce_scale = 1.f / static_cast<float>(B);
+        d.colsum_dev = t->grads[par] + L.b_off[l];
+        d.ce_loss_sum_dev = t->metrics_dev[par];
+        d.ce_correct_dev = reinterpret_cast<int32_t*>(t->metrics_dev[par] + 1);
+        if (par == 0) {  // evaluation: same kernel, no gradient outputs
+          dmlp_gemm_desc_t e = d;
+          e.out_f32_dev = nullptr; e.out_bf16_dev = nullptr; e.colsum_dev = nullptr;
+          TRY(gemm_plan_create(&e, &t->fwd_eval_last));
+        }
+      }
       TRY(gemm_plan_create(&d, &t->fwd[par][l]));
       // ---- wgrad: dW_l = in_l^T . dZ_l  -> grads[par]
       memset(&d, 0, sizeof(d));
@@ -176,37 +198,54 @@ static int enqueue_allreduce(Trainer* t, int par, size_t off, size_t count, cuda
 }
 
 // Enqueues one full training step for input parity `par` on the trainer's streams.
+// Stream layout (captured as parallel graph branches):
+//   s_main : fwd_1 .. fwd_L(+softmax-CE) -> dgrad_L -> ... -> dgrad_2 ........ -> all-reduce+SGD
+//   s_aux  :                      wgrad_L (after dZ_L) ... wgrad_1 (after dZ_1) --^
+//   s_comm : (overlap mode) bucket_l all-reduce+SGD once dgrad_l and wgrad_l are done
 static int enqueue_step(Trainer* t, int par, bool count_kernels) {
   const ParamLayout& L = t->lay;
   const int B = t->cfg.batch;
-  cudaStream_t S = t->s_main;
+  cudaStream_t S = t->s_main, A = t->s_aux;
   int nk = 0;
-  DMLP_CUDA_CHECK(cudaMemsetAsync(t->metrics_dev[par], 0, 8, S));
-  for (int l = 0; l < L.L; ++l)
-    DMLP_CUDA_CHECK(cudaMemsetAsync(t->grads[par] + L.b_off[l], 0, sizeof(float) * L.out_pad[l], S));
+  const int last = L.L - 1;
+  if (!(t->fused_ce && t->direct)) DMLP_CUDA_CHECK(cudaMemsetAsync(t->metrics_dev[par], 0, 8, S));
+  if (!t->direct)
+    for (int l = 0; l < L.L; ++l)
+      DMLP_CUDA_CHECK(cudaMemsetAsync(t->grads[par] + L.b_off[l], 0, sizeof(float) * L.out_pad[l], S));
   if (t->bf16) { TRY(dmlp_cast_f32_to_bf16(t->x[par], t->x16, static_cast<size_t>(B) * L.in[0], S)); ++nk; }
   for (int l = 0; l < L.L; ++l) { TRY(gemm_plan_run(&t->fwd[par][l], S)); ++nk; }
-  const int last = L.L - 1;
-  TRY(dmlp_softmax_ce(t->act[last], L.out_pad[last], t->labels[par], B, L.out[last], 1.f / B,
-                      t->bf16 ? nullptr : t->dz[last], t->bf16 ? static_cast<void*>(t->dz16[last]) : nullptr,
-                      t->metrics_dev[par], reinterpret_cast<int32_t*>(t->metrics_dev[par] + 1),
-                      t->grads[par] + L.b_off[last], S));
-  ++nk;
+  if (!t->fused_ce) {
+    if (t->direct) DMLP_CUDA_CHECK(cudaMemsetAsync(t->grads[par] + L.b_off[last], 0, sizeof(float) * L.out_pad[last], S));
+    TRY(dmlp_softmax_ce(t->act[last], L.out_pad[last], t->labels[par], B, L.out[last], 1.f / B,
+                        t->bf16 ? nullptr : t->dz[last], t->bf16 ? static_cast<void*>(t->dz16[last]) : nullptr,
+                        t->metrics_dev[par], reinterpret_cast<int32_t*>(t->metrics_dev[par] + 1),
+                        t->grads[par] + L.b_off[last], S));
+    ++nk;
+  }
   const bool overlap = t->cfg.overlap != 0 && t->comm != nullptr;
   for (int l = last; l >= 0; --l) {
-    if (l > 0) {  // dgrad first: it reads W_l, which the bucket's fused SGD is about to overwrite
+    // dZ_l is ready on S: the wgrad branch may start
+    DMLP_CUDA_CHECK(cudaEventRecord(t->ev_dz[l], S));
+    DMLP_CUDA_CHECK(cudaStreamWaitEvent(A, t->ev_dz[l], 0));
+    TRY(gemm_plan_run(&t->wgrad[par][l], A));
+    ++nk;
+    if (l > 0) {
       GemmPlan pl = t->dgrad[l];
       pl.p.colsum = t->grads[par] + L.b_off[l - 1];
       TRY(gemm_plan_run(&pl, S));
       ++nk;
     }
-    TRY(gemm_plan_run(&t->wgrad[par][l], S));
-    ++nk;
     if (overlap) {
+      // bucket l = [W_l | b_l]: needs wgrad_l (A) and dgrad_l (S, it reads W_l which the fused SGD rewrites);
+      // b_l came from the producer of dZ_l, which precedes both.
       const size_t lo = L.w_off[l];
       const size_t hi = (l + 1 < L.L) ? L.w_off[l + 1] : L.total;
-      DMLP_CUDA_CHECK(cudaEventRecord(t->ev_bucket[l], S));
+      DMLP_CUDA_CHECK(cudaEventRecord(t->ev_bucket[l], A));
       DMLP_CUDA_CHECK(cudaStreamWaitEvent(t->s_comm, t->ev_bucket[l], 0));
+      if (l > 0) {
+        DMLP_CUDA_CHECK(cudaEventRecord(t->ev_fork, S));
+        DMLP_CUDA_CHECK(cudaStreamWaitEvent(t->s_comm, t->ev_fork, 0));
+      }
       TRY(enqueue_allreduce(t, par, lo, hi - lo, t->s_comm));
       ++nk;
     }
@@ -214,7 +253,11 @@ static int enqueue_step(Trainer* t, int par, bool count_kernels) {
   if (overlap) {
     DMLP_CUDA_CHECK(cudaEventRecord(t->ev_join, t->s_comm));
     DMLP_CUDA_CHECK(cudaStreamWaitEvent(S, t->ev_join, 0));
+    DMLP_CUDA_CHECK(cudaEventRecord(t->ev_aux_done, A));
+    DMLP_CUDA_CHECK(cudaStreamWaitEvent(S, t->ev_aux_done, 0));
   } else {
+    DMLP_CUDA_CHECK(cudaEventRecord(t->ev_aux_done, A));
+    DMLP_CUDA_CHECK(cudaStreamWaitEvent(S, t->ev_aux_done, 0));
     TRY(enqueue_allreduce(t, par, 0, L.total, S));
     ++nk;
   }
@@ -282,11 +325,16 @@ extern "C" int dmlp_trainer_destroy(dmlp_trainer_t h) {
     if (t->ev_done[p]) cudaEventDestroy(t->ev_done[p]);
   }
   if (t->ev_join) cudaEventDestroy(t->ev_join);
+  if (t->ev_fork) cudaEventDestroy(t->ev_fork);
+  if (t->ev_aux_done) cudaEventDestroy(t->ev_aux_done);
+  for (int l = 0; l < kMaxLayers; ++l)
+    if (t->ev_dz[l]) cudaEventDestroy(t->ev_dz[l]);
   for (int l = 0; l < kMaxLayers; ++l)
     if (t->ev_bucket[l]) cudaEventDestroy(t->ev_bucket[l]);
   if (t->s_main) cudaStreamDestroy(t->s_main);
   if (t->s_comm) cudaStreamDestroy(t->s_comm);
   if (t->s_copy) cudaStreamDestroy(t->s_copy);
+  if (t->s_aux) cudaStreamDestroy(t->s_aux);
   for (void* p : t->owned) cudaFree(p);
   if (t->metrics_host) cudaFreeHost(t->metrics_host);
   if (t->lr_host) cudaFreeHost(t->lr_host);
@@ -329,6 +377,10 @@ extern "C" int dmlp_trainer_create(const dmlp_trainer_config_t* cfg, int device,
   make_layout(*cfg, &t->lay);
   const ParamLayout& L = t->lay;
   const int B = cfg->batch;
+  t->fused_ce = L.out_pad[L.L - 1] <= 32;
+  t->direct = B <= 128;
+  memset(t->ev_dz, 0, sizeof(t->ev_dz));
+  t->ev_aux_done = nullptr;
   DeviceGuard guard(device);
   int rc = DMLP_OK;
   auto fail = [&](int code) { dmlp_trainer_destroy(reinterpret_cast<dmlp_trainer_t>(t)); return code; };
@@ -386,11 +438,15 @@ extern "C" int dmlp_trainer_create(const dmlp_trainer_config_t* cfg, int device,
   CUF(cudaStreamCreateWithFlags(&t->s_main, cudaStreamNonBlocking));
   CUF(cudaStreamCreateWithFlags(&t->s_comm, cudaStreamNonBlocking));
   CUF(cudaStreamCreateWithFlags(&t->s_copy, cudaStreamNonBlocking));
+  CUF(cudaStreamCreateWithFlags(&t->s_aux, cudaStreamNonBlocking));
   for (int par = 0; par < 2; ++par) {
     CUF(cudaEventCreateWithFlags(&t->ev_h2d[par], cudaEventDisableTiming));
     CUF(cudaEventCreateWithFlags(&t->ev_done[par], cudaEventDisableTiming));
   }
   CUF(cudaEventCreateWithFlags(&t->ev_join, cudaEventDisableTiming));
+  CUF(cudaEventCreateWithFlags(&t->ev_fork, cudaEventDisableTiming));
+  CUF(cudaEventCreateWithFlags(&t->ev_aux_done, cudaEventDisableTiming));
+  for (int l = 0; l < L.L; ++l) CUF(cudaEventCreateWithFlags(&t->ev_dz[l], cudaEventDisableTiming));
   for (int l = 0; l < L.L; ++l) CUF(cudaEventCreateWithFlags(&t->ev_bucket[l], cudaEventDisableTiming));
   TRYF(build_plans(t));
   *out = reinterpret_cast<dmlp_trainer_t>(t);
@@ -572,9 +628,13 @@ extern "C" int dmlp_trainer_eval(dmlp_trainer_t h, const float* x_host, const in
     DMLP_CUDA_CHECK(cudaMemcpyAsync(t->labels[0], y_host + b * B, sizeof(int) * B, cudaMemcpyHostToDevice, S));
     DMLP_CUDA_CHECK(cudaMemsetAsync(t->metrics_dev[0], 0, 8, S));
     if (t->bf16) TRY(dmlp_cast_f32_to_bf16(t->x[0], t->x16, static_cast<size_t>(B) * L.in[0], S));
-    for (int l = 0; l < L.L; ++l) TRY(gemm_plan_run(&t->fwd[0][l], S));
-    TRY(dmlp_softmax_ce(t->act[last], L.out_pad[last], t->labels[0], B, L.out[last], 1.f / B, nullptr, nullptr,
-                        t->metrics_dev[0], reinterpret_cast<int32_t*>(t->metrics_dev[0] + 1), nullptr, S));
+    for (int l = 0; l < L.L; ++l) {
+      if (l == last && t->fused_ce) TRY(gemm_plan_run(&t->fwd_eval_last, S));
+      else TRY(gemm_plan_run(&t->fwd[0][l], S));
+    }
+    if (!t->fused_ce)
+      TRY(dmlp_softmax_ce(t->act[last], L.out_pad[last], t->labels[0], B, L.out[last], 1.f / B, nullptr, nullptr,
+                          t->metrics_dev[0], reinterpret_cast<int32_t*>(t->metrics_dev[0] + 1), nullptr, S));
     DMLP_CUDA_CHECK(cudaMemcpyAsync(t->metrics_host, t->metrics_dev[0], 8, cudaMemcpyDeviceToHost, S));
     DMLP_CUDA_CHECK(cudaStreamSynchronize(S));
     ls += t->metrics_host[0];

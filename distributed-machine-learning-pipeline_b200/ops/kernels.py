@@ -42,8 +42,11 @@ def gemm(a: torch.Tensor, b: torch.Tensor, *, a_major: int, b_major: int, M: int
          out: Optional[torch.Tensor] = None, out_bf16: Optional[torch.Tensor] = None,
          bias: Optional[torch.Tensor] = None, relu: bool = False,
          mask: Optional[torch.Tensor] = None, colsum: Optional[torch.Tensor] = None,
-         accumulate: bool = False, block_n: int = 0) -> None:
-    """D[M,N] = epilogue(A·B) on tcgen05. See ``include/dmlp_b200.h`` (dmlp_gemm) for semantics."""
+         accumulate: bool = False, block_n: int = 0, ce_labels: Optional[torch.Tensor] = None,
+         ce_classes: int = 0, ce_scale: float = 1.0, ce_logits: Optional[torch.Tensor] = None,
+         ce_loss_sum: Optional[torch.Tensor] = None, ce_correct: Optional[torch.Tensor] = None) -> None:
+    """D[M,N] = epilogue(A·B) on tcgen05. See ``include/dmlp_b200.h`` (dmlp_gemm) for semantics.
+    ``ce_labels`` switches the epilogue to fused softmax cross-entropy (out/out_bf16 receive dlogits)."""
     _check_2d(a, "a")
     _check_2d(b, "b")
     if a.dtype != b.dtype or a.dtype not in _DT:
@@ -74,7 +77,26 @@ def gemm(a: torch.Tensor, b: torch.Tensor, *, a_major: int, b_major: int, M: int
         d.colsum = colsum.data_ptr()
     d.accumulate = int(accumulate)
     d.block_n = block_n
+    if ce_labels is not None:
+        assert ce_labels.dtype == torch.int32 and ce_labels.numel() >= M
+        d.ce_labels, d.ce_classes, d.ce_scale = ce_labels.data_ptr(), ce_classes, float(ce_scale)
+        d.ce_logits, d.ce_loss_sum, d.ce_correct = _ptr(ce_logits), _ptr(ce_loss_sum), _ptr(ce_correct)
     native.check(native.lib().dmlp_gemm(C.byref(d), _stream()))
+
+
+def linear_softmax_ce(x: torch.Tensor, w: torch.Tensor, bias: torch.Tensor, labels: torch.Tensor,
+                      num_classes: int, scale: float, dlogits: Optional[torch.Tensor],
+                      loss_sum: Optional[torch.Tensor], correct: Optional[torch.Tensor],
+                      dbias: Optional[torch.Tensor] = None, logits: Optional[torch.Tensor] = None,
+                      dlogits_bf16: Optional[torch.Tensor] = None) -> None:
+    """Last layer + loss in one kernel: logits = x @ w + bias stay in TMEM/registers; the epilogue
+    emits dlogits=(softmax-onehot)*scale, the bias gradient, the loss sum and the hit count.
+    Reference client.go:130-165,352-382."""
+    B, K = x.shape
+    N = w.shape[1]
+    gemm(x, w, a_major=0, b_major=1, M=B, N=N, K=K, out=dlogits, out_bf16=dlogits_bf16, bias=bias,
+         colsum=dbias, ce_labels=labels, ce_classes=num_classes, ce_scale=scale, ce_logits=logits,
+         ce_loss_sum=loss_sum, ce_correct=correct)
 
 
 def linear_forward(x: torch.Tensor, w: torch.Tensor, bias: Optional[torch.Tensor], relu: bool,

@@ -40,6 +40,8 @@ class GemmDesc(C.Structure):
         ("bias", C.c_void_p), ("relu", C.c_int),
         ("mask", C.c_void_p), ("mask_dtype", C.c_int), ("ld_mask", C.c_int64),
         ("colsum", C.c_void_p), ("accumulate", C.c_int), ("block_n", C.c_int),
+        ("ce_labels", C.c_void_p), ("ce_classes", C.c_int), ("ce_scale", C.c_float),
+        ("ce_logits", C.c_void_p), ("ce_loss_sum", C.c_void_p), ("ce_correct", C.c_void_p),
     ]
 
 

@@ -67,9 +67,22 @@ typedef struct {
   const void* mask_dev;  /* nullable: result is zeroed where mask[m][n] <= 0 (ReLU backward) */
   int mask_dtype;        /* DMLP_F32 or DMLP_BF16 */
   int64_t ld_mask;
-  float* colsum_dev;     /* nullable, length N: += column sums of the result (bias gradient) */
+  float* colsum_dev;     /* nullable, length N: column sums of the result (bias gradient): stored when
+                            M <= 128 (one M tile sees all rows), else atomically accumulated */
   int accumulate;        /* out_f32 += result instead of overwrite */
   int block_n;           /* N tile (multiple of 16, <= 256); 0 = choose automatically */
+  /* Fused softmax cross-entropy epilogue (reference client.go:76-93,144-165,352-382), enabled by a
+   * non-null ce_labels_dev; needs ce_classes <= N <= 32. The GEMM result + bias are the logits; the
+   * kernel writes dlogits = (softmax - onehot) * ce_scale to out_f32/out_bf16 (zero in padded
+   * columns), the bias gradient to colsum_dev, sum of -log(p_true + 1e-10) to ce_loss_sum_dev and the
+   * number of argmax hits to ce_correct_dev. With M <= 128 these reductions are stored (no prior
+   * zeroing needed), otherwise accumulated atomically. ce_logits_dev (nullable) receives the logits. */
+  const int32_t* ce_labels_dev;
+  int ce_classes;
+  float ce_scale;
+  float* ce_logits_dev;
+  float* ce_loss_sum_dev;
+  int32_t* ce_correct_dev;
 } dmlp_gemm_desc_t;
 
 int dmlp_gemm(const dmlp_gemm_desc_t* desc, void* stream);

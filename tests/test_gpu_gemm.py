@@ -105,3 +105,36 @@ def test_forward_explicit_block_n(bn):
     torch.cuda.synchronize()
     ref = _operand_ref(x) @ _operand_ref(w)
     assert (out.double() - ref).abs().max().item() < 1e-3 * ref.abs().max().item()
+
+
+@pytest.mark.parametrize("dtype", [torch.float32, torch.bfloat16])
+@pytest.mark.parametrize("B,K,C,N", [(64, 64, 10, 16), (100, 128, 10, 16), (64, 96, 27, 32), (300, 64, 10, 16)])
+def test_fused_linear_softmax_ce(dtype, B, K, C, N):
+    """Last-layer GEMM with the softmax-CE epilogue: dlogits, db, loss and hits vs PyTorch."""
+    from dmlp_b200.ops import kernels as k
+    torch.manual_seed(4)
+    x = _rand((B, K), dtype)
+    w = torch.zeros(K, N, device="cuda", dtype=dtype)
+    w[:, :C] = (torch.randn(K, C, device="cuda") * 0.3).to(dtype)
+    bias = torch.zeros(N, device="cuda")
+    bias[:C] = torch.randn(C, device="cuda")
+    labels = torch.randint(0, C, (B,), device="cuda", dtype=torch.int32)
+    dl = torch.full((B, N), float("nan"), device="cuda")
+    logits = torch.zeros(B, N, device="cuda")
+    loss = torch.zeros(1, device="cuda")
+    correct = torch.zeros(1, device="cuda", dtype=torch.int32)
+    db = torch.zeros(N, device="cuda")
+    k.linear_softmax_ce(x, w, bias, labels, C, 1.0 / B, dl, loss, correct, dbias=db, logits=logits)
+    torch.cuda.synchronize()
+    z = (_operand_ref(x) @ _operand_ref(w) + bias.double())[:, :C]
+    p = torch.softmax(z, 1)
+    oh = torch.nn.functional.one_hot(labels.long(), C).double()
+    ref_d = (p - oh) / B
+    assert (logits[:, :C].double() - z).abs().max().item() < 2e-3
+    assert (dl[:, :C].double() - ref_d).abs().max().item() < 1e-4
+    assert (dl[:, C:] == 0).all()
+    ref_loss = -(torch.log((p * oh).sum(1) + 1e-10)).sum().item()
+    assert abs(loss.item() - ref_loss) < 2e-3 * max(1.0, abs(ref_loss))
+    hits = (z.argmax(1) == labels.long()).sum().item()
+    assert abs(correct.item() - hits) <= 1  # tf32/bf16 rounding may flip a near-tie
+    assert (db[:C].double() - ref_d.sum(0)).abs().max().item() < 1e-4
