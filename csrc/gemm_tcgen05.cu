@@ -403,7 +403,7 @@ static int launch_gemm(const CUtensorMap& tmA, const CUtensorMap& tmB, const Gem
   DMLP_CUDA_CHECK(cudaGetDevice(&dev));
   if (!(attr_mask & (1ull << dev))) {
     DMLP_CUDA_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                         227 * 1024 - 2048));
+                                         216 * 1024));
     attr_mask |= 1ull << dev;
   }
   kern<<<grid, kGemmThreads, smem_bytes, stream>>>(tmA, tmB, p);
