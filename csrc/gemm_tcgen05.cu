@@ -437,6 +437,7 @@ int dmlp::gemm_plan_create(const dmlp_gemm_desc_t* d, GemmPlan* plan) {
   const int KS = 128 / EB;
   const int ATOM = 128 / EB;
   int bn = d->block_n > 0 ? d->block_n : choose_block_n(d->M, d->N);
+  if (d->ce_labels_dev != nullptr) bn = ((d->N + 15) / 16) * 16;  // fused softmax-CE: one N tile holds the whole row
   DMLP_REQUIRE(bn % 16 == 0 && bn >= 16 && bn <= 256, "dmlp_gemm: block_n %d must be a multiple of 16 in [16,256]", bn);
 
   int rc;
@@ -481,8 +482,6 @@ int dmlp::gemm_plan_create(const dmlp_gemm_desc_t* d, GemmPlan* plan) {
   if (d->ce_labels_dev != nullptr) {
     DMLP_REQUIRE(d->N <= 32 && d->ce_classes >= 1 && d->ce_classes <= d->N, "fused softmax-CE needs classes <= N <= 32 (got N=%d classes=%d)", d->N, d->ce_classes);
     DMLP_REQUIRE(!d->relu && !d->mask_dev && !d->accumulate, "fused softmax-CE excludes relu/mask/accumulate");
-    bn = ((d->N + 15) / 16) * 16;  // one N tile holds the whole row
-    p.block_n = bn;
   }
 
   plan->grid_x = ceil_div(d->N, bn);

@@ -1,0 +1,145 @@
+"""The gRPC contract on ``backend=cuda``: logical devices served from real GPU memory, collectives run
+by the native peer-memory kernels (all logical devices of this test live on GPU 0 → emulated ranks)."""
+import time
+
+import grpc
+import numpy as np
+import pytest
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.fixture
+def cuda_cluster():
+    from dmlp_b200.proto import rpc
+    from dmlp_b200.services import server as srv
+    from dmlp_b200.services.backend import make_backend
+    started = {"devices": [], "coord": None}
+
+    def make(n, mem_size=0x2000, **kw):
+        for i in range(n):
+            started["devices"].append(srv.start_device_server(make_backend("cuda", i + 1, mem_size, 0)))
+        started["coord"] = srv.start_coordinator_server(**kw)
+        return rpc.CoordinatorStub(rpc.insecure_channel(started["coord"].addr)), started["devices"], started["coord"]
+
+    yield make
+    if started["coord"]:
+        started["coord"].stop()
+    for d in started["devices"]:
+        d.stop()
+        d.service.backend.close()
+
+
+def _h2d(pb, client, dev, addr, data):
+    return client.Memcpy(pb.MemcpyRequest(hostToDevice=pb.MemcpyHostToDeviceRequest(
+        hostSrcData=data, dstDeviceId=pb.DeviceId(value=dev), dstMemAddr=pb.MemAddr(value=addr))))
+
+
+def _d2h(pb, client, dev, addr, n=0):
+    return client.Memcpy(pb.MemcpyRequest(deviceToHost=pb.MemcpyDeviceToHostRequest(
+        srcDeviceId=pb.DeviceId(value=dev), srcMemAddr=pb.MemAddr(value=addr), numBytes=n))).deviceToHost.dstData
+
+
+def test_memcpy_roundtrip_through_gpu_memory(cuda_cluster):
+    from dmlp_b200.proto import gpu_sim as pb
+    client, devs, _ = cuda_cluster(1, mem_size=0x1000)
+    init = client.CommInit(pb.CommInitRequest(numDevices=1, device_addresses=[devs[0].addr]))
+    did = init.devices[0].deviceId.value
+    assert _h2d(pb, client, did, 0x1000, b"Hello GPU!").hostToDevice.success
+    assert _d2h(pb, client, did, 0x1000) == b"Hello GPU!"
+    assert devs[0].service.backend.pointer(0x1000) != 0
+    with pytest.raises(grpc.RpcError) as e:
+        _d2h(pb, client, did, 0x1800)
+    assert e.value.code() == grpc.StatusCode.INTERNAL
+
+
+@pytest.mark.parametrize("algo", ["auto", "ring", "oneshot", "twoshot"])
+def test_allreduce_comparison_on_gpu(cuda_cluster, algo):
+    """TestAllReduceComparison analogue: 3 devices, 1 MiB of 0x01, naive then AllReduceRing, with values checked."""
+    from dmlp_b200.proto import gpu_sim as pb
+    client, devs, coord = cuda_cluster(3)
+    init = client.CommInit(pb.CommInitRequest(numDevices=3, device_addresses=[d.addr for d in devs]))
+    assert len(init.devices) == 3
+    assert coord.service.communicators[init.commId].native is not None, "native peer-memory path must be active"
+    size = 1 << 20
+    for md in init.devices:
+        _h2d(pb, client, md.deviceId.value, 0x1000, b"\x01" * size)
+    naive = client.NaiveAllReduce(pb.NaiveAllReduceRequest(commId=init.commId, dataSize=size, latencyMs=1))
+    assert naive.success and naive.totalDataTransferred == 6 * size
+    for md in init.devices:
+        assert _d2h(pb, client, md.deviceId.value, 0x2000) == b"\x03" * size
+    ring = client.AllReduceRing(pb.AllReduceRingRequest(commId=init.commId, count=size // 4),
+                                metadata=(("dmlp-dtype", "u8"), ("dmlp-algo", algo)))
+    assert ring.success
+    for md in init.devices:
+        got = _d2h(pb, client, md.deviceId.value, 0x1000)
+        assert got[:size // 4] == b"\x03" * (size // 4) and got[size // 4:] == b"\x01" * (size - size // 4)
+    assert client.GetCommStatus(pb.GetCommStatusRequest(commId=init.commId)).status == pb.SUCCESS
+
+
+def test_ring_f32_padding_case_and_fused_sgd(cuda_cluster):
+    from dmlp_b200.proto import gpu_sim as pb
+    client, devs, _ = cuda_cluster(3)
+    init = client.CommInit(pb.CommInitRequest(numDevices=3, device_addresses=[d.addr for d in devs]))
+    nelem = 101770  # 407 080 bytes: not divisible by 3 (the reference's padding branch)
+    rng = np.random.default_rng(0)
+    grads = [rng.standard_normal(nelem).astype(np.float32) for _ in range(3)]
+    w0 = rng.standard_normal(nelem).astype(np.float32)
+    for md, g in zip(init.devices, grads):
+        _h2d(pb, client, md.deviceId.value, 0x1000, g.tobytes())
+        _h2d(pb, client, md.deviceId.value, 0x2000, w0.tobytes())
+    # gradient average + SGD fused into the collective: weights at 0x2000 are updated in the same kernel
+    ok = client.AllReduceRing(pb.AllReduceRingRequest(commId=init.commId, count=nelem * 4),
+                              metadata=(("dmlp-sgd-lr", "0.01"), ("dmlp-sgd-weights", "0x2000")))
+    assert ok.success
+    ref = w0.astype(np.float64) - 0.01 * np.mean(np.stack(grads).astype(np.float64), axis=0)
+    ws = [np.frombuffer(_d2h(pb, client, md.deviceId.value, 0x2000), np.float32) for md in init.devices]
+    for w in ws:
+        assert np.abs(w - ref).max() < 1e-5 and np.array_equal(w, ws[0])
+    # plain all-reduce (sum) in place
+    assert client.AllReduceRing(pb.AllReduceRingRequest(commId=init.commId, count=nelem * 4)).success
+    s = np.sum(np.stack(grads).astype(np.float64), axis=0)
+    for md in init.devices:
+        assert np.abs(np.frombuffer(_d2h(pb, client, md.deviceId.value, 0x1000), np.float32) - s).max() < 1e-4
+
+
+def test_p2p_stream_is_a_device_copy_kernel(cuda_cluster):
+    """BeginSend/BeginReceive + payload-free StreamSend → P2P copy kernel; status follows its CUDA event."""
+    from dmlp_b200.proto import gpu_sim as pb
+    from dmlp_b200.proto import rpc
+    client, devs, _ = cuda_cluster(2)
+    client.CommInit(pb.CommInitRequest(numDevices=2, device_addresses=[d.addr for d in devs]))
+    d0 = rpc.DeviceStub(rpc.insecure_channel(devs[0].addr))
+    payload = bytes(range(256)) * 4096  # 1 MiB
+    d0.Memcpy(pb.MemcpyRequest(hostToDevice=pb.MemcpyHostToDeviceRequest(hostSrcData=payload, dstMemAddr=pb.MemAddr(value=0x1000))))
+    s = d0.BeginSend(pb.BeginSendRequest(sendBuffAddr=pb.MemAddr(value=0x1000), numBytes=len(payload), dstRank=pb.Rank(value=1)))
+    d0.BeginReceive(pb.BeginReceiveRequest(streamId=s.streamId, recvBuffAddr=pb.MemAddr(value=0x2000), numBytes=len(payload),
+                                           srcRank=pb.Rank(value=0)))
+    assert d0.StreamSend(iter([pb.DataChunk(streamId=s.streamId.value)])).success
+    deadline = time.time() + 5
+    st = pb.IN_PROGRESS
+    while st == pb.IN_PROGRESS and time.time() < deadline:
+        st = d0.GetStreamStatus(pb.GetStreamStatusRequest(streamId=s.streamId)).status
+    assert st == pb.SUCCESS
+    assert devs[1].service.backend.read(0x2000) == payload
+
+
+def test_gpu_failure_mid_allreduce_is_surfaced(cuda_cluster):
+    """A rank that stops participating (GPU fault injection) → in-kernel watchdog → the AllReduceRing RPC
+    fails, the communicator is FAILED and refuses further collectives (reference :281-285,341-344)."""
+    from dmlp_b200.proto import gpu_sim as pb
+    client, devs, coord = cuda_cluster(3, watchdog_ms=300, health_interval=30)
+    init = client.CommInit(pb.CommInitRequest(numDevices=3, device_addresses=[d.addr for d in devs]))
+    for md in init.devices:
+        _h2d(pb, client, md.deviceId.value, 0x1000, np.ones(4096, np.float32).tobytes())
+    assert client.AllReduceRing(pb.AllReduceRingRequest(commId=init.commId, count=16384)).success
+    coord.service.communicators[init.commId].native.inject_dead_ranks(1 << 2)
+    t0 = time.time()
+    with pytest.raises(grpc.RpcError) as e:
+        client.AllReduceRing(pb.AllReduceRingRequest(commId=init.commId, count=16384))
+    assert e.value.code() == grpc.StatusCode.UNKNOWN and "waited for rank" in e.value.details()
+    assert time.time() - t0 < 5, "the watchdog, not a hang, must end the collective"
+    assert client.GetCommStatus(pb.GetCommStatusRequest(commId=init.commId)).status == pb.FAILED
+    with pytest.raises(grpc.RpcError) as e:
+        client.AllReduceRing(pb.AllReduceRingRequest(commId=init.commId, count=16384))
+    assert e.value.code() == grpc.StatusCode.FAILED_PRECONDITION
