@@ -130,6 +130,8 @@ def main() -> int:
     multi = world > 1
     if multi:
         os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        if os.environ.get("NCCL_DEBUG", "VERSION").upper() == "VERSION":
+            os.environ["NCCL_DEBUG"] = "WARN"  # keep NCCL's version banner off stdout: rank 0 prints ONE JSON line
         dist.init_process_group(backend="nccl", device_id=torch.device("cuda", local_rank))
 
     m = MODELS[a.model]

@@ -27,6 +27,7 @@ def main():
     ap.add_argument("--factor", type=int, default=4)
     ap.add_argument("--out", default="")
     ap.add_argument("--algos", default="auto,oneshot,twoshot,ring,nccl")
+    ap.add_argument("--graph", type=int, default=1, help="time CUDA-graph replays of `iters` launches (default) or eager launches")
     a = ap.parse_args()
     rank, world = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"])
     local = int(os.environ.get("LOCAL_RANK", rank))
@@ -44,7 +45,8 @@ def main():
     my_in = arena_tensor(ins[rank], maxb // 4, local)
     my_in.normal_()
     nccl_buf = torch.empty(maxb // 4, device="cuda")
-    stream = torch.cuda.current_stream()
+    stream = torch.cuda.Stream()
+    torch.cuda.set_stream(stream)
     rows = []
     size = a.min_bytes
     sizes = []
@@ -53,7 +55,7 @@ def main():
         size *= a.factor
     for nbytes in sizes:
         count = nbytes // 4
-        iters = 200 if nbytes <= (1 << 20) else 50 if nbytes <= (64 << 20) else 10
+        iters = 100 if nbytes <= (1 << 20) else 40 if nbytes <= (64 << 20) else 10
         for algo in a.algos.split(","):
             if algo in ("oneshot",) and nbytes > (64 << 20):
                 continue  # (n-1) x bytes pulled per rank: pointless at these sizes
@@ -68,13 +70,26 @@ def main():
             for _ in range(5):
                 launch()
             torch.cuda.synchronize()
+            graph = None
+            if a.graph:
+                # `iters` launches captured into one CUDA graph: removes the host launch cost, which
+                # otherwise dominates every implementation below ~1 MiB
+                graph = torch.cuda.CUDAGraph()
+                with torch.cuda.graph(graph, stream=stream):
+                    for _ in range(iters):
+                        launch()
+                graph.replay()
+                torch.cuda.synchronize()
             dist.barrier()
             torch.cuda.synchronize()
             e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-            e0.record()
-            for _ in range(iters):
-                launch()
-            e1.record()
+            e0.record(stream)
+            if graph is not None:
+                graph.replay()
+            else:
+                for _ in range(iters):
+                    launch()
+            e1.record(stream)
             torch.cuda.synchronize()
             t = torch.tensor([e0.elapsed_time(e1) / iters], device="cuda", dtype=torch.float64)
             dist.all_reduce(t, op=dist.ReduceOp.MAX)
@@ -84,7 +99,8 @@ def main():
             algbw = nbytes / (us * 1e-6) / 1e9
             picked = native.ALGO_NAMES[comm.pick_algo(nbytes)] if algo == "auto" else algo
             row = {"bytes": nbytes, "impl": algo, "picked": picked, "n_gpus": world, "latency_us": round(us, 2),
-                   "algbw_GBs": round(algbw, 2), "busbw_GBs": round(algbw * 2 * (world - 1) / world, 2), "iters": iters}
+                   "algbw_GBs": round(algbw, 2), "busbw_GBs": round(algbw * 2 * (world - 1) / world, 2), "iters": iters,
+                   "timing": "cuda-graph replay" if a.graph else "eager launches"}
             rows.append(row)
             if rank == 0:
                 print(json.dumps(row), flush=True)
