@@ -742,6 +742,26 @@ extern "C" int dmlp_comm_inject_dead_ranks(dmlp_comm_t h, uint32_t mask) {
   return DMLP_OK;
 }
 
+// Used by nvls.cu: the NVLS kernel shares this communicator's signal pads, epochs and watchdog words.
+extern "C" int dmlp_comm_internal_view(dmlp_comm_t h, int local_idx, uint32_t* pad[DMLP_MAX_RANKS], uint32_t** state,
+                                       uint32_t** host_flags, unsigned long long* timeout_ns, uint32_t* dead_mask,
+                                       int* rank, int* world, int* dev) {
+  Comm* c = reinterpret_cast<Comm*>(h);
+  DMLP_REQUIRE(c && local_idx >= 0 && local_idx < c->nlocal, "dmlp_comm_internal_view: bad arguments");
+  for (int r = 0; r < c->world; ++r) {
+    if (!c->segment[local_idx][r]) return set_error(DMLP_ERR_NOT_FOUND, "rank %d's segment is not mapped", r);
+    pad[r] = reinterpret_cast<uint32_t*>(c->segment[local_idx][r]);
+  }
+  *state = c->state[local_idx];
+  *host_flags = c->host_flags;
+  *timeout_ns = c->timeout_ns;
+  *dead_mask = c->dead_mask;
+  *rank = c->local_rank[local_idx];
+  *world = c->world;
+  *dev = c->local_dev[local_idx];
+  return DMLP_OK;
+}
+
 extern "C" int dmlp_allreduce_pick_algo(int world, size_t bytes) {
   if (world <= 1) return DMLP_ALGO_ONESHOT;
   // Latency-bound sizes: one rendezvous, (n-1) x bytes pulled per rank. Above that two-shot moves

@@ -63,6 +63,10 @@ struct Trainer {
   void* peer_shadow[DMLP_MAX_RANKS];
   float* peer_grads[2][DMLP_MAX_RANKS];
   bool owns_params = false;
+  bool nvls = false;  // params/grads live in multicast-bound memory; all-reduce by multimem
+  float* mc_params = nullptr;
+  float* mc_grads[2] = {nullptr, nullptr};
+  void* mc_shadow = nullptr;
   // private buffers
   float* x[2] = {nullptr, nullptr};
   __nv_bfloat16* x16 = nullptr;
@@ -178,6 +182,19 @@ static int enqueue_allreduce(Trainer* t, int par, size_t off, size_t count, cuda
   if (t->comm == nullptr) {
     return dmlp_sgd(t->params + off, t->grads[par] + off, count, t->lr_dev, 1.f,
                     t->bf16 ? static_cast<void*>(t->shadow + off) : nullptr, st);
+  }
+  if (t->nvls) {
+    dmlp_nvls_allreduce_desc_t n;
+    memset(&n, 0, sizeof(n));
+    n.count = count;
+    n.mc_in = t->mc_grads[par] + off;
+    n.mc_out = t->mc_params + off;
+    n.mc_out_bf16 = t->bf16 ? static_cast<void*>(static_cast<__nv_bfloat16*>(t->mc_shadow) + off) : nullptr;
+    n.uc_out = t->params + off;
+    n.lr = t->lr_dev;
+    n.scale = 1.f / static_cast<float>(t->world);
+    n.fuse_sgd = 1;
+    return dmlp_allreduce_nvls(t->comm, t->local_idx, &n, st);
   }
   dmlp_allreduce_desc_t d;
   memset(&d, 0, sizeof(d));
@@ -389,7 +406,26 @@ extern "C" int dmlp_trainer_create(const dmlp_trainer_config_t* cfg, int device,
 
   const size_t pbytes = align_up(L.total * 4, 256);
   const size_t sbytes = align_up(L.total * 2, 256);
-  if (t->comm) {
+  t->nvls = t->comm != nullptr && cfg->allreduce_algo == DMLP_ALGO_NVLS;
+  if (t->nvls) {
+    const size_t need = 3 * pbytes + (t->bf16 ? sbytes : 0);
+    if (!cfg->nvls_uc || !cfg->nvls_mc || cfg->nvls_bytes < need) {
+      set_error(DMLP_ERR_INVALID, "NVLS all-reduce needs a multicast-bound arena of at least %zu bytes", need);
+      return fail(DMLP_ERR_INVALID);
+    }
+    uint8_t* u = static_cast<uint8_t*>(cfg->nvls_uc);
+    uint8_t* m = static_cast<uint8_t*>(cfg->nvls_mc);
+    t->params = reinterpret_cast<float*>(u);
+    t->grads[0] = reinterpret_cast<float*>(u + pbytes);
+    t->grads[1] = reinterpret_cast<float*>(u + 2 * pbytes);
+    t->mc_params = reinterpret_cast<float*>(m);
+    t->mc_grads[0] = reinterpret_cast<float*>(m + pbytes);
+    t->mc_grads[1] = reinterpret_cast<float*>(m + 2 * pbytes);
+    if (t->bf16) {
+      t->shadow = reinterpret_cast<__nv_bfloat16*>(u + 3 * pbytes);
+      t->mc_shadow = m + 3 * pbytes;
+    }
+  } else if (t->comm) {
     for (int r = 0; r < world; ++r) {
       void* base = nullptr;
       size_t cap = 0;

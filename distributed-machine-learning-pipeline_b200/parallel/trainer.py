@@ -30,7 +30,8 @@ log = logging.getLogger("dmlp.trainer")
 
 class _NativeCfg(C.Structure):
     _fields_ = [("num_layers", C.c_int), ("dims", C.c_int * 9), ("batch", C.c_int), ("dtype", C.c_int),
-                ("lr", C.c_float), ("allreduce_algo", C.c_int), ("overlap", C.c_int)]
+                ("lr", C.c_float), ("allreduce_algo", C.c_int), ("overlap", C.c_int),
+                ("nvls_uc", C.c_void_p), ("nvls_mc", C.c_void_p), ("nvls_bytes", C.c_size_t)]
 
 
 @dataclass
@@ -39,7 +40,7 @@ class TrainerConfig:
     batch: int = 64                            # per GPU (reference batchSize, client.go:23)
     lr: float = 0.01                           # reference learningRate (client.go:27)
     precision: str = "tf32"                    # "tf32" (fp32 storage) | "bf16" (fp32 master + bf16 shadow)
-    allreduce: str = "auto"                    # auto | oneshot | twoshot | ring
+    allreduce: str = "auto"                    # auto | oneshot | twoshot | ring | nvls (falls back to auto if unavailable)
     overlap: bool = False                      # per-layer buckets reduced during backward
     use_graph: bool = True
     schedule: str = "constant"
@@ -150,6 +151,7 @@ class Trainer:
         ncfg = cfg.native()
         self.rank, self.world = 0, 1
         self._owns_comm = False
+        self.nvls = None
         self.comm = comm
         if process_group:
             import torch.distributed as dist
@@ -161,6 +163,17 @@ class Trainer:
                                                             arena_bytes=need.value)
                 self.comm.set_timeout_ms(cfg.watchdog_ms)
                 self._owns_comm = True
+            if self.world > 1 and cfg.allreduce == "nvls":
+                from ..runtime.nvls import NvlsArena, NvlsUnavailable
+                need = C.c_size_t()
+                native.check(self.lib.dmlp_trainer_arena_bytes(C.byref(ncfg), C.byref(need)))
+                try:
+                    self.nvls = NvlsArena.from_process_group(device, need.value)
+                    ncfg.nvls_uc, ncfg.nvls_mc, ncfg.nvls_bytes = self.nvls.uc[device], self.nvls.mc, self.nvls.nbytes
+                except NvlsUnavailable as e:
+                    log.warning("NVLS unavailable (%s); using the unicast all-reduce", e)
+                    ncfg.allreduce_algo = native.ALGO_AUTO
+                    self.cfg.allreduce = "auto"
         elif comm is not None:
             self.rank, self.world = comm.local_ranks[local_idx], comm.world
         h = C.c_void_p()
@@ -332,6 +345,9 @@ class Trainer:
         if getattr(self, "_h", None):
             self.lib.dmlp_trainer_destroy(self._h)
             self._h = None
+        if self.nvls is not None:
+            self.nvls.destroy()
+            self.nvls = None
         if self._owns_comm and self.comm is not None:
             self.comm.destroy()
             self.comm = None

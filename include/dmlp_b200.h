@@ -221,6 +221,33 @@ int dmlp_p2p_copy(int src_dev, void* dst_dev, const void* src_dev_ptr, size_t by
 int dmlp_reduce_n(int dev, void* dst_dev, const void* const* srcs_dev, int n, size_t count, int dtype,
                   int op, void* stream);
 
+/* ------------------------------------------------------------------ NVLS (NVSwitch multicast) all-reduce
+ * The multicast variant of AllReduceRing (gpu_coordinator_server.go:272-566): rank r reduces slice r
+ * with multimem.ld_reduce (the switch sums all replicas) and broadcasts the result / the updated
+ * weights with multimem.st. Buffers must live in memory bound to one multicast object:
+ *   creator:  dmlp_nvls_create (returns a POSIX fd for other processes)   others: dmlp_nvls_import
+ *   everyone: dmlp_nvls_add_device for its device(s)  -- barrier --  dmlp_nvls_bind  -- barrier --
+ * Barriers and the watchdog reuse the communicator's signal pads. f32 SUM (+ fused average/SGD). */
+typedef struct dmlp_nvls_opaque* dmlp_nvls_t;
+int dmlp_nvls_supported(int dev, int* supported);
+int dmlp_nvls_create(int world, size_t bytes, int* fd_out, dmlp_nvls_t* out);
+int dmlp_nvls_import(int world, size_t bytes, int fd, dmlp_nvls_t* out);
+int dmlp_nvls_size(dmlp_nvls_t nvls, size_t* bytes);
+int dmlp_nvls_add_device(dmlp_nvls_t nvls, int dev);
+int dmlp_nvls_bind(dmlp_nvls_t nvls, int dev, void** uc_ptr_dev, void** mc_ptr_dev);
+int dmlp_nvls_destroy(dmlp_nvls_t nvls);
+typedef struct {
+  size_t count;          /* floats */
+  const void* mc_in;     /* multicast address of the inputs (gradients) */
+  void* mc_out;          /* multicast address of the outputs (weights when fuse_sgd) */
+  void* mc_out_bf16;     /* optional multicast address of the bf16 weight shadow */
+  const void* uc_out;    /* caller's own replica of the outputs (read by the fused SGD) */
+  const float* lr;       /* device scalar (fuse_sgd) */
+  float scale;
+  int fuse_sgd;
+} dmlp_nvls_allreduce_desc_t;
+int dmlp_allreduce_nvls(dmlp_comm_t comm, int local_idx, const dmlp_nvls_allreduce_desc_t* desc, void* stream);
+
 /* ------------------------------------------------------------------ all-reduce without allocation
  * (No counterpart in the reference: its coordinator allocates freely on the host.)
  *
@@ -265,6 +292,9 @@ typedef struct {
   float lr;
   int allreduce_algo;            /* dmlp_algo_t */
   int overlap;                   /* 1: per-layer buckets reduced on a second stream during backward */
+  void* nvls_uc;                 /* allreduce_algo == DMLP_ALGO_NVLS: this rank's replica of the multicast-bound */
+  void* nvls_mc;                 /* arena and its multicast address; params/grads/shadow are placed there */
+  size_t nvls_bytes;
 } dmlp_trainer_config_t;
 typedef struct dmlp_trainer_opaque* dmlp_trainer_t;
 

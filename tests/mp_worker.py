@@ -64,9 +64,41 @@ def main():
         dist.barrier()
     comm.destroy()
 
+    # ---- 1b. NVLS (multicast) all-reduce, when the fabric supports it
+    from dmlp_b200.runtime.nvls import NvlsArena, NvlsUnavailable
+    nvls_ok = True
+    try:
+        arena = NvlsArena.from_process_group(local, 4 * nbytes)
+    except NvlsUnavailable as e:
+        nvls_ok = False
+        if rank == 0:
+            print("NVLS unavailable:", e)
+    if nvls_ok:
+        comm2 = Communicator.from_process_group(local, staging_bytes=1 << 20)
+        o_in, o_out, o_w = arena.alloc.alloc(nbytes), arena.alloc.alloc(nbytes), arena.alloc.alloc(nbytes)
+        uc = arena.uc[local]
+        native.check(lib.dmlp_memcpy_h2d(local, uc + o_in, all_in[rank].ctypes.data, count * 4, None))
+        w0 = np.ones(count, np.float32)
+        native.check(lib.dmlp_memcpy_h2d(local, uc + o_w, w0.ctypes.data, count * 4, None))
+        dist.barrier()
+        arena.allreduce(comm2, 0, o_in, o_out, count, local)
+        arena.allreduce(comm2, 0, o_in, o_w, count, local, fuse_sgd=True, lr=lr.data_ptr(), scale=1.0 / world)
+        torch.cuda.synchronize()
+        comm2.check()
+        got = np.empty(count, np.float32)
+        native.check(lib.dmlp_memcpy_d2h(local, got.ctypes.data, uc + o_out, count * 4, None))
+        assert np.abs(got - ref).max() < 1e-4, ("nvls", np.abs(got - ref).max())
+        native.check(lib.dmlp_memcpy_d2h(local, got.ctypes.data, uc + o_w, count * 4, None))
+        assert np.abs(got - (1.0 - 0.1 * ref / world)).max() < 1e-4, "nvls sgd"
+        dist.barrier()
+        arena.destroy()
+        comm2.destroy()
+        if rank == 0:
+            print("NVLS_OK")
+
     # ---- 2. data-parallel trainer vs oracle
-    for overlap in (False, True):
-        cfg = TrainerConfig(dims=(784, 128, 64, 10), batch=64, lr=0.1, overlap=overlap, seed=7)
+    for overlap, algo in ((False, "auto"), (True, "auto"), (False, "nvls" if nvls_ok else "twoshot")):
+        cfg = TrainerConfig(dims=(784, 128, 64, 10), batch=64, lr=0.1, overlap=overlap, seed=7, allreduce=algo)
         t = Trainer(cfg, device=local, process_group=True)
         x, y = synthetic_mnist(64 * world * 6, seed=3)
         params = [(w.astype(np.float64), b.astype(np.float64)) for w, b in t.weights()]

@@ -70,3 +70,36 @@ def test_torchrun_ipc_collectives_and_dp_trainer():
            "--master-addr", "127.0.0.1", "--master-port", "29617", os.path.join(ROOT, "tests", "mp_worker.py")]
     r = subprocess.run(cmd, capture_output=True, text=True, timeout=600, cwd=ROOT)
     assert r.returncode == 0 and "MP_WORKER_OK" in r.stdout, r.stdout[-3000:] + r.stderr[-3000:]
+
+
+@needs2
+def test_single_process_nvls_allreduce():
+    """In-switch reduction through the multicast address (skipped when the fabric has no multicast)."""
+    from dmlp_b200.runtime import native
+    from dmlp_b200.runtime.comm import Communicator
+    from dmlp_b200.runtime.nvls import NvlsArena, NvlsUnavailable
+    n = min(_ngpu(), 8)
+    devs = list(range(n))
+    count = 1 << 18
+    try:
+        arena = NvlsArena.local(devs, 3 * count * 4)
+    except NvlsUnavailable as e:
+        pytest.skip(f"NVLS unavailable: {e}")
+    comm = Communicator.local(devs)
+    o_in, o_out = arena.alloc.alloc(count * 4), arena.alloc.alloc(count * 4)
+    from dmlp_b200.parallel.data_parallel import arena_tensor
+    ins = [arena_tensor(arena.uc[d] + o_in, count, d) for d in devs]
+    for t in ins:
+        t.normal_()
+    ref = sum(t.double().cpu() for t in ins)
+    for d in devs:
+        torch.cuda.synchronize(d)
+    for li, d in enumerate(devs):
+        arena.allreduce(comm, li, o_in, o_out, count, d)
+    comm.sync()
+    comm.check()
+    outs = [arena_tensor(arena.uc[d] + o_out, count, d) for d in devs]
+    for o in outs:
+        assert (o.double().cpu() - ref).abs().max().item() < 1e-4
+    arena.destroy()
+    comm.destroy()
