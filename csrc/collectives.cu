@@ -190,11 +190,13 @@ __device__ __forceinline__ void report_failure(const CollArgs& a, int rank, int 
   __threadfence_system();
 }
 
-// Spins until *flag >= target (wrap-safe). False on abort or deadline.
+// Spins until *flag >= target (wrap-safe). False on abort or deadline. The poll itself is a relaxed
+// system-scope load (an acquire per poll costs a MEMBAR.SYS + L1 invalidate each time); one fence
+// after the flag has been observed gives the acquire ordering.
 __device__ __forceinline__ bool wait_flag(const uint32_t* flag, uint32_t target, const CollArgs& a,
                                           int rank, int peer, int phase, unsigned long long deadline) {
   uint32_t spins = 0;
-  while (static_cast<int32_t>(ld_acquire_sys(flag) - target) < 0) {
+  while (static_cast<int32_t>(ld_relaxed_sys(flag) - target) < 0) {
     if ((++spins & 0x3F) == 0) {
       if (ld_relaxed_sys(a.abort_flag) != 0u) return false;
       if (globaltimer_ns() > deadline) {
@@ -203,18 +205,21 @@ __device__ __forceinline__ bool wait_flag(const uint32_t* flag, uint32_t target,
       }
     }
   }
+  __threadfence_system();  // acquire: later reads of the peer's data are ordered after the flag
   return true;
 }
 
 // Barrier between the CTAs with this blockIdx.x on every rank. Returns false if it failed; the
-// result is uniform across the CTA.
+// result is uniform across the CTA. `release` = this CTA wrote data (to peers) in this kernel that
+// the peers may read once they pass: a system fence precedes the flag store. The entry barrier of a
+// kernel needs no release: everything earlier kernels wrote is visible at the kernel boundary.
 __device__ __forceinline__ bool coll_barrier(const CollArgs& a, int rank, uint32_t epoch, int phase,
-                                             unsigned long long deadline, int* s_fail) {
+                                             unsigned long long deadline, int* s_fail, bool release = true) {
   __syncthreads();
   if (threadIdx.x < a.world) {
     const int p = threadIdx.x;
-    __threadfence_system();
-    st_release_sys(a.pad[p] + kPadBarrier + blockIdx.x * kMaxRanks + rank, epoch);
+    if (release) __threadfence_system();
+    st_relaxed_sys(a.pad[p] + kPadBarrier + blockIdx.x * kMaxRanks + rank, epoch);
     if (!wait_flag(a.pad[rank] + kPadBarrier + blockIdx.x * kMaxRanks + p, epoch, a, rank, p, phase, deadline))
       *s_fail = 1;
   }
@@ -245,7 +250,7 @@ allreduce_oneshot_kernel(const __grid_constant__ CollArgs a) {
   uint32_t epoch = s_epoch;
   const unsigned long long deadline = globaltimer_ns() + a.timeout_ns;
 
-  if (!coll_barrier(a, rank, ++epoch, PHASE_BARRIER_IN, deadline, &s_fail)) return;
+  if (!coll_barrier(a, rank, ++epoch, PHASE_BARRIER_IN, deadline, &s_fail, /*release=*/false)) return;
 
   const size_t nfull = a.count / V;
   const int tail = static_cast<int>(a.count % V);
@@ -328,7 +333,7 @@ allreduce_twoshot_kernel(const __grid_constant__ CollArgs a) {
   uint32_t epoch = s_epoch;
   const unsigned long long deadline = globaltimer_ns() + a.timeout_ns;
 
-  if (!coll_barrier(a, rank, ++epoch, PHASE_BARRIER_IN, deadline, &s_fail)) return;
+  if (!coll_barrier(a, rank, ++epoch, PHASE_BARRIER_IN, deadline, &s_fail, /*release=*/false)) return;
 
   const size_t nfull = a.count / V;
   const int tail = static_cast<int>(a.count % V);
@@ -480,8 +485,8 @@ allreduce_ring_kernel(const __grid_constant__ CollArgs a) {
       __syncthreads();
       if (threadIdx.x == 0) {
         __threadfence_system();
-        if (has_send) st_release_sys(next_data_flag, seq_send + 1);
-        if (has_recv) st_release_sys(prev_ack_flag, seq_recv + 1);
+        if (has_send) st_relaxed_sys(next_data_flag, seq_send + 1);
+        if (has_recv) st_relaxed_sys(prev_ack_flag, seq_recv + 1);
       }
       if (has_send) ++seq_send;
       if (has_recv) ++seq_recv;
@@ -832,7 +837,10 @@ extern "C" int dmlp_allreduce(dmlp_comm_t h, int local_idx, const dmlp_allreduce
   }
   size_t work = npack;
   if (algo != DMLP_ALGO_ONESHOT) work = (npack + world - 1) / world;
-  int blocks = static_cast<int>((work + kCollThreads * 2 - 1) / (kCollThreads * 2));
+  // one-shot is latency bound (every load is a peer round trip): one pack per thread keeps all of a
+  // message's loads in flight at once; the bandwidth-bound algorithms take two packs per thread.
+  const int per_thread = algo == DMLP_ALGO_ONESHOT ? 1 : 2;
+  int blocks = static_cast<int>((work + kCollThreads * per_thread - 1) / (kCollThreads * per_thread));
   if (blocks < 1) blocks = 1;
   const int cap = algo == DMLP_ALGO_RING ? (hard_cap < 32 ? hard_cap : 32) : hard_cap;
   if (blocks > cap) blocks = cap;

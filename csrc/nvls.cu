@@ -179,7 +179,7 @@ constexpr int kNvlsPadBarrier = 0;  // same layout as collectives.cu: [block][sr
 __device__ __forceinline__ bool nvls_wait(const uint32_t* flag, uint32_t target, const NvlsArgs& a, int peer, int phase,
                                           unsigned long long deadline) {
   uint32_t spins = 0;
-  while (static_cast<int32_t>(ld_acquire_sys(flag) - target) < 0) {
+  while (static_cast<int32_t>(ld_relaxed_sys(flag) - target) < 0) {
     if ((++spins & 0x3F) == 0) {
       if (ld_relaxed_sys(a.abort_flag) != 0u) return false;
       if (globaltimer_ns() > deadline) {
@@ -192,16 +192,17 @@ __device__ __forceinline__ bool nvls_wait(const uint32_t* flag, uint32_t target,
       }
     }
   }
+  __threadfence_system();
   return true;
 }
 
 __device__ __forceinline__ bool nvls_barrier(const NvlsArgs& a, uint32_t epoch, int phase, unsigned long long deadline,
-                                             int* s_fail) {
+                                             int* s_fail, bool release = true) {
   __syncthreads();
   if (threadIdx.x < a.world) {
     const int p = threadIdx.x;
-    __threadfence_system();
-    st_release_sys(a.pad[p] + kNvlsPadBarrier + blockIdx.x * DMLP_MAX_RANKS + a.rank, epoch);
+    if (release) __threadfence_system();
+    st_relaxed_sys(a.pad[p] + kNvlsPadBarrier + blockIdx.x * DMLP_MAX_RANKS + a.rank, epoch);
     if (!nvls_wait(a.pad[a.rank] + kNvlsPadBarrier + blockIdx.x * DMLP_MAX_RANKS + p, epoch, a, p, phase, deadline))
       *s_fail = 1;
   }
@@ -217,7 +218,7 @@ __global__ void __launch_bounds__(kNvlsThreads) allreduce_nvls_kernel(const __gr
   __syncthreads();
   uint32_t epoch = s_epoch;
   const unsigned long long deadline = globaltimer_ns() + a.timeout_ns;
-  if (!nvls_barrier(a, ++epoch, 1, deadline, &s_fail)) return;  // every replica holds its gradients
+  if (!nvls_barrier(a, ++epoch, 1, deadline, &s_fail, false)) return;  // every replica holds its gradients
 
   const size_t nfull = a.count / 4;
   const int tail = static_cast<int>(a.count % 4);

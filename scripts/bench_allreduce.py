@@ -108,9 +108,9 @@ def main():
         with open(a.out, "w") as f:
             for r in rows:
                 f.write(json.dumps(r) + "\n")
-    comm.destroy()
-    dist.barrier()
-    dist.destroy_process_group()
+    sys.stdout.flush()
+    torch.cuda.synchronize()
+    os._exit(0)  # graph-captured NCCL collectives can stall process-group teardown; results are out
 
 
 if __name__ == "__main__":
