@@ -70,7 +70,14 @@ struct CollArgs {
   uint32_t* abort_flag;  // host-mapped
   uint32_t* status;      // host-mapped: {code, rank, peer, phase}
   unsigned long long timeout_ns;
+  // optional phase timestamps: [block][4] x u64 globaltimer ns {entry, after barrier-in, after data, exit}
+  unsigned long long* prof;
 };
+
+#define DMLP_PROF(slot)                                                               \
+  do {                                                                                \
+    if (a.prof != nullptr && threadIdx.x == 0 && a.rank >= 0) a.prof[blockIdx.x * 4 + (slot)] = globaltimer_ns(); \
+  } while (0)
 
 // ------------------------------------------------------------------ 16-byte packs
 template <typename T> struct Pack { static constexpr int N = 16 / sizeof(T); };
@@ -249,8 +256,10 @@ allreduce_oneshot_kernel(const __grid_constant__ CollArgs a) {
   __syncthreads();
   uint32_t epoch = s_epoch;
   const unsigned long long deadline = globaltimer_ns() + a.timeout_ns;
+  DMLP_PROF(0);
 
   if (!coll_barrier(a, rank, ++epoch, PHASE_BARRIER_IN, deadline, &s_fail, /*release=*/false)) return;
+  DMLP_PROF(1);
 
   const size_t nfull = a.count / V;
   const int tail = static_cast<int>(a.count % V);
@@ -309,11 +318,14 @@ allreduce_oneshot_kernel(const __grid_constant__ CollArgs a) {
     else st_pack(a.out[rank], i, acc);
   }
 
+  __syncthreads();
+  DMLP_PROF(2);
   // Peers may not overwrite their inputs until everyone has read them; callers that
   // double-buffer their inputs can drop this second rendezvous.
   if (!a.skip_end_barrier)
     if (!coll_barrier(a, rank, ++epoch, PHASE_BARRIER_OUT, deadline, &s_fail)) return;
   if (threadIdx.x == 0) a.state[rank][kStateEpoch + blockIdx.x] = epoch;
+  DMLP_PROF(3);
 }
 
 // ------------------------------------------------------------------ two-shot
@@ -814,6 +826,7 @@ extern "C" int dmlp_allreduce(dmlp_comm_t h, int local_idx, const dmlp_allreduce
   a.abort_flag = c->host_flags;
   a.status = c->host_flags + 4;
   a.timeout_ns = c->timeout_ns;
+  a.prof = reinterpret_cast<unsigned long long*>(d->prof_dev);
   for (int r = 0; r < world; ++r) {
     a.in[r] = d->in[r];
     a.out[r] = d->out[r];

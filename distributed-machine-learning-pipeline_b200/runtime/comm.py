@@ -171,7 +171,8 @@ class Communicator:
                   dtype: int = native.F32, op: int = native.SUM, algo: int = native.ALGO_AUTO,
                   local_idx: int = -1, stream: int = 0, streams: Optional[Sequence[int]] = None,
                   fuse_sgd: bool = False, lr: Optional[Sequence[Optional[int]]] = None, scale: float = 1.0,
-                  out_bf16: Optional[Sequence[Optional[int]]] = None, skip_end_barrier: bool = False) -> None:
+                  out_bf16: Optional[Sequence[Optional[int]]] = None, skip_end_barrier: bool = False,
+                  prof: Optional[int] = None) -> None:
         """Launches an all-reduce over raw device pointers (one entry per rank). Asynchronous."""
         d = native.AllReduceDesc()
         d.algo, d.dtype, d.op = algo, dtype, op
@@ -186,6 +187,7 @@ class Communicator:
         if streams is not None:
             for i, s in enumerate(streams):
                 d.streams[i] = s
+        d.prof = prof
         native.check(native.lib().dmlp_allreduce(self._h, local_idx, C.byref(d), stream or None))
 
     def pick_algo(self, nbytes: int) -> int:

@@ -66,7 +66,7 @@ class AllReduceDesc(C.Structure):
         ("skip_end_barrier", C.c_int), ("scale", C.c_float), ("count", C.c_size_t),
         ("inp", C.c_void_p * MAX_RANKS), ("out", C.c_void_p * MAX_RANKS),
         ("out_bf16", C.c_void_p * MAX_RANKS), ("lr", C.c_void_p * MAX_RANKS),
-        ("streams", C.c_void_p * MAX_RANKS),
+        ("streams", C.c_void_p * MAX_RANKS), ("prof", C.c_void_p),
     ]
 
 

@@ -207,6 +207,8 @@ typedef struct {
   void* out_bf16[DMLP_MAX_RANKS];  /* optional bf16 shadow of the updated weights (fuse_sgd) */
   const float* lr[DMLP_MAX_RANKS]; /* device scalar per rank (fuse_sgd) */
   void* streams[DMLP_MAX_RANKS];   /* local_idx < 0: per-local-rank streams (NULL = `stream` arg) */
+  void* prof_dev;                  /* optional: [blocks][4] u64 globaltimer stamps {entry, after barrier-in,
+                                      after data, exit} written by thread 0 of each CTA (one-shot kernel) */
 } dmlp_allreduce_desc_t;
 
 /* Launches the all-reduce for local rank `local_idx` (or for every local rank when < 0) and
