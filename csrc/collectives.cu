@@ -23,6 +23,7 @@
 #include "ptx_sm100.cuh"
 
 #include <cooperative_groups.h>
+#include <stdlib.h>
 #include <string.h>
 
 #include <mutex>
@@ -40,7 +41,8 @@ constexpr int kInplacePerThread = 4;
 constexpr int kPadBarrier = 0;                                 // [block][src rank]
 constexpr int kPadRingData = kMaxCollBlocks * kMaxRanks;       // [block] data sequence (written by prev)
 constexpr int kPadRingAck = kPadRingData + kMaxCollBlocks;     // [block] ack sequence (written by next)
-constexpr int kPadWords = kPadRingAck + kMaxCollBlocks;
+constexpr int kPadAbort = kPadRingAck + kMaxCollBlocks;         // [1] abort word: set by a failing peer or by the host
+constexpr int kPadWords = kPadAbort + 8;
 constexpr size_t kPadBytes = 64 * 1024;                        // reserved at the start of a segment
 static_assert(kPadWords * 4 <= kPadBytes, "signal pad overflow");
 // Local (never peer-accessed) per-rank state: barrier epochs then ring sequence numbers.
@@ -67,11 +69,11 @@ struct CollArgs {
   const float* lr[kMaxRanks];
   float scale;
   uint32_t dead_mask;  // fault injection: these ranks never show up
-  uint32_t* abort_flag;  // host-mapped
-  uint32_t* status;      // host-mapped: {code, rank, peer, phase}
+  uint32_t* status;      // host-mapped, written only on failure: {code, rank, peer, phase}
   unsigned long long timeout_ns;
   // optional phase timestamps: [block][4] x u64 globaltimer ns {entry, after barrier-in, after data, exit}
   unsigned long long* prof;
+  uint32_t strict;  // env DMLP_COLL_STRICT=1: add a system-scope acquire fence after every flag wait
 };
 
 #define DMLP_PROF(slot)                                                               \
@@ -193,26 +195,33 @@ __device__ __forceinline__ void report_failure(const CollArgs& a, int rank, int 
   a.status[3] = static_cast<uint32_t>(phase);
   __threadfence_system();
   a.status[0] = DMLP_ERR_TIMEOUT;
-  *reinterpret_cast<volatile uint32_t*>(a.abort_flag) = 1u;  // release the other ranks quickly
+  // Release everybody quickly: the abort word sits in each rank's (peer-visible) signal pad.
+  for (int p = 0; p < a.world; ++p) st_relaxed_sys(a.pad[p] + kPadAbort, 1u);
   __threadfence_system();
 }
 
-// Spins until *flag >= target (wrap-safe). False on abort or deadline. The poll itself is a relaxed
-// system-scope load (an acquire per poll costs a MEMBAR.SYS + L1 invalidate each time); one fence
-// after the flag has been observed gives the acquire ordering.
+// Spins until *flag >= target (wrap-safe). False on abort or deadline.
+// Cost notes (measured with the in-kernel stamps, profiles/r1_allreduce_phase_experiments.md):
+//  * polling a HOST-mapped abort flag from many CTAs serialises on PCIe and stalls barriers by
+//    40-230 us -> the abort word lives in device memory (this rank's signal pad);
+//  * a system-scope fence (MEMBAR.SYS) costs ~3 us. The poll is a relaxed sys-scope load and no
+//    acquire fence follows: every read of peer-written data in these kernels is a volatile
+//    (sys-scope, L1-bypassing) load issued after the flag was observed (control dependency +
+//    bar.sync), and data a peer pushed into local memory is only read by later kernels.
+//    DMLP_COLL_STRICT=1 restores the fence.
 __device__ __forceinline__ bool wait_flag(const uint32_t* flag, uint32_t target, const CollArgs& a,
                                           int rank, int peer, int phase, unsigned long long deadline) {
   uint32_t spins = 0;
   while (static_cast<int32_t>(ld_relaxed_sys(flag) - target) < 0) {
     if ((++spins & 0x3F) == 0) {
-      if (ld_relaxed_sys(a.abort_flag) != 0u) return false;
+      if (ld_relaxed_sys(a.pad[rank] + kPadAbort) != 0u) return false;
       if (globaltimer_ns() > deadline) {
         report_failure(a, rank, peer, phase);
         return false;
       }
     }
   }
-  __threadfence_system();  // acquire: later reads of the peer's data are ordered after the flag
+  if (a.strict) __threadfence_system();
   return true;
 }
 
@@ -283,7 +292,7 @@ allreduce_oneshot_kernel(const __grid_constant__ CollArgs a) {
         if (a.scale != 1.f) acc[k] = scale_pack<T>(acc[k], a.scale);
       }
     }
-    if (!coll_barrier(a, rank, ++epoch, PHASE_BARRIER_OUT, deadline, &s_fail)) return;
+    if (!coll_barrier(a, rank, ++epoch, PHASE_BARRIER_OUT, deadline, &s_fail, /*release=*/false)) return;
 #pragma unroll
     for (int k = 0; k < kInplacePerThread; ++k) {
       const size_t i = tid + k * stride;
@@ -322,8 +331,9 @@ allreduce_oneshot_kernel(const __grid_constant__ CollArgs a) {
   DMLP_PROF(2);
   // Peers may not overwrite their inputs until everyone has read them; callers that
   // double-buffer their inputs can drop this second rendezvous.
+  // (no release fence: this rank wrote nothing its peers will read; it only says "done reading")
   if (!a.skip_end_barrier)
-    if (!coll_barrier(a, rank, ++epoch, PHASE_BARRIER_OUT, deadline, &s_fail)) return;
+    if (!coll_barrier(a, rank, ++epoch, PHASE_BARRIER_OUT, deadline, &s_fail, /*release=*/false)) return;
   if (threadIdx.x == 0) a.state[rank][kStateEpoch + blockIdx.x] = epoch;
   DMLP_PROF(3);
 }
@@ -560,7 +570,8 @@ struct Comm {
   bool imported[kMaxRanks][kMaxRanks];
   size_t staging_bytes = 0, arena_bytes = 0, segment_bytes = 0;
   uint32_t* state[kMaxRanks];  // per local rank, local device memory
-  uint32_t* host_flags = nullptr;  // host-mapped: [0] abort, [4..8) status
+  uint32_t* host_flags = nullptr;  // host-mapped: [0] abort requested (host-side), [4..8) status written by kernels
+  cudaStream_t abort_stream[kMaxRanks] = {};
   unsigned long long timeout_ns = 10ull * 1000 * 1000 * 1000;
   uint32_t dead_mask = 0;
   bool emulated = false;  // all ranks on one device
@@ -690,6 +701,8 @@ extern "C" int dmlp_comm_destroy(dmlp_comm_t h) {
     if (seg) dmlp_free(c->local_dev[i], seg);
     if (c->state[i]) dmlp_free(c->local_dev[i], c->state[i]);
   }
+  for (int i = 0; i < c->nlocal; ++i)
+    if (c->abort_stream[i]) { cudaSetDevice(c->local_dev[i]); cudaStreamDestroy(c->abort_stream[i]); }
   if (c->host_flags) cudaFreeHost(c->host_flags);
   cudaGetLastError();
   delete c;
@@ -737,7 +750,17 @@ extern "C" int dmlp_comm_set_timeout_ms(dmlp_comm_t h, uint64_t ms) {
 extern "C" int dmlp_comm_abort(dmlp_comm_t h) {
   Comm* c = reinterpret_cast<Comm*>(h);
   DMLP_REQUIRE(c, "null communicator");
-  reinterpret_cast<volatile uint32_t*>(c->host_flags)[0] = 1u;
+  reinterpret_cast<volatile uint32_t*>(c->host_flags)[0] = 1u;  // sticky host-side state (and the copy source)
+  // The kernels poll an abort word in device memory (their own signal pad): push it there with a
+  // copy on a side stream, which runs while the spinning kernels occupy the compute streams.
+  for (int li = 0; li < c->nlocal; ++li) {
+    uint8_t* seg = c->segment[li][c->local_rank[li]];
+    if (!seg) continue;
+    DeviceGuard g(c->local_dev[li]);
+    if (c->abort_stream[li] == nullptr) DMLP_CUDA_CHECK(cudaStreamCreateWithFlags(&c->abort_stream[li], cudaStreamNonBlocking));
+    DMLP_CUDA_CHECK(cudaMemcpyAsync(reinterpret_cast<uint32_t*>(seg) + kPadAbort, c->host_flags, 4,
+                                    cudaMemcpyHostToDevice, c->abort_stream[li]));
+  }
   return DMLP_OK;
 }
 
@@ -823,10 +846,14 @@ extern "C" int dmlp_allreduce(dmlp_comm_t h, int local_idx, const dmlp_allreduce
   a.count = d->count;
   a.staging_bytes = c->staging_bytes;
   a.dead_mask = c->dead_mask;
-  a.abort_flag = c->host_flags;
   a.status = c->host_flags + 4;
   a.timeout_ns = c->timeout_ns;
   a.prof = reinterpret_cast<unsigned long long*>(d->prof_dev);
+  {
+    static int strict = -1;
+    if (strict < 0) { const char* e = getenv("DMLP_COLL_STRICT"); strict = e ? atoi(e) : 0; }
+    a.strict = static_cast<uint32_t>(strict);
+  }
   for (int r = 0; r < world; ++r) {
     a.in[r] = d->in[r];
     a.out[r] = d->out[r];
@@ -1017,7 +1044,6 @@ extern "C" int dmlp_allreduce_sum_f32_noalloc(int world, const float* const* in_
   a.scale = 1.f;
   a.count = count;
   a.staging_bytes = 2 * kNoAllocSlotBytes;
-  a.abort_flag = reinterpret_cast<uint32_t*>(base);
   a.status = reinterpret_cast<uint32_t*>(base) + 4;
   a.timeout_ns = 10ull * 1000 * 1000 * 1000;
   unsigned char* pads = base + kNoAllocFlagBytes;

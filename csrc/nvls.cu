@@ -166,7 +166,6 @@ struct NvlsArgs {
   // flag protocol (same pads as the other algorithms)
   uint32_t* pad[DMLP_MAX_RANKS];
   uint32_t* state;
-  uint32_t* abort_flag;
   uint32_t* status;
   unsigned long long timeout_ns;
   uint32_t dead_mask;
@@ -175,24 +174,25 @@ struct NvlsArgs {
 constexpr int kNvlsThreads = 512;
 constexpr int kNvlsMaxBlocks = 128;
 constexpr int kNvlsPadBarrier = 0;  // same layout as collectives.cu: [block][src rank]
+constexpr int kNvlsPadAbort = 128 * DMLP_MAX_RANKS + 2 * 128;  // == kPadAbort in collectives.cu
 
 __device__ __forceinline__ bool nvls_wait(const uint32_t* flag, uint32_t target, const NvlsArgs& a, int peer, int phase,
                                           unsigned long long deadline) {
   uint32_t spins = 0;
   while (static_cast<int32_t>(ld_relaxed_sys(flag) - target) < 0) {
     if ((++spins & 0x3F) == 0) {
-      if (ld_relaxed_sys(a.abort_flag) != 0u) return false;
+      if (ld_relaxed_sys(a.pad[a.rank] + kNvlsPadAbort) != 0u) return false;
       if (globaltimer_ns() > deadline) {
         a.status[1] = a.rank; a.status[2] = peer; a.status[3] = phase;
         __threadfence_system();
         a.status[0] = DMLP_ERR_TIMEOUT;
-        *reinterpret_cast<volatile uint32_t*>(a.abort_flag) = 1u;
+        for (int p = 0; p < a.world; ++p) st_relaxed_sys(a.pad[p] + kNvlsPadAbort, 1u);
         __threadfence_system();
         return false;
       }
     }
   }
-  __threadfence_system();
+  __threadfence_system();  // multimem loads are not volatile peer loads: keep the acquire here
   return true;
 }
 
@@ -446,7 +446,6 @@ extern "C" int dmlp_allreduce_nvls(dmlp_comm_t comm, int local_idx, const dmlp_n
   volatile uint32_t* hf = host_flags;
   if (hf[4] != 0 || hf[0] != 0) return set_error(DMLP_ERR_ABORTED, "communicator is FAILED");
   a.state = state;
-  a.abort_flag = host_flags;
   a.status = host_flags + 4;
   a.count = d->count;
   a.mc_in = static_cast<const float*>(d->mc_in);

@@ -24,7 +24,8 @@ def main():
     outs = [comm.arena_ptr(0, r, off_out) for r in range(world)]
     stream = torch.cuda.Stream()
     torch.cuda.set_stream(stream)
-    for nbytes in (1024, 65536, 262144, 437544, 1 << 20):
+    sizes = [int(v) for v in os.environ.get('PROF_SIZES', '1024,65536,262144,437544,1048576').split(',')]
+    for nbytes in sizes:
         count = nbytes // 4
         iters = 50
         prof = torch.zeros(iters, 128, 4, dtype=torch.int64, device="cuda")
@@ -51,7 +52,7 @@ def main():
             nb = int(used[0].sum())
             p = p[:, :nb, :]
             entry = p[:, :, 0].min(axis=1)
-            row = {"bytes": nbytes, "skip_end_barrier": skip, "blocks": nb, "n_gpus": world,
+            row = {"debug": os.environ.get("DMLP_COLL_DEBUG", "0"), "maxblocks": os.environ.get("DMLP_COLL_MAXBLOCKS", "0"), "bytes": nbytes, "skip_end_barrier": skip, "blocks": nb, "n_gpus": world,
                    "us_per_iter_events": round(e0.elapsed_time(e1) * 1e3 / iters, 2),
                    "barrier_in_us": round(float((p[:, :, 1] - p[:, :, 0]).mean()) / 1e3, 2),
                    "data_us": round(float((p[:, :, 2] - p[:, :, 1]).mean()) / 1e3, 2),
