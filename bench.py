@@ -128,10 +128,13 @@ def main() -> int:
         print(f"warning: --gpus {a.gpus} but WORLD_SIZE={world}; using WORLD_SIZE", file=sys.stderr)
     torch.cuda.set_device(local_rank)
     multi = world > 1
+    # Native libraries (NCCL's version banner, for one) write to the C-level stdout. The contract is ONE
+    # JSON line on stdout, so fd 1 points at stderr until the result is ready to be printed.
+    sys.stdout.flush()
+    real_stdout = os.dup(1)
+    os.dup2(2, 1)
     if multi:
         os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
-        if os.environ.get("NCCL_DEBUG", "VERSION").upper() == "VERSION":
-            os.environ["NCCL_DEBUG"] = "WARN"  # keep NCCL's version banner off stdout: rank 0 prints ONE JSON line
         dist.init_process_group(backend="nccl", device_id=torch.device("cuda", local_rank))
 
     m = MODELS[a.model]
@@ -224,8 +227,11 @@ def main() -> int:
         "clocks": clocks,
         "impl": "ours",
     }
+    sys.stdout.flush()
+    os.dup2(real_stdout, 1)
     if rank == 0:
-        print(json.dumps(out))
+        print(json.dumps(out), flush=True)
+    os.dup2(2, 1)
     trainer.close()
     if multi:
         dist.barrier()
