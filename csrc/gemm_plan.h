@@ -18,6 +18,7 @@ struct GemmParams {
   int stages;
   uint32_t tmem_cols;
   uint32_t a_stage_bytes, b_stage_bytes;
+  uint32_t a_tx_bytes;  // bytes TMA actually delivers for A per stage (half a tile when M <= 64)
   uint32_t idesc;
   float* out_f32;
   long long ld_out;
@@ -30,6 +31,7 @@ struct GemmParams {
   float* colsum;
   int relu;
   int accumulate;
+  int pdl;  // launched with programmatic stream serialization: the kernel executes griddepcontrol.wait
   // fused softmax cross-entropy epilogue (last layer): non-null labels switch it on
   const int* ce_labels;
   int ce_classes;

@@ -15,6 +15,9 @@
 #include "gemm_plan.h"
 #include "ptx_sm100.cuh"
 
+#include <stdlib.h>
+#include <string.h>
+
 namespace dmlp {
 
 
@@ -72,11 +75,19 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA,
   __syncthreads();
   tc_fence_after_sync();
   const uint32_t tmem_base = tmem_base_slot;
+  if (p.pdl) {
+    // Programmatic dependent launch: everything above (barrier init, TMEM allocation, descriptor
+    // prefetch) overlapped the tail of the previous kernel in the stream. From here on this kernel
+    // reads what its predecessors wrote, so wait for them to complete and flush; then let OUR
+    // dependent start its own prologue right away (single-wave grids only, see launch_gemm).
+    asm volatile("griddepcontrol.wait;" ::: "memory");
+    asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
+  }
 
   if (warp == 0) {
     // ------------------------------------------------------------ TMA producer
     if (lane == 0) {
-      const uint32_t stage_bytes = p.a_stage_bytes + p.b_stage_bytes;
+      const uint32_t stage_bytes = p.a_tx_bytes + p.b_stage_bytes;  // bytes TMA will deliver per stage
       for (int kb = 0; kb < p.num_k_blocks; ++kb) {
         const int s = kb % p.stages;
         const uint32_t ph = (kb / p.stages) & 1;
@@ -406,7 +417,22 @@ static int launch_gemm(const CUtensorMap& tmA, const CUtensorMap& tmB, const Gem
                                          216 * 1024));
     attr_mask |= 1ull << dev;
   }
-  kern<<<grid, kGemmThreads, smem_bytes, stream>>>(tmA, tmB, p);
+  if (p.pdl) {
+    cudaLaunchConfig_t cfg;
+    memset(&cfg, 0, sizeof(cfg));
+    cfg.gridDim = grid;
+    cfg.blockDim = dim3(kGemmThreads);
+    cfg.dynamicSmemBytes = smem_bytes;
+    cfg.stream = stream;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = 1;
+    DMLP_CUDA_CHECK(cudaLaunchKernelEx(&cfg, kern, tmA, tmB, p));
+  } else {
+    kern<<<grid, kGemmThreads, smem_bytes, stream>>>(tmA, tmB, p);
+  }
   DMLP_CUDA_CHECK(cudaGetLastError());
   return DMLP_OK;
 }
@@ -442,8 +468,12 @@ int dmlp::gemm_plan_create(const dmlp_gemm_desc_t* d, GemmPlan* plan) {
 
   int rc;
   const int mn_swz = bf16 ? 1 : 2;  // fp32 MN-major operands need the 32B-atom swizzle
+  // A problem with M <= 64 (the reference's batch) only fills half of the 128-row MMA tile. Loading
+  // just the live rows halves the TMA traffic of these latency-bound launches; the MMA still reads
+  // 128 smem rows, and whatever the dead rows hold only reaches accumulator rows that are never stored.
+  const int a_box_rows = (d->a_major == 0 && d->M <= 64) ? 64 : 128;
   if (d->a_major == 0)
-    rc = make_tensor_map_2d(&plan->tmA, d->A_dev, EB, bf16, d->K, d->M, d->lda, KS, 128, 1);
+    rc = make_tensor_map_2d(&plan->tmA, d->A_dev, EB, bf16, d->K, d->M, d->lda, KS, a_box_rows, 1);
   else
     rc = make_tensor_map_2d(&plan->tmA, d->A_dev, EB, bf16, d->M, d->K, d->lda, ATOM, KS, mn_swz);
   if (rc) return rc;
@@ -459,6 +489,7 @@ int dmlp::gemm_plan_create(const dmlp_gemm_desc_t* d, GemmPlan* plan) {
   p.block_n = bn;
   p.num_k_blocks = ceil_div(d->K, KS);
   p.a_stage_bytes = 128 * 128;
+  p.a_tx_bytes = (d->a_major == 0) ? a_box_rows * 128 : 128 * 128;
   p.b_stage_bytes = d->b_major == 0 ? bn * 128 : ceil_div(bn, ATOM) * KS * 128;
   const size_t stage_bytes = p.a_stage_bytes + p.b_stage_bytes;
   const size_t budget = 200 * 1024;
@@ -488,6 +519,13 @@ int dmlp::gemm_plan_create(const dmlp_gemm_desc_t* d, GemmPlan* plan) {
   plan->grid_y = ceil_div(d->M, 128);
   plan->smem = stages * stage_bytes + 1024;
   plan->key = (bf16 ? 4 : 0) | (d->a_major ? 2 : 0) | (d->b_major ? 1 : 0);
+  // PDL only for single-wave grids: an early-launched dependent must never compete with CTAs of
+  // this grid that are still waiting for an SM.
+  {
+    static int pdl_env = -1;
+    if (pdl_env < 0) { const char* e = getenv("DMLP_PDL"); pdl_env = e ? atoi(e) : 1; }
+    p.pdl = (pdl_env && plan->grid_x * plan->grid_y <= 148) ? 1 : 0;
+  }
   return DMLP_OK;
 }
 
