@@ -497,6 +497,10 @@ int dmlp::gemm_plan_create(const dmlp_gemm_desc_t* d, GemmPlan* plan) {
   if (stages > kMaxStages) stages = kMaxStages;
   if (stages > p.num_k_blocks) stages = p.num_k_blocks;
   if (stages < 1) stages = 1;
+  {
+    const char* e = getenv("DMLP_GEMM_STAGES");  // experiment knob
+    if (e && atoi(e) > 0 && atoi(e) < stages) stages = atoi(e);
+  }
   p.stages = stages;
   uint32_t cols = 32;
   while (cols < static_cast<uint32_t>(bn)) cols <<= 1;
