@@ -1,0 +1,682 @@
+// Cluster-fused training step for the reference-sized MLP (sm_100a): the whole forward, loss and
+// backward of one batch in ONE launch of one 8-CTA thread-block cluster.
+//
+// Why: at batch 64 every layer is latency bound. A tcgen05.mma costs ~200 cycles no matter how
+// narrow N is (profiles/r1_gemm_kloop_probe.md), the layer-1 forward is 98 of them back to back,
+// and each per-layer kernel pays ~3.3 us of fixed cost. Here the K dimension of every layer is
+// split over the 8 CTAs of a cluster; partial sums travel through distributed shared memory
+// (st.shared::cluster) and the output slice a CTA owns after the reduce-scatter is exactly the K
+// slice it needs for the next layer:
+//
+//   P0  TMA: X[:, k-slice], W1[k-slice, :]            F1: P1 = X_j . W1_j            -> reduce-scatter
+//   P1  H1_j = relu(sum P1 + b1_j)                     F2: P2 = H1_j . W2_j           -> reduce-scatter
+//   P2  H2_j = relu(sum P2 + b2_j)                     F3: P3 = H2_j . W3_j           -> all-reduce
+//   P3  logits -> softmax-CE -> dZ3 (every CTA)        dW3_j = H2_j^T dZ3 ; dH2_j = dZ3 W3_j^T
+//       dZ2_j = dH2_j * (H2_j > 0)                                                    -> all-gather
+//   P4  dW2_j = H1_j^T dZ2 ; dH1_j = dZ2 W2_j^T ; dZ1_j = dH1_j * (H1_j > 0)          -> all-gather
+//   P5  dW1_j = X_j^T dZ1
+//
+// Every product is a tcgen05.mma (kind::tf32, M=128, accumulator in TMEM); weights and inputs come
+// in by TMA, activations / gradients are written to shared memory by the epilogue threads in the
+// canonical swizzled layouts the MMA descriptors expect. Gradients leave in the flat parameter
+// layout; the all-reduce + average + SGD kernel (collectives.cu) follows as usual.
+//
+// Reference math: DSML/client/client.go:112-202 (forward, softmax-CE, backward).
+// Supported shapes: batch <= 64 (multiple of 8), in0 % 8 == 0 and <= 832, H1 = 128, H2 in {64, none},
+// classes <= 16. Anything else uses the per-layer kernels.
+#include "common.h"
+#include "ptx_sm100.cuh"
+
+#include <stdlib.h>
+#include <string.h>
+
+#include <new>
+
+namespace dmlp {
+
+int make_tensor_map_2d(CUtensorMap* out, const void* base, int elem_bytes, bool is_bf16, uint64_t cols,
+                       uint64_t rows, uint64_t ld_elems, uint32_t box_cols, uint32_t box_rows, int swizzle);
+
+constexpr int kFC = 8;          // CTAs per cluster (one cluster per step)
+constexpr int kFThreads = 160;  // warp 0: TMA + MMA issue; warps 1..4: one thread per batch row
+constexpr int kFBK = 64;        // batch rows a tile holds
+constexpr int kKGroupsMax = 13; // 8-float K groups of layer 1 per CTA (784/8 = 98 groups over 8 CTAs)
+
+struct FusedParams {
+  int B, in0, C;
+  const float* params;
+  float* grads;
+  unsigned long long w_off[3], b_off[3];
+  const int* labels;
+  float* metrics;  // [0] loss sum, [1] hit count (int bits)
+  float* dbg;      // optional dump of intermediates (tests)
+};
+
+// ---- shared-memory map (bytes). A-operand tiles are written for 64 rows (8 KiB per 128-byte-wide
+// K block); the MMA reads 128 rows, i.e. 8 KiB past each tile: whatever follows it, harmlessly.
+constexpr uint32_t kTileK = 8192;                      // K-major tile: 64 rows x 128 B
+constexpr uint32_t kColM = kFBK * 128;                 // MN-major atom column: 64 K-rows x 128 B
+constexpr uint32_t kW1Col = kKGroupsMax * 8 * 128;     // W1 slice atom column: 104 K-rows x 128 B
+constexpr uint32_t oXA = 0;                            // 4 K blocks (P0)            | RS2, DZ2K later
+constexpr uint32_t oW1B = oXA + 4 * kTileK;            // 4 atoms x 13 KiB (P0)      | AR3, DZ2M, DZ1M later
+constexpr uint32_t oRS1 = oW1B + 4 * kW1Col;           // 8 src x 64 rows x 64 B     | H2K, DZ3K, H2M, DZ3M later
+constexpr uint32_t oXT = oRS1 + 8 * 64 * 64;           // 4 atoms x 8 KiB (used in P5)
+constexpr uint32_t oH1K = oXT + 4 * kColM;
+constexpr uint32_t oH1M = oH1K + kTileK;
+constexpr uint32_t oW2B = oH1M + kColM;                // 2 atoms x 16 rows x 128 B (+ slack)
+constexpr uint32_t oW2K = oW2B + 4096;                 // 2 K blocks x 32 rows x 128 B
+constexpr uint32_t oWLB = oW2K + 8192;
+constexpr uint32_t oWLK = oWLB + 4096;
+constexpr uint32_t oRED = oWLK + 4096;                 // reductions scratch
+constexpr uint32_t oEND = oRED + 4096;
+constexpr uint32_t kFusedSmem = oEND + 32768 + 1024;   // slack: MMA over-read of MN-major A atoms + alignment
+// aliases (lifetimes are disjoint, see the phase table in the header comment)
+constexpr uint32_t oRS2 = oXA;                         // 8 src x 64 rows x 32 B = 16 KiB
+constexpr uint32_t oDZ2K = oXA + 16384;                // 2 K blocks x 8 KiB
+constexpr uint32_t oAR3 = oW1B;                        // 8 src x 64 rows x 64 B = 32 KiB
+constexpr uint32_t oDZ2M = oW1B + 32768;               // 2 atoms x 8 KiB
+constexpr uint32_t oDZ1M = oW1B;                       // 4 atoms x 8 KiB
+constexpr uint32_t oH2K = oRS1;
+constexpr uint32_t oDZ3K = oRS1 + 8192;
+constexpr uint32_t oH2M = oRS1 + 16384;
+constexpr uint32_t oDZ3M = oRS1 + 24576;
+static_assert(kFusedSmem <= 227 * 1024, "fused step does not fit in shared memory");
+
+// TMEM columns
+constexpr uint32_t cF1 = 0, cF2 = 128, cF3 = 192, cWGL = 208, cDGL = 224, cWG2 = 256, cDG2 = 320, cWG1 = 384;
+
+// ---- layouts written by threads -------------------------------------------------------------
+// K-major, SWIZZLE_128B: row r (batch), element k (< 32 per 128-byte block).
+__device__ __forceinline__ uint32_t koff(int r, int k) {
+  return (k >> 5) * kTileK + (r >> 3) * 1024 + (r & 7) * 128 + ((((k & 31) >> 2) ^ (r & 7)) << 4) + (k & 3) * 4;
+}
+// MN-major, SWIZZLE_128B_BASE32B: K-row r (batch), MN element n (32 per atom column of kColM bytes).
+__device__ __forceinline__ uint32_t moff(int r, int n) {
+  return (n >> 5) * kColM + r * 128 + ((((n & 31) >> 3) ^ (r & 3)) << 5) + (n & 7) * 4;
+}
+__device__ __forceinline__ uint32_t mapa(uint32_t a, uint32_t cta) {
+  uint32_t r;
+  asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(r) : "r"(a), "r"(cta));
+  return r;
+}
+__device__ __forceinline__ void st_cluster_f4(uint32_t a, float x, float y, float z, float w) {
+  asm volatile("st.shared::cluster.v4.f32 [%0], {%1, %2, %3, %4};" ::"r"(a), "f"(x), "f"(y), "f"(z), "f"(w) : "memory");
+}
+__device__ __forceinline__ void cluster_sync_all() {
+  asm volatile("barrier.cluster.arrive.release.aligned;\n\tbarrier.cluster.wait.acquire.aligned;" ::: "memory");
+}
+__device__ __forceinline__ uint32_t cluster_ctarank() {
+  uint32_t r;
+  asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(r));
+  return r;
+}
+__device__ __forceinline__ void tmem_ld_x8(uint32_t taddr, uint32_t (&r)[8]) {
+  asm volatile("tcgen05.ld.sync.aligned.32x32b.x8.b32 {%0, %1, %2, %3, %4, %5, %6, %7}, [%8];"
+               : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7])
+               : "r"(taddr) : "memory");
+}
+__device__ __forceinline__ uint64_t kdesc(uint32_t tile, int kstep) {  // K-major A/B, 8 floats per step
+  return make_smem_desc(tile + (kstep >> 2) * kTileK + (kstep & 3) * 32, 16, 1024, 2);
+}
+__device__ __forceinline__ uint64_t mdesc(uint32_t tile, int kstep, uint32_t col_bytes) {  // MN-major, 8 K-rows per step
+  return make_smem_desc(tile + kstep * 1024, col_bytes, 512, 1);
+}
+
+// Column sums over the batch rows held one-per-thread by the 128 worker threads; result (n <= 16
+// columns) is valid in the first n worker threads of worker-warp 0.
+template <int N>
+__device__ __forceinline__ void worker_colsum(const float (&v)[N], float* red, int wwarp, int lane, float (&out)[1],
+                                              int& out_col) {
+#pragma unroll
+  for (int c = 0; c < N; ++c) {
+    float s = v[c];
+    s += __shfl_xor_sync(0xffffffffu, s, 16);
+    s += __shfl_xor_sync(0xffffffffu, s, 8);
+    s += __shfl_xor_sync(0xffffffffu, s, 4);
+    s += __shfl_xor_sync(0xffffffffu, s, 2);
+    s += __shfl_xor_sync(0xffffffffu, s, 1);
+    if (lane == c) red[wwarp * 32 + c] = s;
+  }
+  asm volatile("bar.sync 1, 128;" ::: "memory");
+  out_col = -1;
+  if (wwarp == 0 && lane < N) {
+    out[0] = red[lane] + red[32 + lane] + red[64 + lane] + red[96 + lane];
+    out_col = lane;
+  }
+  asm volatile("bar.sync 1, 128;" ::: "memory");
+}
+
+template <int S1, int S2>  // slice widths: H1/8 and H2/8 (S2 == 0: two-layer model)
+__global__ void __cluster_dims__(kFC, 1, 1) __launch_bounds__(kFThreads, 1)
+mlp_fused_step_kernel(const __grid_constant__ CUtensorMap tmXA, const __grid_constant__ CUtensorMap tmXT,
+                      const __grid_constant__ CUtensorMap tmW1, const __grid_constant__ CUtensorMap tmW2B,
+                      const __grid_constant__ CUtensorMap tmW2K, const __grid_constant__ CUtensorMap tmWLB,
+                      const __grid_constant__ CUtensorMap tmWLK, const FusedParams p) {
+  constexpr int H1 = S1 * kFC;
+  constexpr int H2 = S2 * kFC;
+  constexpr bool kMid = S2 > 0;
+  constexpr int SL = kMid ? S2 : S1;  // K-slice of the last layer
+  constexpr int LAST = kMid ? 2 : 1;
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~static_cast<uintptr_t>(1023));
+  const uint32_t sb = smem_u32(smem);
+  __shared__ __align__(8) uint64_t bar_tma0, bar_tma1, bar_mma;
+  __shared__ uint32_t tmem_slot;
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int j = static_cast<int>(cluster_ctarank());
+  const int B = p.B;
+  const int ngroups = p.in0 / 8;
+  const int g0 = (ngroups * j) / kFC, g1 = (ngroups * (j + 1)) / kFC;
+  const int k0 = g0 * 8, nk1 = g1 - g0;  // layer-1 K slice: floats [k0, k0 + 8*nk1)
+  const bool worker = warp >= 1;
+  const int wwarp = warp - 1;
+  const int row = (warp & 3) * 32 + lane;  // TMEM lane == batch row handled by this worker thread
+  const bool rok = worker && row < B;
+  float* red = reinterpret_cast<float*>(smem + oRED);
+  const uint32_t tq = (static_cast<uint32_t>((warp & 3) * 32) << 16);
+
+  if (threadIdx.x == 0) {
+    mbar_init(&bar_tma0, 1);
+    mbar_init(&bar_tma1, 1);
+    mbar_init(&bar_mma, 1);
+    fence_mbar_init();
+  }
+  if (warp == 0) {
+    tmem_alloc(&tmem_slot, 512);
+    tmem_relinquish();
+  }
+  tc_fence_before_sync();
+  __syncthreads();
+  tc_fence_after_sync();
+  const uint32_t tm = tmem_slot;
+  uint32_t mma_phase = 0;
+  cluster_sync_all();  // every CTA's shared memory is live before anyone writes into it
+
+  // ------------------------------------------------------------------ P0: loads + layer-1 partial
+  if (threadIdx.x == 0) {
+    mbar_arrive_expect_tx(&bar_tma0, 4 * kTileK + (H1 / 32) * kW1Col);
+    for (int b = 0; b < 4; ++b) tma_load_2d(smem + oXA + b * kTileK, &tmXA, &bar_tma0, k0 + 32 * b, 0);
+    for (int a = 0; a < H1 / 32; ++a) tma_load_2d(smem + oW1B + a * kW1Col, &tmW1, &bar_tma0, 32 * a, k0);
+    uint32_t bytes1 = 4 * kColM + 2 * SL * 128;
+    if (kMid) bytes1 += (H2 / 32) * S1 * 128 + (H2 / 32) * S1 * 128;
+    mbar_arrive_expect_tx(&bar_tma1, bytes1);
+    for (int a = 0; a < 4; ++a) tma_load_2d(smem + oXT + a * kColM, &tmXT, &bar_tma1, k0 + 32 * a, 0);
+    if (kMid) {
+      for (int a = 0; a < H2 / 32; ++a) tma_load_2d(smem + oW2B + a * S1 * 128, &tmW2B, &bar_tma1, 32 * a, S1 * j);
+      for (int kb = 0; kb < H2 / 32; ++kb) tma_load_2d(smem + oW2K + kb * 4096, &tmW2K, &bar_tma1, 32 * kb, S1 * j);
+    }
+    tma_load_2d(smem + oWLB, &tmWLB, &bar_tma1, 0, SL * j);
+    tma_load_2d(smem + oWLK, &tmWLK, &bar_tma1, 0, SL * j);
+    mbar_wait(&bar_tma0, 0);
+    tc_fence_after_sync();
+    const uint32_t idesc = make_instr_desc(4, false, true, H1);
+    for (int t = 0; t < nk1; ++t)
+      tc_mma<4>(tm + cF1, kdesc(sb + oXA, t), mdesc(sb + oW1B, t, kW1Col), idesc, t != 0);
+    tc_commit(&bar_mma);
+  }
+  float h1[S1];
+  float h2[kMid ? S2 : 1];
+  if (worker) {
+    mbar_wait(&bar_mma, mma_phase);
+    tc_fence_after_sync();
+    // reduce-scatter: columns [S1*i, S1*i+S1) of my partial go to CTA i
+#pragma unroll
+    for (int i = 0; i < kFC; ++i) {
+      uint32_t r[16];
+      static_assert(S1 == 16, "layer-1 slice width");
+      tmem_ld_x16(tm + tq + cF1 + S1 * i, r);
+      tmem_ld_wait();
+      if (rok) {
+        const uint32_t dst = mapa(sb + oRS1 + (j * 64 + row) * (S1 * 4), i);
+#pragma unroll
+        for (int c = 0; c < S1; c += 4)
+          st_cluster_f4(dst + c * 4, __uint_as_float(r[c]), __uint_as_float(r[c + 1]), __uint_as_float(r[c + 2]),
+                        __uint_as_float(r[c + 3]));
+      }
+    }
+  }
+  mma_phase ^= 1;
+  tc_fence_before_sync();
+  cluster_sync_all();
+  tc_fence_after_sync();
+
+  // ------------------------------------------------------------------ P1: H1_j, layer-2 partial
+  if (worker) {
+#pragma unroll
+    for (int c = 0; c < S1; ++c) h1[c] = 0.f;
+    if (rok) {
+      for (int s = 0; s < kFC; ++s) {  // fixed order: deterministic sums
+        const float4* src = reinterpret_cast<const float4*>(smem + oRS1 + (s * 64 + row) * (S1 * 4));
+#pragma unroll
+        for (int c = 0; c < S1; c += 4) {
+          const float4 v = src[c >> 2];
+          h1[c] += v.x; h1[c + 1] += v.y; h1[c + 2] += v.z; h1[c + 3] += v.w;
+        }
+      }
+      const float* b1 = p.params + p.b_off[0] + S1 * j;
+#pragma unroll
+      for (int c = 0; c < S1; ++c) h1[c] = fmaxf(h1[c] + __ldg(b1 + c), 0.f);
+#pragma unroll
+      for (int c = 0; c < S1; c += 4) {
+        *reinterpret_cast<float4*>(smem + oH1K + koff(row, c)) = make_float4(h1[c], h1[c + 1], h1[c + 2], h1[c + 3]);
+        *reinterpret_cast<float4*>(smem + oH1M + moff(row, c)) = make_float4(h1[c], h1[c + 1], h1[c + 2], h1[c + 3]);
+      }
+      if (p.dbg)
+        for (int c = 0; c < S1; ++c) p.dbg[row * H1 + S1 * j + c] = h1[c];
+    }
+    fence_proxy_async_smem();
+  }
+  __syncthreads();
+  if (kMid) {
+    if (threadIdx.x == 0) {
+      mbar_wait(&bar_tma1, 0);
+      fence_proxy_async_smem();
+      tc_fence_after_sync();
+      const uint32_t idesc = make_instr_desc(4, false, true, H2);
+      for (int t = 0; t < S1 / 8; ++t)
+        tc_mma<4>(tm + cF2, kdesc(sb + oH1K, t), mdesc(sb + oW2B, t, S1 * 128), idesc, t != 0);
+      tc_commit(&bar_mma);
+    }
+    if (worker) {
+      mbar_wait(&bar_mma, mma_phase);
+      tc_fence_after_sync();
+#pragma unroll
+      for (int i = 0; i < kFC; ++i) {
+        uint32_t r[8];
+        tmem_ld_x8(tm + tq + cF2 + S2 * i, r);
+        tmem_ld_wait();
+        if (rok) {
+          const uint32_t dst = mapa(sb + oRS2 + (j * 64 + row) * (S2 * 4), i);
+          st_cluster_f4(dst, __uint_as_float(r[0]), __uint_as_float(r[1]), __uint_as_float(r[2]), __uint_as_float(r[3]));
+          st_cluster_f4(dst + 16, __uint_as_float(r[4]), __uint_as_float(r[5]), __uint_as_float(r[6]), __uint_as_float(r[7]));
+        }
+      }
+    }
+    mma_phase ^= 1;
+    tc_fence_before_sync();
+    cluster_sync_all();
+    tc_fence_after_sync();
+    // ---------------------------------------------------------------- P2: H2_j
+    if (worker) {
+#pragma unroll
+      for (int c = 0; c < S2; ++c) h2[c] = 0.f;
+      if (rok) {
+        for (int s = 0; s < kFC; ++s) {
+          const float4* src = reinterpret_cast<const float4*>(smem + oRS2 + (s * 64 + row) * (S2 * 4));
+#pragma unroll
+          for (int c = 0; c < S2; c += 4) {
+            const float4 v = src[c >> 2];
+            h2[c] += v.x; h2[c + 1] += v.y; h2[c + 2] += v.z; h2[c + 3] += v.w;
+          }
+        }
+        const float* b2 = p.params + p.b_off[1] + S2 * j;
+#pragma unroll
+        for (int c = 0; c < S2; ++c) h2[c] = fmaxf(h2[c] + __ldg(b2 + c), 0.f);
+#pragma unroll
+        for (int c = 0; c < S2; c += 4) {
+          *reinterpret_cast<float4*>(smem + oH2K + koff(row, c)) = make_float4(h2[c], h2[c + 1], h2[c + 2], h2[c + 3]);
+          *reinterpret_cast<float4*>(smem + oH2M + moff(row, c)) = make_float4(h2[c], h2[c + 1], h2[c + 2], h2[c + 3]);
+        }
+        if (p.dbg)
+          for (int c = 0; c < S2; ++c) p.dbg[64 * H1 + row * H2 + S2 * j + c] = h2[c];
+      }
+      fence_proxy_async_smem();
+    }
+    __syncthreads();
+  }
+  // ------------------------------------------------------------------ last layer partial -> all-reduce
+  const uint32_t oHLK = kMid ? oH2K : oH1K;
+  const uint32_t oHLM = kMid ? oH2M : oH1M;
+  if (threadIdx.x == 0) {
+    if (!kMid) mbar_wait(&bar_tma1, 0);
+    fence_proxy_async_smem();
+    tc_fence_after_sync();
+    const uint32_t idesc = make_instr_desc(4, false, true, 16);
+    for (int t = 0; t < SL / 8; ++t)
+      tc_mma<4>(tm + cF3, kdesc(sb + oHLK, t), mdesc(sb + oWLB, t, SL * 128), idesc, t != 0);
+    tc_commit(&bar_mma);
+  }
+  if (worker) {
+    mbar_wait(&bar_mma, mma_phase);
+    tc_fence_after_sync();
+    uint32_t r[16];
+    tmem_ld_x16(tm + tq + cF3, r);
+    tmem_ld_wait();
+    if (rok) {
+#pragma unroll
+      for (int i = 0; i < kFC; ++i) {
+        const uint32_t dst = mapa(sb + oAR3 + (j * 64 + row) * 64, i);
+#pragma unroll
+        for (int c = 0; c < 16; c += 4)
+          st_cluster_f4(dst + c * 4, __uint_as_float(r[c]), __uint_as_float(r[c + 1]), __uint_as_float(r[c + 2]),
+                        __uint_as_float(r[c + 3]));
+      }
+    }
+  }
+  mma_phase ^= 1;
+  tc_fence_before_sync();
+  cluster_sync_all();
+  tc_fence_after_sync();
+
+  // ------------------------------------------------------------------ P3: softmax-CE, last-layer grads
+  float dz3[16];
+  if (worker) {
+    float z[16];
+#pragma unroll
+    for (int c = 0; c < 16; ++c) z[c] = 0.f;
+    float loss = 0.f;
+    int hit = 0;
+    if (rok) {
+      for (int s = 0; s < kFC; ++s) {
+        const float4* src = reinterpret_cast<const float4*>(smem + oAR3 + (s * 64 + row) * 64);
+#pragma unroll
+        for (int c = 0; c < 16; c += 4) {
+          const float4 v = src[c >> 2];
+          z[c] += v.x; z[c + 1] += v.y; z[c + 2] += v.z; z[c + 3] += v.w;
+        }
+      }
+      const float* bl = p.params + p.b_off[LAST];
+      float mx = -INFINITY;
+      int arg = 0;
+#pragma unroll
+      for (int c = 0; c < 16; ++c) {
+        z[c] += __ldg(bl + c);
+        if (c < p.C && z[c] > mx) { mx = z[c]; arg = c; }
+      }
+      float sum = 0.f;
+#pragma unroll
+      for (int c = 0; c < 16; ++c) {
+        z[c] = (c < p.C) ? __expf(z[c] - mx) : 0.f;
+        sum += z[c];
+      }
+      const float inv = 1.f / sum;
+      const int y = p.labels[row];
+      const float scale = 1.f / static_cast<float>(B);
+#pragma unroll
+      for (int c = 0; c < 16; ++c) {
+        const float pr = z[c] * inv;
+        if (c == y) loss = -__logf(pr + 1e-10f);
+        dz3[c] = (c < p.C) ? (pr - (c == y ? 1.f : 0.f)) * scale : 0.f;
+      }
+      hit = (arg == y) ? 1 : 0;
+#pragma unroll
+      for (int c = 0; c < 16; c += 4) {
+        *reinterpret_cast<float4*>(smem + oDZ3K + koff(row, c)) = make_float4(dz3[c], dz3[c + 1], dz3[c + 2], dz3[c + 3]);
+        *reinterpret_cast<float4*>(smem + oDZ3M + moff(row, c)) = make_float4(dz3[c], dz3[c + 1], dz3[c + 2], dz3[c + 3]);
+      }
+      if (p.dbg && j == 0)
+        for (int c = 0; c < 16; ++c) p.dbg[64 * H1 + 64 * (kMid ? H2 : 0) + row * 16 + c] = dz3[c];
+    } else {
+#pragma unroll
+      for (int c = 0; c < 16; ++c) dz3[c] = 0.f;
+    }
+    fence_proxy_async_smem();
+    if (j == 0) {  // loss, hits and the last bias gradient are produced once (CTA 0)
+      float bsum[1];
+      int col;
+      worker_colsum<16>(dz3, red, wwarp, lane, bsum, col);
+      if (col >= 0) p.grads[p.b_off[LAST] + col] = bsum[0];
+#pragma unroll
+      for (int o = 16; o > 0; o >>= 1) {
+        loss += __shfl_xor_sync(0xffffffffu, loss, o);
+        hit += __shfl_xor_sync(0xffffffffu, hit, o);
+      }
+      if (lane == 0) { red[wwarp] = loss; reinterpret_cast<int*>(red)[8 + wwarp] = hit; }
+      asm volatile("bar.sync 1, 128;" ::: "memory");
+      if (wwarp == 0 && lane == 0) {
+        p.metrics[0] = red[0] + red[1] + red[2] + red[3];
+        reinterpret_cast<int*>(p.metrics)[1] = reinterpret_cast<int*>(red)[8] + reinterpret_cast<int*>(red)[9] +
+                                               reinterpret_cast<int*>(red)[10] + reinterpret_cast<int*>(red)[11];
+      }
+      asm volatile("bar.sync 1, 128;" ::: "memory");
+    }
+  }
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    fence_proxy_async_smem();
+    tc_fence_after_sync();
+    // dW_last[SL x 16] = HL_j^T . dZ3   (A and B MN-major, K = batch)
+    const uint32_t idw = make_instr_desc(4, true, true, 16);
+    for (int t = 0; t < B / 8; ++t)
+      tc_mma<4>(tm + cWGL, mdesc(sb + oHLM, t, kColM), mdesc(sb + oDZ3M, t, kColM), idw, t != 0);
+    // dHL_j[B x SL] = dZ3 . W_last_j^T  (A and B K-major, K = 16)
+    const uint32_t idg = make_instr_desc(4, false, false, 16);
+    for (int t = 0; t < 2; ++t) tc_mma<4>(tm + cDGL, kdesc(sb + oDZ3K, t), kdesc(sb + oWLK, t), idg, t != 0);
+    tc_commit(&bar_mma);
+  }
+  float dzl[SL];
+  if (worker) {
+    mbar_wait(&bar_mma, mma_phase);
+    tc_fence_after_sync();
+    {
+      uint32_t r[16];
+      tmem_ld_x16(tm + tq + cWGL, r);
+      tmem_ld_wait();
+      if (row < SL) {
+        float4* g = reinterpret_cast<float4*>(p.grads + p.w_off[LAST] + static_cast<size_t>(SL * j + row) * 16);
+#pragma unroll
+        for (int c = 0; c < 16; c += 4)
+          g[c >> 2] = make_float4(__uint_as_float(r[c]), __uint_as_float(r[c + 1]), __uint_as_float(r[c + 2]), __uint_as_float(r[c + 3]));
+      }
+    }
+    {
+      uint32_t r[16];
+      tmem_ld_x16(tm + tq + cDGL, r);
+      tmem_ld_wait();
+#pragma unroll
+      for (int c = 0; c < SL; ++c) {
+        const float hl = kMid ? h2[kMid ? c : 0] : h1[kMid ? 0 : c];
+        dzl[c] = (rok && hl > 0.f) ? __uint_as_float(r[c]) : 0.f;
+      }
+    }
+    // bias gradient of the layer that produced HL
+    {
+      float bsum[1];
+      int col;
+      worker_colsum<SL>(dzl, red, wwarp, lane, bsum, col);
+      if (col >= 0) p.grads[p.b_off[LAST - 1] + SL * j + col] = bsum[0];
+    }
+  }
+  mma_phase ^= 1;
+
+  float dz1[S1];
+  if (kMid) {
+    // all-gather dZ2_j (= dzl) into every CTA: K-major (A of dgrad2) and MN-major (B of wgrad2)
+    if (rok) {
+#pragma unroll
+      for (int i = 0; i < kFC; ++i) {
+        const uint32_t dk = mapa(sb + oDZ2K + koff(row, S2 * j), i);
+        const uint32_t dm = mapa(sb + oDZ2M + moff(row, S2 * j), i);
+        st_cluster_f4(dk, dzl[0], dzl[1], dzl[2], dzl[3]);
+        st_cluster_f4(mapa(sb + oDZ2K + koff(row, S2 * j + 4), i), dzl[4], dzl[5], dzl[6], dzl[7]);
+        st_cluster_f4(dm, dzl[0], dzl[1], dzl[2], dzl[3]);
+        st_cluster_f4(dm + 16, dzl[4], dzl[5], dzl[6], dzl[7]);
+      }
+      if (p.dbg)
+        for (int c = 0; c < S2; ++c) p.dbg[64 * H1 + 64 * H2 + 64 * 16 + row * H2 + S2 * j + c] = dzl[c];
+    }
+    fence_proxy_async_smem();
+    tc_fence_before_sync();
+    cluster_sync_all();
+    tc_fence_after_sync();
+    // ---------------------------------------------------------------- P4: layer-2 grads
+    if (threadIdx.x == 0) {
+      fence_proxy_async_smem();
+      const uint32_t idw = make_instr_desc(4, true, true, H2);
+      for (int t = 0; t < B / 8; ++t)
+        tc_mma<4>(tm + cWG2, mdesc(sb + oH1M, t, kColM), mdesc(sb + oDZ2M, t, kColM), idw, t != 0);
+      const uint32_t idg = make_instr_desc(4, false, false, 16);
+      for (int t = 0; t < H2 / 8; ++t)
+        tc_mma<4>(tm + cDG2, kdesc(sb + oDZ2K, t), make_smem_desc(sb + oW2K + (t >> 2) * 4096 + (t & 3) * 32, 16, 1024, 2), idg, t != 0);
+      tc_commit(&bar_mma);
+    }
+    if (worker) {
+      mbar_wait(&bar_mma, mma_phase);
+      tc_fence_after_sync();
+#pragma unroll
+      for (int cc = 0; cc < H2; cc += 16) {
+        uint32_t r[16];
+        tmem_ld_x16(tm + tq + cWG2 + cc, r);
+        tmem_ld_wait();
+        if (row < S1) {
+          float4* g = reinterpret_cast<float4*>(p.grads + p.w_off[1] + static_cast<size_t>(S1 * j + row) * H2 + cc);
+#pragma unroll
+          for (int c = 0; c < 16; c += 4)
+            g[c >> 2] = make_float4(__uint_as_float(r[c]), __uint_as_float(r[c + 1]), __uint_as_float(r[c + 2]), __uint_as_float(r[c + 3]));
+        }
+      }
+      uint32_t r[16];
+      tmem_ld_x16(tm + tq + cDG2, r);
+      tmem_ld_wait();
+#pragma unroll
+      for (int c = 0; c < S1; ++c) dz1[c] = (rok && h1[c] > 0.f) ? __uint_as_float(r[c]) : 0.f;
+      float bsum[1];
+      int col;
+      worker_colsum<S1>(dz1, red, wwarp, lane, bsum, col);
+      if (col >= 0) p.grads[p.b_off[0] + S1 * j + col] = bsum[0];
+    }
+    mma_phase ^= 1;
+  } else {
+#pragma unroll
+    for (int c = 0; c < S1; ++c) dz1[c] = dzl[kMid ? 0 : c];
+  }
+  // all-gather dZ1_j into every CTA (MN-major: B operand of the layer-1 weight gradient)
+  if (rok) {
+#pragma unroll
+    for (int i = 0; i < kFC; ++i) {
+      const uint32_t dm = mapa(sb + oDZ1M + moff(row, S1 * j), i);
+      st_cluster_f4(dm, dz1[0], dz1[1], dz1[2], dz1[3]);
+      st_cluster_f4(dm + 16, dz1[4], dz1[5], dz1[6], dz1[7]);
+      const uint32_t dm2 = mapa(sb + oDZ1M + moff(row, S1 * j + 8), i);
+      st_cluster_f4(dm2, dz1[8], dz1[9], dz1[10], dz1[11]);
+      st_cluster_f4(dm2 + 16, dz1[12], dz1[13], dz1[14], dz1[15]);
+    }
+    if (p.dbg)
+      for (int c = 0; c < S1; ++c) p.dbg[64 * H1 + 128 * (kMid ? H2 : 0) + 64 * 16 + row * H1 + S1 * j + c] = dz1[c];
+  }
+  fence_proxy_async_smem();
+  tc_fence_before_sync();
+  cluster_sync_all();
+  tc_fence_after_sync();
+
+  // ------------------------------------------------------------------ P5: dW1_j = X_j^T . dZ1
+  if (threadIdx.x == 0) {
+    fence_proxy_async_smem();
+    const uint32_t idw = make_instr_desc(4, true, true, H1);
+    for (int t = 0; t < B / 8; ++t)
+      tc_mma<4>(tm + cWG1, mdesc(sb + oXT, t, kColM), mdesc(sb + oDZ1M, t, kColM), idw, t != 0);
+    tc_commit(&bar_mma);
+  }
+  if (worker) {
+    mbar_wait(&bar_mma, mma_phase);
+    tc_fence_after_sync();
+#pragma unroll
+    for (int cc = 0; cc < H1; cc += 16) {
+      uint32_t r[16];
+      tmem_ld_x16(tm + tq + cWG1 + cc, r);
+      tmem_ld_wait();
+      if (row < nk1 * 8) {
+        float4* g = reinterpret_cast<float4*>(p.grads + p.w_off[0] + static_cast<size_t>(k0 + row) * H1 + cc);
+#pragma unroll
+        for (int c = 0; c < 16; c += 4)
+          g[c >> 2] = make_float4(__uint_as_float(r[c]), __uint_as_float(r[c + 1]), __uint_as_float(r[c + 2]), __uint_as_float(r[c + 3]));
+      }
+    }
+  }
+  tc_fence_before_sync();
+  __syncthreads();
+  cluster_sync_all();  // nobody leaves while a peer could still be writing into its shared memory
+  if (warp == 0) {
+    tc_fence_after_sync();
+    tmem_dealloc(tm, 512);
+  }
+}
+
+struct FusedPlan {
+  CUtensorMap tmXA, tmXT, tmW1, tmW2B, tmW2K, tmWLB, tmWLK;
+  FusedParams p;
+  int layers;
+};
+
+}  // namespace dmlp
+
+using namespace dmlp;
+
+extern "C" int dmlp_mlp_fused_supported(int num_layers, const int* dims, int batch) {
+  if (num_layers != 2 && num_layers != 3) return 0;
+  if (batch < 8 || batch > 64 || batch % 8) return 0;
+  if (dims[0] % 8 || dims[0] > 832 || dims[0] < 64) return 0;
+  if (dims[1] != 128) return 0;
+  if (num_layers == 3 && dims[2] != 64) return 0;
+  if (dims[num_layers] > 16) return 0;
+  return 1;
+}
+
+extern "C" int dmlp_mlp_fused_plan_create(const dmlp_mlp_fused_desc_t* d, dmlp_mlp_fused_plan_t* out) {
+  DMLP_REQUIRE(d && out, "dmlp_mlp_fused_plan_create: null argument");
+  DMLP_REQUIRE(dmlp_mlp_fused_supported(d->num_layers, d->dims, d->batch),
+               "fused step supports batch<=64 (x8), in<=832 (x8), hidden 128[,64], classes<=16");
+  FusedPlan* pl = new (std::nothrow) FusedPlan();
+  if (!pl) return set_error(DMLP_ERR_CUDA, "out of host memory");
+  const int L = d->num_layers, in0 = d->dims[0], H1 = d->dims[1], H2 = L == 3 ? d->dims[2] : 0;
+  const int SL = L == 3 ? H2 / 8 : H1 / 8;
+  const float* P = d->params_dev;
+  int rc = 0;
+#define MK(expr) do { rc = (expr); if (rc) { delete pl; return rc; } } while (0)
+  // X as K-major A (forward) and as MN-major A (layer-1 weight gradient)
+  MK(make_tensor_map_2d(&pl->tmXA, d->x_dev, 4, false, in0, d->batch, in0, 32, kFBK, 1));
+  MK(make_tensor_map_2d(&pl->tmXT, d->x_dev, 4, false, in0, d->batch, in0, 32, kFBK, 2));
+  MK(make_tensor_map_2d(&pl->tmW1, P + d->w_off[0], 4, false, H1, in0, H1, 32, kKGroupsMax * 8, 2));
+  const int last = L - 1;
+  if (L == 3) {
+    MK(make_tensor_map_2d(&pl->tmW2B, P + d->w_off[1], 4, false, H2, H1, H2, 32, H1 / 8, 2));
+    MK(make_tensor_map_2d(&pl->tmW2K, P + d->w_off[1], 4, false, H2, H1, H2, 32, H1 / 8, 1));
+  } else {
+    pl->tmW2B = pl->tmW1;
+    pl->tmW2K = pl->tmW1;
+  }
+  const int HL = L == 3 ? H2 : H1;
+  MK(make_tensor_map_2d(&pl->tmWLB, P + d->w_off[last], 4, false, 16, HL, 16, 32, SL, 2));
+  MK(make_tensor_map_2d(&pl->tmWLK, P + d->w_off[last], 4, false, 16, HL, 16, 32, SL, 1));
+#undef MK
+  FusedParams& p = pl->p;
+  memset(&p, 0, sizeof(p));
+  p.B = d->batch; p.in0 = in0; p.C = d->dims[L];
+  p.params = P; p.grads = d->grads_dev;
+  for (int l = 0; l < L; ++l) { p.w_off[l] = d->w_off[l]; p.b_off[l] = d->b_off[l]; }
+  p.labels = d->labels_dev;
+  p.metrics = d->metrics_dev;
+  p.dbg = d->debug_dev;
+  pl->layers = L;
+  *out = reinterpret_cast<dmlp_mlp_fused_plan_t>(pl);
+  return DMLP_OK;
+}
+
+extern "C" int dmlp_mlp_fused_plan_destroy(dmlp_mlp_fused_plan_t h) {
+  delete reinterpret_cast<FusedPlan*>(h);
+  return DMLP_OK;
+}
+
+template <int S1, int S2>
+static int launch_fused(const FusedPlan* pl, cudaStream_t st) {
+  auto kern = mlp_fused_step_kernel<S1, S2>;
+  static unsigned long long attr_mask = 0;
+  int dev = 0;
+  DMLP_CUDA_CHECK(cudaGetDevice(&dev));
+  if (!(attr_mask & (1ull << dev))) {
+    DMLP_CUDA_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, kFusedSmem));
+    attr_mask |= 1ull << dev;
+  }
+  kern<<<dim3(kFC), kFThreads, kFusedSmem, st>>>(pl->tmXA, pl->tmXT, pl->tmW1, pl->tmW2B, pl->tmW2K, pl->tmWLB,
+                                                  pl->tmWLK, pl->p);
+  DMLP_CUDA_CHECK(cudaGetLastError());
+  return DMLP_OK;
+}
+
+extern "C" int dmlp_mlp_fused_step(dmlp_mlp_fused_plan_t h, void* stream) {
+  const FusedPlan* pl = reinterpret_cast<const FusedPlan*>(h);
+  DMLP_REQUIRE(pl, "null fused plan");
+  if (pl->layers == 3) return launch_fused<16, 8>(pl, as_stream(stream));
+  return launch_fused<16, 0>(pl, as_stream(stream));
+}

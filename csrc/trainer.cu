@@ -85,6 +85,8 @@ struct Trainer {
   cudaGraph_t graph[2] = {nullptr, nullptr};
   cudaGraphExec_t gexec[2] = {nullptr, nullptr};
   GemmPlan fwd[2][kMaxLayers], wgrad[2][kMaxLayers], dgrad[kMaxLayers], fwd_eval_last;
+  bool fused_step = false;  // whole fwd+loss+bwd in one cluster launch (mlp_fused.cu)
+  dmlp_mlp_fused_plan_t fplan[2] = {nullptr, nullptr};
   bool fused_ce = false;   // softmax-CE runs in the last forward GEMM's epilogue
   bool direct = false;     // batch fits one M tile: reductions are stored, no zeroing needed
   cudaStream_t s_aux = nullptr;  // wgrad branch (runs beside the dgrad chain)
@@ -175,6 +177,22 @@ static int build_plans(Trainer* t) {
     d.colsum_dev = t->grads[0] + L.b_off[l - 1];  // patched per parity in enqueue_step
     TRY(gemm_plan_create(&d, &t->dgrad[l]));
   }
+  if (t->fused_step) {
+    for (int par = 0; par < 2; ++par) {
+      dmlp_mlp_fused_desc_t f;
+      memset(&f, 0, sizeof(f));
+      f.num_layers = L.L;
+      for (int l = 0; l <= L.L; ++l) f.dims[l] = t->cfg.dims[l];
+      f.batch = B;
+      f.x_dev = t->x[par];
+      f.labels_dev = t->labels[par];
+      f.params_dev = t->params;
+      f.grads_dev = t->grads[par];
+      for (int l = 0; l < L.L; ++l) { f.w_off[l] = L.w_off[l]; f.b_off[l] = L.b_off[l]; }
+      f.metrics_dev = t->metrics_dev[par];
+      TRY(dmlp_mlp_fused_plan_create(&f, &t->fplan[par]));
+    }
+  }
   return DMLP_OK;
 }
 
@@ -225,6 +243,17 @@ static int enqueue_step(Trainer* t, int par, bool count_kernels) {
   cudaStream_t S = t->s_main, A = t->s_aux;
   int nk = 0;
   const int last = L.L - 1;
+  if (t->fused_step) {
+    // one cluster launch produces every gradient, the loss and the hit count; then one kernel
+    // reduces + averages + applies SGD (or plain SGD on a single GPU)
+    TRY(dmlp_mlp_fused_step(t->fplan[par], S));
+    ++nk;
+    TRY(enqueue_allreduce(t, par, 0, L.total, S));
+    ++nk;
+    DMLP_CUDA_CHECK(cudaMemcpyAsync(t->metrics_host + 2 * par, t->metrics_dev[par], 8, cudaMemcpyDeviceToHost, S));
+    if (count_kernels) t->kernels_per_step = nk;
+    return DMLP_OK;
+  }
   if (!(t->fused_ce && t->direct)) DMLP_CUDA_CHECK(cudaMemsetAsync(t->metrics_dev[par], 0, 8, S));
   if (!t->direct)
     for (int l = 0; l < L.L; ++l)
@@ -352,6 +381,8 @@ extern "C" int dmlp_trainer_destroy(dmlp_trainer_t h) {
   if (t->s_comm) cudaStreamDestroy(t->s_comm);
   if (t->s_copy) cudaStreamDestroy(t->s_copy);
   if (t->s_aux) cudaStreamDestroy(t->s_aux);
+  for (int p = 0; p < 2; ++p)
+    if (t->fplan[p]) dmlp_mlp_fused_plan_destroy(t->fplan[p]);
   for (void* p : t->owned) cudaFree(p);
   if (t->metrics_host) cudaFreeHost(t->metrics_host);
   if (t->lr_host) cudaFreeHost(t->lr_host);
@@ -395,6 +426,12 @@ extern "C" int dmlp_trainer_create(const dmlp_trainer_config_t* cfg, int device,
   const ParamLayout& L = t->lay;
   const int B = cfg->batch;
   t->fused_ce = L.out_pad[L.L - 1] <= 32;
+  t->fused_step = !t->bf16 && cfg->fused != 0 && dmlp_mlp_fused_supported(cfg->num_layers, cfg->dims, cfg->batch) != 0;
+  if (cfg->fused == 1 && !t->fused_step) {
+    set_error(DMLP_ERR_UNSUPPORTED, "fused step kernel does not support this shape / precision");
+    delete t;
+    return DMLP_ERR_UNSUPPORTED;
+  }
   t->direct = B <= 128;
   memset(t->ev_dz, 0, sizeof(t->ev_dz));
   t->ev_aux_done = nullptr;

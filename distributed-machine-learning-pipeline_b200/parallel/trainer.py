@@ -31,7 +31,7 @@ log = logging.getLogger("dmlp.trainer")
 class _NativeCfg(C.Structure):
     _fields_ = [("num_layers", C.c_int), ("dims", C.c_int * 9), ("batch", C.c_int), ("dtype", C.c_int),
                 ("lr", C.c_float), ("allreduce_algo", C.c_int), ("overlap", C.c_int),
-                ("nvls_uc", C.c_void_p), ("nvls_mc", C.c_void_p), ("nvls_bytes", C.c_size_t)]
+                ("nvls_uc", C.c_void_p), ("nvls_mc", C.c_void_p), ("nvls_bytes", C.c_size_t), ("fused", C.c_int)]
 
 
 @dataclass
@@ -43,6 +43,7 @@ class TrainerConfig:
     allreduce: str = "auto"                    # auto | oneshot | twoshot | ring | nvls (falls back to auto if unavailable)
     overlap: bool = False                      # per-layer buckets reduced during backward
     use_graph: bool = True
+    fused: int = -1                            # cluster-fused step kernel: -1 auto, 0 off, 1 require
     schedule: str = "constant"
     seed: int = 0
     watchdog_ms: int = 10000
@@ -57,6 +58,7 @@ class TrainerConfig:
         c.dtype = native.BF16 if self.precision == "bf16" else native.F32
         c.allreduce_algo = native.ALGO_BY_NAME[self.allreduce]
         c.overlap = int(self.overlap)
+        c.fused = int(self.fused)
         return c
 
 

@@ -274,6 +274,30 @@ int dmlp_allreduce_nvls(dmlp_comm_t comm, int local_idx, const dmlp_nvls_allredu
 int dmlp_allreduce_sum_f32_noalloc(int world, const float* const* in_dev, float* const* out_dev,
                                    size_t count, void* stream);
 
+/* ------------------------------------------------------------------ cluster-fused MLP step
+ * Forward + softmax-CE + backward of one batch of the reference-sized MLP in ONE launch of an 8-CTA
+ * thread-block cluster (K split across CTAs, partial sums exchanged through distributed shared
+ * memory, every product a tcgen05.mma). Reference: DSML/client/client.go:112-202.
+ * Shapes: batch <= 64 (x8), dims[0] % 8 == 0 and <= 832, dims[1] == 128, optional dims[2] == 64,
+ * classes <= 16. Writes all gradients (flat parameter layout), loss sum and hit count. */
+typedef struct {
+  int num_layers;            /* 2 or 3 */
+  int dims[4];
+  int batch;
+  const float* x_dev;        /* [batch][dims[0]] */
+  const int32_t* labels_dev;
+  const float* params_dev;   /* flat parameters (see trainer layout) */
+  float* grads_dev;          /* flat gradients, same layout */
+  size_t w_off[3], b_off[3]; /* in floats */
+  float* metrics_dev;        /* [0] loss sum (float), [1] hit count (int32) */
+  float* debug_dev;          /* optional dump of intermediates */
+} dmlp_mlp_fused_desc_t;
+typedef struct dmlp_mlp_fused_opaque* dmlp_mlp_fused_plan_t;
+int dmlp_mlp_fused_supported(int num_layers, const int* dims, int batch);
+int dmlp_mlp_fused_plan_create(const dmlp_mlp_fused_desc_t* desc, dmlp_mlp_fused_plan_t* out);
+int dmlp_mlp_fused_plan_destroy(dmlp_mlp_fused_plan_t plan);
+int dmlp_mlp_fused_step(dmlp_mlp_fused_plan_t plan, void* stream);
+
 /* ------------------------------------------------------------------ native data-parallel MLP trainer
  * Reference: the client's model, step and epoch loop (DSML/client/client.go:22-58 model/init,
  * :112-202 forward/backward, :254-267 SGD, :462-502 eval, :516-659 training loop).
@@ -297,6 +321,7 @@ typedef struct {
   void* nvls_uc;                 /* allreduce_algo == DMLP_ALGO_NVLS: this rank's replica of the multicast-bound */
   void* nvls_mc;                 /* arena and its multicast address; params/grads/shadow are placed there */
   size_t nvls_bytes;
+  int fused;                     /* cluster-fused step kernel: -1 auto (when the shape allows), 0 off, 1 on */
 } dmlp_trainer_config_t;
 typedef struct dmlp_trainer_opaque* dmlp_trainer_t;
 
