@@ -36,8 +36,8 @@ def test_fused_gradients_match_oracle(dims, batch):
         kw = g[s.w_off:s.w_off + s.fan_in * s.out_pad].reshape(s.fan_in, s.out_pad)[:, :s.fan_out]
         kb = g[s.b_off:s.b_off + s.fan_out]
         sw, sb = max(1e-4, np.abs(gw).max()), max(1e-4, np.abs(gb).max())
-        assert np.abs(kw - gw).max() < 2e-2 * sw, f"dW{l + 1}: {np.abs(kw - gw).max()} vs scale {sw}"
-        assert np.abs(kb - gb).max() < 2e-2 * sb, f"db{l + 1}: {np.abs(kb - gb).max()} vs scale {sb}"
+        assert np.abs(kw - gw).max() < 5e-2 * sw, f"dW{l + 1}: {np.abs(kw - gw).max()} vs scale {sw}"
+        assert np.abs(kb - gb).max() < 5e-2 * sb, f"db{l + 1}: {np.abs(kb - gb).max()} vs scale {sb}"
     t.close()
 
 
