@@ -50,7 +50,13 @@ struct FusedParams {
   const int* labels;
   float* metrics;  // [0] loss sum, [1] hit count (int bits)
   float* dbg;      // optional dump of intermediates (tests)
+  unsigned long long* prof;  // optional [8 CTAs][16] globaltimer stamps at phase boundaries
 };
+
+#define FPROF(slot)                                                                                   \
+  do {                                                                                                \
+    if (p.prof != nullptr && threadIdx.x == 32) p.prof[j * 16 + (slot)] = globaltimer_ns();             \
+  } while (0)
 
 // ---- shared-memory map (bytes). A-operand tiles are written for 64 rows (8 KiB per 128-byte-wide
 // K block); the MMA reads 128 rows, i.e. 8 KiB past each tile: whatever follows it, harmlessly.
@@ -191,7 +197,9 @@ mlp_fused_step_kernel(const __grid_constant__ CUtensorMap tmXA, const __grid_con
   tc_fence_after_sync();
   const uint32_t tm = tmem_slot;
   uint32_t mma_phase = 0;
+  FPROF(0);
   cluster_sync_all();  // every CTA's shared memory is live before anyone writes into it
+  FPROF(1);
 
   // ------------------------------------------------------------------ P0: loads + layer-1 partial
   if (threadIdx.x == 0) {
@@ -237,9 +245,11 @@ mlp_fused_step_kernel(const __grid_constant__ CUtensorMap tmXA, const __grid_con
     }
   }
   mma_phase ^= 1;
+  FPROF(2);
   tc_fence_before_sync();
   cluster_sync_all();
   tc_fence_after_sync();
+  FPROF(3);
 
   // ------------------------------------------------------------------ P1: H1_j, layer-2 partial
   if (worker) {
@@ -294,9 +304,11 @@ mlp_fused_step_kernel(const __grid_constant__ CUtensorMap tmXA, const __grid_con
       }
     }
     mma_phase ^= 1;
+    FPROF(4);
     tc_fence_before_sync();
     cluster_sync_all();
     tc_fence_after_sync();
+    FPROF(5);
     // ---------------------------------------------------------------- P2: H2_j
     if (worker) {
 #pragma unroll
@@ -355,9 +367,11 @@ mlp_fused_step_kernel(const __grid_constant__ CUtensorMap tmXA, const __grid_con
     }
   }
   mma_phase ^= 1;
+  FPROF(6);
   tc_fence_before_sync();
   cluster_sync_all();
   tc_fence_after_sync();
+  FPROF(7);
 
   // ------------------------------------------------------------------ P3: softmax-CE, last-layer grads
   float dz3[16];
@@ -497,9 +511,11 @@ mlp_fused_step_kernel(const __grid_constant__ CUtensorMap tmXA, const __grid_con
         for (int c = 0; c < S2; ++c) p.dbg[64 * H1 + 64 * H2 + 64 * 16 + row * H2 + S2 * j + c] = dzl[c];
     }
     fence_proxy_async_smem();
+    FPROF(8);
     tc_fence_before_sync();
     cluster_sync_all();
     tc_fence_after_sync();
+    FPROF(9);
     // ---------------------------------------------------------------- P4: layer-2 grads
     if (threadIdx.x == 0) {
       fence_proxy_async_smem();
@@ -556,9 +572,11 @@ mlp_fused_step_kernel(const __grid_constant__ CUtensorMap tmXA, const __grid_con
       for (int c = 0; c < S1; ++c) p.dbg[64 * H1 + 128 * (kMid ? H2 : 0) + 64 * 16 + row * H1 + S1 * j + c] = dz1[c];
   }
   fence_proxy_async_smem();
+  FPROF(10);
   tc_fence_before_sync();
   cluster_sync_all();
   tc_fence_after_sync();
+  FPROF(11);
 
   // ------------------------------------------------------------------ P5: dW1_j = X_j^T . dZ1
   if (threadIdx.x == 0) {
@@ -584,6 +602,7 @@ mlp_fused_step_kernel(const __grid_constant__ CUtensorMap tmXA, const __grid_con
       }
     }
   }
+  FPROF(12);
   tc_fence_before_sync();
   __syncthreads();
   cluster_sync_all();  // nobody leaves while a peer could still be writing into its shared memory
@@ -648,6 +667,7 @@ extern "C" int dmlp_mlp_fused_plan_create(const dmlp_mlp_fused_desc_t* d, dmlp_m
   p.labels = d->labels_dev;
   p.metrics = d->metrics_dev;
   p.dbg = d->debug_dev;
+  p.prof = reinterpret_cast<unsigned long long*>(d->prof_dev);
   pl->layers = L;
   *out = reinterpret_cast<dmlp_mlp_fused_plan_t>(pl);
   return DMLP_OK;

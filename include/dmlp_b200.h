@@ -291,6 +291,7 @@ typedef struct {
   size_t w_off[3], b_off[3]; /* in floats */
   float* metrics_dev;        /* [0] loss sum (float), [1] hit count (int32) */
   float* debug_dev;          /* optional dump of intermediates */
+  void* prof_dev;            /* optional [8][16] u64 globaltimer stamps at the phase boundaries */
 } dmlp_mlp_fused_desc_t;
 typedef struct dmlp_mlp_fused_opaque* dmlp_mlp_fused_plan_t;
 int dmlp_mlp_fused_supported(int num_layers, const int* dims, int batch);

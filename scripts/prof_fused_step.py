@@ -1,0 +1,79 @@
+"""Phase timing of the cluster-fused step kernel from in-kernel globaltimer stamps (1 GPU)."""
+import ctypes as C
+import json
+import os
+import sys
+
+import numpy as np
+import torch
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+from dmlp_b200.models.layout import ParamLayout  # noqa: E402
+from dmlp_b200.runtime import native  # noqa: E402
+
+
+class Desc(C.Structure):
+    _fields_ = [("num_layers", C.c_int), ("dims", C.c_int * 4), ("batch", C.c_int), ("x", C.c_void_p), ("labels", C.c_void_p),
+                ("params", C.c_void_p), ("grads", C.c_void_p), ("w_off", C.c_size_t * 3), ("b_off", C.c_size_t * 3),
+                ("metrics", C.c_void_p), ("debug", C.c_void_p), ("prof", C.c_void_p)]
+
+
+def main():
+    lib = native.lib()
+    dims = (784, 128, 64, 10)
+    lay = ParamLayout(dims)
+    B = 64
+    x = torch.rand(B, 784, device="cuda")
+    y = torch.randint(0, 10, (B,), device="cuda", dtype=torch.int32)
+    params = torch.from_numpy(lay.init_reference(0)).cuda()
+    grads = torch.zeros_like(params)
+    metrics = torch.zeros(4, device="cuda")
+    prof = torch.zeros(8, 16, dtype=torch.int64, device="cuda")
+    d = Desc()
+    d.num_layers = 3
+    for i, v in enumerate(dims):
+        d.dims[i] = v
+    d.batch = B
+    d.x, d.labels, d.params, d.grads = x.data_ptr(), y.data_ptr(), params.data_ptr(), grads.data_ptr()
+    for l, s in enumerate(lay.layers):
+        d.w_off[l], d.b_off[l] = s.w_off, s.b_off
+    d.metrics, d.prof = metrics.data_ptr(), prof.data_ptr()
+    plan = C.c_void_p()
+    lib.dmlp_mlp_fused_plan_create.argtypes = [C.POINTER(Desc), C.POINTER(C.c_void_p)]
+    lib.dmlp_mlp_fused_step.argtypes = [C.c_void_p, C.c_void_p]
+    native.check(lib.dmlp_mlp_fused_plan_create(C.byref(d), C.byref(plan)))
+    st = torch.cuda.Stream()
+    acc = np.zeros((8, 16))
+    n = 0
+    with torch.cuda.stream(st):
+        for it in range(30):
+            native.check(lib.dmlp_mlp_fused_step(plan, st.cuda_stream))
+            torch.cuda.synchronize()
+            if it >= 10:
+                p = prof.cpu().numpy().astype(np.float64)
+                acc += p - p[:, :1].min()
+                n += 1
+        g = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(g, stream=st):
+            for _ in range(50):
+                native.check(lib.dmlp_mlp_fused_step(plan, st.cuda_stream))
+        g.replay()
+        torch.cuda.synchronize()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record(st)
+        g.replay()
+        e1.record(st)
+        torch.cuda.synchronize()
+    acc /= n
+    names = ["entry", "cluster live", "F1 mma+scatter", "sync1", "H1+F2+scatter", "sync2", "H2+F3+allreduce", "sync3",
+             "CE+wgL+dgL+gather", "sync4", "wg2+dg2+gather", "sync5", "wg1+store"]
+    mean = acc.mean(axis=0)
+    out = {"us_per_launch_graph": round(e0.elapsed_time(e1) * 1e3 / 50, 2),
+           "phase_end_us_mean_over_ctas": {names[i]: round(mean[i] / 1e3, 2) for i in range(13)},
+           "phase_us": {names[i]: round((mean[i] - mean[i - 1]) / 1e3, 2) for i in range(1, 13)}}
+    print(json.dumps(out, indent=1))
+
+
+if __name__ == "__main__":
+    main()
