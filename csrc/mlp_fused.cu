@@ -48,7 +48,9 @@ struct FusedParams {
   float* grads;
   unsigned long long w_off[3], b_off[3];
   const int* labels;
-  float* metrics;  // [0] loss sum, [1] hit count (int bits)
+  float* metrics;  // [0] loss sum, [1] hit count (int bits); may be host-mapped memory
+  float* wparams;  // non-null: single-GPU mode, apply w -= lr*g in place instead of writing gradients
+  const float* lr;
   float* dbg;      // optional dump of intermediates (tests)
   unsigned long long* prof;  // optional [8 CTAs][16] globaltimer stamps at phase boundaries
 };
@@ -128,6 +130,19 @@ __device__ __forceinline__ uint64_t mdesc(uint32_t tile, int kstep, uint32_t col
   return make_smem_desc(tile + kstep * 1024, col_bytes, 512, 1);
 }
 
+// Emits 4 consecutive gradient values: either into the gradient buffer (multi-GPU: the all-reduce
+// kernel consumes it) or straight into the weights as w -= lr*g (single GPU).
+__device__ __forceinline__ void emit_grad4(const FusedParams& p, float step, size_t off, float a, float b, float c, float d) {
+  if (p.wparams != nullptr) {
+    float4* w = reinterpret_cast<float4*>(p.wparams + off);
+    float4 v = *w;
+    v.x -= step * a; v.y -= step * b; v.z -= step * c; v.w -= step * d;
+    *w = v;
+  } else {
+    *reinterpret_cast<float4*>(p.grads + off) = make_float4(a, b, c, d);
+  }
+}
+
 // Column sums over the batch rows held one-per-thread by the 128 worker threads; result (n <= 16
 // columns) is valid in the first n worker threads of worker-warp 0.
 template <int N>
@@ -180,6 +195,7 @@ mlp_fused_step_kernel(const __grid_constant__ CUtensorMap tmXA, const __grid_con
   const int row = (warp & 3) * 32 + lane;  // TMEM lane == batch row handled by this worker thread
   const bool rok = worker && row < B;
   float* red = reinterpret_cast<float*>(smem + oRED);
+  const float step = p.wparams != nullptr ? __ldg(p.lr) : 0.f;
   const uint32_t tq = (static_cast<uint32_t>((warp & 3) * 32) << 16);
 
   if (threadIdx.x == 0) {
@@ -272,9 +288,14 @@ mlp_fused_step_kernel(const __grid_constant__ CUtensorMap tmXA, const __grid_con
         *reinterpret_cast<float4*>(smem + oH1K + koff(row, c)) = make_float4(h1[c], h1[c + 1], h1[c + 2], h1[c + 3]);
         *reinterpret_cast<float4*>(smem + oH1M + moff(row, c)) = make_float4(h1[c], h1[c + 1], h1[c + 2], h1[c + 3]);
       }
+      // "ones" column: row S1 of H1_j^T . dZ is then the column sum of dZ = a bias gradient, for free
+      *reinterpret_cast<float*>(smem + oH1M + moff(row, S1)) = 1.f;
       if (p.dbg)
         for (int c = 0; c < S1; ++c) p.dbg[row * H1 + S1 * j + c] = h1[c];
     }
+    // X^T tile: column 127 lies outside every CTA's K slice (<= 104 wide) -> make it the ones column
+    mbar_wait(&bar_tma1, 0);
+    if (rok) *reinterpret_cast<float*>(smem + oXT + moff(row, 127)) = 1.f;
     fence_proxy_async_smem();
   }
   __syncthreads();
@@ -330,6 +351,7 @@ mlp_fused_step_kernel(const __grid_constant__ CUtensorMap tmXA, const __grid_con
           *reinterpret_cast<float4*>(smem + oH2K + koff(row, c)) = make_float4(h2[c], h2[c + 1], h2[c + 2], h2[c + 3]);
           *reinterpret_cast<float4*>(smem + oH2M + moff(row, c)) = make_float4(h2[c], h2[c + 1], h2[c + 2], h2[c + 3]);
         }
+        *reinterpret_cast<float*>(smem + oH2M + moff(row, S2)) = 1.f;
         if (p.dbg)
           for (int c = 0; c < S2; ++c) p.dbg[64 * H1 + row * H2 + S2 * j + c] = h2[c];
       }
@@ -426,11 +448,7 @@ mlp_fused_step_kernel(const __grid_constant__ CUtensorMap tmXA, const __grid_con
       for (int c = 0; c < 16; ++c) dz3[c] = 0.f;
     }
     fence_proxy_async_smem();
-    if (j == 0) {  // loss, hits and the last bias gradient are produced once (CTA 0)
-      float bsum[1];
-      int col;
-      worker_colsum<16>(dz3, red, wwarp, lane, bsum, col);
-      if (col >= 0) p.grads[p.b_off[LAST] + col] = bsum[0];
+    if (j == 0) {  // loss and hits are produced once (CTA 0)
 #pragma unroll
       for (int o = 16; o > 0; o >>= 1) {
         loss += __shfl_xor_sync(0xffffffffu, loss, o);
@@ -443,7 +461,6 @@ mlp_fused_step_kernel(const __grid_constant__ CUtensorMap tmXA, const __grid_con
         reinterpret_cast<int*>(p.metrics)[1] = reinterpret_cast<int*>(red)[8] + reinterpret_cast<int*>(red)[9] +
                                                reinterpret_cast<int*>(red)[10] + reinterpret_cast<int*>(red)[11];
       }
-      asm volatile("bar.sync 1, 128;" ::: "memory");
     }
   }
   __syncthreads();
@@ -460,6 +477,7 @@ mlp_fused_step_kernel(const __grid_constant__ CUtensorMap tmXA, const __grid_con
     tc_commit(&bar_mma);
   }
   float dzl[SL];
+  float dbl[16];  // last-layer bias gradient (valid in the thread that owns accumulator row SL)
   if (worker) {
     mbar_wait(&bar_mma, mma_phase);
     tc_fence_after_sync();
@@ -468,10 +486,14 @@ mlp_fused_step_kernel(const __grid_constant__ CUtensorMap tmXA, const __grid_con
       tmem_ld_x16(tm + tq + cWGL, r);
       tmem_ld_wait();
       if (row < SL) {
-        float4* g = reinterpret_cast<float4*>(p.grads + p.w_off[LAST] + static_cast<size_t>(SL * j + row) * 16);
+        const size_t off = p.w_off[LAST] + static_cast<size_t>(SL * j + row) * 16;
 #pragma unroll
         for (int c = 0; c < 16; c += 4)
-          g[c >> 2] = make_float4(__uint_as_float(r[c]), __uint_as_float(r[c + 1]), __uint_as_float(r[c + 2]), __uint_as_float(r[c + 3]));
+          emit_grad4(p, step, off + c, __uint_as_float(r[c]), __uint_as_float(r[c + 1]), __uint_as_float(r[c + 2]), __uint_as_float(r[c + 3]));
+      }
+      if (row == SL) {  // the ones row: column sums of dZ_last = gradient of the last bias
+#pragma unroll
+        for (int c = 0; c < 16; ++c) dbl[c] = __uint_as_float(r[c]);
       }
     }
     {
@@ -483,13 +505,6 @@ mlp_fused_step_kernel(const __grid_constant__ CUtensorMap tmXA, const __grid_con
         const float hl = kMid ? h2[kMid ? c : 0] : h1[kMid ? 0 : c];
         dzl[c] = (rok && hl > 0.f) ? __uint_as_float(r[c]) : 0.f;
       }
-    }
-    // bias gradient of the layer that produced HL
-    {
-      float bsum[1];
-      int col;
-      worker_colsum<SL>(dzl, red, wwarp, lane, bsum, col);
-      if (col >= 0) p.grads[p.b_off[LAST - 1] + SL * j + col] = bsum[0];
     }
   }
   mma_phase ^= 1;
@@ -536,10 +551,18 @@ mlp_fused_step_kernel(const __grid_constant__ CUtensorMap tmXA, const __grid_con
         tmem_ld_x16(tm + tq + cWG2 + cc, r);
         tmem_ld_wait();
         if (row < S1) {
-          float4* g = reinterpret_cast<float4*>(p.grads + p.w_off[1] + static_cast<size_t>(S1 * j + row) * H2 + cc);
+          const size_t off = p.w_off[1] + static_cast<size_t>(S1 * j + row) * H2 + cc;
 #pragma unroll
           for (int c = 0; c < 16; c += 4)
-            g[c >> 2] = make_float4(__uint_as_float(r[c]), __uint_as_float(r[c + 1]), __uint_as_float(r[c + 2]), __uint_as_float(r[c + 3]));
+            emit_grad4(p, step, off + c, __uint_as_float(r[c]), __uint_as_float(r[c + 1]), __uint_as_float(r[c + 2]), __uint_as_float(r[c + 3]));
+        }
+        if (row == S1 && (S2 * j) / 16 == cc / 16) {  // ones row: db2; this CTA owns b2[S2*j, S2*j+S2)
+          const int c0 = (S2 * j) % 16;
+          const size_t off = p.b_off[1] + S2 * j;
+#pragma unroll
+          for (int c = 0; c < 16; c += 4)
+            if (c >= c0 && c < c0 + S2)
+              emit_grad4(p, step, off + (c - c0), __uint_as_float(r[c]), __uint_as_float(r[c + 1]), __uint_as_float(r[c + 2]), __uint_as_float(r[c + 3]));
         }
       }
       uint32_t r[16];
@@ -547,10 +570,6 @@ mlp_fused_step_kernel(const __grid_constant__ CUtensorMap tmXA, const __grid_con
       tmem_ld_wait();
 #pragma unroll
       for (int c = 0; c < S1; ++c) dz1[c] = (rok && h1[c] > 0.f) ? __uint_as_float(r[c]) : 0.f;
-      float bsum[1];
-      int col;
-      worker_colsum<S1>(dz1, red, wwarp, lane, bsum, col);
-      if (col >= 0) p.grads[p.b_off[0] + S1 * j + col] = bsum[0];
     }
     mma_phase ^= 1;
   } else {
@@ -595,10 +614,16 @@ mlp_fused_step_kernel(const __grid_constant__ CUtensorMap tmXA, const __grid_con
       tmem_ld_x16(tm + tq + cWG1 + cc, r);
       tmem_ld_wait();
       if (row < nk1 * 8) {
-        float4* g = reinterpret_cast<float4*>(p.grads + p.w_off[0] + static_cast<size_t>(k0 + row) * H1 + cc);
+        const size_t off = p.w_off[0] + static_cast<size_t>(k0 + row) * H1 + cc;
 #pragma unroll
         for (int c = 0; c < 16; c += 4)
-          g[c >> 2] = make_float4(__uint_as_float(r[c]), __uint_as_float(r[c + 1]), __uint_as_float(r[c + 2]), __uint_as_float(r[c + 3]));
+          emit_grad4(p, step, off + c, __uint_as_float(r[c]), __uint_as_float(r[c + 1]), __uint_as_float(r[c + 2]), __uint_as_float(r[c + 3]));
+      }
+      if (row == 127 && cc == S1 * j) {  // ones row: db1; this CTA owns b1[S1*j, S1*j+S1)
+        const size_t off = p.b_off[0] + S1 * j;
+#pragma unroll
+        for (int c = 0; c < 16; c += 4)
+          emit_grad4(p, step, off + c, __uint_as_float(r[c]), __uint_as_float(r[c + 1]), __uint_as_float(r[c + 2]), __uint_as_float(r[c + 3]));
       }
     }
   }
@@ -606,6 +631,11 @@ mlp_fused_step_kernel(const __grid_constant__ CUtensorMap tmXA, const __grid_con
   tc_fence_before_sync();
   __syncthreads();
   cluster_sync_all();  // nobody leaves while a peer could still be writing into its shared memory
+  if (j == 0 && worker && row == SL) {  // every CTA has read the last bias by now: CTA 0 may update it
+    const size_t off = p.b_off[LAST];
+#pragma unroll
+    for (int c = 0; c < 16; c += 4) emit_grad4(p, step, off + c, dbl[c], dbl[c + 1], dbl[c + 2], dbl[c + 3]);
+  }
   if (warp == 0) {
     tc_fence_after_sync();
     tmem_dealloc(tm, 512);
@@ -667,6 +697,8 @@ extern "C" int dmlp_mlp_fused_plan_create(const dmlp_mlp_fused_desc_t* d, dmlp_m
   p.labels = d->labels_dev;
   p.metrics = d->metrics_dev;
   p.dbg = d->debug_dev;
+  p.wparams = d->sgd_params_dev;
+  p.lr = d->lr_dev;
   p.prof = reinterpret_cast<unsigned long long*>(d->prof_dev);
   pl->layers = L;
   *out = reinterpret_cast<dmlp_mlp_fused_plan_t>(pl);

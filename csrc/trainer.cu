@@ -189,7 +189,9 @@ static int build_plans(Trainer* t) {
       f.params_dev = t->params;
       f.grads_dev = t->grads[par];
       for (int l = 0; l < L.L; ++l) { f.w_off[l] = L.w_off[l]; f.b_off[l] = L.b_off[l]; }
-      f.metrics_dev = t->metrics_dev[par];
+      // metrics go straight to pinned host memory (mapped): no D2H copy node in the step graph
+      f.metrics_dev = t->metrics_host + 2 * par;
+      if (t->comm == nullptr && t->cfg.fused != 2) { f.sgd_params_dev = t->params; f.lr_dev = t->lr_dev; }
       TRY(dmlp_mlp_fused_plan_create(&f, &t->fplan[par]));
     }
   }
@@ -248,9 +250,10 @@ static int enqueue_step(Trainer* t, int par, bool count_kernels) {
     // reduces + averages + applies SGD (or plain SGD on a single GPU)
     TRY(dmlp_mlp_fused_step(t->fplan[par], S));
     ++nk;
-    TRY(enqueue_allreduce(t, par, 0, L.total, S));
-    ++nk;
-    DMLP_CUDA_CHECK(cudaMemcpyAsync(t->metrics_host + 2 * par, t->metrics_dev[par], 8, cudaMemcpyDeviceToHost, S));
+    if (t->comm != nullptr || t->cfg.fused == 2) {  // single GPU: the fused kernel already applied SGD in place
+      TRY(enqueue_allreduce(t, par, 0, L.total, S));
+      ++nk;
+    }
     if (count_kernels) t->kernels_per_step = nk;
     return DMLP_OK;
   }
@@ -503,7 +506,7 @@ extern "C" int dmlp_trainer_create(const dmlp_trainer_config_t* cfg, int device,
     else { TRYF(dev_alloc(t, n * 4, &p)); t->dz[l] = static_cast<float*>(p); }
   }
   TRYF(dev_alloc(t, 16, &p)); t->lr_dev = static_cast<float*>(p);
-  CUF(cudaHostAlloc(reinterpret_cast<void**>(&t->metrics_host), 64, cudaHostAllocPortable));
+  CUF(cudaHostAlloc(reinterpret_cast<void**>(&t->metrics_host), 64, cudaHostAllocPortable | cudaHostAllocMapped));
   CUF(cudaHostAlloc(reinterpret_cast<void**>(&t->lr_host), 64, cudaHostAllocPortable));
   memset(t->metrics_host, 0, 64);
   t->lr_host[0] = cfg->lr;

@@ -292,6 +292,8 @@ typedef struct {
   float* metrics_dev;        /* [0] loss sum (float), [1] hit count (int32) */
   float* debug_dev;          /* optional dump of intermediates */
   void* prof_dev;            /* optional [8][16] u64 globaltimer stamps at the phase boundaries */
+  float* sgd_params_dev;     /* non-null (single GPU): apply w -= lr*g in place (== params_dev) and write no gradients */
+  const float* lr_dev;       /* device scalar, with sgd_params_dev */
 } dmlp_mlp_fused_desc_t;
 typedef struct dmlp_mlp_fused_opaque* dmlp_mlp_fused_plan_t;
 int dmlp_mlp_fused_supported(int num_layers, const int* dims, int batch);
@@ -322,7 +324,8 @@ typedef struct {
   void* nvls_uc;                 /* allreduce_algo == DMLP_ALGO_NVLS: this rank's replica of the multicast-bound */
   void* nvls_mc;                 /* arena and its multicast address; params/grads/shadow are placed there */
   size_t nvls_bytes;
-  int fused;                     /* cluster-fused step kernel: -1 auto (when the shape allows), 0 off, 1 on */
+  int fused;                     /* cluster-fused step kernel: -1 auto (when the shape allows), 0 off, 1 on,
+                                    2 on but always write gradients + run the separate update kernel */
 } dmlp_trainer_config_t;
 typedef struct dmlp_trainer_opaque* dmlp_trainer_t;
 
