@@ -23,6 +23,7 @@
 namespace dmlp {
 
 constexpr int kMaxLayers = DMLP_MAX_LAYERS;
+constexpr int kRingChunk = 8, kRingChunks = 2, kRingSlots = kRingChunk * kRingChunks;
 
 static size_t align_up(size_t v, size_t a) { return (v + a - 1) / a * a; }
 
@@ -87,6 +88,13 @@ struct Trainer {
   GemmPlan fwd[2][kMaxLayers], wgrad[2][kMaxLayers], dgrad[kMaxLayers], fwd_eval_last;
   bool fused_step = false;  // whole fwd+loss+bwd in one cluster launch (mlp_fused.cu)
   dmlp_mlp_fused_plan_t fplan[2] = {nullptr, nullptr};
+  // fused path input ring: kRingChunks chunks of kRingChunk steps; one H2D + one event per chunk so the
+  // step kernels run back to back with no stream operation between them
+  float* x_ring = nullptr;
+  int* y_ring = nullptr;
+  dmlp_mlp_fused_plan_t rplan[16];
+  cudaEvent_t ev_ring_h2d[2], ev_ring_done[2];
+  bool ring_launched[2] = {false, false};
   bool fused_ce = false;   // softmax-CE runs in the last forward GEMM's epilogue
   bool direct = false;     // batch fits one M tile: reductions are stored, no zeroing needed
   cudaStream_t s_aux = nullptr;  // wgrad branch (runs beside the dgrad chain)
@@ -193,6 +201,21 @@ static int build_plans(Trainer* t) {
       f.metrics_dev = t->metrics_host + 2 * par;
       if (t->comm == nullptr && t->cfg.fused != 2) { f.sgd_params_dev = t->params; f.lr_dev = t->lr_dev; }
       TRY(dmlp_mlp_fused_plan_create(&f, &t->fplan[par]));
+    }
+    for (int slot = 0; slot < kRingSlots; ++slot) {
+      dmlp_mlp_fused_desc_t f;
+      memset(&f, 0, sizeof(f));
+      f.num_layers = L.L;
+      for (int l = 0; l <= L.L; ++l) f.dims[l] = t->cfg.dims[l];
+      f.batch = B;
+      f.x_dev = t->x_ring + static_cast<size_t>(slot) * B * L.in[0];
+      f.labels_dev = t->y_ring + static_cast<size_t>(slot) * B;
+      f.params_dev = t->params;
+      f.grads_dev = t->grads[slot & 1];
+      for (int l = 0; l < L.L; ++l) { f.w_off[l] = L.w_off[l]; f.b_off[l] = L.b_off[l]; }
+      f.metrics_dev = t->metrics_host + 4 + 2 * slot;
+      if (t->comm == nullptr && t->cfg.fused != 2) { f.sgd_params_dev = t->params; f.lr_dev = t->lr_dev; }
+      TRY(dmlp_mlp_fused_plan_create(&f, &t->rplan[slot]));
     }
   }
   return DMLP_OK;
@@ -329,6 +352,89 @@ static int capture_graphs(Trainer* t) {
   return DMLP_OK;
 }
 
+// Fused-path step loop. Inputs are staged chunk-wise into a device ring (one H2D per chunk when the
+// batches are contiguous in the source), so the step kernels of a chunk are launched back to back
+// with no event between them; loss / hit count arrive in mapped host memory, one slot per step.
+static int run_fused_ring(Trainer* t, const float* x_host, const int32_t* y_host, size_t num_batches,
+                          size_t first_batch, size_t batch_stride, int steps, const float* lr_schedule,
+                          float* metrics_out, void* start_event, void* stop_event) {
+  const int B = t->cfg.batch;
+  const size_t xin = t->lay.in[0];
+  const ParamLayout& L = t->lay;
+  int chunk_first_step[kRingChunks] = {-1, -1}, chunk_n[kRingChunks] = {0, 0};
+  int chunk_off_rec[kRingChunks] = {0, 0};
+  auto collect = [&](int c) {
+    if (chunk_first_step[c] < 0 || !metrics_out) return;
+    for (int i = 0; i < chunk_n[c]; ++i) {
+      const int slot = c * kRingChunk + chunk_off_rec[c] + i, s = chunk_first_step[c] + i;
+      metrics_out[2 * s] = t->metrics_host[4 + 2 * slot];
+      metrics_out[2 * s + 1] = static_cast<float>(reinterpret_cast<int*>(t->metrics_host)[4 + 2 * slot + 1]);
+    }
+    chunk_first_step[c] = -1;
+  };
+  if (start_event) DMLP_CUDA_CHECK(cudaEventRecord(reinterpret_cast<cudaEvent_t>(start_event), t->s_main));
+  // Gradient buffers alternate with the GLOBAL step parity (slot parity == step parity), also across
+  // calls: a call that starts on an odd step begins at slot 1 of its first chunk.
+  int s0 = 0, ci = 0, last_c = -1;
+  while (s0 < steps) {
+    const int c = ci % kRingChunks;
+    const int off = (ci == 0) ? static_cast<int>(t->steps_done & 1) : 0;
+    const int n = steps - s0 < kRingChunk - off ? steps - s0 : kRingChunk - off;
+    if (t->ring_launched[c]) {
+      DMLP_CUDA_CHECK(cudaEventSynchronize(t->ev_ring_done[c]));
+      collect(c);
+    }
+    const size_t b0 = (first_batch + static_cast<size_t>(s0) * batch_stride) % num_batches;
+    float* xdst = t->x_ring + static_cast<size_t>(c * kRingChunk + off) * B * xin;
+    int* ydst = t->y_ring + static_cast<size_t>(c * kRingChunk + off) * B;
+    if (batch_stride == 1 && b0 + n <= num_batches) {
+      DMLP_CUDA_CHECK(cudaMemcpyAsync(xdst, x_host + b0 * B * xin, sizeof(float) * n * B * xin, cudaMemcpyDefault, t->s_copy));
+      DMLP_CUDA_CHECK(cudaMemcpyAsync(ydst, y_host + b0 * B, sizeof(int) * n * B, cudaMemcpyDefault, t->s_copy));
+    } else {
+      for (int i = 0; i < n; ++i) {
+        const size_t bi = (first_batch + static_cast<size_t>(s0 + i) * batch_stride) % num_batches;
+        DMLP_CUDA_CHECK(cudaMemcpyAsync(xdst + static_cast<size_t>(i) * B * xin, x_host + bi * B * xin, sizeof(float) * B * xin,
+                                        cudaMemcpyDefault, t->s_copy));
+        DMLP_CUDA_CHECK(cudaMemcpyAsync(ydst + static_cast<size_t>(i) * B, y_host + bi * B, sizeof(int) * B, cudaMemcpyDefault, t->s_copy));
+      }
+    }
+    DMLP_CUDA_CHECK(cudaEventRecord(t->ev_ring_h2d[c], t->s_copy));
+    DMLP_CUDA_CHECK(cudaStreamWaitEvent(t->s_main, t->ev_ring_h2d[c], 0));
+    for (int i = 0; i < n; ++i) {
+      const int s = s0 + i;
+      if (lr_schedule && lr_schedule[s] != t->lr_host[0]) {
+        DMLP_CUDA_CHECK(cudaStreamSynchronize(t->s_main));
+        t->lr_host[0] = lr_schedule[s];
+        DMLP_CUDA_CHECK(cudaMemcpyAsync(t->lr_dev, t->lr_host, 4, cudaMemcpyHostToDevice, t->s_main));
+      }
+      const int slot = c * kRingChunk + off + i;
+      TRY(dmlp_mlp_fused_step(t->rplan[slot], t->s_main));
+      if (t->comm != nullptr || t->cfg.fused == 2) TRY(enqueue_allreduce(t, slot & 1, 0, L.total, t->s_main));
+    }
+    DMLP_CUDA_CHECK(cudaEventRecord(t->ev_ring_done[c], t->s_main));
+    t->ring_launched[c] = true;
+    chunk_first_step[c] = s0;
+    chunk_n[c] = n;
+    chunk_off_rec[c] = off;
+    last_c = c;
+    s0 += n;
+    ++ci;
+  }
+  if (stop_event) DMLP_CUDA_CHECK(cudaEventRecord(reinterpret_cast<cudaEvent_t>(stop_event), t->s_main));
+  DMLP_CUDA_CHECK(cudaStreamSynchronize(t->s_main));
+  // drain in launch order
+  if (last_c >= 0) { collect((last_c + 1) % kRingChunks); collect(last_c); }
+  t->kernels_per_step = (t->comm != nullptr || t->cfg.fused == 2) ? 2 : 1;
+  t->steps_done += steps;
+  if (t->comm) {
+    uint32_t st[5];
+    TRY(dmlp_comm_status(t->comm, st));
+    if (st[0] != 0)
+      return set_error(DMLP_ERR_TIMEOUT, "collective watchdog: rank %u waited for rank %u (phase %u)", st[1], st[2], st[3]);
+  }
+  return DMLP_OK;
+}
+
 }  // namespace dmlp
 
 using namespace dmlp;
@@ -386,6 +492,12 @@ extern "C" int dmlp_trainer_destroy(dmlp_trainer_t h) {
   if (t->s_aux) cudaStreamDestroy(t->s_aux);
   for (int p = 0; p < 2; ++p)
     if (t->fplan[p]) dmlp_mlp_fused_plan_destroy(t->fplan[p]);
+  for (int sl = 0; sl < kRingSlots; ++sl)
+    if (t->rplan[sl]) dmlp_mlp_fused_plan_destroy(t->rplan[sl]);
+  for (int c = 0; c < kRingChunks; ++c) {
+    if (t->ev_ring_h2d[c]) cudaEventDestroy(t->ev_ring_h2d[c]);
+    if (t->ev_ring_done[c]) cudaEventDestroy(t->ev_ring_done[c]);
+  }
   for (void* p : t->owned) cudaFree(p);
   if (t->metrics_host) cudaFreeHost(t->metrics_host);
   if (t->lr_host) cudaFreeHost(t->lr_host);
@@ -408,6 +520,9 @@ extern "C" int dmlp_trainer_create(const dmlp_trainer_config_t* cfg, int device,
   Trainer* t = new (std::nothrow) Trainer();
   if (!t) return set_error(DMLP_ERR_CUDA, "out of host memory");
   memset(t->ev_h2d, 0, sizeof(t->ev_h2d));
+  memset(t->rplan, 0, sizeof(t->rplan));
+  memset(t->ev_ring_h2d, 0, sizeof(t->ev_ring_h2d));
+  memset(t->ev_ring_done, 0, sizeof(t->ev_ring_done));
   memset(t->ev_done, 0, sizeof(t->ev_done));
   memset(t->ev_bucket, 0, sizeof(t->ev_bucket));
   t->ev_fork = t->ev_join = nullptr;
@@ -506,9 +621,9 @@ extern "C" int dmlp_trainer_create(const dmlp_trainer_config_t* cfg, int device,
     else { TRYF(dev_alloc(t, n * 4, &p)); t->dz[l] = static_cast<float*>(p); }
   }
   TRYF(dev_alloc(t, 16, &p)); t->lr_dev = static_cast<float*>(p);
-  CUF(cudaHostAlloc(reinterpret_cast<void**>(&t->metrics_host), 64, cudaHostAllocPortable | cudaHostAllocMapped));
+  CUF(cudaHostAlloc(reinterpret_cast<void**>(&t->metrics_host), 512, cudaHostAllocPortable | cudaHostAllocMapped));
   CUF(cudaHostAlloc(reinterpret_cast<void**>(&t->lr_host), 64, cudaHostAllocPortable));
-  memset(t->metrics_host, 0, 64);
+  memset(t->metrics_host, 0, 512);
   t->lr_host[0] = cfg->lr;
   CUF(cudaMemcpy(t->lr_dev, t->lr_host, 4, cudaMemcpyHostToDevice));
   CUF(cudaStreamCreateWithFlags(&t->s_main, cudaStreamNonBlocking));
@@ -524,6 +639,14 @@ extern "C" int dmlp_trainer_create(const dmlp_trainer_config_t* cfg, int device,
   CUF(cudaEventCreateWithFlags(&t->ev_aux_done, cudaEventDisableTiming));
   for (int l = 0; l < L.L; ++l) CUF(cudaEventCreateWithFlags(&t->ev_dz[l], cudaEventDisableTiming));
   for (int l = 0; l < L.L; ++l) CUF(cudaEventCreateWithFlags(&t->ev_bucket[l], cudaEventDisableTiming));
+  if (t->fused_step) {
+    TRYF(dev_alloc(t, static_cast<size_t>(kRingSlots) * B * L.in[0] * 4, &p)); t->x_ring = static_cast<float*>(p);
+    TRYF(dev_alloc(t, static_cast<size_t>(kRingSlots) * B * 4, &p)); t->y_ring = static_cast<int*>(p);
+    for (int c = 0; c < kRingChunks; ++c) {
+      CUF(cudaEventCreateWithFlags(&t->ev_ring_h2d[c], cudaEventDisableTiming));
+      CUF(cudaEventCreateWithFlags(&t->ev_ring_done[c], cudaEventDisableTiming));
+    }
+  }
   TRYF(build_plans(t));
   *out = reinterpret_cast<dmlp_trainer_t>(t);
   return DMLP_OK;
@@ -582,6 +705,9 @@ extern "C" int dmlp_trainer_run(dmlp_trainer_t h, const float* x_host, const int
   DeviceGuard g(t->dev);
   const int B = t->cfg.batch;
   const size_t xin = t->lay.in[0];
+  if (t->fused_step)
+    return run_fused_ring(t, x_host, y_host, num_batches, first_batch, batch_stride, steps, lr_schedule, metrics_out,
+                          start_event, stop_event);
   if (use_graph && t->gexec[0] == nullptr) {
     // One eager warm-up pass per parity sets function attributes / loads modules outside capture.
     // It must not change the model: run it with lr = 0.

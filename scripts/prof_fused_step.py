@@ -16,7 +16,8 @@ from dmlp_b200.runtime import native  # noqa: E402
 class Desc(C.Structure):
     _fields_ = [("num_layers", C.c_int), ("dims", C.c_int * 4), ("batch", C.c_int), ("x", C.c_void_p), ("labels", C.c_void_p),
                 ("params", C.c_void_p), ("grads", C.c_void_p), ("w_off", C.c_size_t * 3), ("b_off", C.c_size_t * 3),
-                ("metrics", C.c_void_p), ("debug", C.c_void_p), ("prof", C.c_void_p)]
+                ("metrics", C.c_void_p), ("debug", C.c_void_p), ("prof", C.c_void_p),
+                ("sgd_params", C.c_void_p), ("lr", C.c_void_p)]
 
 
 def main():
