@@ -134,10 +134,10 @@ __device__ __forceinline__ uint64_t mdesc(uint32_t tile, int kstep, uint32_t col
 // kernel consumes it) or straight into the weights as w -= lr*g (single GPU).
 __device__ __forceinline__ void emit_grad4(const FusedParams& p, float step, size_t off, float a, float b, float c, float d) {
   if (p.wparams != nullptr) {
-    float4* w = reinterpret_cast<float4*>(p.wparams + off);
-    float4 v = *w;
-    v.x -= step * a; v.y -= step * b; v.z -= step * c; v.w -= step * d;
-    *w = v;
+    // w += (-lr*g) as a fire-and-forget vector reduction: no load latency in the epilogue. Every
+    // element is touched by exactly one thread, so the result equals w - lr*g bit for bit.
+    asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(p.wparams + off), "f"(-step * a), "f"(-step * b),
+                 "f"(-step * c), "f"(-step * d) : "memory");
   } else {
     *reinterpret_cast<float4*>(p.grads + off) = make_float4(a, b, c, d);
   }

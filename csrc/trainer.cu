@@ -92,6 +92,7 @@ struct Trainer {
   // step kernels run back to back with no stream operation between them
   float* x_ring = nullptr;
   int* y_ring = nullptr;
+  float* metrics_ring = nullptr;  // [kRingSlots][2] on the device, copied to the host once per chunk
   dmlp_mlp_fused_plan_t rplan[16];
   cudaEvent_t ev_ring_h2d[2], ev_ring_done[2];
   bool ring_launched[2] = {false, false};
@@ -213,7 +214,7 @@ static int build_plans(Trainer* t) {
       f.params_dev = t->params;
       f.grads_dev = t->grads[slot & 1];
       for (int l = 0; l < L.L; ++l) { f.w_off[l] = L.w_off[l]; f.b_off[l] = L.b_off[l]; }
-      f.metrics_dev = t->metrics_host + 4 + 2 * slot;
+      f.metrics_dev = t->metrics_ring + 2 * slot;  // device memory: a write to mapped host memory stalls kernel completion
       if (t->comm == nullptr && t->cfg.fused != 2) { f.sgd_params_dev = t->params; f.lr_dev = t->lr_dev; }
       TRY(dmlp_mlp_fused_plan_create(&f, &t->rplan[slot]));
     }
@@ -411,6 +412,8 @@ static int run_fused_ring(Trainer* t, const float* x_host, const int32_t* y_host
       TRY(dmlp_mlp_fused_step(t->rplan[slot], t->s_main));
       if (t->comm != nullptr || t->cfg.fused == 2) TRY(enqueue_allreduce(t, slot & 1, 0, L.total, t->s_main));
     }
+    DMLP_CUDA_CHECK(cudaMemcpyAsync(t->metrics_host + 4 + 2 * (c * kRingChunk + off), t->metrics_ring + 2 * (c * kRingChunk + off),
+                                    8 * n, cudaMemcpyDeviceToHost, t->s_main));
     DMLP_CUDA_CHECK(cudaEventRecord(t->ev_ring_done[c], t->s_main));
     t->ring_launched[c] = true;
     chunk_first_step[c] = s0;
@@ -642,6 +645,7 @@ extern "C" int dmlp_trainer_create(const dmlp_trainer_config_t* cfg, int device,
   if (t->fused_step) {
     TRYF(dev_alloc(t, static_cast<size_t>(kRingSlots) * B * L.in[0] * 4, &p)); t->x_ring = static_cast<float*>(p);
     TRYF(dev_alloc(t, static_cast<size_t>(kRingSlots) * B * 4, &p)); t->y_ring = static_cast<int*>(p);
+    TRYF(dev_alloc(t, static_cast<size_t>(kRingSlots) * 8, &p)); t->metrics_ring = static_cast<float*>(p);
     for (int c = 0; c < kRingChunks; ++c) {
       CUF(cudaEventCreateWithFlags(&t->ev_ring_h2d[c], cudaEventDisableTiming));
       CUF(cudaEventCreateWithFlags(&t->ev_ring_done[c], cudaEventDisableTiming));
