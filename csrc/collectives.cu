@@ -253,6 +253,7 @@ struct Prologue {
 template <typename T, bool SGD>
 __global__ void __launch_bounds__(kCollThreads)
 allreduce_oneshot_kernel(const __grid_constant__ CollArgs a) {
+  asm volatile("griddepcontrol.launch_dependents;" ::: "memory");  // a PDL successor may begin its prologue now
   constexpr int V = Pack<T>::N;
   const int rank = a.rank >= 0 ? a.rank : blockIdx.y;
   if ((a.dead_mask >> rank) & 1u) return;
@@ -342,6 +343,7 @@ allreduce_oneshot_kernel(const __grid_constant__ CollArgs a) {
 template <typename T, bool SGD>
 __global__ void __launch_bounds__(kCollThreads)
 allreduce_twoshot_kernel(const __grid_constant__ CollArgs a) {
+  asm volatile("griddepcontrol.launch_dependents;" ::: "memory");  // a PDL successor may begin its prologue now
   constexpr int V = Pack<T>::N;
   const int rank = a.rank >= 0 ? a.rank : blockIdx.y;
   if ((a.dead_mask >> rank) & 1u) return;

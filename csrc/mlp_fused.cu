@@ -195,7 +195,6 @@ mlp_fused_step_kernel(const __grid_constant__ CUtensorMap tmXA, const __grid_con
   const int row = (warp & 3) * 32 + lane;  // TMEM lane == batch row handled by this worker thread
   const bool rok = worker && row < B;
   float* red = reinterpret_cast<float*>(smem + oRED);
-  const float step = p.wparams != nullptr ? __ldg(p.lr) : 0.f;
   const uint32_t tq = (static_cast<uint32_t>((warp & 3) * 32) << 16);
 
   if (threadIdx.x == 0) {
@@ -218,14 +217,22 @@ mlp_fused_step_kernel(const __grid_constant__ CUtensorMap tmXA, const __grid_con
   FPROF(1);
 
   // ------------------------------------------------------------------ P0: loads + layer-1 partial
+  // Programmatic dependent launch: this grid may start while its predecessor in the stream (the previous
+  // step's kernel, or its all-reduce) is still finishing. Everything so far — and the input loads
+  // just below — touch nothing the predecessor writes; parameters and gradients are only accessed
+  // after griddepcontrol.wait.
+  asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
   if (threadIdx.x == 0) {
     mbar_arrive_expect_tx(&bar_tma0, 4 * kTileK + (H1 / 32) * kW1Col);
     for (int b = 0; b < 4; ++b) tma_load_2d(smem + oXA + b * kTileK, &tmXA, &bar_tma0, k0 + 32 * b, 0);
-    for (int a = 0; a < H1 / 32; ++a) tma_load_2d(smem + oW1B + a * kW1Col, &tmW1, &bar_tma0, 32 * a, k0);
     uint32_t bytes1 = 4 * kColM + 2 * SL * 128;
     if (kMid) bytes1 += (H2 / 32) * S1 * 128 + (H2 / 32) * S1 * 128;
     mbar_arrive_expect_tx(&bar_tma1, bytes1);
     for (int a = 0; a < 4; ++a) tma_load_2d(smem + oXT + a * kColM, &tmXT, &bar_tma1, k0 + 32 * a, 0);
+  }
+  asm volatile("griddepcontrol.wait;" ::: "memory");
+  if (threadIdx.x == 0) {
+    for (int a = 0; a < H1 / 32; ++a) tma_load_2d(smem + oW1B + a * kW1Col, &tmW1, &bar_tma0, 32 * a, k0);
     if (kMid) {
       for (int a = 0; a < H2 / 32; ++a) tma_load_2d(smem + oW2B + a * S1 * 128, &tmW2B, &bar_tma1, 32 * a, S1 * j);
       for (int kb = 0; kb < H2 / 32; ++kb) tma_load_2d(smem + oW2K + kb * 4096, &tmW2K, &bar_tma1, 32 * kb, S1 * j);
@@ -239,6 +246,7 @@ mlp_fused_step_kernel(const __grid_constant__ CUtensorMap tmXA, const __grid_con
       tc_mma<4>(tm + cF1, kdesc(sb + oXA, t), mdesc(sb + oW1B, t, kW1Col), idesc, t != 0);
     tc_commit(&bar_mma);
   }
+  const float step = p.wparams != nullptr ? __ldg(p.lr) : 0.f;  // (after griddepcontrol.wait)
   float h1[S1];
   float h2[kMid ? S2 : 1];
   if (worker) {
@@ -720,8 +728,18 @@ static int launch_fused(const FusedPlan* pl, cudaStream_t st) {
     DMLP_CUDA_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, kFusedSmem));
     attr_mask |= 1ull << dev;
   }
-  kern<<<dim3(kFC), kFThreads, kFusedSmem, st>>>(pl->tmXA, pl->tmXT, pl->tmW1, pl->tmW2B, pl->tmW2K, pl->tmWLB,
-                                                  pl->tmWLK, pl->p);
+  cudaLaunchConfig_t cfg;
+  memset(&cfg, 0, sizeof(cfg));
+  cfg.gridDim = dim3(kFC);
+  cfg.blockDim = dim3(kFThreads);
+  cfg.dynamicSmemBytes = kFusedSmem;
+  cfg.stream = st;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  attr[0].val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = 1;
+  DMLP_CUDA_CHECK(cudaLaunchKernelEx(&cfg, kern, pl->tmXA, pl->tmXT, pl->tmW1, pl->tmW2B, pl->tmW2K, pl->tmWLB, pl->tmWLK, pl->p));
   DMLP_CUDA_CHECK(cudaGetLastError());
   return DMLP_OK;
 }
