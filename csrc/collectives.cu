@@ -254,6 +254,7 @@ template <typename T, bool SGD>
 __global__ void __launch_bounds__(kCollThreads)
 allreduce_oneshot_kernel(const __grid_constant__ CollArgs a) {
   asm volatile("griddepcontrol.launch_dependents;" ::: "memory");  // a PDL successor may begin its prologue now
+  asm volatile("griddepcontrol.wait;" ::: "memory");               // predecessors' gradients are complete and visible
   constexpr int V = Pack<T>::N;
   const int rank = a.rank >= 0 ? a.rank : blockIdx.y;
   if ((a.dead_mask >> rank) & 1u) return;
@@ -344,6 +345,7 @@ template <typename T, bool SGD>
 __global__ void __launch_bounds__(kCollThreads)
 allreduce_twoshot_kernel(const __grid_constant__ CollArgs a) {
   asm volatile("griddepcontrol.launch_dependents;" ::: "memory");  // a PDL successor may begin its prologue now
+  asm volatile("griddepcontrol.wait;" ::: "memory");               // predecessors' gradients are complete and visible
   constexpr int V = Pack<T>::N;
   const int rank = a.rank >= 0 ? a.rank : blockIdx.y;
   if ((a.dead_mask >> rank) & 1u) return;
@@ -409,6 +411,7 @@ allreduce_twoshot_kernel(const __grid_constant__ CollArgs a) {
 template <typename T, bool SGD>
 __global__ void __launch_bounds__(kCollThreads)
 allreduce_ring_kernel(const __grid_constant__ CollArgs a) {
+  asm volatile("griddepcontrol.wait;" ::: "memory");
   constexpr int V = Pack<T>::N;
   const int rank = a.rank >= 0 ? a.rank : blockIdx.y;
   if ((a.dead_mask >> rank) & 1u) return;
@@ -593,7 +596,19 @@ static int launch_coll(K kern, const CollArgs& args, int blocks, int world_y, cu
     void* params[] = {const_cast<CollArgs*>(&args)};
     DMLP_CUDA_CHECK(cudaLaunchCooperativeKernel(reinterpret_cast<void*>(kern), grid, dim3(kCollThreads), params, 0, st));
   } else {
-    kern<<<grid, kCollThreads, 0, st>>>(args);
+    // Programmatic stream serialization: the kernel may be scheduled while its predecessor drains; it
+    // executes griddepcontrol.wait before touching any data.
+    cudaLaunchConfig_t cfg;
+    memset(&cfg, 0, sizeof(cfg));
+    cfg.gridDim = grid;
+    cfg.blockDim = dim3(kCollThreads);
+    cfg.stream = st;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = 1;
+    DMLP_CUDA_CHECK(cudaLaunchKernelEx(&cfg, kern, args));
     DMLP_CUDA_CHECK(cudaGetLastError());
   }
   return DMLP_OK;
