@@ -16,7 +16,8 @@ struct GemmParams {
   int block_n;
   int num_k_blocks;
   int stages;
-  uint32_t tmem_cols;
+  uint32_t tmem_cols;      // allocated TMEM columns (two accumulator buffers)
+  uint32_t tmem_buf_cols;  // columns of one buffer
   uint32_t a_stage_bytes, b_stage_bytes;
   uint32_t a_tx_bytes;  // bytes TMA actually delivers for A per stage (half a tile when M <= 64)
   uint32_t idesc;
@@ -45,6 +46,7 @@ struct GemmPlan {
   CUtensorMap tmA, tmB;
   GemmParams p;
   int grid_x, grid_y;
+  int total_tiles;
   size_t smem;
   int key;  // kernel instantiation: (bf16 << 2) | (a_mn << 1) | b_mn
 };

@@ -46,7 +46,8 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA,
 
   __shared__ __align__(8) uint64_t full_bar[kMaxStages];
   __shared__ __align__(8) uint64_t empty_bar[kMaxStages];
-  __shared__ __align__(8) uint64_t tmem_full_bar;
+  __shared__ __align__(8) uint64_t tmem_full_bar[2];   // accumulator buffer b holds a finished tile
+  __shared__ __align__(8) uint64_t tmem_empty_bar[2];  // the epilogue has drained buffer b
   __shared__ uint32_t tmem_base_slot;
   __shared__ float s_part[4][256];  // per-epilogue-warp column partials
   __shared__ float s_loss[4];
@@ -54,8 +55,11 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA,
 
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
-  const int m0 = blockIdx.y * BM;
-  const int n0 = blockIdx.x * p.block_n;
+  // Persistent CTA: tiles blockIdx.x, blockIdx.x + gridDim.x, ... (M fastest, so CTAs that run together share
+  // the same B tile through L2). Two TMEM accumulator buffers let the epilogue of one tile overlap the
+  // mainloop of the next.
+  const int tiles_m = (p.M + BM - 1) / BM;
+  const int total_tiles = tiles_m * ((p.N + p.block_n - 1) / p.block_n);
 
   if (warp == 0 && lane == 0) {
     tma_prefetch_desc(&tmA);
@@ -64,7 +68,10 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA,
       mbar_init(&full_bar[s], 1);
       mbar_init(&empty_bar[s], 1);
     }
-    mbar_init(&tmem_full_bar, 1);
+    for (int b = 0; b < 2; ++b) {
+      mbar_init(&tmem_full_bar[b], 1);
+      mbar_init(&tmem_empty_bar[b], 128);
+    }
     fence_mbar_init();
   }
   if (warp == 1) {
@@ -88,9 +95,13 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA,
     // ------------------------------------------------------------ TMA producer
     if (lane == 0) {
       const uint32_t stage_bytes = p.a_tx_bytes + p.b_stage_bytes;  // bytes TMA will deliver per stage
-      for (int kb = 0; kb < p.num_k_blocks; ++kb) {
-        const int s = kb % p.stages;
-        const uint32_t ph = (kb / p.stages) & 1;
+      uint32_t it = 0;  // k-block counter across all tiles of this CTA: the smem ring never drains between tiles
+      for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
+      const int m0 = (tile % tiles_m) * BM;
+      const int n0 = (tile / tiles_m) * p.block_n;
+      for (int kb = 0; kb < p.num_k_blocks; ++kb, ++it) {
+        const int s = it % p.stages;
+        const uint32_t ph = (it / p.stages) & 1;
         mbar_wait(&empty_bar[s], ph ^ 1);
         mbar_arrive_expect_tx(&full_bar[s], stage_bytes);
         uint8_t* a_dst = smem_a + static_cast<size_t>(s) * p.a_stage_bytes;
@@ -111,13 +122,20 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA,
             tma_load_2d(b_dst + j * MN_ATOM_COL_BYTES, &tmB, &full_bar[s], n0 + j * ATOM_MN, k0);
         }
       }
+      }
     }
   } else if (warp == 1) {
     // ------------------------------------------------------------ MMA issuer (one thread)
     if (lane == 0) {
-      for (int kb = 0; kb < p.num_k_blocks; ++kb) {
-        const int s = kb % p.stages;
-        const uint32_t ph = (kb / p.stages) & 1;
+      uint32_t it = 0, tcount = 0;
+      for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x, ++tcount) {
+      const uint32_t buf = tcount & 1;
+      mbar_wait(&tmem_empty_bar[buf], ((tcount >> 1) & 1) ^ 1);  // epilogue drained this buffer (free at first use)
+      tc_fence_after_sync();
+      const uint32_t tmem_acc = tmem_base + buf * p.tmem_buf_cols;
+      for (int kb = 0; kb < p.num_k_blocks; ++kb, ++it) {
+        const int s = it % p.stages;
+        const uint32_t ph = (it / p.stages) & 1;
         mbar_wait(&full_bar[s], ph);
         tc_fence_after_sync();
         const uint32_t a_addr = smem_u32(smem_a + static_cast<size_t>(s) * p.a_stage_bytes);
@@ -129,25 +147,31 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA,
                                       : make_smem_desc(a_addr + k * 32, 16, 1024);
           const uint64_t bdesc = B_MN ? make_smem_desc(b_addr + k * UK * 128, MN_ATOM_COL_BYTES, MN_SBO, MN_LAYOUT)
                                       : make_smem_desc(b_addr + k * 32, 16, 1024);
-          tc_mma<EB>(tmem_base, adesc, bdesc, p.idesc, (kb | k) != 0 ? 1u : 0u);
+          tc_mma<EB>(tmem_acc, adesc, bdesc, p.idesc, (kb | k) != 0 ? 1u : 0u);
         }
         tc_commit(&empty_bar[s]);  // frees the smem slot once these MMAs have read it
-        if (kb == p.num_k_blocks - 1) tc_commit(&tmem_full_bar);
+        if (kb == p.num_k_blocks - 1) tc_commit(&tmem_full_bar[buf]);
+      }
       }
     }
   } else {
     // ------------------------------------------------------------ epilogue warps
     const int q = warp & 3;  // TMEM lane quadrant this warp may access
     const int row = q * 32 + lane;
-    const int m = m0 + row;
-    const bool m_ok = m < p.M;
     const int etid = (warp - 2) * 32 + lane;   // 0..127 among the epilogue threads
     // A single M tile sees every row of the problem: its reductions (bias gradient, loss, hits) are
     // final and can be stored; otherwise they are accumulated atomically into zeroed buffers.
-    const bool direct = gridDim.y == 1;
-    mbar_wait(&tmem_full_bar, 0);
+    const bool direct = tiles_m == 1;
+    uint32_t tcount = 0;
+    for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x, ++tcount) {
+    const int m0 = (tile % tiles_m) * BM;
+    const int n0 = (tile / tiles_m) * p.block_n;
+    const int m = m0 + row;
+    const bool m_ok = m < p.M;
+    const uint32_t buf = tcount & 1;
+    mbar_wait(&tmem_full_bar[buf], (tcount >> 1) & 1);
     tc_fence_after_sync();
-    const uint32_t t_row = tmem_base + (static_cast<uint32_t>(q * 32) << 16);
+    const uint32_t t_row = tmem_base + buf * p.tmem_buf_cols + (static_cast<uint32_t>(q * 32) << 16);
 
     if (p.ce_labels != nullptr) {
       // ---- fused softmax cross-entropy (reference client.go:76-93,144-165,352-382): the whole logits
@@ -348,6 +372,11 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA,
         }
       }
     }
+    // this tile's accumulator has been read out: hand the TMEM buffer back to the MMA warp
+    if (p.colsum != nullptr || p.ce_labels != nullptr) asm volatile("bar.sync 1, 128;" ::: "memory");  // s_part reuse
+    tc_fence_before_sync();
+    mbar_arrive(&tmem_empty_bar[buf]);
+    }
   }
 
   tc_fence_before_sync();
@@ -504,7 +533,8 @@ int dmlp::gemm_plan_create(const dmlp_gemm_desc_t* d, GemmPlan* plan) {
   p.stages = stages;
   uint32_t cols = 32;
   while (cols < static_cast<uint32_t>(bn)) cols <<= 1;
-  p.tmem_cols = cols;
+  p.tmem_buf_cols = cols;   // one accumulator buffer
+  p.tmem_cols = 2 * cols;   // two of them (<= 512 columns)
   p.idesc = make_instr_desc(EB, d->a_major != 0, d->b_major != 0, bn);
   p.out_f32 = d->out_f32_dev; p.ld_out = d->ld_out;
   p.out_bf16 = reinterpret_cast<__nv_bfloat16*>(d->out_bf16_dev); p.ld_out_bf16 = d->ld_out_bf16;
@@ -519,8 +549,12 @@ int dmlp::gemm_plan_create(const dmlp_gemm_desc_t* d, GemmPlan* plan) {
     DMLP_REQUIRE(!d->relu && !d->mask_dev && !d->accumulate, "fused softmax-CE excludes relu/mask/accumulate");
   }
 
-  plan->grid_x = ceil_div(d->N, bn);
-  plan->grid_y = ceil_div(d->M, 128);
+  {
+    const int total = ceil_div(d->N, bn) * ceil_div(d->M, 128);
+    plan->total_tiles = total;
+    plan->grid_x = total < 148 ? total : 148;  // persistent: at most one CTA per SM
+    plan->grid_y = 1;
+  }
   plan->smem = stages * stage_bytes + 1024;
   plan->key = (bf16 ? 4 : 0) | (d->a_major ? 2 : 0) | (d->b_major ? 1 : 0);
   // PDL only for single-wave grids: an early-launched dependent must never compete with CTAs of
@@ -528,7 +562,7 @@ int dmlp::gemm_plan_create(const dmlp_gemm_desc_t* d, GemmPlan* plan) {
   {
     static int pdl_env = -1;
     if (pdl_env < 0) { const char* e = getenv("DMLP_PDL"); pdl_env = e ? atoi(e) : 1; }
-    p.pdl = (pdl_env && plan->grid_x * plan->grid_y <= 148) ? 1 : 0;
+    p.pdl = (pdl_env && plan->total_tiles <= 148) ? 1 : 0;
   }
   return DMLP_OK;
 }
