@@ -83,7 +83,9 @@ constexpr uint32_t oRS2 = oXA;                         // 8 src x 64 rows x 32 B
 constexpr uint32_t oDZ2K = oXA + 16384;                // 2 K blocks x 8 KiB
 constexpr uint32_t oAR3 = oW1B;                        // 8 src x 64 rows x 64 B = 32 KiB
 constexpr uint32_t oDZ2M = oW1B + 32768;               // 2 atoms x 8 KiB
-constexpr uint32_t oDZ1M = oW1B;                       // 4 atoms x 8 KiB
+constexpr uint32_t oDZ1M = oW1B;                       // 4 atoms x 8 KiB (three-layer model)
+constexpr uint32_t oDZ1M2 = oXA;                       // same, two-layer model: a peer may deliver dZ1 while this CTA
+                                                       // still reads the logits exchange (AR3), so it must not alias it
 constexpr uint32_t oH2K = oRS1;
 constexpr uint32_t oDZ3K = oRS1 + 8192;
 constexpr uint32_t oH2M = oRS1 + 16384;
@@ -109,6 +111,12 @@ __device__ __forceinline__ uint32_t mapa(uint32_t a, uint32_t cta) {
 }
 __device__ __forceinline__ void st_cluster_f4(uint32_t a, float x, float y, float z, float w) {
   asm volatile("st.shared::cluster.v4.f32 [%0], {%1, %2, %3, %4};" ::"r"(a), "f"(x), "f"(y), "f"(z), "f"(w) : "memory");
+}
+// Remote store whose completion is counted (in bytes) on an mbarrier in the destination CTA.
+__device__ __forceinline__ void st_async_f4(uint32_t a, uint32_t bar, float x, float y, float z, float w) {
+  asm volatile("st.async.weak.shared::cluster.mbarrier::complete_tx::bytes.v4.f32 [%0], {%1, %2, %3, %4}, [%5];" ::"r"(a),
+               "f"(x), "f"(y), "f"(z), "f"(w), "r"(bar)
+               : "memory");
 }
 __device__ __forceinline__ void cluster_sync_all() {
   asm volatile("barrier.cluster.arrive.release.aligned;\n\tbarrier.cluster.wait.acquire.aligned;" ::: "memory");
@@ -178,10 +186,14 @@ mlp_fused_step_kernel(const __grid_constant__ CUtensorMap tmXA, const __grid_con
   constexpr bool kMid = S2 > 0;
   constexpr int SL = kMid ? S2 : S1;  // K-slice of the last layer
   constexpr int LAST = kMid ? 2 : 1;
+  static_assert(S1 == 16 && (S2 == 8 || S2 == 0), "slice widths this kernel was laid out for");
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~static_cast<uintptr_t>(1023));
   const uint32_t sb = smem_u32(smem);
-  __shared__ __align__(8) uint64_t bar_tma0, bar_tma1, bar_mma;
+  // bar_mma: the critical chain F1 -> F2 -> F3 -> dgrad_last -> dgrad2 -> wgrad1 (phase toggles per use);
+  // bar_wgl / bar_wg2: weight-gradient GEMMs that run beside the chain; bar_ex[k]: arrival of exchange k
+  // (remote st.async stores complete transaction bytes on the DESTINATION's barrier: no cluster-wide barrier).
+  __shared__ __align__(8) uint64_t bar_tma0, bar_tma1, bar_mma, bar_wgl, bar_wg2, bar_ex[5];
   __shared__ uint32_t tmem_slot;
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -201,7 +213,18 @@ mlp_fused_step_kernel(const __grid_constant__ CUtensorMap tmXA, const __grid_con
     mbar_init(&bar_tma0, 1);
     mbar_init(&bar_tma1, 1);
     mbar_init(&bar_mma, 1);
+    mbar_init(&bar_wgl, 1);
+    mbar_init(&bar_wg2, 1);
+    for (int k = 0; k < 5; ++k) mbar_init(&bar_ex[k], 1);
     fence_mbar_init();
+    // arm the exchange barriers: bytes every CTA of the cluster (this one included) will deliver
+    mbar_arrive_expect_tx(&bar_ex[0], kFC * B * S1 * 4);
+    mbar_arrive_expect_tx(&bar_ex[2], kFC * B * 64);
+    mbar_arrive_expect_tx(&bar_ex[4], kFC * B * S1 * 4);
+    if (kMid) {
+      mbar_arrive_expect_tx(&bar_ex[1], kFC * B * S2 * 4);
+      mbar_arrive_expect_tx(&bar_ex[3], kFC * B * S2 * 4 * 2);
+    }
   }
   if (warp == 0) {
     tmem_alloc(&tmem_slot, 512);
@@ -213,10 +236,9 @@ mlp_fused_step_kernel(const __grid_constant__ CUtensorMap tmXA, const __grid_con
   const uint32_t tm = tmem_slot;
   uint32_t mma_phase = 0;
   FPROF(0);
-  cluster_sync_all();  // every CTA's shared memory is live before anyone writes into it
+  cluster_sync_all();  // every CTA's shared memory and barriers are live before anyone writes into them
   FPROF(1);
 
-  // ------------------------------------------------------------------ P0: loads + layer-1 partial
   // Programmatic dependent launch: this grid may start while its predecessor in the stream (the previous
   // step's kernel, or its all-reduce) is still finishing. Everything so far — and the input loads
   // just below — touch nothing the predecessor writes; parameters and gradients are only accessed
@@ -239,6 +261,7 @@ mlp_fused_step_kernel(const __grid_constant__ CUtensorMap tmXA, const __grid_con
     }
     tma_load_2d(smem + oWLB, &tmWLB, &bar_tma1, 0, SL * j);
     tma_load_2d(smem + oWLK, &tmWLK, &bar_tma1, 0, SL * j);
+    // ---------------------------------------------------------------- F1: P1 = X_j . W1_j
     mbar_wait(&bar_tma0, 0);
     tc_fence_after_sync();
     const uint32_t idesc = make_instr_desc(4, false, true, H1);
@@ -256,27 +279,25 @@ mlp_fused_step_kernel(const __grid_constant__ CUtensorMap tmXA, const __grid_con
 #pragma unroll
     for (int i = 0; i < kFC; ++i) {
       uint32_t r[16];
-      static_assert(S1 == 16, "layer-1 slice width");
       tmem_ld_x16(tm + tq + cF1 + S1 * i, r);
       tmem_ld_wait();
       if (rok) {
         const uint32_t dst = mapa(sb + oRS1 + (j * 64 + row) * (S1 * 4), i);
+        const uint32_t bar = mapa(smem_u32(&bar_ex[0]), i);
 #pragma unroll
         for (int c = 0; c < S1; c += 4)
-          st_cluster_f4(dst + c * 4, __uint_as_float(r[c]), __uint_as_float(r[c + 1]), __uint_as_float(r[c + 2]),
-                        __uint_as_float(r[c + 3]));
+          st_async_f4(dst + c * 4, bar, __uint_as_float(r[c]), __uint_as_float(r[c + 1]), __uint_as_float(r[c + 2]),
+                      __uint_as_float(r[c + 3]));
       }
     }
   }
   mma_phase ^= 1;
   FPROF(2);
-  tc_fence_before_sync();
-  cluster_sync_all();
-  tc_fence_after_sync();
-  FPROF(3);
 
   // ------------------------------------------------------------------ P1: H1_j, layer-2 partial
   if (worker) {
+    mbar_wait(&bar_ex[0], 0);
+    FPROF(3);
 #pragma unroll
     for (int c = 0; c < S1; ++c) h1[c] = 0.f;
     if (rok) {
@@ -327,19 +348,18 @@ mlp_fused_step_kernel(const __grid_constant__ CUtensorMap tmXA, const __grid_con
         tmem_ld_wait();
         if (rok) {
           const uint32_t dst = mapa(sb + oRS2 + (j * 64 + row) * (S2 * 4), i);
-          st_cluster_f4(dst, __uint_as_float(r[0]), __uint_as_float(r[1]), __uint_as_float(r[2]), __uint_as_float(r[3]));
-          st_cluster_f4(dst + 16, __uint_as_float(r[4]), __uint_as_float(r[5]), __uint_as_float(r[6]), __uint_as_float(r[7]));
+          const uint32_t bar = mapa(smem_u32(&bar_ex[1]), i);
+          st_async_f4(dst, bar, __uint_as_float(r[0]), __uint_as_float(r[1]), __uint_as_float(r[2]), __uint_as_float(r[3]));
+          st_async_f4(dst + 16, bar, __uint_as_float(r[4]), __uint_as_float(r[5]), __uint_as_float(r[6]), __uint_as_float(r[7]));
         }
       }
     }
     mma_phase ^= 1;
     FPROF(4);
-    tc_fence_before_sync();
-    cluster_sync_all();
-    tc_fence_after_sync();
-    FPROF(5);
     // ---------------------------------------------------------------- P2: H2_j
     if (worker) {
+      mbar_wait(&bar_ex[1], 0);
+      FPROF(5);
 #pragma unroll
       for (int c = 0; c < S2; ++c) h2[c] = 0.f;
       if (rok) {
@@ -369,6 +389,7 @@ mlp_fused_step_kernel(const __grid_constant__ CUtensorMap tmXA, const __grid_con
   }
   // ------------------------------------------------------------------ last layer partial -> all-reduce
   const uint32_t oHLK = kMid ? oH2K : oH1K;
+  const uint32_t oDZ1 = kMid ? oDZ1M : oDZ1M2;
   const uint32_t oHLM = kMid ? oH2M : oH1M;
   if (threadIdx.x == 0) {
     if (!kMid) mbar_wait(&bar_tma1, 0);
@@ -389,23 +410,22 @@ mlp_fused_step_kernel(const __grid_constant__ CUtensorMap tmXA, const __grid_con
 #pragma unroll
       for (int i = 0; i < kFC; ++i) {
         const uint32_t dst = mapa(sb + oAR3 + (j * 64 + row) * 64, i);
+        const uint32_t bar = mapa(smem_u32(&bar_ex[2]), i);
 #pragma unroll
         for (int c = 0; c < 16; c += 4)
-          st_cluster_f4(dst + c * 4, __uint_as_float(r[c]), __uint_as_float(r[c + 1]), __uint_as_float(r[c + 2]),
-                        __uint_as_float(r[c + 3]));
+          st_async_f4(dst + c * 4, bar, __uint_as_float(r[c]), __uint_as_float(r[c + 1]), __uint_as_float(r[c + 2]),
+                      __uint_as_float(r[c + 3]));
       }
     }
   }
   mma_phase ^= 1;
   FPROF(6);
-  tc_fence_before_sync();
-  cluster_sync_all();
-  tc_fence_after_sync();
-  FPROF(7);
 
   // ------------------------------------------------------------------ P3: softmax-CE, last-layer grads
   float dz3[16];
   if (worker) {
+    mbar_wait(&bar_ex[2], 0);
+    FPROF(7);
     float z[16];
 #pragma unroll
     for (int c = 0; c < 16; ++c) z[c] = 0.f;
@@ -463,31 +483,119 @@ mlp_fused_step_kernel(const __grid_constant__ CUtensorMap tmXA, const __grid_con
         hit += __shfl_xor_sync(0xffffffffu, hit, o);
       }
       if (lane == 0) { red[wwarp] = loss; reinterpret_cast<int*>(red)[8 + wwarp] = hit; }
-      asm volatile("bar.sync 1, 128;" ::: "memory");
-      if (wwarp == 0 && lane == 0) {
-        p.metrics[0] = red[0] + red[1] + red[2] + red[3];
-        reinterpret_cast<int*>(p.metrics)[1] = reinterpret_cast<int*>(red)[8] + reinterpret_cast<int*>(red)[9] +
-                                               reinterpret_cast<int*>(red)[10] + reinterpret_cast<int*>(red)[11];
-      }
     }
   }
   __syncthreads();
   if (threadIdx.x == 0) {
     fence_proxy_async_smem();
     tc_fence_after_sync();
-    // dW_last[SL x 16] = HL_j^T . dZ3   (A and B MN-major, K = batch)
-    const uint32_t idw = make_instr_desc(4, true, true, 16);
-    for (int t = 0; t < B / 8; ++t)
-      tc_mma<4>(tm + cWGL, mdesc(sb + oHLM, t, kColM), mdesc(sb + oDZ3M, t, kColM), idw, t != 0);
-    // dHL_j[B x SL] = dZ3 . W_last_j^T  (A and B K-major, K = 16)
+    // critical: dHL_j[B x SL] = dZ3 . W_last_j^T  (A and B K-major, K = 16)
     const uint32_t idg = make_instr_desc(4, false, false, 16);
     for (int t = 0; t < 2; ++t) tc_mma<4>(tm + cDGL, kdesc(sb + oDZ3K, t), kdesc(sb + oWLK, t), idg, t != 0);
     tc_commit(&bar_mma);
+    // beside the chain: dW_last[SL x 16] = HL_j^T . dZ3   (A and B MN-major, K = batch)
+    const uint32_t idw = make_instr_desc(4, true, true, 16);
+    for (int t = 0; t < B / 8; ++t)
+      tc_mma<4>(tm + cWGL, mdesc(sb + oHLM, t, kColM), mdesc(sb + oDZ3M, t, kColM), idw, t != 0);
+    tc_commit(&bar_wgl);
+  }
+  if (worker && j == 0 && wwarp == 0 && lane == 0) {  // (red[] was filled before the __syncthreads above)
+    p.metrics[0] = red[0] + red[1] + red[2] + red[3];
+    reinterpret_cast<int*>(p.metrics)[1] = reinterpret_cast<int*>(red)[8] + reinterpret_cast<int*>(red)[9] +
+                                           reinterpret_cast<int*>(red)[10] + reinterpret_cast<int*>(red)[11];
   }
   float dzl[SL];
-  float dbl[16];  // last-layer bias gradient (valid in the thread that owns accumulator row SL)
   if (worker) {
     mbar_wait(&bar_mma, mma_phase);
+    tc_fence_after_sync();
+    uint32_t r[16];
+    tmem_ld_x16(tm + tq + cDGL, r);
+    tmem_ld_wait();
+#pragma unroll
+    for (int c = 0; c < SL; ++c) {
+      const float hl = kMid ? h2[kMid ? c : 0] : h1[kMid ? 0 : c];
+      dzl[c] = (rok && hl > 0.f) ? __uint_as_float(r[c]) : 0.f;
+    }
+  }
+  mma_phase ^= 1;
+
+  float dz1[S1];
+  if (kMid) {
+    // all-gather dZ2_j (= dzl) into every CTA: K-major (A of dgrad2) and MN-major (B of wgrad2)
+    if (rok) {
+#pragma unroll
+      for (int i = 0; i < kFC; ++i) {
+        const uint32_t bar = mapa(smem_u32(&bar_ex[3]), i);
+        const uint32_t dm = mapa(sb + oDZ2M + moff(row, S2 * j), i);
+        st_async_f4(mapa(sb + oDZ2K + koff(row, S2 * j), i), bar, dzl[0], dzl[1], dzl[2], dzl[3]);
+        st_async_f4(mapa(sb + oDZ2K + koff(row, S2 * j + 4), i), bar, dzl[4], dzl[5], dzl[6], dzl[7]);
+        st_async_f4(dm, bar, dzl[0], dzl[1], dzl[2], dzl[3]);
+        st_async_f4(dm + 16, bar, dzl[4], dzl[5], dzl[6], dzl[7]);
+      }
+      if (p.dbg)
+        for (int c = 0; c < S2; ++c) p.dbg[64 * H1 + 64 * H2 + 64 * 16 + row * H2 + S2 * j + c] = dzl[c];
+    }
+    FPROF(8);
+    // ---------------------------------------------------------------- P4: layer-2 grads
+    if (threadIdx.x == 0) {
+      mbar_wait(&bar_ex[3], 0);
+      fence_proxy_async_smem();
+      tc_fence_after_sync();
+      const uint32_t idg = make_instr_desc(4, false, false, 16);
+      for (int t = 0; t < H2 / 8; ++t)
+        tc_mma<4>(tm + cDG2, kdesc(sb + oDZ2K, t), make_smem_desc(sb + oW2K + (t >> 2) * 4096 + (t & 3) * 32, 16, 1024, 2), idg, t != 0);
+      tc_commit(&bar_mma);
+      const uint32_t idw = make_instr_desc(4, true, true, H2);
+      for (int t = 0; t < B / 8; ++t)
+        tc_mma<4>(tm + cWG2, mdesc(sb + oH1M, t, kColM), mdesc(sb + oDZ2M, t, kColM), idw, t != 0);
+      tc_commit(&bar_wg2);
+    }
+    if (worker) {
+      mbar_wait(&bar_mma, mma_phase);
+      FPROF(9);
+      tc_fence_after_sync();
+      uint32_t r[16];
+      tmem_ld_x16(tm + tq + cDG2, r);
+      tmem_ld_wait();
+#pragma unroll
+      for (int c = 0; c < S1; ++c) dz1[c] = (rok && h1[c] > 0.f) ? __uint_as_float(r[c]) : 0.f;
+    }
+    mma_phase ^= 1;
+  } else {
+#pragma unroll
+    for (int c = 0; c < S1; ++c) dz1[c] = dzl[kMid ? 0 : c];
+  }
+  // all-gather dZ1_j into every CTA (MN-major: B operand of the layer-1 weight gradient)
+  if (rok) {
+#pragma unroll
+    for (int i = 0; i < kFC; ++i) {
+      const uint32_t bar = mapa(smem_u32(&bar_ex[4]), i);
+      const uint32_t dm = mapa(sb + oDZ1 + moff(row, S1 * j), i);
+      st_async_f4(dm, bar, dz1[0], dz1[1], dz1[2], dz1[3]);
+      st_async_f4(dm + 16, bar, dz1[4], dz1[5], dz1[6], dz1[7]);
+      const uint32_t dm2 = mapa(sb + oDZ1 + moff(row, S1 * j + 8), i);
+      st_async_f4(dm2, bar, dz1[8], dz1[9], dz1[10], dz1[11]);
+      st_async_f4(dm2 + 16, bar, dz1[12], dz1[13], dz1[14], dz1[15]);
+    }
+    if (p.dbg)
+      for (int c = 0; c < S1; ++c) p.dbg[64 * H1 + 128 * (kMid ? H2 : 0) + 64 * 16 + row * H1 + S1 * j + c] = dz1[c];
+  }
+  FPROF(10);
+
+  // ------------------------------------------------------------------ P5: dW1_j = X_j^T . dZ1
+  if (threadIdx.x == 0) {
+    mbar_wait(&bar_ex[4], 0);
+    fence_proxy_async_smem();
+    tc_fence_after_sync();
+    const uint32_t idw = make_instr_desc(4, true, true, H1);
+    for (int t = 0; t < B / 8; ++t)
+      tc_mma<4>(tm + cWG1, mdesc(sb + oXT, t, kColM), mdesc(sb + oDZ1, t, kColM), idw, t != 0);
+    tc_commit(&bar_mma);
+  }
+  float dbl[16];  // last-layer bias gradient (valid in the thread that owns accumulator row SL)
+  if (worker) {
+    // while dW1 runs on the tensor core: drain the weight-gradient GEMMs that ran beside the chain
+    mbar_wait(&bar_wgl, 0);
     tc_fence_after_sync();
     {
       uint32_t r[16];
@@ -504,54 +612,8 @@ mlp_fused_step_kernel(const __grid_constant__ CUtensorMap tmXA, const __grid_con
         for (int c = 0; c < 16; ++c) dbl[c] = __uint_as_float(r[c]);
       }
     }
-    {
-      uint32_t r[16];
-      tmem_ld_x16(tm + tq + cDGL, r);
-      tmem_ld_wait();
-#pragma unroll
-      for (int c = 0; c < SL; ++c) {
-        const float hl = kMid ? h2[kMid ? c : 0] : h1[kMid ? 0 : c];
-        dzl[c] = (rok && hl > 0.f) ? __uint_as_float(r[c]) : 0.f;
-      }
-    }
-  }
-  mma_phase ^= 1;
-
-  float dz1[S1];
-  if (kMid) {
-    // all-gather dZ2_j (= dzl) into every CTA: K-major (A of dgrad2) and MN-major (B of wgrad2)
-    if (rok) {
-#pragma unroll
-      for (int i = 0; i < kFC; ++i) {
-        const uint32_t dk = mapa(sb + oDZ2K + koff(row, S2 * j), i);
-        const uint32_t dm = mapa(sb + oDZ2M + moff(row, S2 * j), i);
-        st_cluster_f4(dk, dzl[0], dzl[1], dzl[2], dzl[3]);
-        st_cluster_f4(mapa(sb + oDZ2K + koff(row, S2 * j + 4), i), dzl[4], dzl[5], dzl[6], dzl[7]);
-        st_cluster_f4(dm, dzl[0], dzl[1], dzl[2], dzl[3]);
-        st_cluster_f4(dm + 16, dzl[4], dzl[5], dzl[6], dzl[7]);
-      }
-      if (p.dbg)
-        for (int c = 0; c < S2; ++c) p.dbg[64 * H1 + 64 * H2 + 64 * 16 + row * H2 + S2 * j + c] = dzl[c];
-    }
-    fence_proxy_async_smem();
-    FPROF(8);
-    tc_fence_before_sync();
-    cluster_sync_all();
-    tc_fence_after_sync();
-    FPROF(9);
-    // ---------------------------------------------------------------- P4: layer-2 grads
-    if (threadIdx.x == 0) {
-      fence_proxy_async_smem();
-      const uint32_t idw = make_instr_desc(4, true, true, H2);
-      for (int t = 0; t < B / 8; ++t)
-        tc_mma<4>(tm + cWG2, mdesc(sb + oH1M, t, kColM), mdesc(sb + oDZ2M, t, kColM), idw, t != 0);
-      const uint32_t idg = make_instr_desc(4, false, false, 16);
-      for (int t = 0; t < H2 / 8; ++t)
-        tc_mma<4>(tm + cDG2, kdesc(sb + oDZ2K, t), make_smem_desc(sb + oW2K + (t >> 2) * 4096 + (t & 3) * 32, 16, 1024, 2), idg, t != 0);
-      tc_commit(&bar_mma);
-    }
-    if (worker) {
-      mbar_wait(&bar_mma, mma_phase);
+    if (kMid) {
+      mbar_wait(&bar_wg2, 0);
       tc_fence_after_sync();
 #pragma unroll
       for (int cc = 0; cc < H2; cc += 16) {
@@ -573,48 +635,9 @@ mlp_fused_step_kernel(const __grid_constant__ CUtensorMap tmXA, const __grid_con
               emit_grad4(p, step, off + (c - c0), __uint_as_float(r[c]), __uint_as_float(r[c + 1]), __uint_as_float(r[c + 2]), __uint_as_float(r[c + 3]));
         }
       }
-      uint32_t r[16];
-      tmem_ld_x16(tm + tq + cDG2, r);
-      tmem_ld_wait();
-#pragma unroll
-      for (int c = 0; c < S1; ++c) dz1[c] = (rok && h1[c] > 0.f) ? __uint_as_float(r[c]) : 0.f;
     }
-    mma_phase ^= 1;
-  } else {
-#pragma unroll
-    for (int c = 0; c < S1; ++c) dz1[c] = dzl[kMid ? 0 : c];
-  }
-  // all-gather dZ1_j into every CTA (MN-major: B operand of the layer-1 weight gradient)
-  if (rok) {
-#pragma unroll
-    for (int i = 0; i < kFC; ++i) {
-      const uint32_t dm = mapa(sb + oDZ1M + moff(row, S1 * j), i);
-      st_cluster_f4(dm, dz1[0], dz1[1], dz1[2], dz1[3]);
-      st_cluster_f4(dm + 16, dz1[4], dz1[5], dz1[6], dz1[7]);
-      const uint32_t dm2 = mapa(sb + oDZ1M + moff(row, S1 * j + 8), i);
-      st_cluster_f4(dm2, dz1[8], dz1[9], dz1[10], dz1[11]);
-      st_cluster_f4(dm2 + 16, dz1[12], dz1[13], dz1[14], dz1[15]);
-    }
-    if (p.dbg)
-      for (int c = 0; c < S1; ++c) p.dbg[64 * H1 + 128 * (kMid ? H2 : 0) + 64 * 16 + row * H1 + S1 * j + c] = dz1[c];
-  }
-  fence_proxy_async_smem();
-  FPROF(10);
-  tc_fence_before_sync();
-  cluster_sync_all();
-  tc_fence_after_sync();
-  FPROF(11);
-
-  // ------------------------------------------------------------------ P5: dW1_j = X_j^T . dZ1
-  if (threadIdx.x == 0) {
-    fence_proxy_async_smem();
-    const uint32_t idw = make_instr_desc(4, true, true, H1);
-    for (int t = 0; t < B / 8; ++t)
-      tc_mma<4>(tm + cWG1, mdesc(sb + oXT, t, kColM), mdesc(sb + oDZ1M, t, kColM), idw, t != 0);
-    tc_commit(&bar_mma);
-  }
-  if (worker) {
     mbar_wait(&bar_mma, mma_phase);
+    FPROF(11);
     tc_fence_after_sync();
 #pragma unroll
     for (int cc = 0; cc < H1; cc += 16) {

@@ -67,8 +67,8 @@ def main():
         e1.record(st)
         torch.cuda.synchronize()
     acc /= n
-    names = ["entry", "cluster live", "F1 mma+scatter", "sync1", "H1+F2+scatter", "sync2", "H2+F3+allreduce", "sync3",
-             "CE+wgL+dgL+gather", "sync4", "wg2+dg2+gather", "sync5", "wg1+store"]
+    names = ["entry", "cluster live", "F1 mma+scatter", "RS1 arrived", "H1+F2+scatter", "RS2 arrived", "H2+F3+allreduce",
+             "logits arrived", "CE+dgL+gather dZ2", "dgrad2 done", "gather dZ1", "wgrads drained + wg1 done", "stores"]
     mean = acc.mean(axis=0)
     out = {"us_per_launch_graph": round(e0.elapsed_time(e1) * 1e3 / 50, 2),
            "phase_end_us_mean_over_ctas": {names[i]: round(mean[i] / 1e3, 2) for i in range(13)},
