@@ -53,7 +53,11 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA,
   __shared__ float s_loss[4];
   __shared__ int s_hit[4];
 
-  const int warp = threadIdx.x >> 5;
+  // Warp index through a shuffle: the compiler then knows the role branches below are warp-uniform and
+  // keeps descriptors, barrier addresses and loop counters in uniform registers. With a thread-dependent
+  // branch (`lane == 0`) every tcgen05.mma / TMA issue is wrapped in a per-lane "waterfall" loop of
+  // R2UR moves and costs ~170 cycles instead of ~40 (scripts/probe_mma_issue.cu, profiles/r1_mma_issue_probe.md).
+  const int warp = __shfl_sync(0xffffffffu, threadIdx.x >> 5, 0);
   const int lane = threadIdx.x & 31;
   // Persistent CTA: tiles blockIdx.x, blockIdx.x + gridDim.x, ... (M fastest, so CTAs that run together share
   // the same B tile through L2). Two TMEM accumulator buffers let the epilogue of one tile overlap the
@@ -81,7 +85,7 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA,
   tc_fence_before_sync();
   __syncthreads();
   tc_fence_after_sync();
-  const uint32_t tmem_base = tmem_base_slot;
+  const uint32_t tmem_base = __shfl_sync(0xffffffffu, tmem_base_slot, 0);
   if (p.pdl) {
     // Programmatic dependent launch: everything above (barrier init, TMEM allocation, descriptor
     // prefetch) overlapped the tail of the previous kernel in the stream. From here on this kernel
@@ -92,66 +96,73 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA,
   }
 
   if (warp == 0) {
-    // ------------------------------------------------------------ TMA producer
-    if (lane == 0) {
+    // ------------------------------------------------------------ TMA producer (whole warp loops, one lane issues)
+    {
       const uint32_t stage_bytes = p.a_tx_bytes + p.b_stage_bytes;  // bytes TMA will deliver per stage
-      uint32_t it = 0;  // k-block counter across all tiles of this CTA: the smem ring never drains between tiles
+      const int n_atoms = (p.block_n + ATOM_MN - 1) / ATOM_MN;
+      // k-block counter across all tiles of this CTA: the smem ring never drains between tiles
+      int s = 0;
+      uint32_t ph = 0;
       for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
-      const int m0 = (tile % tiles_m) * BM;
-      const int n0 = (tile / tiles_m) * p.block_n;
-      for (int kb = 0; kb < p.num_k_blocks; ++kb, ++it) {
-        const int s = it % p.stages;
-        const uint32_t ph = (it / p.stages) & 1;
-        mbar_wait(&empty_bar[s], ph ^ 1);
-        mbar_arrive_expect_tx(&full_bar[s], stage_bytes);
-        uint8_t* a_dst = smem_a + static_cast<size_t>(s) * p.a_stage_bytes;
-        uint8_t* b_dst = smem_b + static_cast<size_t>(s) * p.b_stage_bytes;
-        const int k0 = kb * KS;
-        if constexpr (!A_MN) {
-          tma_load_2d(a_dst, &tmA, &full_bar[s], k0, m0);
-        } else {
+        const int m0 = (tile % tiles_m) * BM;
+        const int n0 = (tile / tiles_m) * p.block_n;
+        for (int kb = 0; kb < p.num_k_blocks; ++kb) {
+          mbar_wait(&empty_bar[s], ph ^ 1);
+          if (elect_one()) {
+            mbar_arrive_expect_tx(&full_bar[s], stage_bytes);
+            uint8_t* a_dst = smem_a + static_cast<size_t>(s) * p.a_stage_bytes;
+            uint8_t* b_dst = smem_b + static_cast<size_t>(s) * p.b_stage_bytes;
+            const int k0 = kb * KS;
+            if constexpr (!A_MN) {
+              tma_load_2d(a_dst, &tmA, &full_bar[s], k0, m0);
+            } else {
 #pragma unroll
-          for (int j = 0; j < BM / ATOM_MN; ++j)
-            tma_load_2d(a_dst + j * MN_ATOM_COL_BYTES, &tmA, &full_bar[s], m0 + j * ATOM_MN, k0);
+              for (int j = 0; j < BM / ATOM_MN; ++j)
+                tma_load_2d(a_dst + j * MN_ATOM_COL_BYTES, &tmA, &full_bar[s], m0 + j * ATOM_MN, k0);
+            }
+            if constexpr (!B_MN) {
+              tma_load_2d(b_dst, &tmB, &full_bar[s], k0, n0);
+            } else {
+              for (int j = 0; j < n_atoms; ++j)
+                tma_load_2d(b_dst + j * MN_ATOM_COL_BYTES, &tmB, &full_bar[s], n0 + j * ATOM_MN, k0);
+            }
+          }
+          __syncwarp();
+          if (++s == p.stages) { s = 0; ph ^= 1; }
         }
-        if constexpr (!B_MN) {
-          tma_load_2d(b_dst, &tmB, &full_bar[s], k0, n0);
-        } else {
-          const int n_atoms = (p.block_n + ATOM_MN - 1) / ATOM_MN;
-          for (int j = 0; j < n_atoms; ++j)
-            tma_load_2d(b_dst + j * MN_ATOM_COL_BYTES, &tmB, &full_bar[s], n0 + j * ATOM_MN, k0);
-        }
-      }
       }
     }
   } else if (warp == 1) {
-    // ------------------------------------------------------------ MMA issuer (one thread)
-    if (lane == 0) {
-      uint32_t it = 0, tcount = 0;
+    // ------------------------------------------------------------ MMA issuer (whole warp loops, one lane issues)
+    {
+      const uint32_t a_base = smem_u32(smem_a), b_base = smem_u32(smem_b);
+      // descriptor bits that never change; the 14-bit start address (>> 4) is added per stage / k step
+      const uint64_t adesc0 = A_MN ? make_smem_desc(0, MN_ATOM_COL_BYTES, MN_SBO, MN_LAYOUT) : make_smem_desc(0, 16, 1024);
+      const uint64_t bdesc0 = B_MN ? make_smem_desc(0, MN_ATOM_COL_BYTES, MN_SBO, MN_LAYOUT) : make_smem_desc(0, 16, 1024);
+      constexpr uint32_t A_KSTEP = (A_MN ? UK * 128 : 32) >> 4, B_KSTEP = (B_MN ? UK * 128 : 32) >> 4;
+      int s = 0;
+      uint32_t ph = 0, tcount = 0;
       for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x, ++tcount) {
-      const uint32_t buf = tcount & 1;
-      mbar_wait(&tmem_empty_bar[buf], ((tcount >> 1) & 1) ^ 1);  // epilogue drained this buffer (free at first use)
-      tc_fence_after_sync();
-      const uint32_t tmem_acc = tmem_base + buf * p.tmem_buf_cols;
-      for (int kb = 0; kb < p.num_k_blocks; ++kb, ++it) {
-        const int s = it % p.stages;
-        const uint32_t ph = (it / p.stages) & 1;
-        mbar_wait(&full_bar[s], ph);
+        const uint32_t buf = tcount & 1;
+        mbar_wait(&tmem_empty_bar[buf], ((tcount >> 1) & 1) ^ 1);  // epilogue drained this buffer (free at first use)
         tc_fence_after_sync();
-        const uint32_t a_addr = smem_u32(smem_a + static_cast<size_t>(s) * p.a_stage_bytes);
-        const uint32_t b_addr = smem_u32(smem_b + static_cast<size_t>(s) * p.b_stage_bytes);
-#pragma unroll
-        for (int k = 0; k < KS / UK; ++k) {
+        const uint32_t tmem_acc = tmem_base + buf * p.tmem_buf_cols;
+        for (int kb = 0; kb < p.num_k_blocks; ++kb) {
+          mbar_wait(&full_bar[s], ph);
+          tc_fence_after_sync();
           // K-major: step 32 B inside the 128 B swizzle row. MN-major: step UK k-rows of 128 B.
-          const uint64_t adesc = A_MN ? make_smem_desc(a_addr + k * UK * 128, MN_ATOM_COL_BYTES, MN_SBO, MN_LAYOUT)
-                                      : make_smem_desc(a_addr + k * 32, 16, 1024);
-          const uint64_t bdesc = B_MN ? make_smem_desc(b_addr + k * UK * 128, MN_ATOM_COL_BYTES, MN_SBO, MN_LAYOUT)
-                                      : make_smem_desc(b_addr + k * 32, 16, 1024);
-          tc_mma<EB>(tmem_acc, adesc, bdesc, p.idesc, (kb | k) != 0 ? 1u : 0u);
+          const uint64_t adesc = adesc0 + ((a_base + s * p.a_stage_bytes) >> 4);
+          const uint64_t bdesc = bdesc0 + ((b_base + s * p.b_stage_bytes) >> 4);
+          if (elect_one()) {
+#pragma unroll
+            for (int k = 0; k < KS / UK; ++k)
+              tc_mma<EB>(tmem_acc, adesc + k * A_KSTEP, bdesc + k * B_KSTEP, p.idesc, (kb | k) != 0 ? 1u : 0u);
+            tc_commit(&empty_bar[s]);  // frees the smem slot once these MMAs have read it
+            if (kb == p.num_k_blocks - 1) tc_commit(&tmem_full_bar[buf]);
+          }
+          __syncwarp();
+          if (++s == p.stages) { s = 0; ph ^= 1; }
         }
-        tc_commit(&empty_bar[s]);  // frees the smem slot once these MMAs have read it
-        if (kb == p.num_k_blocks - 1) tc_commit(&tmem_full_bar[buf]);
-      }
       }
     }
   } else {

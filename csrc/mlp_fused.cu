@@ -196,7 +196,11 @@ mlp_fused_step_kernel(const __grid_constant__ CUtensorMap tmXA, const __grid_con
   __shared__ __align__(8) uint64_t bar_tma0, bar_tma1, bar_mma, bar_wgl, bar_wg2, bar_ex[5];
   __shared__ uint32_t tmem_slot;
 
-  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  // Warp index through a shuffle: the role branches are then provably warp-uniform and the control warp's
+  // descriptors live in uniform registers (a `threadIdx.x == 0` branch wraps every tcgen05.mma / TMA issue in a
+  // per-lane R2UR loop: ~170 instead of ~40 cycles per instruction, profiles/r1_mma_issue_probe.md).
+  // Control work is done by warp 0: all lanes wait, one elected lane issues.
+  const int warp = __shfl_sync(0xffffffffu, threadIdx.x >> 5, 0), lane = threadIdx.x & 31;
   const int j = static_cast<int>(cluster_ctarank());
   const int B = p.B;
   const int ngroups = p.in0 / 8;
@@ -233,7 +237,7 @@ mlp_fused_step_kernel(const __grid_constant__ CUtensorMap tmXA, const __grid_con
   tc_fence_before_sync();
   __syncthreads();
   tc_fence_after_sync();
-  const uint32_t tm = tmem_slot;
+  const uint32_t tm = __shfl_sync(0xffffffffu, tmem_slot, 0);
   uint32_t mma_phase = 0;
   FPROF(0);
   cluster_sync_all();  // every CTA's shared memory and barriers are live before anyone writes into them
@@ -244,7 +248,7 @@ mlp_fused_step_kernel(const __grid_constant__ CUtensorMap tmXA, const __grid_con
   // just below — touch nothing the predecessor writes; parameters and gradients are only accessed
   // after griddepcontrol.wait.
   asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
-  if (threadIdx.x == 0) {
+  if (warp == 0 && elect_one()) {
     mbar_arrive_expect_tx(&bar_tma0, 4 * kTileK + (H1 / 32) * kW1Col);
     for (int b = 0; b < 4; ++b) tma_load_2d(smem + oXA + b * kTileK, &tmXA, &bar_tma0, k0 + 32 * b, 0);
     uint32_t bytes1 = 4 * kColM + 2 * SL * 128;
@@ -253,7 +257,8 @@ mlp_fused_step_kernel(const __grid_constant__ CUtensorMap tmXA, const __grid_con
     for (int a = 0; a < 4; ++a) tma_load_2d(smem + oXT + a * kColM, &tmXT, &bar_tma1, k0 + 32 * a, 0);
   }
   asm volatile("griddepcontrol.wait;" ::: "memory");
-  if (threadIdx.x == 0) {
+  if (warp == 0) {
+    if (elect_one()) {
     for (int a = 0; a < H1 / 32; ++a) tma_load_2d(smem + oW1B + a * kW1Col, &tmW1, &bar_tma0, 32 * a, k0);
     if (kMid) {
       for (int a = 0; a < H2 / 32; ++a) tma_load_2d(smem + oW2B + a * S1 * 128, &tmW2B, &bar_tma1, 32 * a, S1 * j);
@@ -261,13 +266,19 @@ mlp_fused_step_kernel(const __grid_constant__ CUtensorMap tmXA, const __grid_con
     }
     tma_load_2d(smem + oWLB, &tmWLB, &bar_tma1, 0, SL * j);
     tma_load_2d(smem + oWLK, &tmWLK, &bar_tma1, 0, SL * j);
+    }
+    __syncwarp();
     // ---------------------------------------------------------------- F1: P1 = X_j . W1_j
     mbar_wait(&bar_tma0, 0);
     tc_fence_after_sync();
-    const uint32_t idesc = make_instr_desc(4, false, true, H1);
-    for (int t = 0; t < nk1; ++t)
-      tc_mma<4>(tm + cF1, kdesc(sb + oXA, t), mdesc(sb + oW1B, t, kW1Col), idesc, t != 0);
-    tc_commit(&bar_mma);
+    if (elect_one()) {
+      const uint32_t idesc = make_instr_desc(4, false, true, H1);
+#pragma unroll
+      for (int t = 0; t < kKGroupsMax; ++t)
+        if (t < nk1) tc_mma<4>(tm + cF1, kdesc(sb + oXA, t), mdesc(sb + oW1B, t, kW1Col), idesc, t != 0);
+      tc_commit(&bar_mma);
+    }
+    __syncwarp();
   }
   const float step = p.wparams != nullptr ? __ldg(p.lr) : 0.f;  // (after griddepcontrol.wait)
   float h1[S1];
@@ -329,14 +340,18 @@ mlp_fused_step_kernel(const __grid_constant__ CUtensorMap tmXA, const __grid_con
   }
   __syncthreads();
   if (kMid) {
-    if (threadIdx.x == 0) {
+    if (warp == 0) {
       mbar_wait(&bar_tma1, 0);
       fence_proxy_async_smem();
       tc_fence_after_sync();
-      const uint32_t idesc = make_instr_desc(4, false, true, H2);
-      for (int t = 0; t < S1 / 8; ++t)
-        tc_mma<4>(tm + cF2, kdesc(sb + oH1K, t), mdesc(sb + oW2B, t, S1 * 128), idesc, t != 0);
-      tc_commit(&bar_mma);
+      if (elect_one()) {
+        const uint32_t idesc = make_instr_desc(4, false, true, H2);
+#pragma unroll
+        for (int t = 0; t < S1 / 8; ++t)
+          tc_mma<4>(tm + cF2, kdesc(sb + oH1K, t), mdesc(sb + oW2B, t, S1 * 128), idesc, t != 0);
+        tc_commit(&bar_mma);
+      }
+      __syncwarp();
     }
     if (worker) {
       mbar_wait(&bar_mma, mma_phase);
@@ -391,14 +406,18 @@ mlp_fused_step_kernel(const __grid_constant__ CUtensorMap tmXA, const __grid_con
   const uint32_t oHLK = kMid ? oH2K : oH1K;
   const uint32_t oDZ1 = kMid ? oDZ1M : oDZ1M2;
   const uint32_t oHLM = kMid ? oH2M : oH1M;
-  if (threadIdx.x == 0) {
+  if (warp == 0) {
     if (!kMid) mbar_wait(&bar_tma1, 0);
     fence_proxy_async_smem();
     tc_fence_after_sync();
-    const uint32_t idesc = make_instr_desc(4, false, true, 16);
-    for (int t = 0; t < SL / 8; ++t)
-      tc_mma<4>(tm + cF3, kdesc(sb + oHLK, t), mdesc(sb + oWLB, t, SL * 128), idesc, t != 0);
-    tc_commit(&bar_mma);
+    if (elect_one()) {
+      const uint32_t idesc = make_instr_desc(4, false, true, 16);
+#pragma unroll
+      for (int t = 0; t < SL / 8; ++t)
+        tc_mma<4>(tm + cF3, kdesc(sb + oHLK, t), mdesc(sb + oWLB, t, SL * 128), idesc, t != 0);
+      tc_commit(&bar_mma);
+    }
+    __syncwarp();
   }
   if (worker) {
     mbar_wait(&bar_mma, mma_phase);
@@ -486,18 +505,24 @@ mlp_fused_step_kernel(const __grid_constant__ CUtensorMap tmXA, const __grid_con
     }
   }
   __syncthreads();
-  if (threadIdx.x == 0) {
+  const int nb8 = B / 8;  // K steps of the weight-gradient GEMMs (K = batch)
+  if (warp == 0) {
     fence_proxy_async_smem();
     tc_fence_after_sync();
-    // critical: dHL_j[B x SL] = dZ3 . W_last_j^T  (A and B K-major, K = 16)
-    const uint32_t idg = make_instr_desc(4, false, false, 16);
-    for (int t = 0; t < 2; ++t) tc_mma<4>(tm + cDGL, kdesc(sb + oDZ3K, t), kdesc(sb + oWLK, t), idg, t != 0);
-    tc_commit(&bar_mma);
-    // beside the chain: dW_last[SL x 16] = HL_j^T . dZ3   (A and B MN-major, K = batch)
-    const uint32_t idw = make_instr_desc(4, true, true, 16);
-    for (int t = 0; t < B / 8; ++t)
-      tc_mma<4>(tm + cWGL, mdesc(sb + oHLM, t, kColM), mdesc(sb + oDZ3M, t, kColM), idw, t != 0);
-    tc_commit(&bar_wgl);
+    if (elect_one()) {
+      // critical: dHL_j[B x SL] = dZ3 . W_last_j^T  (A and B K-major, K = 16)
+      const uint32_t idg = make_instr_desc(4, false, false, 16);
+#pragma unroll
+      for (int t = 0; t < 2; ++t) tc_mma<4>(tm + cDGL, kdesc(sb + oDZ3K, t), kdesc(sb + oWLK, t), idg, t != 0);
+      tc_commit(&bar_mma);
+      // beside the chain: dW_last[SL x 16] = HL_j^T . dZ3   (A and B MN-major, K = batch)
+      const uint32_t idw = make_instr_desc(4, true, true, 16);
+#pragma unroll
+      for (int t = 0; t < 8; ++t)
+        if (t < nb8) tc_mma<4>(tm + cWGL, mdesc(sb + oHLM, t, kColM), mdesc(sb + oDZ3M, t, kColM), idw, t != 0);
+      tc_commit(&bar_wgl);
+    }
+    __syncwarp();
   }
   if (worker && j == 0 && wwarp == 0 && lane == 0) {  // (red[] was filled before the __syncthreads above)
     p.metrics[0] = red[0] + red[1] + red[2] + red[3];
@@ -537,18 +562,23 @@ mlp_fused_step_kernel(const __grid_constant__ CUtensorMap tmXA, const __grid_con
     }
     FPROF(8);
     // ---------------------------------------------------------------- P4: layer-2 grads
-    if (threadIdx.x == 0) {
+    if (warp == 0) {
       mbar_wait(&bar_ex[3], 0);
       fence_proxy_async_smem();
       tc_fence_after_sync();
-      const uint32_t idg = make_instr_desc(4, false, false, 16);
-      for (int t = 0; t < H2 / 8; ++t)
-        tc_mma<4>(tm + cDG2, kdesc(sb + oDZ2K, t), make_smem_desc(sb + oW2K + (t >> 2) * 4096 + (t & 3) * 32, 16, 1024, 2), idg, t != 0);
-      tc_commit(&bar_mma);
-      const uint32_t idw = make_instr_desc(4, true, true, H2);
-      for (int t = 0; t < B / 8; ++t)
-        tc_mma<4>(tm + cWG2, mdesc(sb + oH1M, t, kColM), mdesc(sb + oDZ2M, t, kColM), idw, t != 0);
-      tc_commit(&bar_wg2);
+      if (elect_one()) {
+        const uint32_t idg = make_instr_desc(4, false, false, 16);
+#pragma unroll
+        for (int t = 0; t < H2 / 8; ++t)
+          tc_mma<4>(tm + cDG2, kdesc(sb + oDZ2K, t), make_smem_desc(sb + oW2K + (t >> 2) * 4096 + (t & 3) * 32, 16, 1024, 2), idg, t != 0);
+        tc_commit(&bar_mma);
+        const uint32_t idw = make_instr_desc(4, true, true, H2);
+#pragma unroll
+        for (int t = 0; t < 8; ++t)
+          if (t < nb8) tc_mma<4>(tm + cWG2, mdesc(sb + oH1M, t, kColM), mdesc(sb + oDZ2M, t, kColM), idw, t != 0);
+        tc_commit(&bar_wg2);
+      }
+      __syncwarp();
     }
     if (worker) {
       mbar_wait(&bar_mma, mma_phase);
@@ -583,14 +613,18 @@ mlp_fused_step_kernel(const __grid_constant__ CUtensorMap tmXA, const __grid_con
   FPROF(10);
 
   // ------------------------------------------------------------------ P5: dW1_j = X_j^T . dZ1
-  if (threadIdx.x == 0) {
+  if (warp == 0) {
     mbar_wait(&bar_ex[4], 0);
     fence_proxy_async_smem();
     tc_fence_after_sync();
-    const uint32_t idw = make_instr_desc(4, true, true, H1);
-    for (int t = 0; t < B / 8; ++t)
-      tc_mma<4>(tm + cWG1, mdesc(sb + oXT, t, kColM), mdesc(sb + oDZ1, t, kColM), idw, t != 0);
-    tc_commit(&bar_mma);
+    if (elect_one()) {
+      const uint32_t idw = make_instr_desc(4, true, true, H1);
+#pragma unroll
+      for (int t = 0; t < 8; ++t)
+        if (t < nb8) tc_mma<4>(tm + cWG1, mdesc(sb + oXT, t, kColM), mdesc(sb + oDZ1, t, kColM), idw, t != 0);
+      tc_commit(&bar_mma);
+    }
+    __syncwarp();
   }
   float dbl[16];  // last-layer bias gradient (valid in the thread that owns accumulator row SL)
   if (worker) {
