@@ -11,6 +11,11 @@
 
 namespace dmlp {
 
+// Epilogue transpose patch: 32 rows x 32 fp32 columns per epilogue warp, rows padded to 36 floats so that
+// both the row-wise float4 writes and the column-group float4 reads are bank-conflict free.
+constexpr int kEpiLd = 36;
+constexpr uint32_t kEpiStageBytes = 4 * 32 * kEpiLd * 4;
+
 struct GemmParams {
   int M, N, K;
   int block_n;
@@ -21,6 +26,7 @@ struct GemmParams {
   uint32_t a_stage_bytes, b_stage_bytes;
   uint32_t a_tx_bytes;  // bytes TMA actually delivers for A per stage (half a tile when M <= 64)
   uint32_t idesc;
+  uint32_t epi_stage_off;  // byte offset (from the aligned smem base) of the epilogue's transpose patches
   float* out_f32;
   long long ld_out;
   __nv_bfloat16* out_bf16;
@@ -32,6 +38,7 @@ struct GemmParams {
   float* colsum;
   int relu;
   int accumulate;
+  int prof;  // debug: CTA 0 stamps a per-tile timeline into g_gemm_prof
   int pdl;  // launched with programmatic stream serialization: the kernel executes griddepcontrol.wait
   // fused softmax cross-entropy epilogue (last layer): non-null labels switch it on
   const int* ce_labels;

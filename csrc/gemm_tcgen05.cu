@@ -24,6 +24,18 @@ namespace dmlp {
 constexpr int kMaxStages = 8;
 constexpr int kGemmThreads = 192;
 
+// Per-tile timeline of CTA 0 (debug, DMLP_GEMM_PROF=1 at plan creation): 8 globaltimer stamps per tile.
+//  0 producer: first smem slot of the tile acquired   1 producer: last TMA of the tile issued
+//  2 MMA: accumulator buffer acquired                 3 MMA: first operands landed      4 MMA: last commit issued
+//  5 epilogue: accumulator ready                      6 epilogue: accumulator drained   7 epilogue: tile done
+constexpr int kProfTiles = 64;
+__device__ unsigned long long g_gemm_prof[kProfTiles * 16];
+#define GPROF(slot, tile_i)                                                                          \
+  do {                                                                                               \
+    if (p.prof && blockIdx.x == 0 && (tile_i) < kProfTiles && (threadIdx.x & 31) == 0)               \
+      g_gemm_prof[(tile_i) * 16 + (slot)] = globaltimer_ns();                                         \
+  } while (0)
+
 template <int EB, bool A_MN, bool B_MN>
 __global__ void __launch_bounds__(kGemmThreads, 1)
 gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA,
@@ -103,11 +115,13 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA,
       // k-block counter across all tiles of this CTA: the smem ring never drains between tiles
       int s = 0;
       uint32_t ph = 0;
-      for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
+      int ti = 0;
+      for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x, ++ti) {
         const int m0 = (tile % tiles_m) * BM;
         const int n0 = (tile / tiles_m) * p.block_n;
         for (int kb = 0; kb < p.num_k_blocks; ++kb) {
           mbar_wait(&empty_bar[s], ph ^ 1);
+          if (kb == 0) GPROF(0, ti);
           if (elect_one()) {
             mbar_arrive_expect_tx(&full_bar[s], stage_bytes);
             uint8_t* a_dst = smem_a + static_cast<size_t>(s) * p.a_stage_bytes;
@@ -128,6 +142,7 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA,
             }
           }
           __syncwarp();
+          if (kb == p.num_k_blocks - 1) GPROF(1, ti);
           if (++s == p.stages) { s = 0; ph ^= 1; }
         }
       }
@@ -146,10 +161,12 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA,
         const uint32_t buf = tcount & 1;
         mbar_wait(&tmem_empty_bar[buf], ((tcount >> 1) & 1) ^ 1);  // epilogue drained this buffer (free at first use)
         tc_fence_after_sync();
+        GPROF(2, tcount);
         const uint32_t tmem_acc = tmem_base + buf * p.tmem_buf_cols;
         for (int kb = 0; kb < p.num_k_blocks; ++kb) {
           mbar_wait(&full_bar[s], ph);
           tc_fence_after_sync();
+          if (kb == 0) GPROF(3, tcount);
           // K-major: step 32 B inside the 128 B swizzle row. MN-major: step UK k-rows of 128 B.
           const uint64_t adesc = adesc0 + ((a_base + s * p.a_stage_bytes) >> 4);
           const uint64_t bdesc = bdesc0 + ((b_base + s * p.b_stage_bytes) >> 4);
@@ -161,6 +178,7 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA,
             if (kb == p.num_k_blocks - 1) tc_commit(&tmem_full_bar[buf]);
           }
           __syncwarp();
+          if (kb == p.num_k_blocks - 1) GPROF(4, tcount);
           if (++s == p.stages) { s = 0; ph ^= 1; }
         }
       }
@@ -180,8 +198,46 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA,
     const int m = m0 + row;
     const bool m_ok = m < p.M;
     const uint32_t buf = tcount & 1;
+    float* stg = reinterpret_cast<float*>(smem + p.epi_stage_off) + q * (32 * kEpiLd);
+    const int rsub = lane >> 3, c4 = (lane & 7) * 4;
+    const bool vec_f32 = p.out_f32 != nullptr && ((reinterpret_cast<uintptr_t>(p.out_f32) & 15) == 0) && (p.ld_out & 3) == 0;
+    const bool vec_b16 = p.out_bf16 != nullptr && ((reinterpret_cast<uintptr_t>(p.out_bf16) & 7) == 0) && (p.ld_out_bf16 & 3) == 0;
+    const bool vec_mask = p.mask != nullptr && (p.ld_mask & 3) == 0 &&
+                          ((reinterpret_cast<uintptr_t>(p.mask) & (p.mask_is_bf16 ? 7 : 15)) == 0);
+    // Interior tile with vectorisable pointers: straight-line code, no per-element bounds checks, loads
+    // batched ahead of their uses. (One epilogue warp per scheduler: nothing hides latency but ILP.)
+    const bool fast = m0 + BM <= p.M && n0 + p.block_n <= p.N && (p.block_n & 31) == 0 &&
+                    (p.out_f32 == nullptr || vec_f32) && (p.out_bf16 == nullptr || vec_b16) &&
+                    (p.mask == nullptr || vec_mask) && ((reinterpret_cast<uintptr_t>(p.bias) & 15) == 0);
+    const uint32_t stg_s = smem_u32(stg);
+    const uint32_t wr_s = stg_s + lane * (kEpiLd * 4);
+    const uint32_t rd_s = stg_s + (rsub * kEpiLd + c4) * 4;
+    const long long rbase = m0 + q * 32 + rsub;
+    float* of = p.out_f32 != nullptr ? p.out_f32 + rbase * p.ld_out + n0 + c4 : nullptr;
+    __nv_bfloat16* oh = p.out_bf16 != nullptr ? p.out_bf16 + rbase * p.ld_out_bf16 + n0 + c4 : nullptr;
+    const __nv_bfloat16* mh = (p.mask != nullptr && p.mask_is_bf16)
+                                  ? reinterpret_cast<const __nv_bfloat16*>(p.mask) + rbase * p.ld_mask + n0 + c4 : nullptr;
+    const float* mf = (p.mask != nullptr && !p.mask_is_bf16)
+                          ? reinterpret_cast<const float*>(p.mask) + rbase * p.ld_mask + n0 + c4 : nullptr;
+    const long long of_step = 4 * p.ld_out, oh_step = 4 * p.ld_out_bf16, mk_step = 4 * p.ld_mask;
+    // first chunk's bias / mask values: requested before waiting for the accumulator
+    float4 b_nx = make_float4(0.f, 0.f, 0.f, 0.f);
+    uint2 mh_nx[8];
+    float4 mf_nx[8];
+    if (fast && p.ce_labels == nullptr) {
+      if (p.bias != nullptr) b_nx = __ldg(reinterpret_cast<const float4*>(p.bias + n0 + c4));
+      if (mh != nullptr) {
+#pragma unroll
+        for (int i = 0; i < 8; ++i) mh_nx[i] = __ldg(reinterpret_cast<const uint2*>(mh + i * mk_step));
+      }
+      if (mf != nullptr) {
+#pragma unroll
+        for (int i = 0; i < 8; ++i) mf_nx[i] = __ldg(reinterpret_cast<const float4*>(mf + i * mk_step));
+      }
+    }
     mbar_wait(&tmem_full_bar[buf], (tcount >> 1) & 1);
     tc_fence_after_sync();
+    if (warp == 2) GPROF(5, tcount);
     const uint32_t t_row = tmem_base + buf * p.tmem_buf_cols + (static_cast<uint32_t>(q * 32) << 16);
 
     if (p.ce_labels != nullptr) {
@@ -277,104 +333,255 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA,
         if (p.ce_correct != nullptr) { if (direct) *p.ce_correct = h; else if (h) atomicAdd(p.ce_correct, h); }
       }
     } else {
-      int chunks_done = 0;
-      for (int c = 0; c < p.block_n; c += 16) {
-        uint32_t r[16];
-        tmem_ld_x16(t_row + c, r);
-        tmem_ld_wait();
+      // ---- generic epilogue. A thread owns one accumulator ROW in TMEM, but rows are ld_out apart in
+      // memory: storing from that layout makes every warp-wide access touch 32 cache lines. So each warp
+      // turns its 32 rows x 32 columns around through a private shared-memory patch: rows go in, then
+      // lane l picks up columns 4*(l%8)..+3 of rows l/8 + 4*i. In that layout one instruction covers
+      // 4 rows x 128 contiguous bytes: mask / accumulate loads and the stores are coalesced, and a column
+      // sum is 8 register adds + 2 shuffles instead of 5 shuffles per element.
+      int cols_done = 0;
+      if (fast) {
+        for (int c = 0; c < p.block_n; c += 32) {
+          const float4 b = b_nx;
+          uint2 mh_cur[8];
+          float4 mf_cur[8];
+          if (mh != nullptr) {
+#pragma unroll
+            for (int i = 0; i < 8; ++i) mh_cur[i] = mh_nx[i];
+          }
+          if (mf != nullptr) {
+#pragma unroll
+            for (int i = 0; i < 8; ++i) mf_cur[i] = mf_nx[i];
+          }
+          if (c + 32 < p.block_n) {  // next chunk's values travel while this chunk is processed
+            if (p.bias != nullptr) b_nx = __ldg(reinterpret_cast<const float4*>(p.bias + n0 + c + 32 + c4));
+            if (mh != nullptr) {
+#pragma unroll
+              for (int i = 0; i < 8; ++i) mh_nx[i] = __ldg(reinterpret_cast<const uint2*>(mh + c + 32 + i * mk_step));
+            }
+            if (mf != nullptr) {
+#pragma unroll
+              for (int i = 0; i < 8; ++i) mf_nx[i] = __ldg(reinterpret_cast<const float4*>(mf + c + 32 + i * mk_step));
+            }
+          }
+          {
+            uint32_t r0[16], r1[16];
+            tmem_ld_x16(t_row + c, r0);
+            tmem_ld_x16(t_row + c + 16, r1);
+            tmem_ld_wait();
+#pragma unroll
+            for (int j = 0; j < 4; ++j) {
+              sts128(wr_s + j * 16, __uint_as_float(r0[4 * j]), __uint_as_float(r0[4 * j + 1]), __uint_as_float(r0[4 * j + 2]),
+                     __uint_as_float(r0[4 * j + 3]));
+              sts128(wr_s + 64 + j * 16, __uint_as_float(r1[4 * j]), __uint_as_float(r1[4 * j + 1]),
+                     __uint_as_float(r1[4 * j + 2]), __uint_as_float(r1[4 * j + 3]));
+            }
+          }
+          __syncwarp();
+          float4 t[8];
+#pragma unroll
+          for (int i = 0; i < 8; ++i) t[i] = lds128(rd_s + i * (4 * kEpiLd * 4));
+          if (p.bias != nullptr) {
+#pragma unroll
+            for (int i = 0; i < 8; ++i) { t[i].x += b.x; t[i].y += b.y; t[i].z += b.z; t[i].w += b.w; }
+          }
+          if (p.relu) {
+#pragma unroll
+            for (int i = 0; i < 8; ++i) {
+              t[i].x = fmaxf(t[i].x, 0.f); t[i].y = fmaxf(t[i].y, 0.f); t[i].z = fmaxf(t[i].z, 0.f); t[i].w = fmaxf(t[i].w, 0.f);
+            }
+          }
+          if (mh != nullptr) {
+            const uint2* mr = mh_cur;
+#pragma unroll
+            for (int i = 0; i < 8; ++i) {
+              // bf16 > 0  <=>  sign clear and magnitude non-zero (NaN masks count as positive: never produced here)
+              if (!(__uint_as_float(mr[i].x << 16) > 0.f)) t[i].x = 0.f;
+              if (!(__uint_as_float(mr[i].x & 0xffff0000u) > 0.f)) t[i].y = 0.f;
+              if (!(__uint_as_float(mr[i].y << 16) > 0.f)) t[i].z = 0.f;
+              if (!(__uint_as_float(mr[i].y & 0xffff0000u) > 0.f)) t[i].w = 0.f;
+            }
+          } else if (mf != nullptr) {
+            const float4* mr = mf_cur;
+#pragma unroll
+            for (int i = 0; i < 8; ++i) {
+              if (!(mr[i].x > 0.f)) t[i].x = 0.f;
+              if (!(mr[i].y > 0.f)) t[i].y = 0.f;
+              if (!(mr[i].z > 0.f)) t[i].z = 0.f;
+              if (!(mr[i].w > 0.f)) t[i].w = 0.f;
+            }
+          }
+          if (of != nullptr) {
+            if (p.accumulate) {
+              float4 o[8];
+#pragma unroll
+              for (int i = 0; i < 8; ++i) o[i] = *reinterpret_cast<const float4*>(of + c + i * of_step);
+#pragma unroll
+              for (int i = 0; i < 8; ++i) { t[i].x += o[i].x; t[i].y += o[i].y; t[i].z += o[i].z; t[i].w += o[i].w; }
+            }
+#pragma unroll
+            for (int i = 0; i < 8; ++i) *reinterpret_cast<float4*>(of + c + i * of_step) = t[i];
+          }
+          if (oh != nullptr) {
+#pragma unroll
+            for (int i = 0; i < 8; ++i) {
+              const __nv_bfloat162 h0 = __floats2bfloat162_rn(t[i].x, t[i].y);
+              const __nv_bfloat162 h1 = __floats2bfloat162_rn(t[i].z, t[i].w);
+              uint2 pk;
+              pk.x = *reinterpret_cast<const uint32_t*>(&h0);
+              pk.y = *reinterpret_cast<const uint32_t*>(&h1);
+              *reinterpret_cast<uint2*>(oh + c + i * oh_step) = pk;
+            }
+          }
+          if (p.colsum != nullptr) {
+            float cs[4] = {0.f, 0.f, 0.f, 0.f};
+#pragma unroll
+            for (int i = 0; i < 8; ++i) { cs[0] += t[i].x; cs[1] += t[i].y; cs[2] += t[i].z; cs[3] += t[i].w; }
+#pragma unroll
+            for (int k = 0; k < 4; ++k) {
+              cs[k] += __shfl_xor_sync(0xffffffffu, cs[k], 8);
+              cs[k] += __shfl_xor_sync(0xffffffffu, cs[k], 16);
+            }
+            if (lane < 8) {
+#pragma unroll
+              for (int k = 0; k < 4; ++k) s_part[q][c + c4 + k] = cs[k];
+            }
+          }
+          __syncwarp();  // the patch is rewritten by the next chunk
+        }
+        cols_done = p.block_n;
+      } else
+      for (int c = 0; c < p.block_n; c += 32) {
         const int nb = n0 + c;
         if (nb >= p.N) break;  // uniform across the CTA
-        ++chunks_done;
-        float v[16];
+        {
+          uint32_t r0[16], r1[16];
+          tmem_ld_x16(t_row + c, r0);
+          const bool second = c + 16 < p.block_n;  // block_n is a multiple of 16, not always of 32
+          if (second) tmem_ld_x16(t_row + c + 16, r1);
+          tmem_ld_wait();
+          float4* dst = reinterpret_cast<float4*>(stg + lane * kEpiLd);
 #pragma unroll
-        for (int j = 0; j < 16; ++j) v[j] = __uint_as_float(r[j]);
-        const bool full = (nb + 16 <= p.N);
+          for (int j = 0; j < 4; ++j)
+            dst[j] = make_float4(__uint_as_float(r0[4 * j]), __uint_as_float(r0[4 * j + 1]), __uint_as_float(r0[4 * j + 2]),
+                                 __uint_as_float(r0[4 * j + 3]));
+          if (second) {
+#pragma unroll
+            for (int j = 0; j < 4; ++j)
+              dst[4 + j] = make_float4(__uint_as_float(r1[4 * j]), __uint_as_float(r1[4 * j + 1]),
+                                       __uint_as_float(r1[4 * j + 2]), __uint_as_float(r1[4 * j + 3]));
+          }
+        }
+        __syncwarp();
+        const int cw = min(32, p.block_n - c);  // live columns of this patch
+        cols_done = c + cw;
+        const int col = nb + c4;
+        const int nvalid = (c4 < cw) ? min(4, p.N - col) : 0;  // columns of mine that exist (<= 0: none)
+        float bia[4] = {0.f, 0.f, 0.f, 0.f};
         if (p.bias != nullptr) {
 #pragma unroll
-          for (int j = 0; j < 16; ++j)
-            if (full || nb + j < p.N) v[j] += __ldg(p.bias + nb + j);
+          for (int k = 0; k < 4; ++k)
+            if (k < nvalid) bia[k] = __ldg(p.bias + col + k);
         }
-        if (p.relu) {
+        float cs[4] = {0.f, 0.f, 0.f, 0.f};
 #pragma unroll
-          for (int j = 0; j < 16; ++j) v[j] = fmaxf(v[j], 0.f);
-        }
-        if (p.mask != nullptr && m_ok) {
-          if (p.mask_is_bf16) {
-            const __nv_bfloat16* mk =
-                reinterpret_cast<const __nv_bfloat16*>(p.mask) + static_cast<long long>(m) * p.ld_mask + nb;
+        for (int i = 0; i < 8; ++i) {
+          const int rr = i * 4 + rsub;
+          const int mm = m0 + q * 32 + rr;
+          const float4 t = *reinterpret_cast<const float4*>(stg + rr * kEpiLd + c4);
+          float v[4] = {t.x + bia[0], t.y + bia[1], t.z + bia[2], t.w + bia[3]};
+          if (p.relu) {
 #pragma unroll
-            for (int j = 0; j < 16; ++j)
-              if (full || nb + j < p.N)
-                if (!(__bfloat162float(mk[j]) > 0.f)) v[j] = 0.f;
-          } else {
-            const float* mk = reinterpret_cast<const float*>(p.mask) + static_cast<long long>(m) * p.ld_mask + nb;
-#pragma unroll
-            for (int j = 0; j < 16; ++j)
-              if (full || nb + j < p.N)
-                if (!(mk[j] > 0.f)) v[j] = 0.f;
+            for (int k = 0; k < 4; ++k) v[k] = fmaxf(v[k], 0.f);
           }
-        }
-        if (m_ok) {
-          if (p.out_f32 != nullptr) {
-            float* o = p.out_f32 + static_cast<long long>(m) * p.ld_out + nb;
-            const bool vec = full && ((reinterpret_cast<uintptr_t>(o) & 15) == 0);
-            if (p.accumulate) {
+          if (mm < p.M && nvalid > 0) {
+            const bool full4 = nvalid == 4;
+            if (p.mask != nullptr) {
+              if (p.mask_is_bf16) {
+                const __nv_bfloat16* mk = reinterpret_cast<const __nv_bfloat16*>(p.mask) + static_cast<long long>(mm) * p.ld_mask + col;
+                if (full4 && vec_mask) {
+                  const uint2 raw = *reinterpret_cast<const uint2*>(mk);
+                  const __nv_bfloat162 a = *reinterpret_cast<const __nv_bfloat162*>(&raw.x);
+                  const __nv_bfloat162 b = *reinterpret_cast<const __nv_bfloat162*>(&raw.y);
+                  if (!(__low2float(a) > 0.f)) v[0] = 0.f;
+                  if (!(__high2float(a) > 0.f)) v[1] = 0.f;
+                  if (!(__low2float(b) > 0.f)) v[2] = 0.f;
+                  if (!(__high2float(b) > 0.f)) v[3] = 0.f;
+                } else {
 #pragma unroll
-              for (int j = 0; j < 16; ++j)
-                if (full || nb + j < p.N) v[j] += o[j];
-            }
-            if (vec) {
+                  for (int k = 0; k < 4; ++k)
+                    if (k < nvalid && !(__bfloat162float(mk[k]) > 0.f)) v[k] = 0.f;
+                }
+              } else {
+                const float* mk = reinterpret_cast<const float*>(p.mask) + static_cast<long long>(mm) * p.ld_mask + col;
+                if (full4 && vec_mask) {
+                  const float4 mv = *reinterpret_cast<const float4*>(mk);
+                  if (!(mv.x > 0.f)) v[0] = 0.f;
+                  if (!(mv.y > 0.f)) v[1] = 0.f;
+                  if (!(mv.z > 0.f)) v[2] = 0.f;
+                  if (!(mv.w > 0.f)) v[3] = 0.f;
+                } else {
 #pragma unroll
-              for (int j = 0; j < 16; j += 4)
-                *reinterpret_cast<float4*>(o + j) = make_float4(v[j], v[j + 1], v[j + 2], v[j + 3]);
-            } else {
-#pragma unroll
-              for (int j = 0; j < 16; ++j)
-                if (full || nb + j < p.N) o[j] = v[j];
-            }
-          }
-          if (p.out_bf16 != nullptr) {
-            __nv_bfloat16* o = p.out_bf16 + static_cast<long long>(m) * p.ld_out_bf16 + nb;
-            const bool vec = full && ((reinterpret_cast<uintptr_t>(o) & 15) == 0);
-            if (vec) {
-#pragma unroll
-              for (int j = 0; j < 16; j += 8) {
-                __nv_bfloat162 h0 = __floats2bfloat162_rn(v[j], v[j + 1]);
-                __nv_bfloat162 h1 = __floats2bfloat162_rn(v[j + 2], v[j + 3]);
-                __nv_bfloat162 h2 = __floats2bfloat162_rn(v[j + 4], v[j + 5]);
-                __nv_bfloat162 h3 = __floats2bfloat162_rn(v[j + 6], v[j + 7]);
-                uint4 pk;
-                pk.x = *reinterpret_cast<uint32_t*>(&h0);
-                pk.y = *reinterpret_cast<uint32_t*>(&h1);
-                pk.z = *reinterpret_cast<uint32_t*>(&h2);
-                pk.w = *reinterpret_cast<uint32_t*>(&h3);
-                *reinterpret_cast<uint4*>(o + j) = pk;
+                  for (int k = 0; k < 4; ++k)
+                    if (k < nvalid && !(mk[k] > 0.f)) v[k] = 0.f;
+                }
               }
-            } else {
-#pragma unroll
-              for (int j = 0; j < 16; ++j)
-                if (full || nb + j < p.N) o[j] = __float2bfloat16_rn(v[j]);
             }
+            if (p.out_f32 != nullptr) {
+              float* o = p.out_f32 + static_cast<long long>(mm) * p.ld_out + col;
+              if (full4 && vec_f32) {
+                if (p.accumulate) {
+                  const float4 old = *reinterpret_cast<const float4*>(o);
+                  v[0] += old.x; v[1] += old.y; v[2] += old.z; v[3] += old.w;
+                }
+                *reinterpret_cast<float4*>(o) = make_float4(v[0], v[1], v[2], v[3]);
+              } else {
+#pragma unroll
+                for (int k = 0; k < 4; ++k)
+                  if (k < nvalid) {
+                    if (p.accumulate) v[k] += o[k];
+                    o[k] = v[k];
+                  }
+              }
+            }
+            if (p.out_bf16 != nullptr) {
+              __nv_bfloat16* o = p.out_bf16 + static_cast<long long>(mm) * p.ld_out_bf16 + col;
+              if (full4 && vec_b16) {
+                const __nv_bfloat162 h0 = __floats2bfloat162_rn(v[0], v[1]);
+                const __nv_bfloat162 h1 = __floats2bfloat162_rn(v[2], v[3]);
+                uint2 pk;
+                pk.x = *reinterpret_cast<const uint32_t*>(&h0);
+                pk.y = *reinterpret_cast<const uint32_t*>(&h1);
+                *reinterpret_cast<uint2*>(o) = pk;
+              } else {
+#pragma unroll
+                for (int k = 0; k < 4; ++k)
+                  if (k < nvalid) o[k] = __float2bfloat16_rn(v[k]);
+              }
+            }
+#pragma unroll
+            for (int k = 0; k < 4; ++k) cs[k] += v[k];  // rows past M and columns past N never get here
           }
         }
         if (p.colsum != nullptr) {
-          // Bias gradient: column sums over this warp's 32 rows (rows past M contribute zero).
+          // Bias gradient: column sums over this warp's 32 rows
 #pragma unroll
-          for (int j = 0; j < 16; ++j) {
-            float sj = m_ok ? v[j] : 0.f;
-            sj += __shfl_xor_sync(0xffffffffu, sj, 16);
-            sj += __shfl_xor_sync(0xffffffffu, sj, 8);
-            sj += __shfl_xor_sync(0xffffffffu, sj, 4);
-            sj += __shfl_xor_sync(0xffffffffu, sj, 2);
-            sj += __shfl_xor_sync(0xffffffffu, sj, 1);
-            if (lane == j) s_part[q][c + j] = sj;
+          for (int k = 0; k < 4; ++k) {
+            cs[k] += __shfl_xor_sync(0xffffffffu, cs[k], 8);
+            cs[k] += __shfl_xor_sync(0xffffffffu, cs[k], 16);
+          }
+          if (lane < 8) {
+#pragma unroll
+            for (int k = 0; k < 4; ++k) s_part[q][c + c4 + k] = cs[k];
           }
         }
+        __syncwarp();  // the patch is rewritten by the next chunk
       }
+      if (warp == 2) GPROF(6, tcount);
       if (p.colsum != nullptr) {
         // combine the four warps' partials: one store (or one atomic) per column per CTA
         asm volatile("bar.sync 1, 128;" ::: "memory");
-        for (int cidx = etid; cidx < chunks_done * 16; cidx += 128) {
+        for (int cidx = etid; cidx < cols_done; cidx += 128) {
           const int n = n0 + cidx;
           if (n < p.N) {
             const float t = s_part[0][cidx] + s_part[1][cidx] + s_part[2][cidx] + s_part[3][cidx];
@@ -387,6 +594,7 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA,
     if (p.colsum != nullptr || p.ce_labels != nullptr) asm volatile("bar.sync 1, 128;" ::: "memory");  // s_part reuse
     tc_fence_before_sync();
     mbar_arrive(&tmem_empty_bar[buf]);
+    if (warp == 2) GPROF(7, tcount);
     }
   }
 
@@ -532,7 +740,7 @@ int dmlp::gemm_plan_create(const dmlp_gemm_desc_t* d, GemmPlan* plan) {
   p.a_tx_bytes = (d->a_major == 0) ? a_box_rows * 128 : 128 * 128;
   p.b_stage_bytes = d->b_major == 0 ? bn * 128 : ceil_div(bn, ATOM) * KS * 128;
   const size_t stage_bytes = p.a_stage_bytes + p.b_stage_bytes;
-  const size_t budget = 200 * 1024;
+  const size_t budget = 196 * 1024;  // + 18 KiB of epilogue patches + 1 KiB alignment slack <= the 216 KiB opt-in
   int stages = static_cast<int>(budget / stage_bytes);
   if (stages > kMaxStages) stages = kMaxStages;
   if (stages > p.num_k_blocks) stages = p.num_k_blocks;
@@ -542,6 +750,10 @@ int dmlp::gemm_plan_create(const dmlp_gemm_desc_t* d, GemmPlan* plan) {
     if (e && atoi(e) > 0 && atoi(e) < stages) stages = atoi(e);
   }
   p.stages = stages;
+  {
+    const char* e = getenv("DMLP_GEMM_PROF");
+    p.prof = (e && atoi(e) > 0) ? 1 : 0;
+  }
   uint32_t cols = 32;
   while (cols < static_cast<uint32_t>(bn)) cols <<= 1;
   p.tmem_buf_cols = cols;   // one accumulator buffer
@@ -566,7 +778,8 @@ int dmlp::gemm_plan_create(const dmlp_gemm_desc_t* d, GemmPlan* plan) {
     plan->grid_x = total < 148 ? total : 148;  // persistent: at most one CTA per SM
     plan->grid_y = 1;
   }
-  plan->smem = stages * stage_bytes + 1024;
+  p.epi_stage_off = static_cast<uint32_t>(stages * stage_bytes);
+  plan->smem = stages * stage_bytes + kEpiStageBytes + 1024;
   plan->key = (bf16 ? 4 : 0) | (d->a_major ? 2 : 0) | (d->b_major ? 1 : 0);
   // PDL only for single-wave grids: an early-launched dependent must never compete with CTAs of
   // this grid that are still waiting for an SM.
@@ -597,4 +810,11 @@ extern "C" int dmlp_gemm(const dmlp_gemm_desc_t* d, void* stream) {
   int rc = gemm_plan_create(d, &plan);
   if (rc) return rc;
   return gemm_plan_run(&plan, as_stream(stream));
+}
+
+// Debug: copies the per-tile timeline of CTA 0 of the most recent profiled GEMM (DMLP_GEMM_PROF=1) to the host.
+extern "C" int dmlp_gemm_prof_read(unsigned long long* host, int n_words) {
+  DMLP_REQUIRE(host != nullptr && n_words > 0 && n_words <= dmlp::kProfTiles * 16, "dmlp_gemm_prof_read: bad arguments");
+  DMLP_CUDA_CHECK(cudaMemcpyFromSymbol(host, dmlp::g_gemm_prof, sizeof(unsigned long long) * n_words));
+  return DMLP_OK;
 }

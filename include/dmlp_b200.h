@@ -32,6 +32,9 @@ extern "C" {
 const char* dmlp_last_error(void);
 /* Library build description: arch, version, compile flags. */
 const char* dmlp_build_info(void);
+/* Debug aid: per-tile timeline (8 globaltimer stamps per tile, first 64 tiles) of CTA 0 of the last GEMM whose
+ * plan was created with DMLP_GEMM_PROF=1 in the environment. See csrc/gemm_tcgen05.cu for the slot meanings. */
+int dmlp_gemm_prof_read(unsigned long long* host, int n_words);
 
 /* ------------------------------------------------------------------ data types / ops */
 typedef enum { DMLP_F32 = 0, DMLP_BF16 = 1, DMLP_U8 = 2, DMLP_I32 = 3, DMLP_F16 = 4 } dmlp_dtype_t;
