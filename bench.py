@@ -190,6 +190,7 @@ def main() -> int:
     barrier()
     t_start = time.time()
     st_dev = timed(dset, a.steps)
+    launches_dev = trainer.launches_last_run or trainer.kernels_per_step * a.steps
     barrier()
     ms_dev = max_over_ranks(st_dev["device_ms"])
     # ---- end to end: pinned host -> device every step, loss/correct read back every step
@@ -222,8 +223,10 @@ def main() -> int:
                 "h2d_bytes_per_step": batch * feat * 4 + batch * 4, "d2h_bytes_per_step": 8,
                 "api": "dmlp_b200.parallel.trainer.Trainer.fit (pinned host dataset, per-step loss/correct read back)",
                 "final_loss": st_e2e.get("last_loss")},
-        "gpu_launches": trainer.kernels_per_step * a.steps,
+        "gpu_launches": launches_dev,  # launches inside the device-timed region (fused path: one launch runs a whole
+                                        # chunk of steps, weights updated in place between them inside the kernel)
         "kernels_per_step": trainer.kernels_per_step,
+        "steps_per_launch": round(a.steps / max(launches_dev, 1), 2),
         "clocks": clocks,
         "impl": "ours",
     }

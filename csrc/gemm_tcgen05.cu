@@ -51,8 +51,9 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA,
   constexpr uint32_t MN_LAYOUT = (EB == 4) ? 1 : 2;
 
   extern __shared__ uint8_t smem_raw[];
-  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) &
-                                             ~static_cast<uintptr_t>(1023));
+  // 1024-byte alignment by pointer arithmetic on the shared array itself (a round trip through an integer makes
+  // the compiler fall back to generic LD/ST for everything addressed off this base)
+  uint8_t* smem = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);
   uint8_t* smem_a = smem;
   uint8_t* smem_b = smem + static_cast<size_t>(p.stages) * p.a_stage_bytes;
 

@@ -53,6 +53,8 @@ struct FusedParams {
   const float* lr;
   float* dbg;      // optional dump of intermediates (tests)
   unsigned long long* prof;  // optional [8 CTAs][16] globaltimer stamps at phase boundaries
+  int nsteps;      // steps this launch performs back to back (> 1 only with in-place SGD: wparams != null)
+  int slot0;       // first input slot: step s reads rows [(slot0+s)*B, +B) of the X maps, labels + s*B, metrics + 2*s
 };
 
 #define FPROF(slot)                                                                                   \
@@ -131,6 +133,13 @@ __device__ __forceinline__ void tmem_ld_x8(uint32_t taddr, uint32_t (&r)[8]) {
                : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7])
                : "r"(taddr) : "memory");
 }
+__device__ __forceinline__ void fence_proxy_async_all() { asm volatile("fence.proxy.async;" ::: "memory"); }
+// L2 prefetch of one TMA box (no shared-memory destination, no barrier)
+__device__ __forceinline__ void tma_prefetch_2d(const CUtensorMap* m, int c0, int c1) {
+  asm volatile("cp.async.bulk.prefetch.tensor.2d.L2.global.tile [%0, {%1, %2}];" ::"l"(reinterpret_cast<uint64_t>(m)), "r"(c0),
+               "r"(c1)
+               : "memory");
+}
 __device__ __forceinline__ uint64_t kdesc(uint32_t tile, int kstep) {  // K-major A/B, 8 floats per step
   return make_smem_desc(tile + (kstep >> 2) * kTileK + (kstep & 3) * 32, 16, 1024, 2);
 }
@@ -188,7 +197,9 @@ mlp_fused_step_kernel(const __grid_constant__ CUtensorMap tmXA, const __grid_con
   constexpr int LAST = kMid ? 2 : 1;
   static_assert(S1 == 16 && (S2 == 8 || S2 == 0), "slice widths this kernel was laid out for");
   extern __shared__ uint8_t smem_raw[];
-  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~static_cast<uintptr_t>(1023));
+  // 1024-byte alignment by pointer arithmetic on the shared array itself (a round trip through an integer makes
+  // the compiler fall back to generic LD/ST for everything addressed off this base)
+  uint8_t* smem = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);
   const uint32_t sb = smem_u32(smem);
   // bar_mma: the critical chain F1 -> F2 -> F3 -> dgrad_last -> dgrad2 -> wgrad1 (phase toggles per use);
   // bar_wgl / bar_wg2: weight-gradient GEMMs that run beside the chain; bar_ex[k]: arrival of exchange k
@@ -213,6 +224,16 @@ mlp_fused_step_kernel(const __grid_constant__ CUtensorMap tmXA, const __grid_con
   float* red = reinterpret_cast<float*>(smem + oRED);
   const uint32_t tq = (static_cast<uint32_t>((warp & 3) * 32) << 16);
 
+  // arm the exchange barriers: bytes every CTA of the cluster (this one included) will deliver in one step
+  auto arm_exchanges = [&]() {
+    mbar_arrive_expect_tx(&bar_ex[0], kFC * B * S1 * 4);
+    mbar_arrive_expect_tx(&bar_ex[2], kFC * B * 64);
+    mbar_arrive_expect_tx(&bar_ex[4], kFC * B * S1 * 4);
+    if (kMid) {
+      mbar_arrive_expect_tx(&bar_ex[1], kFC * B * S2 * 4);
+      mbar_arrive_expect_tx(&bar_ex[3], kFC * B * S2 * 4 * 2);
+    }
+  };
   if (threadIdx.x == 0) {
     mbar_init(&bar_tma0, 1);
     mbar_init(&bar_tma1, 1);
@@ -221,14 +242,7 @@ mlp_fused_step_kernel(const __grid_constant__ CUtensorMap tmXA, const __grid_con
     mbar_init(&bar_wg2, 1);
     for (int k = 0; k < 5; ++k) mbar_init(&bar_ex[k], 1);
     fence_mbar_init();
-    // arm the exchange barriers: bytes every CTA of the cluster (this one included) will deliver
-    mbar_arrive_expect_tx(&bar_ex[0], kFC * B * S1 * 4);
-    mbar_arrive_expect_tx(&bar_ex[2], kFC * B * 64);
-    mbar_arrive_expect_tx(&bar_ex[4], kFC * B * S1 * 4);
-    if (kMid) {
-      mbar_arrive_expect_tx(&bar_ex[1], kFC * B * S2 * 4);
-      mbar_arrive_expect_tx(&bar_ex[3], kFC * B * S2 * 4 * 2);
-    }
+    arm_exchanges();
   }
   if (warp == 0) {
     tmem_alloc(&tmem_slot, 512);
@@ -248,15 +262,26 @@ mlp_fused_step_kernel(const __grid_constant__ CUtensorMap tmXA, const __grid_con
   // just below — touch nothing the predecessor writes; parameters and gradients are only accessed
   // after griddepcontrol.wait.
   asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
+  // ================================================================== step loop
+  // One launch can run several optimisation steps back to back (single-GPU mode, SGD applied in place): the
+  // launch gap, TMEM allocation and barrier set-up are paid once; steps are separated by one cluster barrier
+  // that also publishes the weight updates (red.global + __threadfence) to the next step's loads.
+  const int nsteps = p.nsteps > 0 ? p.nsteps : 1;
+  for (int st = 0; st < nsteps; ++st) {
+  const uint32_t sp = st & 1;  // parity of the barriers that complete once per step
+  FPROF(13);
   if (warp == 0 && elect_one()) {
+    const int xr = (p.slot0 + st) * B;
     mbar_arrive_expect_tx(&bar_tma0, 4 * kTileK + (H1 / 32) * kW1Col);
-    for (int b = 0; b < 4; ++b) tma_load_2d(smem + oXA + b * kTileK, &tmXA, &bar_tma0, k0 + 32 * b, 0);
+    for (int b = 0; b < 4; ++b) tma_load_2d(smem + oXA + b * kTileK, &tmXA, &bar_tma0, k0 + 32 * b, xr);
     uint32_t bytes1 = 4 * kColM + 2 * SL * 128;
     if (kMid) bytes1 += (H2 / 32) * S1 * 128 + (H2 / 32) * S1 * 128;
     mbar_arrive_expect_tx(&bar_tma1, bytes1);
-    for (int a = 0; a < 4; ++a) tma_load_2d(smem + oXT + a * kColM, &tmXT, &bar_tma1, k0 + 32 * a, 0);
+    for (int a = 0; a < 4; ++a) tma_load_2d(smem + oXT + a * kColM, &tmXT, &bar_tma1, k0 + 32 * a, xr);
+    if (st + 1 < nsteps)  // pull the next step's inputs from HBM into L2 while this step computes
+      for (int b = 0; b < 4; ++b) tma_prefetch_2d(&tmXA, k0 + 32 * b, xr + B);
   }
-  asm volatile("griddepcontrol.wait;" ::: "memory");
+  if (st == 0) asm volatile("griddepcontrol.wait;" ::: "memory");
   if (warp == 0) {
     if (elect_one()) {
     for (int a = 0; a < H1 / 32; ++a) tma_load_2d(smem + oW1B + a * kW1Col, &tmW1, &bar_tma0, 32 * a, k0);
@@ -269,7 +294,7 @@ mlp_fused_step_kernel(const __grid_constant__ CUtensorMap tmXA, const __grid_con
     }
     __syncwarp();
     // ---------------------------------------------------------------- F1: P1 = X_j . W1_j
-    mbar_wait(&bar_tma0, 0);
+    mbar_wait(&bar_tma0, sp);
     tc_fence_after_sync();
     if (elect_one()) {
       const uint32_t idesc = make_instr_desc(4, false, true, H1);
@@ -280,7 +305,31 @@ mlp_fused_step_kernel(const __grid_constant__ CUtensorMap tmXA, const __grid_con
     }
     __syncwarp();
   }
-  const float step = p.wparams != nullptr ? __ldg(p.lr) : 0.f;  // (after griddepcontrol.wait)
+  const float step = p.wparams != nullptr ? __ldcg(p.lr) : 0.f;  // (after griddepcontrol.wait)
+  // Biases of this CTA's slices and this row's label: requested now, consumed phases later (a cold global load
+  // on the critical chain costs ~0.6 us each time).
+  float b1r[S1], b2r[kMid ? S2 : 1], blr[16];
+  int ylab = 0;
+  if (rok) {
+    ylab = __ldg(p.labels + st * B + row);
+#pragma unroll
+    for (int c = 0; c < S1; c += 4) {
+      const float4 v = __ldcg(reinterpret_cast<const float4*>(p.params + p.b_off[0] + S1 * j + c));
+      b1r[c] = v.x; b1r[c + 1] = v.y; b1r[c + 2] = v.z; b1r[c + 3] = v.w;
+    }
+    if (kMid) {
+#pragma unroll
+      for (int c = 0; c < S2; c += 4) {
+        const float4 v = __ldcg(reinterpret_cast<const float4*>(p.params + p.b_off[1] + S2 * j + c));
+        b2r[c] = v.x; b2r[c + 1] = v.y; b2r[c + 2] = v.z; b2r[c + 3] = v.w;
+      }
+    }
+#pragma unroll
+    for (int c = 0; c < 16; c += 4) {
+      const float4 v = __ldcg(reinterpret_cast<const float4*>(p.params + p.b_off[LAST] + c));
+      blr[c] = v.x; blr[c + 1] = v.y; blr[c + 2] = v.z; blr[c + 3] = v.w;
+    }
+  }
   float h1[S1];
   float h2[kMid ? S2 : 1];
   if (worker) {
@@ -307,7 +356,7 @@ mlp_fused_step_kernel(const __grid_constant__ CUtensorMap tmXA, const __grid_con
 
   // ------------------------------------------------------------------ P1: H1_j, layer-2 partial
   if (worker) {
-    mbar_wait(&bar_ex[0], 0);
+    mbar_wait(&bar_ex[0], sp);
     FPROF(3);
 #pragma unroll
     for (int c = 0; c < S1; ++c) h1[c] = 0.f;
@@ -320,9 +369,8 @@ mlp_fused_step_kernel(const __grid_constant__ CUtensorMap tmXA, const __grid_con
           h1[c] += v.x; h1[c + 1] += v.y; h1[c + 2] += v.z; h1[c + 3] += v.w;
         }
       }
-      const float* b1 = p.params + p.b_off[0] + S1 * j;
 #pragma unroll
-      for (int c = 0; c < S1; ++c) h1[c] = fmaxf(h1[c] + __ldg(b1 + c), 0.f);
+      for (int c = 0; c < S1; ++c) h1[c] = fmaxf(h1[c] + b1r[c], 0.f);
 #pragma unroll
       for (int c = 0; c < S1; c += 4) {
         *reinterpret_cast<float4*>(smem + oH1K + koff(row, c)) = make_float4(h1[c], h1[c + 1], h1[c + 2], h1[c + 3]);
@@ -334,14 +382,14 @@ mlp_fused_step_kernel(const __grid_constant__ CUtensorMap tmXA, const __grid_con
         for (int c = 0; c < S1; ++c) p.dbg[row * H1 + S1 * j + c] = h1[c];
     }
     // X^T tile: column 127 lies outside every CTA's K slice (<= 104 wide) -> make it the ones column
-    mbar_wait(&bar_tma1, 0);
+    mbar_wait(&bar_tma1, sp);
     if (rok) *reinterpret_cast<float*>(smem + oXT + moff(row, 127)) = 1.f;
     fence_proxy_async_smem();
   }
   __syncthreads();
   if (kMid) {
     if (warp == 0) {
-      mbar_wait(&bar_tma1, 0);
+      mbar_wait(&bar_tma1, sp);
       fence_proxy_async_smem();
       tc_fence_after_sync();
       if (elect_one()) {
@@ -373,7 +421,7 @@ mlp_fused_step_kernel(const __grid_constant__ CUtensorMap tmXA, const __grid_con
     FPROF(4);
     // ---------------------------------------------------------------- P2: H2_j
     if (worker) {
-      mbar_wait(&bar_ex[1], 0);
+      mbar_wait(&bar_ex[1], sp);
       FPROF(5);
 #pragma unroll
       for (int c = 0; c < S2; ++c) h2[c] = 0.f;
@@ -386,9 +434,8 @@ mlp_fused_step_kernel(const __grid_constant__ CUtensorMap tmXA, const __grid_con
             h2[c] += v.x; h2[c + 1] += v.y; h2[c + 2] += v.z; h2[c + 3] += v.w;
           }
         }
-        const float* b2 = p.params + p.b_off[1] + S2 * j;
 #pragma unroll
-        for (int c = 0; c < S2; ++c) h2[c] = fmaxf(h2[c] + __ldg(b2 + c), 0.f);
+        for (int c = 0; c < S2; ++c) h2[c] = fmaxf(h2[c] + b2r[kMid ? c : 0], 0.f);
 #pragma unroll
         for (int c = 0; c < S2; c += 4) {
           *reinterpret_cast<float4*>(smem + oH2K + koff(row, c)) = make_float4(h2[c], h2[c + 1], h2[c + 2], h2[c + 3]);
@@ -407,7 +454,7 @@ mlp_fused_step_kernel(const __grid_constant__ CUtensorMap tmXA, const __grid_con
   const uint32_t oDZ1 = kMid ? oDZ1M : oDZ1M2;
   const uint32_t oHLM = kMid ? oH2M : oH1M;
   if (warp == 0) {
-    if (!kMid) mbar_wait(&bar_tma1, 0);
+    if (!kMid) mbar_wait(&bar_tma1, sp);
     fence_proxy_async_smem();
     tc_fence_after_sync();
     if (elect_one()) {
@@ -443,7 +490,7 @@ mlp_fused_step_kernel(const __grid_constant__ CUtensorMap tmXA, const __grid_con
   // ------------------------------------------------------------------ P3: softmax-CE, last-layer grads
   float dz3[16];
   if (worker) {
-    mbar_wait(&bar_ex[2], 0);
+    mbar_wait(&bar_ex[2], sp);
     FPROF(7);
     float z[16];
 #pragma unroll
@@ -459,12 +506,11 @@ mlp_fused_step_kernel(const __grid_constant__ CUtensorMap tmXA, const __grid_con
           z[c] += v.x; z[c + 1] += v.y; z[c + 2] += v.z; z[c + 3] += v.w;
         }
       }
-      const float* bl = p.params + p.b_off[LAST];
       float mx = -INFINITY;
       int arg = 0;
 #pragma unroll
       for (int c = 0; c < 16; ++c) {
-        z[c] += __ldg(bl + c);
+        z[c] += blr[c];
         if (c < p.C && z[c] > mx) { mx = z[c]; arg = c; }
       }
       float sum = 0.f;
@@ -474,7 +520,7 @@ mlp_fused_step_kernel(const __grid_constant__ CUtensorMap tmXA, const __grid_con
         sum += z[c];
       }
       const float inv = 1.f / sum;
-      const int y = p.labels[row];
+      const int y = ylab;
       const float scale = 1.f / static_cast<float>(B);
 #pragma unroll
       for (int c = 0; c < 16; ++c) {
@@ -525,8 +571,8 @@ mlp_fused_step_kernel(const __grid_constant__ CUtensorMap tmXA, const __grid_con
     __syncwarp();
   }
   if (worker && j == 0 && wwarp == 0 && lane == 0) {  // (red[] was filled before the __syncthreads above)
-    p.metrics[0] = red[0] + red[1] + red[2] + red[3];
-    reinterpret_cast<int*>(p.metrics)[1] = reinterpret_cast<int*>(red)[8] + reinterpret_cast<int*>(red)[9] +
+    p.metrics[2 * st] = red[0] + red[1] + red[2] + red[3];
+    reinterpret_cast<int*>(p.metrics)[2 * st + 1] = reinterpret_cast<int*>(red)[8] + reinterpret_cast<int*>(red)[9] +
                                            reinterpret_cast<int*>(red)[10] + reinterpret_cast<int*>(red)[11];
   }
   float dzl[SL];
@@ -563,7 +609,7 @@ mlp_fused_step_kernel(const __grid_constant__ CUtensorMap tmXA, const __grid_con
     FPROF(8);
     // ---------------------------------------------------------------- P4: layer-2 grads
     if (warp == 0) {
-      mbar_wait(&bar_ex[3], 0);
+      mbar_wait(&bar_ex[3], sp);
       fence_proxy_async_smem();
       tc_fence_after_sync();
       if (elect_one()) {
@@ -614,7 +660,7 @@ mlp_fused_step_kernel(const __grid_constant__ CUtensorMap tmXA, const __grid_con
 
   // ------------------------------------------------------------------ P5: dW1_j = X_j^T . dZ1
   if (warp == 0) {
-    mbar_wait(&bar_ex[4], 0);
+    mbar_wait(&bar_ex[4], sp);
     fence_proxy_async_smem();
     tc_fence_after_sync();
     if (elect_one()) {
@@ -629,7 +675,7 @@ mlp_fused_step_kernel(const __grid_constant__ CUtensorMap tmXA, const __grid_con
   float dbl[16];  // last-layer bias gradient (valid in the thread that owns accumulator row SL)
   if (worker) {
     // while dW1 runs on the tensor core: drain the weight-gradient GEMMs that ran beside the chain
-    mbar_wait(&bar_wgl, 0);
+    mbar_wait(&bar_wgl, sp);
     tc_fence_after_sync();
     {
       uint32_t r[16];
@@ -647,7 +693,7 @@ mlp_fused_step_kernel(const __grid_constant__ CUtensorMap tmXA, const __grid_con
       }
     }
     if (kMid) {
-      mbar_wait(&bar_wg2, 0);
+      mbar_wait(&bar_wg2, sp);
       tc_fence_after_sync();
 #pragma unroll
       for (int cc = 0; cc < H2; cc += 16) {
@@ -692,15 +738,28 @@ mlp_fused_step_kernel(const __grid_constant__ CUtensorMap tmXA, const __grid_con
       }
     }
   }
-  FPROF(12);
-  tc_fence_before_sync();
-  __syncthreads();
-  cluster_sync_all();  // nobody leaves while a peer could still be writing into its shared memory
-  if (j == 0 && worker && row == SL) {  // every CTA has read the last bias by now: CTA 0 may update it
+  mma_phase ^= 1;
+  // Last-layer bias: every CTA consumed its copy before delivering dZ1, and wgrad1 (just waited for) was issued
+  // after all dZ1 arrived -> CTA 0 may update it now; the end-of-step barrier publishes it.
+  if (j == 0 && worker && row == SL) {
     const size_t off = p.b_off[LAST];
 #pragma unroll
     for (int c = 0; c < 16; c += 4) emit_grad4(p, step, off + c, dbl[c], dbl[c + 1], dbl[c + 2], dbl[c + 3]);
   }
+  FPROF(12);
+  // ---- end of step: my weight updates are performed (fence), my reads of exchanged data are done, the
+  // exchange barriers are re-armed BEFORE any peer can pass the barrier and start sending the next step's data.
+  if (st + 1 < nsteps) {
+    __threadfence();
+    fence_proxy_async_all();  // the next step's TMA loads (async proxy) re-read weights updated by red.global
+    if (threadIdx.x == 0) arm_exchanges();
+  }
+  tc_fence_before_sync();
+  __syncthreads();
+  cluster_sync_all();  // last step: nobody leaves while a peer could still be writing into its shared memory
+  tc_fence_after_sync();
+  FPROF(14);
+  }  // step loop
   if (warp == 0) {
     tc_fence_after_sync();
     tmem_dealloc(tm, 512);
@@ -711,6 +770,7 @@ struct FusedPlan {
   CUtensorMap tmXA, tmXT, tmW1, tmW2B, tmW2K, tmWLB, tmWLK;
   FusedParams p;
   int layers;
+  int slots;
 };
 
 }  // namespace dmlp
@@ -739,8 +799,10 @@ extern "C" int dmlp_mlp_fused_plan_create(const dmlp_mlp_fused_desc_t* d, dmlp_m
   int rc = 0;
 #define MK(expr) do { rc = (expr); if (rc) { delete pl; return rc; } } while (0)
   // X as K-major A (forward) and as MN-major A (layer-1 weight gradient)
-  MK(make_tensor_map_2d(&pl->tmXA, d->x_dev, 4, false, in0, d->batch, in0, 32, kFBK, 1));
-  MK(make_tensor_map_2d(&pl->tmXT, d->x_dev, 4, false, in0, d->batch, in0, 32, kFBK, 2));
+  const int slots = d->x_slots > 1 ? d->x_slots : 1;
+  DMLP_REQUIRE(slots == 1 || d->sgd_params_dev != nullptr, "multi-step launches need in-place SGD (sgd_params_dev)");
+  MK(make_tensor_map_2d(&pl->tmXA, d->x_dev, 4, false, in0, d->batch * slots, in0, 32, kFBK, 1));
+  MK(make_tensor_map_2d(&pl->tmXT, d->x_dev, 4, false, in0, d->batch * slots, in0, 32, kFBK, 2));
   MK(make_tensor_map_2d(&pl->tmW1, P + d->w_off[0], 4, false, H1, in0, H1, 32, kKGroupsMax * 8, 2));
   const int last = L - 1;
   if (L == 3) {
@@ -766,6 +828,9 @@ extern "C" int dmlp_mlp_fused_plan_create(const dmlp_mlp_fused_desc_t* d, dmlp_m
   p.lr = d->lr_dev;
   p.prof = reinterpret_cast<unsigned long long*>(d->prof_dev);
   pl->layers = L;
+  pl->slots = slots;
+  p.nsteps = 1;
+  p.slot0 = 0;
   *out = reinterpret_cast<dmlp_mlp_fused_plan_t>(pl);
   return DMLP_OK;
 }
@@ -776,7 +841,7 @@ extern "C" int dmlp_mlp_fused_plan_destroy(dmlp_mlp_fused_plan_t h) {
 }
 
 template <int S1, int S2>
-static int launch_fused(const FusedPlan* pl, cudaStream_t st) {
+static int launch_fused(const FusedPlan* pl, const FusedParams& prm, cudaStream_t st) {
   auto kern = mlp_fused_step_kernel<S1, S2>;
   static unsigned long long attr_mask = 0;
   int dev = 0;
@@ -796,7 +861,7 @@ static int launch_fused(const FusedPlan* pl, cudaStream_t st) {
   attr[0].val.programmaticStreamSerializationAllowed = 1;
   cfg.attrs = attr;
   cfg.numAttrs = 1;
-  DMLP_CUDA_CHECK(cudaLaunchKernelEx(&cfg, kern, pl->tmXA, pl->tmXT, pl->tmW1, pl->tmW2B, pl->tmW2K, pl->tmWLB, pl->tmWLK, pl->p));
+  DMLP_CUDA_CHECK(cudaLaunchKernelEx(&cfg, kern, pl->tmXA, pl->tmXT, pl->tmW1, pl->tmW2B, pl->tmW2K, pl->tmWLB, pl->tmWLK, prm));
   DMLP_CUDA_CHECK(cudaGetLastError());
   return DMLP_OK;
 }
@@ -804,6 +869,21 @@ static int launch_fused(const FusedPlan* pl, cudaStream_t st) {
 extern "C" int dmlp_mlp_fused_step(dmlp_mlp_fused_plan_t h, void* stream) {
   const FusedPlan* pl = reinterpret_cast<const FusedPlan*>(h);
   DMLP_REQUIRE(pl, "null fused plan");
-  if (pl->layers == 3) return launch_fused<16, 8>(pl, as_stream(stream));
-  return launch_fused<16, 0>(pl, as_stream(stream));
+  if (pl->layers == 3) return launch_fused<16, 8>(pl, pl->p, as_stream(stream));
+  return launch_fused<16, 0>(pl, pl->p, as_stream(stream));
+}
+
+extern "C" int dmlp_mlp_fused_steps(dmlp_mlp_fused_plan_t h, int slot0, int nsteps, void* stream) {
+  const FusedPlan* pl = reinterpret_cast<const FusedPlan*>(h);
+  DMLP_REQUIRE(pl, "null fused plan");
+  DMLP_REQUIRE(nsteps >= 1 && slot0 >= 0 && slot0 + nsteps <= pl->slots, "dmlp_mlp_fused_steps: slots [%d, %d) outside the plan's %d",
+               slot0, slot0 + nsteps, pl->slots);
+  DMLP_REQUIRE(nsteps == 1 || pl->p.wparams != nullptr, "dmlp_mlp_fused_steps: several steps per launch need in-place SGD");
+  FusedParams prm = pl->p;
+  prm.nsteps = nsteps;
+  prm.slot0 = slot0;
+  prm.labels = pl->p.labels + static_cast<size_t>(slot0) * pl->p.B;
+  prm.metrics = pl->p.metrics + 2 * static_cast<size_t>(slot0);
+  if (pl->layers == 3) return launch_fused<16, 8>(pl, prm, as_stream(stream));
+  return launch_fused<16, 0>(pl, prm, as_stream(stream));
 }

@@ -93,7 +93,10 @@ struct Trainer {
   float* x_ring = nullptr;
   int* y_ring = nullptr;
   float* metrics_ring = nullptr;  // [kRingSlots][2] on the device, copied to the host once per chunk
-  dmlp_mlp_fused_plan_t rplan[16];
+  dmlp_mlp_fused_plan_t rplan[kRingSlots];
+  // single-GPU mode: ONE plan over the whole ring; a chunk's steps run inside one launch (weights updated in place
+  // between steps inside the kernel), see dmlp_mlp_fused_steps
+  dmlp_mlp_fused_plan_t ring_plan = nullptr;
   cudaEvent_t ev_ring_h2d[2], ev_ring_done[2];
   bool ring_launched[2] = {false, false};
   bool fused_ce = false;   // softmax-CE runs in the last forward GEMM's epilogue
@@ -101,6 +104,7 @@ struct Trainer {
   cudaStream_t s_aux = nullptr;  // wgrad branch (runs beside the dgrad chain)
   cudaEvent_t ev_dz[kMaxLayers], ev_aux_done;
   int kernels_per_step = 0;
+  long long launches_last_run = 0;  // kernel launches of the most recent run (fused path: a launch may cover several steps)
   unsigned long long steps_done = 0;
   std::vector<void*> owned;
 };
@@ -217,6 +221,23 @@ static int build_plans(Trainer* t) {
       f.metrics_dev = t->metrics_ring + 2 * slot;  // device memory: a write to mapped host memory stalls kernel completion
       if (t->comm == nullptr && t->cfg.fused != 2) { f.sgd_params_dev = t->params; f.lr_dev = t->lr_dev; }
       TRY(dmlp_mlp_fused_plan_create(&f, &t->rplan[slot]));
+    }
+    if (t->comm == nullptr && t->cfg.fused != 2) {
+      dmlp_mlp_fused_desc_t f;
+      memset(&f, 0, sizeof(f));
+      f.num_layers = L.L;
+      for (int l = 0; l <= L.L; ++l) f.dims[l] = t->cfg.dims[l];
+      f.batch = B;
+      f.x_dev = t->x_ring;
+      f.labels_dev = t->y_ring;
+      f.params_dev = t->params;
+      f.grads_dev = t->grads[0];
+      for (int l = 0; l < L.L; ++l) { f.w_off[l] = L.w_off[l]; f.b_off[l] = L.b_off[l]; }
+      f.metrics_dev = t->metrics_ring;
+      f.sgd_params_dev = t->params;
+      f.lr_dev = t->lr_dev;
+      f.x_slots = kRingSlots;
+      TRY(dmlp_mlp_fused_plan_create(&f, &t->ring_plan));
     }
   }
   return DMLP_OK;
@@ -377,6 +398,7 @@ static int run_fused_ring(Trainer* t, const float* x_host, const int32_t* y_host
   // Gradient buffers alternate with the GLOBAL step parity (slot parity == step parity), also across
   // calls: a call that starts on an odd step begins at slot 1 of its first chunk.
   int s0 = 0, ci = 0, last_c = -1;
+  long long launches = 0;
   while (s0 < steps) {
     const int c = ci % kRingChunks;
     const int off = (ci == 0) ? static_cast<int>(t->steps_done & 1) : 0;
@@ -401,7 +423,9 @@ static int run_fused_ring(Trainer* t, const float* x_host, const int32_t* y_host
     }
     DMLP_CUDA_CHECK(cudaEventRecord(t->ev_ring_h2d[c], t->s_copy));
     DMLP_CUDA_CHECK(cudaStreamWaitEvent(t->s_main, t->ev_ring_h2d[c], 0));
-    for (int i = 0; i < n; ++i) {
+    static int per_launch_env = -1;  // experiment knob: cap on steps per launch (default: the whole chunk)
+    if (per_launch_env < 0) { const char* e = getenv("DMLP_FUSED_STEPS_PER_LAUNCH"); per_launch_env = (e && atoi(e) > 0) ? atoi(e) : kRingChunk; }
+    for (int i = 0; i < n;) {
       const int s = s0 + i;
       if (lr_schedule && lr_schedule[s] != t->lr_host[0]) {
         DMLP_CUDA_CHECK(cudaStreamSynchronize(t->s_main));
@@ -409,8 +433,19 @@ static int run_fused_ring(Trainer* t, const float* x_host, const int32_t* y_host
         DMLP_CUDA_CHECK(cudaMemcpyAsync(t->lr_dev, t->lr_host, 4, cudaMemcpyHostToDevice, t->s_main));
       }
       const int slot = c * kRingChunk + off + i;
-      TRY(dmlp_mlp_fused_step(t->rplan[slot], t->s_main));
-      if (t->comm != nullptr || t->cfg.fused == 2) TRY(enqueue_allreduce(t, slot & 1, 0, L.total, t->s_main));
+      if (t->ring_plan != nullptr) {
+        // as many steps as share this learning rate, in one launch
+        int m = 1;
+        while (i + m < n && m < per_launch_env && (!lr_schedule || lr_schedule[s + m] == t->lr_host[0])) ++m;
+        TRY(dmlp_mlp_fused_steps(t->ring_plan, slot, m, t->s_main));
+        ++launches;
+        i += m;
+      } else {
+        TRY(dmlp_mlp_fused_step(t->rplan[slot], t->s_main));
+        TRY(enqueue_allreduce(t, slot & 1, 0, L.total, t->s_main));
+        launches += 2;
+        i += 1;
+      }
     }
     DMLP_CUDA_CHECK(cudaMemcpyAsync(t->metrics_host + 4 + 2 * (c * kRingChunk + off), t->metrics_ring + 2 * (c * kRingChunk + off),
                                     8 * n, cudaMemcpyDeviceToHost, t->s_main));
@@ -428,6 +463,7 @@ static int run_fused_ring(Trainer* t, const float* x_host, const int32_t* y_host
   // drain in launch order
   if (last_c >= 0) { collect((last_c + 1) % kRingChunks); collect(last_c); }
   t->kernels_per_step = (t->comm != nullptr || t->cfg.fused == 2) ? 2 : 1;
+  t->launches_last_run = launches;
   t->steps_done += steps;
   if (t->comm) {
     uint32_t st[5];
@@ -497,6 +533,7 @@ extern "C" int dmlp_trainer_destroy(dmlp_trainer_t h) {
     if (t->fplan[p]) dmlp_mlp_fused_plan_destroy(t->fplan[p]);
   for (int sl = 0; sl < kRingSlots; ++sl)
     if (t->rplan[sl]) dmlp_mlp_fused_plan_destroy(t->rplan[sl]);
+  if (t->ring_plan) dmlp_mlp_fused_plan_destroy(t->ring_plan);
   for (int c = 0; c < kRingChunks; ++c) {
     if (t->ev_ring_h2d[c]) cudaEventDestroy(t->ev_ring_h2d[c]);
     if (t->ev_ring_done[c]) cudaEventDestroy(t->ev_ring_done[c]);
@@ -624,7 +661,7 @@ extern "C" int dmlp_trainer_create(const dmlp_trainer_config_t* cfg, int device,
     else { TRYF(dev_alloc(t, n * 4, &p)); t->dz[l] = static_cast<float*>(p); }
   }
   TRYF(dev_alloc(t, 16, &p)); t->lr_dev = static_cast<float*>(p);
-  CUF(cudaHostAlloc(reinterpret_cast<void**>(&t->metrics_host), 512, cudaHostAllocPortable | cudaHostAllocMapped));
+  CUF(cudaHostAlloc(reinterpret_cast<void**>(&t->metrics_host), 1024, cudaHostAllocPortable | cudaHostAllocMapped));
   CUF(cudaHostAlloc(reinterpret_cast<void**>(&t->lr_host), 64, cudaHostAllocPortable));
   memset(t->metrics_host, 0, 512);
   t->lr_host[0] = cfg->lr;
@@ -684,6 +721,13 @@ extern "C" int dmlp_trainer_set_lr(dmlp_trainer_t h, float lr) {
   t->lr_host[0] = lr;
   DMLP_CUDA_CHECK(cudaMemcpyAsync(t->lr_dev, t->lr_host, 4, cudaMemcpyHostToDevice, t->s_main));
   DMLP_CUDA_CHECK(cudaStreamSynchronize(t->s_main));
+  return DMLP_OK;
+}
+
+extern "C" int dmlp_trainer_launches_last_run(dmlp_trainer_t h, long long* n) {
+  Trainer* t = reinterpret_cast<Trainer*>(h);
+  DMLP_REQUIRE(t && n, "bad arguments");
+  *n = t->launches_last_run;
   return DMLP_OK;
 }
 

@@ -81,6 +81,7 @@ def _declare(lib) -> None:
         "dmlp_trainer_params_updated": [vp],
         "dmlp_trainer_set_lr": [vp, C.c_float],
         "dmlp_trainer_kernels_per_step": [vp, C.POINTER(i32)],
+        "dmlp_trainer_launches_last_run": [vp, C.POINTER(C.c_longlong)],
         "dmlp_trainer_run": [vp, vp, vp, sz, sz, sz, i32, vp, vp, i32, vp, vp],
         "dmlp_trainer_load_inputs": [vp, i32, vp, vp],
         "dmlp_trainer_run_resident": [vp, i32, i32, vp, vp],
@@ -227,6 +228,14 @@ class Trainer:
     def kernels_per_step(self) -> int:
         n = C.c_int()
         native.check(self.lib.dmlp_trainer_kernels_per_step(self._h, C.byref(n)))
+        return n.value
+
+    @property
+    def launches_last_run(self) -> int:
+        """Kernel launches of the most recent ``fit`` on the cluster-fused path (one launch may run several
+        steps); 0 on the per-layer path, where it is ``kernels_per_step * steps``."""
+        n = C.c_longlong()
+        native.check(self.lib.dmlp_trainer_launches_last_run(self._h, C.byref(n)))
         return n.value
 
     # ------------------------------------------------------------------ training

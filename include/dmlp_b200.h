@@ -297,10 +297,15 @@ typedef struct {
   void* prof_dev;            /* optional [8][16] u64 globaltimer stamps at the phase boundaries */
   float* sgd_params_dev;     /* non-null (single GPU): apply w -= lr*g in place (== params_dev) and write no gradients */
   const float* lr_dev;       /* device scalar, with sgd_params_dev */
+  int x_slots;               /* 0/1: x_dev is one batch. n > 1: x_dev / labels_dev / metrics_dev are rings of n slots
+                              * ([n][batch][dims[0]], [n][batch], [n][2]) addressed by dmlp_mlp_fused_steps */
 } dmlp_mlp_fused_desc_t;
 typedef struct dmlp_mlp_fused_opaque* dmlp_mlp_fused_plan_t;
 int dmlp_mlp_fused_supported(int num_layers, const int* dims, int batch);
 int dmlp_mlp_fused_plan_create(const dmlp_mlp_fused_desc_t* desc, dmlp_mlp_fused_plan_t* out);
+/* Runs `nsteps` consecutive optimisation steps on ring slots slot0 .. slot0+nsteps-1 in ONE launch (plan created with
+ * x_slots > 1 and sgd_params_dev: the weights are updated in place between the steps inside the kernel). */
+int dmlp_mlp_fused_steps(dmlp_mlp_fused_plan_t plan, int slot0, int nsteps, void* stream);
 int dmlp_mlp_fused_plan_destroy(dmlp_mlp_fused_plan_t plan);
 int dmlp_mlp_fused_step(dmlp_mlp_fused_plan_t plan, void* stream);
 
@@ -342,6 +347,9 @@ int dmlp_trainer_params(dmlp_trainer_t t, float** params_dev, size_t* count);
 int dmlp_trainer_params_updated(dmlp_trainer_t t);
 int dmlp_trainer_set_lr(dmlp_trainer_t t, float lr);
 int dmlp_trainer_kernels_per_step(dmlp_trainer_t t, int* n);
+/* Kernel launches issued by the most recent dmlp_trainer_run on the fused path (a launch may cover several steps);
+ * 0 when the per-layer path ran (use kernels_per_step * steps there). */
+int dmlp_trainer_launches_last_run(dmlp_trainer_t t, long long* n);
 int dmlp_trainer_run(dmlp_trainer_t t, const float* x_host, const int32_t* y_host, size_t num_batches,
                      size_t first_batch, size_t batch_stride, int steps, const float* lr_schedule,
                      float* metrics_out, int use_graph, void* start_event, void* stop_event);

@@ -17,7 +17,56 @@ class Desc(C.Structure):
     _fields_ = [("num_layers", C.c_int), ("dims", C.c_int * 4), ("batch", C.c_int), ("x", C.c_void_p), ("labels", C.c_void_p),
                 ("params", C.c_void_p), ("grads", C.c_void_p), ("w_off", C.c_size_t * 3), ("b_off", C.c_size_t * 3),
                 ("metrics", C.c_void_p), ("debug", C.c_void_p), ("prof", C.c_void_p),
-                ("sgd_params", C.c_void_p), ("lr", C.c_void_p)]
+                ("sgd_params", C.c_void_p), ("lr", C.c_void_p), ("x_slots", C.c_int)]
+
+
+def multi_step_profile(lib, dims, lay, B, slots=8):
+    """Timeline of the LAST step of an 8-step launch (in-place SGD with lr = 0), relative to that step's start."""
+    x = torch.rand(slots * B, 784, device="cuda")
+    y = torch.randint(0, 10, (slots * B,), device="cuda", dtype=torch.int32)
+    params = torch.from_numpy(lay.init_reference(0)).cuda()
+    grads = torch.zeros_like(params)
+    metrics = torch.zeros(2 * slots, device="cuda")
+    lr = torch.zeros(1, device="cuda")
+    prof = torch.zeros(8, 16, dtype=torch.int64, device="cuda")
+    d = Desc()
+    d.num_layers = 3
+    for i, v in enumerate(dims):
+        d.dims[i] = v
+    d.batch = B
+    d.x, d.labels, d.params, d.grads = x.data_ptr(), y.data_ptr(), params.data_ptr(), grads.data_ptr()
+    for l, s in enumerate(lay.layers):
+        d.w_off[l], d.b_off[l] = s.w_off, s.b_off
+    d.metrics, d.prof = metrics.data_ptr(), prof.data_ptr()
+    d.sgd_params, d.lr, d.x_slots = params.data_ptr(), lr.data_ptr(), slots
+    plan = C.c_void_p()
+    native.check(lib.dmlp_mlp_fused_plan_create(C.byref(d), C.byref(plan)))
+    lib.dmlp_mlp_fused_steps.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_void_p]
+    acc = np.zeros((8, 16))
+    n = 0
+    for it in range(30):
+        native.check(lib.dmlp_mlp_fused_steps(plan, 0, slots, None))
+        torch.cuda.synchronize()
+        if it >= 10:
+            p = prof.cpu().numpy().astype(np.float64)
+            acc += p - p[:, 13:14].min()
+            n += 1
+    acc /= n
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(50):
+        native.check(lib.dmlp_mlp_fused_steps(plan, 0, slots, None))
+    e1.record()
+    torch.cuda.synchronize()
+    names = ["-", "-", "F1 mma+scatter", "RS1 arrived", "H1+F2+scatter", "RS2 arrived", "H2+F3+allreduce",
+             "logits arrived", "CE+dgL+gather dZ2", "dgrad2 done", "gather dZ1", "wgrads drained + wg1 done", "stores",
+             "step start", "end-of-step barrier passed"]
+    mean = acc.mean(axis=0)
+    order = [13, 2, 3, 4, 5, 6, 7, 8, 9, 10, 11, 12, 14]
+    out = {"multi_step_launch_us_per_step": round(e0.elapsed_time(e1) * 1e3 / 50 / slots, 2),
+           "last_step_phase_end_us": {names[i]: round(mean[i] / 1e3, 2) for i in order},
+           "last_step_phase_us": {names[order[k]]: round((mean[order[k]] - mean[order[k - 1]]) / 1e3, 2) for k in range(1, len(order))}}
+    print(json.dumps(out, indent=1))
 
 
 def main():
@@ -67,6 +116,7 @@ def main():
         e1.record(st)
         torch.cuda.synchronize()
     acc /= n
+    multi_step_profile(lib, dims, lay, B)
     names = ["entry", "cluster live", "F1 mma+scatter", "RS1 arrived", "H1+F2+scatter", "RS2 arrived", "H2+F3+allreduce",
              "logits arrived", "CE+dgL+gather dZ2", "dgrad2 done", "gather dZ1", "wgrads drained + wg1 done", "stores"]
     mean = acc.mean(axis=0)

@@ -51,6 +51,23 @@ def test_fused_training_matches_per_layer_path(dims, use_graph):
     assert np.allclose(sa["per_step_loss"], sb["per_step_loss"], rtol=2e-2, atol=2e-3)
     assert np.abs(a.get_params() - b.get_params()).max() < 3e-3
     assert a.kernels_per_step == 1 and b.kernels_per_step >= 6
+    # single-GPU fused path: a chunk of steps runs inside ONE launch (weights updated in place between steps)
+    assert a.launches_last_run == 3 and b.launches_last_run == 0
+    a.close()
+    b.close()
+
+
+def test_fused_multi_step_launch_with_lr_schedule():
+    """A learning-rate change inside a chunk splits the launch; results still follow the per-layer path."""
+    from dmlp_b200.utils.data import synthetic_mnist
+    dims = (784, 128, 64, 10)
+    x, y = synthetic_mnist(64 * 24, seed=5)
+    sched = lambda s: 0.1 if s < 5 else (0.05 if s < 13 else 0.02)  # noqa: E731
+    a, b = _trainer(dims, fused=1, lr=0.1), _trainer(dims, fused=0, lr=0.1)
+    sa, sb = a.fit(x, y, 24, lr_schedule=sched), b.fit(x, y, 24, lr_schedule=sched)
+    assert np.allclose(sa["per_step_loss"], sb["per_step_loss"], rtol=2e-2, atol=2e-3)
+    assert np.abs(a.get_params() - b.get_params()).max() < 3e-3
+    assert a.launches_last_run == 5  # [0,5) [5,8) [8,13) [13,16) [16,24)
     a.close()
     b.close()
 
