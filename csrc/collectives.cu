@@ -45,6 +45,8 @@ constexpr int kPadAbort = kPadRingAck + kMaxCollBlocks;         // [1] abort wor
 constexpr int kPadWords = kPadAbort + 8;
 constexpr size_t kPadBytes = 64 * 1024;                        // reserved at the start of a segment
 static_assert(kPadWords * 4 <= kPadBytes, "signal pad overflow");
+static_assert(kPadAbort == kPadAbortWord && kPadWords <= kPadFusedFlags && (kPadFusedEpoch + 1) * 4 <= kPadBytes,
+              "common.h pad words out of sync with this layout");
 // Local (never peer-accessed) per-rank state: barrier epochs then ring sequence numbers.
 constexpr int kStateEpoch = 0;
 constexpr int kStateRingSeq = kMaxCollBlocks;

@@ -41,3 +41,11 @@ struct DeviceGuard {
 };
 
 }  // namespace dmlp
+
+// Words of a rank's peer-visible signal pad (64 KiB at the start of its communicator segment) that more than one
+// translation unit addresses. collectives.cu owns the layout and static_asserts these against it.
+namespace dmlp {
+constexpr int kPadAbortWord = 1280;          // abort word (== kPadAbort in collectives.cu)
+constexpr int kPadFusedFlags = 8192;         // fused step kernel: [source rank][cta] arrival epochs (64 words)
+constexpr int kPadFusedEpoch = 8192 + 64;    // fused step kernel: this rank's step epoch (local use)
+}  // namespace dmlp

@@ -53,6 +53,13 @@ struct FusedParams {
   const float* lr;
   float* dbg;      // optional dump of intermediates (tests)
   unsigned long long* prof;  // optional [8 CTAs][16] globaltimer stamps at phase boundaries
+  // ---- in-kernel data-parallel gradient exchange (world > 1), see the "gradient exchange" block in the kernel
+  int world, rank;
+  float* xrecv[8];          // rank r's receive area as mapped here: [2 parities][world sources][total floats]
+  uint32_t* xpad[8];        // rank r's signal pad (flags at kPadFusedFlags + src*8 + cta; epoch word at kPadFusedEpoch)
+  uint32_t* xstatus;        // host-mapped failure record {code, rank, peer, phase} (watchdog), may be null
+  unsigned long long xtimeout_ns;
+  unsigned long long total;  // floats in the flat parameter vector
   int nsteps;      // steps this launch performs back to back (> 1 only with in-place SGD: wparams != null)
   int slot0;       // first input slot: step s reads rows [(slot0+s)*B, +B) of the X maps, labels + s*B, metrics + 2*s
 };
@@ -81,6 +88,16 @@ constexpr uint32_t oRED = oWLK + 4096;                 // reductions scratch
 constexpr uint32_t oEND = oRED + 4096;
 constexpr uint32_t kFusedSmem = oEND + 32768 + 1024;   // slack: MMA over-read of MN-major A atoms + alignment
 // aliases (lifetimes are disjoint, see the phase table in the header comment)
+// Gradient exchange (data parallel): staging image of this CTA's gradients and the receive stages of the reduction.
+// All of it aliases regions that are dead by then (the W1 image is written after the last MMA has completed; the
+// small images sit in the layer-2/3 weight tiles, which no MMA reads after dgrad2).
+constexpr uint32_t kXsW1 = oXA;              // [nk1*8][128] fp32 <= 53,248 B
+constexpr uint32_t kXsW2 = oW2B;             // [16][64]
+constexpr uint32_t kXsWL = oW2B + 4096;      // [SL][16]
+constexpr uint32_t kXsB1 = oW2B + 5120, kXsB2 = oW2B + 5184, kXsBL = oW2B + 5248;
+constexpr uint32_t kXChunk = kKGroupsMax * 2 * 128 * 4;  // 13,312 B: a quarter of the W1 slice
+constexpr uint32_t kXr = kKGroupsMax * 8 * 128 * 4;      // receive stages start right after the W1 image ...
+static_assert(kXr + 8 * kXChunk <= oW2B, "receive stages run into the small staging images");  // ... 8 chunk buffers
 constexpr uint32_t oRS2 = oXA;                         // 8 src x 64 rows x 32 B = 16 KiB
 constexpr uint32_t oDZ2K = oXA + 16384;                // 2 K blocks x 8 KiB
 constexpr uint32_t oAR3 = oW1B;                        // 8 src x 64 rows x 64 B = 32 KiB
@@ -133,6 +150,18 @@ __device__ __forceinline__ void tmem_ld_x8(uint32_t taddr, uint32_t (&r)[8]) {
                : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7])
                : "r"(taddr) : "memory");
 }
+// Bulk (non-tensor) asynchronous copies: global -> shared with mbarrier completion, shared -> global in bulk groups.
+__device__ __forceinline__ void bulk_g2s(uint32_t dst_s, const void* src, uint32_t bytes, uint64_t* bar) {
+  asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(dst_s), "l"(src),
+               "r"(bytes), "r"(smem_u32(bar))
+               : "memory");
+}
+__device__ __forceinline__ void bulk_s2g(void* dst, uint32_t src_s, uint32_t bytes) {
+  asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;" ::"l"(dst), "r"(src_s), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void bulk_commit() { asm volatile("cp.async.bulk.commit_group;" ::: "memory"); }
+__device__ __forceinline__ void bulk_wait_all() { asm volatile("cp.async.bulk.wait_group 0;" ::: "memory"); }
+__device__ __forceinline__ void bulk_wait_read() { asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory"); }
 __device__ __forceinline__ void fence_proxy_async_all() { asm volatile("fence.proxy.async;" ::: "memory"); }
 // L2 prefetch of one TMA box (no shared-memory destination, no barrier)
 __device__ __forceinline__ void tma_prefetch_2d(const CUtensorMap* m, int c0, int c1) {
@@ -149,8 +178,13 @@ __device__ __forceinline__ uint64_t mdesc(uint32_t tile, int kstep, uint32_t col
 
 // Emits 4 consecutive gradient values: either into the gradient buffer (multi-GPU: the all-reduce
 // kernel consumes it) or straight into the weights as w -= lr*g (single GPU).
-__device__ __forceinline__ void emit_grad4(const FusedParams& p, float step, size_t off, float a, float b, float c, float d) {
-  if (p.wparams != nullptr) {
+// Exchange mode (xs != 0): the gradient goes to this CTA's staging image in shared memory (byte offset soff); the bulk
+// copy engine pushes the image to the peers afterwards.
+__device__ __forceinline__ void emit_grad4(const FusedParams& p, float step, size_t off, uint32_t xs, uint32_t soff, float a,
+                                           float b, float c, float d) {
+  if (xs != 0u) {
+    sts128(xs + soff, a, b, c, d);
+  } else if (p.wparams != nullptr) {
     // w += (-lr*g) as a fire-and-forget vector reduction: no load latency in the epilogue. Every
     // element is touched by exactly one thread, so the result equals w - lr*g bit for bit.
     asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(p.wparams + off), "f"(-step * a), "f"(-step * b),
@@ -204,7 +238,7 @@ mlp_fused_step_kernel(const __grid_constant__ CUtensorMap tmXA, const __grid_con
   // bar_mma: the critical chain F1 -> F2 -> F3 -> dgrad_last -> dgrad2 -> wgrad1 (phase toggles per use);
   // bar_wgl / bar_wg2: weight-gradient GEMMs that run beside the chain; bar_ex[k]: arrival of exchange k
   // (remote st.async stores complete transaction bytes on the DESTINATION's barrier: no cluster-wide barrier).
-  __shared__ __align__(8) uint64_t bar_tma0, bar_tma1, bar_mma, bar_wgl, bar_wg2, bar_ex[5];
+  __shared__ __align__(8) uint64_t bar_tma0, bar_tma1, bar_mma, bar_wgl, bar_wg2, bar_ex[5], bar_xr[4];
   __shared__ uint32_t tmem_slot;
 
   // Warp index through a shuffle: the role branches are then provably warp-uniform and the control warp's
@@ -241,6 +275,7 @@ mlp_fused_step_kernel(const __grid_constant__ CUtensorMap tmXA, const __grid_con
     mbar_init(&bar_wgl, 1);
     mbar_init(&bar_wg2, 1);
     for (int k = 0; k < 5; ++k) mbar_init(&bar_ex[k], 1);
+    for (int k = 0; k < 4; ++k) mbar_init(&bar_xr[k], 1);
     fence_mbar_init();
     arm_exchanges();
   }
@@ -267,6 +302,11 @@ mlp_fused_step_kernel(const __grid_constant__ CUtensorMap tmXA, const __grid_con
   // launch gap, TMEM allocation and barrier set-up are paid once; steps are separated by one cluster barrier
   // that also publishes the weight updates (red.global + __threadfence) to the next step's loads.
   const int nsteps = p.nsteps > 0 ? p.nsteps : 1;
+  const bool xmode = p.world > 1;
+  uint32_t xr_phase = 0;  // bit s: parity the next wait on receive stage s expects
+  uint32_t epoch0 = 0;  // steps this rank completed before this launch (every rank holds the same count)
+  __shared__ int s_xfail;
+  if (threadIdx.x == 0) s_xfail = 0;
   for (int st = 0; st < nsteps; ++st) {
   const uint32_t sp = st & 1;  // parity of the barriers that complete once per step
   FPROF(13);
@@ -281,7 +321,13 @@ mlp_fused_step_kernel(const __grid_constant__ CUtensorMap tmXA, const __grid_con
     if (st + 1 < nsteps)  // pull the next step's inputs from HBM into L2 while this step computes
       for (int b = 0; b < 4; ++b) tma_prefetch_2d(&tmXA, k0 + 32 * b, xr + B);
   }
-  if (st == 0) asm volatile("griddepcontrol.wait;" ::: "memory");
+  if (st == 0) {
+    asm volatile("griddepcontrol.wait;" ::: "memory");
+    if (xmode) epoch0 = __ldcg(p.xpad[p.rank] + kPadFusedEpoch);
+  }
+  const uint32_t epoch = epoch0 + static_cast<uint32_t>(st) + 1u;
+  const uint32_t xpar = epoch & 1u;  // receive areas are double-buffered by step parity
+  const uint32_t xs = xmode ? sb : 0u;  // exchange mode: gradients are staged in shared memory
   if (warp == 0) {
     if (elect_one()) {
     for (int a = 0; a < H1 / 32; ++a) tma_load_2d(smem + oW1B + a * kW1Col, &tmW1, &bar_tma0, 32 * a, k0);
@@ -685,7 +731,7 @@ mlp_fused_step_kernel(const __grid_constant__ CUtensorMap tmXA, const __grid_con
         const size_t off = p.w_off[LAST] + static_cast<size_t>(SL * j + row) * 16;
 #pragma unroll
         for (int c = 0; c < 16; c += 4)
-          emit_grad4(p, step, off + c, __uint_as_float(r[c]), __uint_as_float(r[c + 1]), __uint_as_float(r[c + 2]), __uint_as_float(r[c + 3]));
+          emit_grad4(p, step, off + c, xs, kXsWL + row * 64 + c * 4, __uint_as_float(r[c]), __uint_as_float(r[c + 1]), __uint_as_float(r[c + 2]), __uint_as_float(r[c + 3]));
       }
       if (row == SL) {  // the ones row: column sums of dZ_last = gradient of the last bias
 #pragma unroll
@@ -704,7 +750,7 @@ mlp_fused_step_kernel(const __grid_constant__ CUtensorMap tmXA, const __grid_con
           const size_t off = p.w_off[1] + static_cast<size_t>(S1 * j + row) * H2 + cc;
 #pragma unroll
           for (int c = 0; c < 16; c += 4)
-            emit_grad4(p, step, off + c, __uint_as_float(r[c]), __uint_as_float(r[c + 1]), __uint_as_float(r[c + 2]), __uint_as_float(r[c + 3]));
+            emit_grad4(p, step, off + c, xs, kXsW2 + row * (H2 * 4) + (cc + c) * 4, __uint_as_float(r[c]), __uint_as_float(r[c + 1]), __uint_as_float(r[c + 2]), __uint_as_float(r[c + 3]));
         }
         if (row == S1 && (S2 * j) / 16 == cc / 16) {  // ones row: db2; this CTA owns b2[S2*j, S2*j+S2)
           const int c0 = (S2 * j) % 16;
@@ -712,7 +758,7 @@ mlp_fused_step_kernel(const __grid_constant__ CUtensorMap tmXA, const __grid_con
 #pragma unroll
           for (int c = 0; c < 16; c += 4)
             if (c >= c0 && c < c0 + S2)
-              emit_grad4(p, step, off + (c - c0), __uint_as_float(r[c]), __uint_as_float(r[c + 1]), __uint_as_float(r[c + 2]), __uint_as_float(r[c + 3]));
+              emit_grad4(p, step, off + (c - c0), xs, kXsB2 + (c - c0) * 4, __uint_as_float(r[c]), __uint_as_float(r[c + 1]), __uint_as_float(r[c + 2]), __uint_as_float(r[c + 3]));
         }
       }
     }
@@ -728,13 +774,13 @@ mlp_fused_step_kernel(const __grid_constant__ CUtensorMap tmXA, const __grid_con
         const size_t off = p.w_off[0] + static_cast<size_t>(k0 + row) * H1 + cc;
 #pragma unroll
         for (int c = 0; c < 16; c += 4)
-          emit_grad4(p, step, off + c, __uint_as_float(r[c]), __uint_as_float(r[c + 1]), __uint_as_float(r[c + 2]), __uint_as_float(r[c + 3]));
+          emit_grad4(p, step, off + c, xs, kXsW1 + row * (H1 * 4) + (cc + c) * 4, __uint_as_float(r[c]), __uint_as_float(r[c + 1]), __uint_as_float(r[c + 2]), __uint_as_float(r[c + 3]));
       }
       if (row == 127 && cc == S1 * j) {  // ones row: db1; this CTA owns b1[S1*j, S1*j+S1)
         const size_t off = p.b_off[0] + S1 * j;
 #pragma unroll
         for (int c = 0; c < 16; c += 4)
-          emit_grad4(p, step, off + c, __uint_as_float(r[c]), __uint_as_float(r[c + 1]), __uint_as_float(r[c + 2]), __uint_as_float(r[c + 3]));
+          emit_grad4(p, step, off + c, xs, kXsB1 + c * 4, __uint_as_float(r[c]), __uint_as_float(r[c + 1]), __uint_as_float(r[c + 2]), __uint_as_float(r[c + 3]));
       }
     }
   }
@@ -744,9 +790,161 @@ mlp_fused_step_kernel(const __grid_constant__ CUtensorMap tmXA, const __grid_con
   if (j == 0 && worker && row == SL) {
     const size_t off = p.b_off[LAST];
 #pragma unroll
-    for (int c = 0; c < 16; c += 4) emit_grad4(p, step, off + c, dbl[c], dbl[c + 1], dbl[c + 2], dbl[c + 3]);
+    for (int c = 0; c < 16; c += 4) emit_grad4(p, step, off + c, xs, kXsBL + c * 4, dbl[c], dbl[c + 1], dbl[c + 2], dbl[c + 3]);
   }
   FPROF(12);
+  if (xmode) {
+    // ---------------------------------------------------------------- gradient exchange (data parallel)
+    // This CTA's gradient slices sit in a staging image in shared memory. The bulk copy engine pushes the image
+    // into slot [step parity][my rank] of every PEER's receive area (posted writes over NVLink: no round trips,
+    // one instruction per range). One arrival flag per (source rank, CTA): CTA j only needs the peers' CTA j
+    // (the last bias belongs to CTA 0 on every rank). Then the peers' slices and my weights are bulk-loaded
+    // back into shared memory chunk by chunk, summed in RANK ORDER — the same order on every rank, so the
+    // replicas stay bit-identical — w -= lr/world * sum is applied and the weights are bulk-stored.
+    // Slot reuse two steps later is safe: a peer's CTA j cannot send step s+1 before it has consumed step s.
+    fence_proxy_async_smem();  // staged gradients (generic stores) -> bulk copies (async proxy)
+    __syncthreads();
+    const int W = p.world;
+    const size_t slot_me = (static_cast<size_t>(xpar) * W + p.rank) * p.total;
+    const float* rbase = p.xrecv[p.rank] + static_cast<size_t>(xpar) * W * p.total;  // my receive area, this parity
+    const size_t w1_off = p.w_off[0] + static_cast<size_t>(k0) * H1;
+    // The layer-1 slice goes through the receive stages in 4 (world <= 4) or 8 chunks; a stage holds my weights
+    // chunk + one chunk per peer, and as many stages as fit into the 8 x 13 KiB of dead shared memory are in flight
+    // (world 2: the whole slice at once).
+    const int nchunk = W <= 4 ? 4 : 8;
+    const uint32_t chunk_rows = nk1 * 8 / nchunk, chunk_bytes = chunk_rows * H1 * 4;
+    const uint32_t buf_stride = W <= 4 ? kXChunk : kXChunk / 2;
+    int nstage = static_cast<int>((8 * kXChunk) / (W * buf_stride));
+    if (nstage > 4) nstage = 4;
+    // receive stage s: buffer 0 = my weights chunk, buffers 1.. = the peers' gradient chunks in rank order
+    auto stage_buf = [&](int sidx, int b) -> uint32_t { return sb + kXr + (sidx * W + b) * buf_stride; };
+    auto issue_chunk = [&](int c) {  // elected lane of warp 0
+      const int sidx = c % nstage;
+      mbar_arrive_expect_tx(&bar_xr[sidx], W * chunk_bytes);
+      const size_t o = w1_off + static_cast<size_t>(c) * chunk_rows * H1;
+      bulk_g2s(stage_buf(sidx, 0), p.wparams + o, chunk_bytes, &bar_xr[sidx]);
+      int b = 1;
+      for (int r = 0; r < W; ++r)
+        if (r != p.rank) bulk_g2s(stage_buf(sidx, b++), rbase + static_cast<size_t>(r) * p.total + o, chunk_bytes, &bar_xr[sidx]);
+    };
+    if (warp == 0) {
+      if (elect_one()) {
+        for (int r = 0; r < W; ++r) {
+          if (r == p.rank) continue;
+          float* d = p.xrecv[r] + slot_me;
+          bulk_s2g(d + w1_off, sb + kXsW1, nk1 * 8 * H1 * 4);
+          if (kMid) {
+            bulk_s2g(d + p.w_off[1] + static_cast<size_t>(S1 * j) * H2, sb + kXsW2, S1 * H2 * 4);
+            bulk_s2g(d + p.b_off[1] + S2 * j, sb + kXsB2, S2 * 4);
+          }
+          bulk_s2g(d + p.w_off[LAST] + static_cast<size_t>(SL * j) * 16, sb + kXsWL, SL * 16 * 4);
+          bulk_s2g(d + p.b_off[0] + S1 * j, sb + kXsB1, S1 * 4);
+          if (j == 0) bulk_s2g(d + p.b_off[LAST], sb + kXsBL, 64);
+        }
+        bulk_commit();
+        bulk_wait_all();         // the pushes are complete ...
+        fence_proxy_async_all();
+        __threadfence_system();  // ... and ordered before the flags
+        for (int r = 0; r < W; ++r)
+          if (r != p.rank) st_relaxed_sys(p.xpad[r] + kPadFusedFlags + p.rank * 8 + j, epoch);
+      }
+      __syncwarp();
+      if (lane < W && lane != p.rank) {
+        const int peer = lane;
+        const uint32_t* f = p.xpad[p.rank] + kPadFusedFlags + peer * 8 + j;
+        const unsigned long long deadline = globaltimer_ns() + p.xtimeout_ns;
+        uint32_t spins = 0;
+        while (static_cast<int32_t>(ld_relaxed_sys(f) - epoch) < 0) {
+          if ((++spins & 0x3F) == 0) {
+            if (ld_relaxed_sys(p.xpad[p.rank] + kPadAbortWord) != 0u) { s_xfail = 1; break; }
+            if (globaltimer_ns() > deadline) {
+              if (p.xstatus != nullptr) {
+                p.xstatus[1] = static_cast<uint32_t>(p.rank);
+                p.xstatus[2] = static_cast<uint32_t>(peer);
+                p.xstatus[3] = 5u;  // phase: fused-step gradient exchange
+                __threadfence_system();
+                p.xstatus[0] = DMLP_ERR_TIMEOUT;
+              }
+              for (int q = 0; q < W; ++q) st_relaxed_sys(p.xpad[q] + kPadAbortWord, 1u);
+              s_xfail = 1;
+              break;
+            }
+          }
+        }
+      }
+      __syncwarp();
+    }
+    __syncthreads();
+    FPROF(15);
+    if (s_xfail == 0) {
+      const float sc = step / static_cast<float>(W);
+      if (warp == 0 && elect_one()) {
+        for (int c = 0; c < nstage; ++c) issue_chunk(c);
+      }
+      FPROF(0);  // (slots 0/1 are re-used inside the step loop: first loads issued / layer-1 slice reduced)
+      // the layer-1 slice: 4 chunks through the receive stages
+      const int items = chunk_rows * H1 / 4;
+      for (int c = 0; c < nchunk; ++c) {
+        const int sidx = c % nstage;
+        mbar_wait(&bar_xr[sidx], (xr_phase >> sidx) & 1u);
+        xr_phase ^= 1u << sidx;
+        for (int i = threadIdx.x; i < items; i += kFThreads) {
+          float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
+          int b = 1;
+#pragma unroll
+          for (int r = 0; r < 8; ++r)
+            if (r < W) {
+              const float4 g = (r == p.rank) ? lds128(sb + kXsW1 + c * chunk_bytes + i * 16) : lds128(stage_buf(sidx, b++) + i * 16);
+              acc.x += g.x; acc.y += g.y; acc.z += g.z; acc.w += g.w;
+            }
+          float4 w = lds128(stage_buf(sidx, 0) + i * 16);
+          w.x -= sc * acc.x; w.y -= sc * acc.y; w.z -= sc * acc.z; w.w -= sc * acc.w;
+          sts128(stage_buf(sidx, 0) + i * 16, w.x, w.y, w.z, w.w);
+        }
+        fence_proxy_async_smem();
+        __syncthreads();
+        if (warp == 0 && elect_one()) {
+          bulk_s2g(p.wparams + w1_off + static_cast<size_t>(c) * chunk_rows * H1, stage_buf(sidx, 0), chunk_bytes);
+          bulk_commit();
+          if (c + nstage < nchunk) {
+            bulk_wait_read();  // the engine has read this stage's weights buffer: the stage may be refilled
+            issue_chunk(c + nstage);
+          }
+        }
+      }
+      FPROF(1);
+      // Small ranges (layer-2/3 slices, bias slices) through registers while the first chunks travel: one flat item
+      // list so that every thread issues all its loads at once (mine from the staging image, the peers' from my
+      // receive area with L1-bypassing loads: a peer wrote them).
+      {
+        constexpr int nW2 = kMid ? S1 * H2 / 4 : 0, nWL = SL * 16 / 4, nB1 = S1 / 4, nB2 = kMid ? S2 / 4 : 0;
+        const int n_items = nW2 + nWL + nB1 + nB2 + (j == 0 ? 4 : 0);
+        for (int it = threadIdx.x; it < n_items; it += kFThreads) {
+          size_t off;
+          uint32_t soff;
+          int k = it;
+          if (k < nW2) { off = p.w_off[1] + static_cast<size_t>(S1 * j) * H2; soff = kXsW2; }
+          else if ((k -= nW2) < nWL) { off = p.w_off[LAST] + static_cast<size_t>(SL * j) * 16; soff = kXsWL; }
+          else if ((k -= nWL) < nB1) { off = p.b_off[0] + S1 * j; soff = kXsB1; }
+          else if ((k -= nB1) < nB2) { off = p.b_off[1] + S2 * j; soff = kXsB2; }
+          else { k -= nB2; off = p.b_off[LAST]; soff = kXsBL; }
+          off += static_cast<size_t>(k) * 4;
+          float4 w = __ldcg(reinterpret_cast<const float4*>(p.wparams + off));
+          float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll
+          for (int r = 0; r < 8; ++r)
+            if (r < W) {
+              const float4 g = (r == p.rank) ? lds128(sb + soff + k * 16)
+                                             : __ldcg(reinterpret_cast<const float4*>(rbase + static_cast<size_t>(r) * p.total + off));
+              acc.x += g.x; acc.y += g.y; acc.z += g.z; acc.w += g.w;
+            }
+          w.x -= sc * acc.x; w.y -= sc * acc.y; w.z -= sc * acc.z; w.w -= sc * acc.w;
+          *reinterpret_cast<float4*>(p.wparams + off) = w;
+        }
+      }
+      if (warp == 0 && elect_one()) bulk_wait_all();  // updated weights are in memory before the step ends
+    }
+  }
   // ---- end of step: my weight updates are performed (fence), my reads of exchanged data are done, the
   // exchange barriers are re-armed BEFORE any peer can pass the barrier and start sending the next step's data.
   if (st + 1 < nsteps) {
@@ -760,6 +958,7 @@ mlp_fused_step_kernel(const __grid_constant__ CUtensorMap tmXA, const __grid_con
   tc_fence_after_sync();
   FPROF(14);
   }  // step loop
+  if (xmode && j == 0 && threadIdx.x == 0) p.xpad[p.rank][kPadFusedEpoch] = epoch0 + static_cast<uint32_t>(nsteps);
   if (warp == 0) {
     tc_fence_after_sync();
     tmem_dealloc(tm, 512);
@@ -829,6 +1028,21 @@ extern "C" int dmlp_mlp_fused_plan_create(const dmlp_mlp_fused_desc_t* d, dmlp_m
   p.prof = reinterpret_cast<unsigned long long*>(d->prof_dev);
   pl->layers = L;
   pl->slots = slots;
+  if (d->xchg_world > 1) {
+    DMLP_REQUIRE(d->xchg_world <= 8 && d->xchg_rank >= 0 && d->xchg_rank < d->xchg_world, "fused step: bad exchange rank/world");
+    DMLP_REQUIRE(d->sgd_params_dev != nullptr && d->lr_dev != nullptr && d->param_count > 0,
+                 "fused step: the in-kernel gradient exchange applies SGD itself (sgd_params_dev, lr_dev, param_count)");
+    p.world = d->xchg_world;
+    p.rank = d->xchg_rank;
+    for (int r = 0; r < d->xchg_world; ++r) {
+      DMLP_REQUIRE(d->xchg_recv_dev[r] && d->xchg_pad_dev[r], "fused step: rank %d's receive area / signal pad is not mapped", r);
+      p.xrecv[r] = d->xchg_recv_dev[r];
+      p.xpad[r] = d->xchg_pad_dev[r];
+    }
+    p.xstatus = d->xchg_status;
+    p.xtimeout_ns = d->xchg_timeout_ns ? d->xchg_timeout_ns : 10ull * 1000 * 1000 * 1000;
+    p.total = d->param_count;
+  }
   p.nsteps = 1;
   p.slot0 = 0;
   *out = reinterpret_cast<dmlp_mlp_fused_plan_t>(pl);

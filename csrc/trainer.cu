@@ -20,6 +20,11 @@
 #include <new>
 #include <vector>
 
+// Implemented in collectives.cu: hands out the communicator's pads / state / watchdog words.
+extern "C" int dmlp_comm_internal_view(dmlp_comm_t comm, int local_idx, uint32_t* pad[DMLP_MAX_RANKS], uint32_t** state,
+                                       uint32_t** host_flags, unsigned long long* timeout_ns, uint32_t* dead_mask,
+                                       int* rank, int* world, int* dev);
+
 namespace dmlp {
 
 constexpr int kMaxLayers = DMLP_MAX_LAYERS;
@@ -63,6 +68,9 @@ struct Trainer {
   float* peer_params[DMLP_MAX_RANKS];
   void* peer_shadow[DMLP_MAX_RANKS];
   float* peer_grads[2][DMLP_MAX_RANKS];
+  float* peer_recv[DMLP_MAX_RANKS];  // fused step with in-kernel gradient exchange: [2][world][total] receive areas
+  unsigned long long* fused_prof = nullptr;  // DMLP_FUSED_PROF=1: [8 CTAs][16] phase stamps of the ring plan's last step
+  bool xchg = false;                  // ... is in use (multi-GPU, fused step, fused != 2, no NVLS arena)
   bool owns_params = false;
   bool nvls = false;  // params/grads live in multicast-bound memory; all-reduce by multimem
   float* mc_params = nullptr;
@@ -222,7 +230,7 @@ static int build_plans(Trainer* t) {
       if (t->comm == nullptr && t->cfg.fused != 2) { f.sgd_params_dev = t->params; f.lr_dev = t->lr_dev; }
       TRY(dmlp_mlp_fused_plan_create(&f, &t->rplan[slot]));
     }
-    if (t->comm == nullptr && t->cfg.fused != 2) {
+    if ((t->comm == nullptr && t->cfg.fused != 2) || t->xchg) {
       dmlp_mlp_fused_desc_t f;
       memset(&f, 0, sizeof(f));
       f.num_layers = L.L;
@@ -237,6 +245,28 @@ static int build_plans(Trainer* t) {
       f.sgd_params_dev = t->params;
       f.lr_dev = t->lr_dev;
       f.x_slots = kRingSlots;
+      {
+        const char* e = getenv("DMLP_FUSED_PROF");
+        if (e && atoi(e) > 0) {
+          void* pp = nullptr;
+          TRY(dev_alloc(t, 8 * 16 * 8, &pp));
+          t->fused_prof = static_cast<unsigned long long*>(pp);
+          f.prof_dev = pp;
+        }
+      }
+      if (t->xchg) {
+        uint32_t* pads[DMLP_MAX_RANKS];
+        uint32_t *state = nullptr, *host_flags = nullptr, dead = 0;
+        unsigned long long timeout_ns = 0;
+        int crank = 0, cworld = 0, cdev = 0;
+        TRY(dmlp_comm_internal_view(t->comm, t->local_idx, pads, &state, &host_flags, &timeout_ns, &dead, &crank, &cworld, &cdev));
+        f.xchg_world = t->world;
+        f.xchg_rank = t->rank;
+        for (int r = 0; r < t->world; ++r) { f.xchg_recv_dev[r] = t->peer_recv[r]; f.xchg_pad_dev[r] = pads[r]; }
+        f.xchg_status = host_flags + 4;
+        f.xchg_timeout_ns = timeout_ns;
+        f.param_count = L.total;
+      }
       TRY(dmlp_mlp_fused_plan_create(&f, &t->ring_plan));
     }
   }
@@ -462,7 +492,7 @@ static int run_fused_ring(Trainer* t, const float* x_host, const int32_t* y_host
   DMLP_CUDA_CHECK(cudaStreamSynchronize(t->s_main));
   // drain in launch order
   if (last_c >= 0) { collect((last_c + 1) % kRingChunks); collect(last_c); }
-  t->kernels_per_step = (t->comm != nullptr || t->cfg.fused == 2) ? 2 : 1;
+  t->kernels_per_step = t->ring_plan != nullptr ? 1 : 2;
   t->launches_last_run = launches;
   t->steps_done += steps;
   if (t->comm) {
@@ -492,6 +522,9 @@ extern "C" int dmlp_trainer_arena_bytes(const dmlp_trainer_config_t* cfg, size_t
   TRY(dmlp_trainer_param_count(cfg, &n));
   size_t b = 3 * align_up(n * 4, 256);
   if (cfg->dtype == DMLP_BF16) b += align_up(n * 2, 256);
+  // fused step with in-kernel gradient exchange: receive slots [2 parities][up to 8 ranks][params]
+  if (cfg->dtype == DMLP_F32 && cfg->fused == 3 && dmlp_mlp_fused_supported(cfg->num_layers, cfg->dims, cfg->batch))
+    b += 2 * DMLP_MAX_RANKS * align_up(n * 4, 256);
   *bytes = b;
   return DMLP_OK;
 }
@@ -573,6 +606,7 @@ extern "C" int dmlp_trainer_create(const dmlp_trainer_config_t* cfg, int device,
   memset(t->peer_params, 0, sizeof(t->peer_params));
   memset(t->peer_shadow, 0, sizeof(t->peer_shadow));
   memset(t->peer_grads, 0, sizeof(t->peer_grads));
+  memset(t->peer_recv, 0, sizeof(t->peer_recv));
   t->cfg = *cfg;
   t->dev = device;
   t->comm = (world > 1) ? comm : nullptr;
@@ -585,7 +619,7 @@ extern "C" int dmlp_trainer_create(const dmlp_trainer_config_t* cfg, int device,
   const int B = cfg->batch;
   t->fused_ce = L.out_pad[L.L - 1] <= 32;
   t->fused_step = !t->bf16 && cfg->fused != 0 && dmlp_mlp_fused_supported(cfg->num_layers, cfg->dims, cfg->batch) != 0;
-  if (cfg->fused == 1 && !t->fused_step) {
+  if ((cfg->fused == 1 || cfg->fused == 3) && !t->fused_step) {
     set_error(DMLP_ERR_UNSUPPORTED, "fused step kernel does not support this shape / precision");
     delete t;
     return DMLP_ERR_UNSUPPORTED;
@@ -626,14 +660,18 @@ extern "C" int dmlp_trainer_create(const dmlp_trainer_config_t* cfg, int device,
       size_t cap = 0;
       int e = dmlp_comm_arena_ptr(t->comm, local_idx, r, &base, &cap);
       if (e != DMLP_OK) { if (r == rank) return fail(e); continue; }  // peers unmapped: ring still works
-      size_t need = arena_offset + 3 * pbytes + (t->bf16 ? sbytes : 0);
+      const bool want_x = t->fused_step && cfg->fused == 3;
+      size_t need = arena_offset + 3 * pbytes + (t->bf16 ? sbytes : 0) + (want_x ? 2 * static_cast<size_t>(world) * pbytes : 0);
       if (cap < need) { set_error(DMLP_ERR_INVALID, "communicator arena too small: %zu < %zu", cap, need); return fail(DMLP_ERR_INVALID); }
       uint8_t* b = static_cast<uint8_t*>(base) + arena_offset;
       t->peer_params[r] = reinterpret_cast<float*>(b);
       t->peer_grads[0][r] = reinterpret_cast<float*>(b + pbytes);
       t->peer_grads[1][r] = reinterpret_cast<float*>(b + 2 * pbytes);
       if (t->bf16) t->peer_shadow[r] = b + 3 * pbytes;
+      if (want_x) t->peer_recv[r] = reinterpret_cast<float*>(b + 3 * pbytes);
     }
+    t->xchg = t->fused_step && cfg->fused == 3;
+    for (int r = 0; r < world; ++r) t->xchg = t->xchg && t->peer_recv[r] != nullptr;
     t->params = t->peer_params[rank];
     t->grads[0] = t->peer_grads[0][rank];
     t->grads[1] = t->peer_grads[1][rank];
@@ -905,6 +943,7 @@ extern "C" int dmlp_trainer_buffer(dmlp_trainer_t h, int kind, int l, void** ptr
     case 1: *ptr = t->dz[l]; break;
     case 2: *ptr = t->grads[l & 1]; break;
     case 3: *ptr = t->act[t->lay.L - 1]; break;
+    case 9: *ptr = t->fused_prof; break;  // null unless DMLP_FUSED_PROF=1
     default: return set_error(DMLP_ERR_INVALID, "unknown buffer kind %d", kind);
   }
   return DMLP_OK;

@@ -43,7 +43,8 @@ class TrainerConfig:
     allreduce: str = "auto"                    # auto | oneshot | twoshot | ring | nvls (falls back to auto if unavailable)
     overlap: bool = False                      # per-layer buckets reduced during backward
     use_graph: bool = True
-    fused: int = -1                            # cluster-fused step kernel: -1 auto, 0 off, 1 require
+    fused: int = -1                            # cluster-fused step kernel: -1 auto, 0 off, 1 require, 2 require + separate
+                                               # update kernel, 3 require + gradient exchange inside the step kernel (world > 1)
     schedule: str = "constant"
     seed: int = 0
     watchdog_ms: int = 10000

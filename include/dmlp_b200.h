@@ -299,6 +299,16 @@ typedef struct {
   const float* lr_dev;       /* device scalar, with sgd_params_dev */
   int x_slots;               /* 0/1: x_dev is one batch. n > 1: x_dev / labels_dev / metrics_dev are rings of n slots
                               * ([n][batch][dims[0]], [n][batch], [n][2]) addressed by dmlp_mlp_fused_steps */
+  /* Data-parallel mode (xchg_world > 1, needs sgd_params_dev): the kernel itself exchanges the gradients. Every rank
+   * pushes its gradient slices over NVLink into slot [step parity][its rank] of every rank's receive area
+   * ([2][world][param_count] floats, peer-mapped), raises one flag per CTA in the peers' signal pads, waits for the
+   * peers' flags, sums the slots in rank order and applies w -= lr/world * sum. No separate all-reduce kernel. */
+  int xchg_world, xchg_rank;
+  float* xchg_recv_dev[DMLP_MAX_RANKS];     /* rank r's receive area as addressable from this device (own rank: local) */
+  uint32_t* xchg_pad_dev[DMLP_MAX_RANKS];   /* rank r's communicator signal pad */
+  uint32_t* xchg_status;                    /* host-mapped {code, rank, peer, phase} failure record (nullable) */
+  unsigned long long xchg_timeout_ns;       /* watchdog for the flag wait */
+  size_t param_count;                       /* floats in the flat parameter vector (slot size) */
 } dmlp_mlp_fused_desc_t;
 typedef struct dmlp_mlp_fused_opaque* dmlp_mlp_fused_plan_t;
 int dmlp_mlp_fused_supported(int num_layers, const int* dims, int batch);
@@ -333,7 +343,11 @@ typedef struct {
   void* nvls_mc;                 /* arena and its multicast address; params/grads/shadow are placed there */
   size_t nvls_bytes;
   int fused;                     /* cluster-fused step kernel: -1 auto (when the shape allows), 0 off, 1 on,
-                                    2 on but always write gradients + run the separate update kernel */
+                                    2 on but always write gradients + run the separate update kernel,
+                                    3 (world > 1) on with the gradient exchange INSIDE the step kernel: bulk-copy push into
+                                      the peers' receive slots, rank-ordered reduce + SGD; one kernel per step, several
+                                      steps per launch. Measured slower than 1 + all-reduce kernel at this model size (only
+                                      8 SMs drive NVLink, profiles/r1_fused_exchange.md): opt-in */
 } dmlp_trainer_config_t;
 typedef struct dmlp_trainer_opaque* dmlp_trainer_t;
 

@@ -97,13 +97,17 @@ def main():
             print("NVLS_OK")
 
     # ---- 2. data-parallel trainer vs oracle
-    for overlap, algo in ((False, "auto"), (True, "auto"), (False, "nvls" if nvls_ok else "twoshot")):
-        cfg = TrainerConfig(dims=(784, 128, 64, 10), batch=64, lr=0.1, overlap=overlap, seed=7, allreduce=algo)
+    # (fused=3: the step kernel exchanges the gradients itself - push over NVLink, rank-ordered reduce + SGD)
+    for overlap, algo, fused in ((False, "auto", -1), (True, "auto", -1), (False, "nvls" if nvls_ok else "twoshot", -1),
+                                 (False, "auto", 3)):
+        cfg = TrainerConfig(dims=(784, 128, 64, 10), batch=64, lr=0.1, overlap=overlap, seed=7, allreduce=algo, fused=fused)
         t = Trainer(cfg, device=local, process_group=True)
         x, y = synthetic_mnist(64 * world * 6, seed=3)
         params = [(w.astype(np.float64), b.astype(np.float64)) for w, b in t.weights()]
         steps = 6
         st = t.fit(x, y, steps)
+        if fused == 3:
+            assert t.kernels_per_step == 1 and t.launches_last_run == 1, (t.kernels_per_step, t.launches_last_run)
         for s in range(steps):
             shards = [(x[(s * world + r) * 64:(s * world + r + 1) * 64].astype(np.float64),
                        y[(s * world + r) * 64:(s * world + r + 1) * 64]) for r in range(world)]
