@@ -47,10 +47,22 @@ class ClockSampler:
               "clocks_event_reasons.sw_power_cap")
 
     def __init__(self, gpu_index: int):
-        self.gpu, self.rows, self.proc = gpu_index, [], None
+        self.gpu, self.rows, self.proc, self._nvml = gpu_index, [], None, None
         self._t = None
 
     def start(self):
+        # NVML in-process (10 ms period) when available: short runs still get samples under load
+        try:
+            import pynvml
+            pynvml.nvmlInit()
+            self._nvml = pynvml
+            self._h = pynvml.nvmlDeviceGetHandleByIndex(self.gpu)
+            self._stop = False
+            self._t = threading.Thread(target=self._pump_nvml, daemon=True)
+            self._t.start()
+            return
+        except Exception:
+            self._nvml = None
         try:
             self.proc = subprocess.Popen(["nvidia-smi", f"--query-gpu={self.FIELDS}", "--format=csv,noheader,nounits",
                                           "-lms", "100", "-i", str(self.gpu)], stdout=subprocess.PIPE,
@@ -61,16 +73,35 @@ class ClockSampler:
         self._t = threading.Thread(target=self._pump, daemon=True)
         self._t.start()
 
+    def _pump_nvml(self):
+        n = self._nvml
+        get_reasons = getattr(n, "nvmlDeviceGetCurrentClocksEventReasons", None) or n.nvmlDeviceGetCurrentClocksThrottleReasons
+        while not self._stop:
+            try:
+                sm = n.nvmlDeviceGetClockInfo(self._h, n.NVML_CLOCK_SM)
+                mx = n.nvmlDeviceGetMaxClockInfo(self._h, n.NVML_CLOCK_SM)
+                bits = get_reasons(self._h)
+                act = lambda b: "Active" if bits & b else "Not Active"  # noqa: E731
+                # same column layout as the nvidia-smi query
+                self.rows.append((time.time(), [str(self.gpu), str(sm), str(mx), "", act(0x8), act(0x40), act(0x20), act(0x4)]))
+            except Exception:
+                pass
+            time.sleep(0.01)
+
     def _pump(self):
         for line in self.proc.stdout:
             self.rows.append((time.time(), [c.strip() for c in line.split(",")]))
 
     def stop(self, t0: float, t1: float) -> dict:
-        if self.proc is None:
+        if getattr(self, "_nvml", None) is not None:
+            self._stop = True
+            self._t.join(timeout=1.0)
+        elif self.proc is None:
             return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
-        time.sleep(0.15)
-        self.proc.terminate()
-        rows = [r for ts, r in self.rows if t0 - 0.1 <= ts <= t1 + 0.1] or [r for _, r in self.rows]
+        else:
+            time.sleep(0.15)
+            self.proc.terminate()
+        rows = [r for ts, r in self.rows if t0 <= ts <= t1] or [r for ts, r in self.rows if t0 - 0.1 <= ts <= t1 + 0.1] or [r for _, r in self.rows]
         sm, mx, reasons = [], None, set()
         for r in rows:
             try:

@@ -45,6 +45,15 @@ def main():
     my_in = arena_tensor(ins[rank], maxb // 4, local)
     my_in.normal_()
     nccl_buf = torch.empty(maxb // 4, device="cuda")
+    nvls = None
+    if "nvls" in a.algos.split(","):
+        from dmlp_b200.runtime.nvls import NvlsArena, NvlsUnavailable
+        try:
+            nvls = NvlsArena.from_process_group(local, 2 * maxb + 4096)
+            nv_in, nv_out = nvls.alloc.alloc(maxb), nvls.alloc.alloc(maxb)
+        except NvlsUnavailable as e:
+            if rank == 0:
+                print(json.dumps({"nvls": "unavailable", "why": str(e)}), flush=True)
     stream = torch.cuda.Stream()
     torch.cuda.set_stream(stream)
     rows = []
@@ -59,10 +68,14 @@ def main():
         for algo in a.algos.split(","):
             if algo in ("oneshot",) and nbytes > (64 << 20):
                 continue  # (n-1) x bytes pulled per rank: pointless at these sizes
+            if algo == "nvls" and (nvls is None or count % 4):
+                continue
 
             def launch():
                 if algo == "nccl":
                     dist.all_reduce(nccl_buf[:count])
+                elif algo == "nvls":  # multimem.ld_reduce -> multimem.st through the NVSwitch
+                    nvls.allreduce(comm, 0, nv_in, nv_out, count, local, stream=stream.cuda_stream)
                 else:
                     comm.allreduce(ins, outs, count, algo=native.ALGO_BY_NAME[algo], local_idx=0,
                                    stream=stream.cuda_stream)
@@ -97,7 +110,7 @@ def main():
                 comm.check()
             us = t.item() * 1e3
             algbw = nbytes / (us * 1e-6) / 1e9
-            picked = native.ALGO_NAMES[comm.pick_algo(nbytes)] if algo == "auto" else algo
+            picked = native.ALGO_NAMES.get(comm.pick_algo(nbytes), "?") if algo == "auto" else algo
             row = {"bytes": nbytes, "impl": algo, "picked": picked, "n_gpus": world, "latency_us": round(us, 2),
                    "algbw_GBs": round(algbw, 2), "busbw_GBs": round(algbw * 2 * (world - 1) / world, 2), "iters": iters,
                    "timing": "cuda-graph replay" if a.graph else "eager launches"}
