@@ -36,7 +36,9 @@ __device__ unsigned long long g_gemm_prof[kProfTiles * 16];
       g_gemm_prof[(tile_i) * 16 + (slot)] = globaltimer_ns();                                         \
   } while (0)
 
-template <int EB, bool A_MN, bool B_MN>
+// TWO: CTA pairs (cluster of 2) run tcgen05.mma.cta_group::2 on 256 x block_n tiles: each CTA stages its 128 rows of A
+// and HALF of the B tile, which halves the shared-memory fill + read traffic per SM that bounds the 1-CTA mainloop.
+template <int EB, bool A_MN, bool B_MN, bool TWO>
 __global__ void __launch_bounds__(kGemmThreads, 1)
 gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA,
                     const __grid_constant__ CUtensorMap tmB, const GemmParams p) {
@@ -75,8 +77,13 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA,
   // Persistent CTA: tiles blockIdx.x, blockIdx.x + gridDim.x, ... (M fastest, so CTAs that run together share
   // the same B tile through L2). Two TMEM accumulator buffers let the epilogue of one tile overlap the
   // mainloop of the next.
-  const int tiles_m = (p.M + BM - 1) / BM;
+  constexpr int TM = TWO ? 2 * BM : BM;  // rows of a (pair's) tile
+  const int tiles_m = (p.M + TM - 1) / TM;
   const int total_tiles = tiles_m * ((p.N + p.block_n - 1) / p.block_n);
+  const int crank = TWO ? static_cast<int>(cl_rank()) : 0;  // 0: leader (issues the MMAs)
+  const int tile_first = TWO ? static_cast<int>(blockIdx.x >> 1) : static_cast<int>(blockIdx.x);
+  const int tile_step = TWO ? static_cast<int>(gridDim.x >> 1) : static_cast<int>(gridDim.x);
+  const int b_cols = TWO ? p.block_n / 2 : p.block_n;       // N columns of the B tile this CTA stages
 
   if (warp == 0 && lane == 0) {
     tma_prefetch_desc(&tmA);
@@ -87,16 +94,22 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA,
     }
     for (int b = 0; b < 2; ++b) {
       mbar_init(&tmem_full_bar[b], 1);
-      mbar_init(&tmem_empty_bar[b], 128);
+      mbar_init(&tmem_empty_bar[b], TWO ? 256 : 128);  // pair: the leader's barrier collects both CTAs' epilogues
     }
     fence_mbar_init();
   }
   if (warp == 1) {
-    tmem_alloc(&tmem_base_slot, p.tmem_cols);
-    tmem_relinquish();
+    if constexpr (TWO) {
+      tmem_alloc_2sm(&tmem_base_slot, p.tmem_cols);
+      tmem_relinquish_2sm();
+    } else {
+      tmem_alloc(&tmem_base_slot, p.tmem_cols);
+      tmem_relinquish();
+    }
   }
   tc_fence_before_sync();
   __syncthreads();
+  if constexpr (TWO) cl_sync();  // the peer's barriers are initialised before anything signals them
   tc_fence_after_sync();
   const uint32_t tmem_base = __shfl_sync(0xffffffffu, tmem_base_slot, 0);
   if (p.pdl) {
@@ -112,34 +125,40 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA,
     // ------------------------------------------------------------ TMA producer (whole warp loops, one lane issues)
     {
       const uint32_t stage_bytes = p.a_tx_bytes + p.b_stage_bytes;  // bytes TMA will deliver per stage
-      const int n_atoms = (p.block_n + ATOM_MN - 1) / ATOM_MN;
+      const int n_atoms = (b_cols + ATOM_MN - 1) / ATOM_MN;
       // k-block counter across all tiles of this CTA: the smem ring never drains between tiles
       int s = 0;
       uint32_t ph = 0;
       int ti = 0;
-      for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x, ++ti) {
-        const int m0 = (tile % tiles_m) * BM;
-        const int n0 = (tile / tiles_m) * p.block_n;
+      for (int tile = tile_first; tile < total_tiles; tile += tile_step, ++ti) {
+        const int m0 = (tile % tiles_m) * TM + crank * BM;                 // my 128 rows of the (pair's) tile
+        const int n0 = (tile / tiles_m) * p.block_n + crank * b_cols;      // my share of the tile's B columns
         for (int kb = 0; kb < p.num_k_blocks; ++kb) {
           mbar_wait(&empty_bar[s], ph ^ 1);
           if (kb == 0) GPROF(0, ti);
           if (elect_one()) {
-            mbar_arrive_expect_tx(&full_bar[s], stage_bytes);
+            // pair: both CTAs' loads complete bytes on the LEADER's barrier, which only the leader arms
+            if (crank == 0) mbar_arrive_expect_tx(&full_bar[s], TWO ? 2 * stage_bytes : stage_bytes);
+            const uint32_t fb = TWO ? cl_mapa(smem_u32(&full_bar[s]), 0) : 0u;
+            auto load = [&](void* dst, const CUtensorMap* tm, int c0, int c1) {
+              if constexpr (TWO) tma_load_2d_2sm(dst, tm, fb, c0, c1);
+              else tma_load_2d(dst, tm, &full_bar[s], c0, c1);
+            };
             uint8_t* a_dst = smem_a + static_cast<size_t>(s) * p.a_stage_bytes;
             uint8_t* b_dst = smem_b + static_cast<size_t>(s) * p.b_stage_bytes;
             const int k0 = kb * KS;
             if constexpr (!A_MN) {
-              tma_load_2d(a_dst, &tmA, &full_bar[s], k0, m0);
+              load(a_dst, &tmA, k0, m0);
             } else {
 #pragma unroll
               for (int j = 0; j < BM / ATOM_MN; ++j)
-                tma_load_2d(a_dst + j * MN_ATOM_COL_BYTES, &tmA, &full_bar[s], m0 + j * ATOM_MN, k0);
+                load(a_dst + j * MN_ATOM_COL_BYTES, &tmA, m0 + j * ATOM_MN, k0);
             }
             if constexpr (!B_MN) {
-              tma_load_2d(b_dst, &tmB, &full_bar[s], k0, n0);
+              load(b_dst, &tmB, k0, n0);
             } else {
               for (int j = 0; j < n_atoms; ++j)
-                tma_load_2d(b_dst + j * MN_ATOM_COL_BYTES, &tmB, &full_bar[s], n0 + j * ATOM_MN, k0);
+                load(b_dst + j * MN_ATOM_COL_BYTES, &tmB, n0 + j * ATOM_MN, k0);
             }
           }
           __syncwarp();
@@ -150,7 +169,7 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA,
     }
   } else if (warp == 1) {
     // ------------------------------------------------------------ MMA issuer (whole warp loops, one lane issues)
-    {
+    if (crank == 0) {  // pair: the leader issues for both CTAs
       const uint32_t a_base = smem_u32(smem_a), b_base = smem_u32(smem_b);
       // descriptor bits that never change; the 14-bit start address (>> 4) is added per stage / k step
       const uint64_t adesc0 = A_MN ? make_smem_desc(0, MN_ATOM_COL_BYTES, MN_SBO, MN_LAYOUT) : make_smem_desc(0, 16, 1024);
@@ -158,7 +177,7 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA,
       constexpr uint32_t A_KSTEP = (A_MN ? UK * 128 : 32) >> 4, B_KSTEP = (B_MN ? UK * 128 : 32) >> 4;
       int s = 0;
       uint32_t ph = 0, tcount = 0;
-      for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x, ++tcount) {
+      for (int tile = tile_first; tile < total_tiles; tile += tile_step, ++tcount) {
         const uint32_t buf = tcount & 1;
         mbar_wait(&tmem_empty_bar[buf], ((tcount >> 1) & 1) ^ 1);  // epilogue drained this buffer (free at first use)
         tc_fence_after_sync();
@@ -173,10 +192,15 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA,
           const uint64_t bdesc = bdesc0 + ((b_base + s * p.b_stage_bytes) >> 4);
           if (elect_one()) {
 #pragma unroll
-            for (int k = 0; k < KS / UK; ++k)
-              tc_mma<EB>(tmem_acc, adesc + k * A_KSTEP, bdesc + k * B_KSTEP, p.idesc, (kb | k) != 0 ? 1u : 0u);
-            tc_commit(&empty_bar[s]);  // frees the smem slot once these MMAs have read it
-            if (kb == p.num_k_blocks - 1) tc_commit(&tmem_full_bar[buf]);
+            for (int k = 0; k < KS / UK; ++k) {
+              if constexpr (TWO) tc_mma_2sm<EB>(tmem_acc, adesc + k * A_KSTEP, bdesc + k * B_KSTEP, p.idesc, (kb | k) != 0 ? 1u : 0u);
+              else tc_mma<EB>(tmem_acc, adesc + k * A_KSTEP, bdesc + k * B_KSTEP, p.idesc, (kb | k) != 0 ? 1u : 0u);
+            }
+            // frees the smem slot (in both CTAs of a pair) once these MMAs have read it
+            if constexpr (TWO) tc_commit_2sm(&empty_bar[s], 3); else tc_commit(&empty_bar[s]);
+            if (kb == p.num_k_blocks - 1) {
+              if constexpr (TWO) tc_commit_2sm(&tmem_full_bar[buf], 3); else tc_commit(&tmem_full_bar[buf]);
+            }
           }
           __syncwarp();
           if (kb == p.num_k_blocks - 1) GPROF(4, tcount);
@@ -191,10 +215,10 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA,
     const int etid = (warp - 2) * 32 + lane;   // 0..127 among the epilogue threads
     // A single M tile sees every row of the problem: its reductions (bias gradient, loss, hits) are
     // final and can be stored; otherwise they are accumulated atomically into zeroed buffers.
-    const bool direct = tiles_m == 1;
+    const bool direct = tiles_m == 1 && !TWO;  // (a pair's two CTAs each hold half the rows of the tile)
     uint32_t tcount = 0;
-    for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x, ++tcount) {
-    const int m0 = (tile % tiles_m) * BM;
+    for (int tile = tile_first; tile < total_tiles; tile += tile_step, ++tcount) {
+    const int m0 = (tile % tiles_m) * TM + crank * BM;
     const int n0 = (tile / tiles_m) * p.block_n;
     const int m = m0 + row;
     const bool m_ok = m < p.M;
@@ -594,16 +618,19 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA,
     // this tile's accumulator has been read out: hand the TMEM buffer back to the MMA warp
     if (p.colsum != nullptr || p.ce_labels != nullptr) asm volatile("bar.sync 1, 128;" ::: "memory");  // s_part reuse
     tc_fence_before_sync();
-    mbar_arrive(&tmem_empty_bar[buf]);
+    if (TWO && crank != 0) mbar_arrive_cluster(cl_mapa(smem_u32(&tmem_empty_bar[buf]), 0));  // the leader's barrier
+    else mbar_arrive(&tmem_empty_bar[buf]);
     if (warp == 2) GPROF(7, tcount);
     }
   }
 
   tc_fence_before_sync();
   __syncthreads();
+  if constexpr (TWO) cl_sync();  // the peer may still be signalling my barriers / the pair's MMAs use both TMEMs
   if (warp == 1) {
     tc_fence_after_sync();
-    tmem_dealloc(tmem_base, p.tmem_cols);
+    if constexpr (TWO) tmem_dealloc_2sm(tmem_base, p.tmem_cols);
+    else tmem_dealloc(tmem_base, p.tmem_cols);
   }
 }
 
@@ -654,10 +681,10 @@ int make_tensor_map_2d(CUtensorMap* out, const void* base, int elem_bytes, bool 
   return DMLP_OK;
 }
 
-template <int EB, bool A_MN, bool B_MN>
+template <int EB, bool A_MN, bool B_MN, bool TWO = false>
 static int launch_gemm(const CUtensorMap& tmA, const CUtensorMap& tmB, const GemmParams& p,
                        dim3 grid, size_t smem_bytes, cudaStream_t stream) {
-  auto kern = gemm_tcgen05_kernel<EB, A_MN, B_MN>;
+  auto kern = gemm_tcgen05_kernel<EB, A_MN, B_MN, TWO>;
   static unsigned long long attr_mask = 0;  // devices on which the smem opt-in has been applied
   int dev = 0;
   DMLP_CUDA_CHECK(cudaGetDevice(&dev));
@@ -666,18 +693,29 @@ static int launch_gemm(const CUtensorMap& tmA, const CUtensorMap& tmB, const Gem
                                          216 * 1024));
     attr_mask |= 1ull << dev;
   }
-  if (p.pdl) {
+  if (p.pdl || TWO) {
     cudaLaunchConfig_t cfg;
     memset(&cfg, 0, sizeof(cfg));
     cfg.gridDim = grid;
     cfg.blockDim = dim3(kGemmThreads);
     cfg.dynamicSmemBytes = smem_bytes;
     cfg.stream = stream;
-    cudaLaunchAttribute attr[1];
-    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
-    attr[0].val.programmaticStreamSerializationAllowed = 1;
+    cudaLaunchAttribute attr[2];
+    int na = 0;
+    if (p.pdl) {
+      attr[na].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+      attr[na].val.programmaticStreamSerializationAllowed = 1;
+      ++na;
+    }
+    if (TWO) {  // CTA pairs: clusters of 2 (ranks 2i, 2i+1 share a TPC)
+      attr[na].id = cudaLaunchAttributeClusterDimension;
+      attr[na].val.clusterDim.x = 2;
+      attr[na].val.clusterDim.y = 1;
+      attr[na].val.clusterDim.z = 1;
+      ++na;
+    }
     cfg.attrs = attr;
-    cfg.numAttrs = 1;
+    cfg.numAttrs = na;
     DMLP_CUDA_CHECK(cudaLaunchKernelEx(&cfg, kern, tmA, tmB, p));
   } else {
     kern<<<grid, kGemmThreads, smem_bytes, stream>>>(tmA, tmB, p);
@@ -715,6 +753,15 @@ int dmlp::gemm_plan_create(const dmlp_gemm_desc_t* d, GemmPlan* plan) {
   if (d->ce_labels_dev != nullptr) bn = ((d->N + 15) / 16) * 16;  // fused softmax-CE: one N tile holds the whole row
   DMLP_REQUIRE(bn % 16 == 0 && bn >= 16 && bn <= 256, "dmlp_gemm: block_n %d must be a multiple of 16 in [16,256]", bn);
 
+  // CTA pairs (tcgen05.mma.cta_group::2, 256 x 256 tiles) for problems with at least one full wave of pair tiles
+  bool two = false;
+  {
+    static int pair_env = -1;
+    if (pair_env < 0) { const char* e = getenv("DMLP_GEMM_PAIR"); pair_env = e ? atoi(e) : 1; }
+    two = pair_env != 0 && bn == 256 && d->ce_labels_dev == nullptr && d->M >= 256 &&
+          ceil_div(d->M, 256) * ceil_div(d->N, 256) >= 74;
+  }
+  const int b_cols = two ? bn / 2 : bn;  // B columns one CTA stages
   int rc;
   const int mn_swz = bf16 ? 1 : 2;  // fp32 MN-major operands need the 32B-atom swizzle
   // A problem with M <= 64 (the reference's batch) only fills half of the 128-row MMA tile. Loading
@@ -727,7 +774,7 @@ int dmlp::gemm_plan_create(const dmlp_gemm_desc_t* d, GemmPlan* plan) {
     rc = make_tensor_map_2d(&plan->tmA, d->A_dev, EB, bf16, d->M, d->K, d->lda, ATOM, KS, mn_swz);
   if (rc) return rc;
   if (d->b_major == 0)
-    rc = make_tensor_map_2d(&plan->tmB, d->B_dev, EB, bf16, d->K, d->N, d->ldb, KS, bn, 1);
+    rc = make_tensor_map_2d(&plan->tmB, d->B_dev, EB, bf16, d->K, d->N, d->ldb, KS, b_cols, 1);
   else
     rc = make_tensor_map_2d(&plan->tmB, d->B_dev, EB, bf16, d->N, d->K, d->ldb, ATOM, KS, mn_swz);
   if (rc) return rc;
@@ -739,7 +786,7 @@ int dmlp::gemm_plan_create(const dmlp_gemm_desc_t* d, GemmPlan* plan) {
   p.num_k_blocks = ceil_div(d->K, KS);
   p.a_stage_bytes = 128 * 128;
   p.a_tx_bytes = (d->a_major == 0) ? a_box_rows * 128 : 128 * 128;
-  p.b_stage_bytes = d->b_major == 0 ? bn * 128 : ceil_div(bn, ATOM) * KS * 128;
+  p.b_stage_bytes = d->b_major == 0 ? b_cols * 128 : ceil_div(b_cols, ATOM) * KS * 128;  // per CTA
   const size_t stage_bytes = p.a_stage_bytes + p.b_stage_bytes;
   const size_t budget = 196 * 1024;  // + 18 KiB of epilogue patches + 1 KiB alignment slack <= the 216 KiB opt-in
   int stages = static_cast<int>(budget / stage_bytes);
@@ -760,6 +807,7 @@ int dmlp::gemm_plan_create(const dmlp_gemm_desc_t* d, GemmPlan* plan) {
   p.tmem_buf_cols = cols;   // one accumulator buffer
   p.tmem_cols = 2 * cols;   // two of them (<= 512 columns)
   p.idesc = make_instr_desc(EB, d->a_major != 0, d->b_major != 0, bn);
+  if (two) p.idesc = (p.idesc & ~(0x1Fu << 24)) | (static_cast<uint32_t>(256 >> 4) << 24);  // M = 256 across the pair
   p.out_f32 = d->out_f32_dev; p.ld_out = d->ld_out;
   p.out_bf16 = reinterpret_cast<__nv_bfloat16*>(d->out_bf16_dev); p.ld_out_bf16 = d->ld_out_bf16;
   p.bias = d->bias_dev;
@@ -774,20 +822,21 @@ int dmlp::gemm_plan_create(const dmlp_gemm_desc_t* d, GemmPlan* plan) {
   }
 
   {
-    const int total = ceil_div(d->N, bn) * ceil_div(d->M, 128);
+    const int total = ceil_div(d->N, bn) * ceil_div(d->M, two ? 256 : 128);
     plan->total_tiles = total;
     plan->grid_x = total < 148 ? total : 148;  // persistent: at most one CTA per SM
+    if (two) plan->grid_x = 2 * (total < 74 ? total : 74);  // one CTA pair (cluster of 2) per TPC
     plan->grid_y = 1;
   }
   p.epi_stage_off = static_cast<uint32_t>(stages * stage_bytes);
   plan->smem = stages * stage_bytes + kEpiStageBytes + 1024;
-  plan->key = (bf16 ? 4 : 0) | (d->a_major ? 2 : 0) | (d->b_major ? 1 : 0);
+  plan->key = (two ? 8 : 0) | (bf16 ? 4 : 0) | (d->a_major ? 2 : 0) | (d->b_major ? 1 : 0);
   // PDL only for single-wave grids: an early-launched dependent must never compete with CTAs of
   // this grid that are still waiting for an SM.
   {
     static int pdl_env = -1;
     if (pdl_env < 0) { const char* e = getenv("DMLP_PDL"); pdl_env = e ? atoi(e) : 1; }
-    p.pdl = (pdl_env && plan->total_tiles <= 148) ? 1 : 0;
+    p.pdl = (pdl_env && !two && plan->total_tiles <= 148) ? 1 : 0;
   }
   return DMLP_OK;
 }
@@ -802,7 +851,15 @@ int dmlp::gemm_plan_run(const GemmPlan* plan, cudaStream_t st) {
     case 4: return launch_gemm<2, false, false>(plan->tmA, plan->tmB, plan->p, grid, plan->smem, st);
     case 5: return launch_gemm<2, false, true>(plan->tmA, plan->tmB, plan->p, grid, plan->smem, st);
     case 6: return launch_gemm<2, true, false>(plan->tmA, plan->tmB, plan->p, grid, plan->smem, st);
-    default: return launch_gemm<2, true, true>(plan->tmA, plan->tmB, plan->p, grid, plan->smem, st);
+    case 7: return launch_gemm<2, true, true>(plan->tmA, plan->tmB, plan->p, grid, plan->smem, st);
+    case 8: return launch_gemm<4, false, false, true>(plan->tmA, plan->tmB, plan->p, grid, plan->smem, st);
+    case 9: return launch_gemm<4, false, true, true>(plan->tmA, plan->tmB, plan->p, grid, plan->smem, st);
+    case 10: return launch_gemm<4, true, false, true>(plan->tmA, plan->tmB, plan->p, grid, plan->smem, st);
+    case 11: return launch_gemm<4, true, true, true>(plan->tmA, plan->tmB, plan->p, grid, plan->smem, st);
+    case 12: return launch_gemm<2, false, false, true>(plan->tmA, plan->tmB, plan->p, grid, plan->smem, st);
+    case 13: return launch_gemm<2, false, true, true>(plan->tmA, plan->tmB, plan->p, grid, plan->smem, st);
+    case 14: return launch_gemm<2, true, false, true>(plan->tmA, plan->tmB, plan->p, grid, plan->smem, st);
+    default: return launch_gemm<2, true, true, true>(plan->tmA, plan->tmB, plan->p, grid, plan->smem, st);
   }
 }
 

@@ -29,6 +29,8 @@ CASES = [
     # (M(batch), K(in), N(out)) — reference shapes, north-star small, ragged, multi-tile
     (64, 784, 128), (64, 128, 64), (64, 64, 16), (64, 128, 16),
     (128, 256, 256), (200, 104, 72), (512, 1024, 384), (1024, 512, 1024),
+    # >= 74 tiles of 256 x 256: the CTA-pair (tcgen05.mma.cta_group::2) path, ragged in M, N and K
+    (2304, 200, 2320), (2200, 328, 2560), (2304, 2320, 200), (200, 2304, 2320),
 ]
 
 
