@@ -26,6 +26,7 @@ struct GemmParams {
   uint32_t a_stage_bytes, b_stage_bytes;
   uint32_t a_tx_bytes;  // bytes TMA actually delivers for A per stage (half a tile when M <= 64)
   uint32_t idesc;
+  int raster_g;            // tile order: height (in tiles) of the M bands, see the kernel
   uint32_t epi_stage_off;  // byte offset (from the aligned smem base) of the epilogue's transpose patches
   float* out_f32;
   long long ld_out;
