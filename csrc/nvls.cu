@@ -169,6 +169,7 @@ struct NvlsArgs {
   uint32_t* status;
   unsigned long long timeout_ns;
   uint32_t dead_mask;
+  int oneshot;  // every rank reduces EVERYTHING through the switch and updates only its own replica (no broadcast)
 };
 
 constexpr int kNvlsThreads = 512;
@@ -211,6 +212,8 @@ __device__ __forceinline__ bool nvls_barrier(const NvlsArgs& a, uint32_t epoch, 
 }
 
 __global__ void __launch_bounds__(kNvlsThreads) allreduce_nvls_kernel(const __grid_constant__ NvlsArgs a) {
+  asm volatile("griddepcontrol.launch_dependents;" ::: "memory");  // a PDL successor may begin its prologue now
+  asm volatile("griddepcontrol.wait;" ::: "memory");               // predecessors' gradients are complete and visible
   if ((a.dead_mask >> a.rank) & 1u) return;
   __shared__ int s_fail;
   __shared__ uint32_t s_epoch;
@@ -222,6 +225,32 @@ __global__ void __launch_bounds__(kNvlsThreads) allreduce_nvls_kernel(const __gr
 
   const size_t nfull = a.count / 4;
   const int tail = static_cast<int>(a.count % 4);
+  if (a.oneshot) {
+    // Latency-bound sizes: one rendezvous, then every rank pulls the switch-reduced sum of ALL elements
+    // (inbound traffic = 1 x bytes instead of the (n-1) x bytes of a peer-memory one-shot) and updates its own
+    // replica. No broadcast, no trailing rendezvous: the caller double-buffers the inputs by step parity, and a
+    // peer cannot reach the next-but-one step before this rank has passed the next rendezvous.
+    const float step1 = a.fuse_sgd ? a.lr[0] * a.scale : 0.f;
+    float* out = const_cast<float*>(a.uc_out);
+    const size_t stride1 = static_cast<size_t>(gridDim.x) * blockDim.x;
+    for (size_t i = blockIdx.x * static_cast<size_t>(blockDim.x) + threadIdx.x; i < nfull; i += stride1) {
+      float4 v = multimem_ld_reduce_add_f32x4(a.mc_in + 4 * i);
+      if (a.fuse_sgd) {
+        const float4 w = *reinterpret_cast<const float4*>(out + 4 * i);
+        v = make_float4(w.x - step1 * v.x, w.y - step1 * v.y, w.z - step1 * v.z, w.w - step1 * v.w);
+      } else if (a.scale != 1.f) {
+        v = make_float4(v.x * a.scale, v.y * a.scale, v.z * a.scale, v.w * a.scale);
+      }
+      *reinterpret_cast<float4*>(out + 4 * i) = v;
+    }
+    if (tail && blockIdx.x == 0 && threadIdx.x < tail) {
+      const size_t e = nfull * 4 + threadIdx.x;
+      const float v = multimem_ld_reduce_add_f32(a.mc_in + e);
+      out[e] = a.fuse_sgd ? out[e] - step1 * v : v * a.scale;
+    }
+    if (threadIdx.x == 0) a.state[blockIdx.x] = epoch;
+    return;
+  }
   const size_t per = (nfull + a.world - 1) / a.world;
   const size_t lo = static_cast<size_t>(a.rank) * per;
   const size_t hi = (lo + per < nfull) ? lo + per : nfull;
@@ -455,12 +484,29 @@ extern "C" int dmlp_allreduce_nvls(dmlp_comm_t comm, int local_idx, const dmlp_n
   a.lr = d->lr;
   a.scale = d->scale != 0.f ? d->scale : 1.f;
   a.fuse_sgd = d->fuse_sgd;
-  const size_t work = (d->count / 4 + a.world - 1) / a.world;
-  int blocks = static_cast<int>((work + kNvlsThreads * 2 - 1) / (kNvlsThreads * 2));
+  // one-shot flavour: outputs land in the caller's own replica only (uc_out), so it needs one and cannot feed a shadow
+  a.oneshot = (d->oneshot && d->uc_out != nullptr && d->mc_out_bf16 == nullptr) ? 1 : 0;
+  const size_t work = a.oneshot ? d->count / 4 : (d->count / 4 + a.world - 1) / a.world;
+  // one-shot: one 16-byte pack per thread (a switch-reduced load is a ~3 us round trip: no serial loop over packs)
+  int blocks = a.oneshot ? static_cast<int>((work + kNvlsThreads - 1) / kNvlsThreads)
+                         : static_cast<int>((work + kNvlsThreads * 2 - 1) / (kNvlsThreads * 2));
   if (blocks < 1) blocks = 1;
   if (blocks > kNvlsMaxBlocks) blocks = kNvlsMaxBlocks;
   DeviceGuard guard(dev);
-  allreduce_nvls_kernel<<<blocks, kNvlsThreads, 0, as_stream(stream)>>>(a);
+  {
+    // Programmatic stream serialization: may be scheduled while its predecessor drains (griddepcontrol.wait inside)
+    cudaLaunchConfig_t cfg;
+    memset(&cfg, 0, sizeof(cfg));
+    cfg.gridDim = dim3(blocks);
+    cfg.blockDim = dim3(kNvlsThreads);
+    cfg.stream = as_stream(stream);
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = 1;
+    DMLP_CUDA_CHECK(cudaLaunchKernelEx(&cfg, allreduce_nvls_kernel, a));
+  }
   DMLP_CUDA_CHECK(cudaGetLastError());
   return DMLP_OK;
 }

@@ -289,6 +289,8 @@ static int enqueue_allreduce(Trainer* t, int par, size_t off, size_t count, cuda
     n.lr = t->lr_dev;
     n.scale = 1.f / static_cast<float>(t->world);
     n.fuse_sgd = 1;
+    // small (latency-bound) gradients: one-shot pull through the switch; gradients are double-buffered by parity
+    n.oneshot = (!t->bf16 && count * 4 <= (1u << 20)) ? 1 : 0;
     return dmlp_allreduce_nvls(t->comm, t->local_idx, &n, st);
   }
   dmlp_allreduce_desc_t d;

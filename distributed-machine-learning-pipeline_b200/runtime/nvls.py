@@ -53,7 +53,7 @@ def _lib():
 
 class NvlsAllReduceDesc(C.Structure):
     _fields_ = [("count", C.c_size_t), ("mc_in", C.c_void_p), ("mc_out", C.c_void_p), ("mc_out_bf16", C.c_void_p),
-                ("uc_out", C.c_void_p), ("lr", C.c_void_p), ("scale", C.c_float), ("fuse_sgd", C.c_int)]
+                ("uc_out", C.c_void_p), ("lr", C.c_void_p), ("scale", C.c_float), ("fuse_sgd", C.c_int), ("oneshot", C.c_int)]
 
 
 def supported(dev: int) -> bool:
@@ -158,13 +158,14 @@ class NvlsArena:
     # ------------------------------------------------------------------ use
     def allreduce(self, comm, local_idx: int, off_in: int, off_out: int, count: int, device: int, stream: int = 0,
                   fuse_sgd: bool = False, lr: Optional[int] = None, scale: float = 1.0,
-                  off_out_bf16: Optional[int] = None) -> None:
+                  off_out_bf16: Optional[int] = None, oneshot: bool = False) -> None:
         d = NvlsAllReduceDesc()
         d.count = count
         d.mc_in, d.mc_out = self.mc + off_in, self.mc + off_out
         d.mc_out_bf16 = (self.mc + off_out_bf16) if off_out_bf16 is not None else None
         d.uc_out = self.uc[device] + off_out
         d.lr, d.scale, d.fuse_sgd = lr, scale, int(fuse_sgd)
+        d.oneshot = int(oneshot)
         native.check(_lib().dmlp_allreduce_nvls(comm._h, local_idx, C.byref(d), stream or None))
 
     def destroy(self) -> None:

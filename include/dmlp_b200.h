@@ -250,6 +250,9 @@ typedef struct {
   const float* lr;       /* device scalar (fuse_sgd) */
   float scale;
   int fuse_sgd;
+  int oneshot;           /* 1: latency-bound flavour - every rank pulls the switch-reduced sum of all elements into
+                          * its own replica (uc_out required, no bf16 shadow); no broadcast, one rendezvous; the
+                          * caller must double-buffer the inputs across consecutive calls */
 } dmlp_nvls_allreduce_desc_t;
 int dmlp_allreduce_nvls(dmlp_comm_t comm, int local_idx, const dmlp_nvls_allreduce_desc_t* desc, void* stream);
 

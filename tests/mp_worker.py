@@ -68,13 +68,14 @@ def main():
     from dmlp_b200.runtime.nvls import NvlsArena, NvlsUnavailable
     nvls_ok = True
     try:
-        arena = NvlsArena.from_process_group(local, 4 * nbytes)
+        arena = NvlsArena.from_process_group(local, 6 * nbytes)
     except NvlsUnavailable as e:
         nvls_ok = False
         if rank == 0:
             print("NVLS unavailable:", e)
     if nvls_ok:
         comm2 = Communicator.from_process_group(local, staging_bytes=1 << 20)
+        count4 = count // 4 * 4
         o_in, o_out, o_w = arena.alloc.alloc(nbytes), arena.alloc.alloc(nbytes), arena.alloc.alloc(nbytes)
         uc = arena.uc[local]
         native.check(lib.dmlp_memcpy_h2d(local, uc + o_in, all_in[rank].ctypes.data, count * 4, None))
@@ -90,6 +91,22 @@ def main():
         assert np.abs(got - ref).max() < 1e-4, ("nvls", np.abs(got - ref).max())
         native.check(lib.dmlp_memcpy_d2h(local, got.ctypes.data, uc + o_w, count * 4, None))
         assert np.abs(got - (1.0 - 0.1 * ref / world)).max() < 1e-4, "nvls sgd"
+        # one-shot flavour: every rank pulls the switch-reduced sum of everything into its own replica
+        o_in2, o_w2 = arena.alloc.alloc(nbytes), arena.alloc.alloc(nbytes)
+        native.check(lib.dmlp_memcpy_h2d(local, uc + o_in2, all_in[rank].ctypes.data, count4 * 4, None))
+        native.check(lib.dmlp_memcpy_h2d(local, uc + o_w2, w0.ctypes.data, count4 * 4, None))
+        torch.cuda.synchronize()
+        dist.barrier()
+        arena.allreduce(comm2, 0, o_in2, o_w2, count4, local, fuse_sgd=True, lr=lr.data_ptr(), scale=1.0 / world, oneshot=True)
+        torch.cuda.synchronize()
+        comm2.check()
+        got4 = np.empty(count4, np.float32)
+        native.check(lib.dmlp_memcpy_d2h(local, got4.ctypes.data, uc + o_w2, count4 * 4, None))
+        assert np.abs(got4 - (1.0 - 0.1 * ref[:count4] / world)).max() < 1e-4, "nvls one-shot sgd"
+        rep = torch.from_numpy(got4).cuda()
+        reps = [torch.empty_like(rep) for _ in range(world)]
+        dist.all_gather(reps, rep)
+        assert all(torch.equal(r_, reps[0]) for r_ in reps), "nvls one-shot: replicas differ"
         dist.barrier()
         arena.destroy()
         comm2.destroy()
