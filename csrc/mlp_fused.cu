@@ -60,6 +60,7 @@ struct FusedParams {
   uint32_t* xstatus;        // host-mapped failure record {code, rank, peer, phase} (watchdog), may be null
   unsigned long long xtimeout_ns;
   unsigned long long total;  // floats in the flat parameter vector
+  int bulk_update; // single GPU: apply the update with bulk reduce-adds from a staged image (else red.global per thread)
   int nsteps;      // steps this launch performs back to back (> 1 only with in-place SGD: wparams != null)
   int slot0;       // first input slot: step s reads rows [(slot0+s)*B, +B) of the X maps, labels + s*B, metrics + 2*s
 };
@@ -159,6 +160,11 @@ __device__ __forceinline__ void bulk_g2s(uint32_t dst_s, const void* src, uint32
 __device__ __forceinline__ void bulk_s2g(void* dst, uint32_t src_s, uint32_t bytes) {
   asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;" ::"l"(dst), "r"(src_s), "r"(bytes) : "memory");
 }
+// global[i] += shared[i] (fp32) for a contiguous range, performed by the bulk copy engine
+__device__ __forceinline__ void bulk_red_add_f32(void* dst, uint32_t src_s, uint32_t bytes) {
+  asm volatile("cp.reduce.async.bulk.global.shared::cta.bulk_group.add.f32 [%0], [%1], %2;" ::"l"(dst), "r"(src_s), "r"(bytes)
+               : "memory");
+}
 __device__ __forceinline__ void bulk_commit() { asm volatile("cp.async.bulk.commit_group;" ::: "memory"); }
 __device__ __forceinline__ void bulk_wait_all() { asm volatile("cp.async.bulk.wait_group 0;" ::: "memory"); }
 __device__ __forceinline__ void bulk_wait_read() { asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory"); }
@@ -183,7 +189,9 @@ __device__ __forceinline__ uint64_t mdesc(uint32_t tile, int kstep, uint32_t col
 __device__ __forceinline__ void emit_grad4(const FusedParams& p, float step, size_t off, uint32_t xs, uint32_t soff, float a,
                                            float b, float c, float d) {
   if (xs != 0u) {
-    sts128(xs + soff, a, b, c, d);
+    // staged: raw gradients (exchange mode) or -lr*g (single GPU: one bulk reduce-add per range applies them)
+    const float gs = p.world > 1 ? 1.f : -step;
+    sts128(xs + soff, gs * a, gs * b, gs * c, gs * d);
   } else if (p.wparams != nullptr) {
     // w += (-lr*g) as a fire-and-forget vector reduction: no load latency in the epilogue. Every
     // element is touched by exactly one thread, so the result equals w - lr*g bit for bit.
@@ -327,7 +335,9 @@ mlp_fused_step_kernel(const __grid_constant__ CUtensorMap tmXA, const __grid_con
   }
   const uint32_t epoch = epoch0 + static_cast<uint32_t>(st) + 1u;
   const uint32_t xpar = epoch & 1u;  // receive areas are double-buffered by step parity
-  const uint32_t xs = xmode ? sb : 0u;  // exchange mode: gradients are staged in shared memory
+  // gradients are staged in shared memory in exchange mode and (single GPU) when the update is applied by bulk reduce-adds
+  const bool bmode = !xmode && p.wparams != nullptr && p.bulk_update != 0;
+  const uint32_t xs = (xmode || bmode) ? sb : 0u;
   if (warp == 0) {
     if (elect_one()) {
     for (int a = 0; a < H1 / 32; ++a) tma_load_2d(smem + oW1B + a * kW1Col, &tmW1, &bar_tma0, 32 * a, k0);
@@ -793,6 +803,25 @@ mlp_fused_step_kernel(const __grid_constant__ CUtensorMap tmXA, const __grid_con
     for (int c = 0; c < 16; c += 4) emit_grad4(p, step, off + c, xs, kXsBL + c * 4, dbl[c], dbl[c + 1], dbl[c + 2], dbl[c + 3]);
   }
   FPROF(12);
+  if (bmode) {
+    // Single GPU: the staged -lr*g images are added to the weights by the bulk copy engine
+    // (cp.reduce.async.bulk ... add.f32): one instruction per range instead of ~3,300 red.global.add.v4 from the
+    // epilogue threads.
+    fence_proxy_async_smem();
+    __syncthreads();
+    if (warp == 0 && elect_one()) {
+      bulk_red_add_f32(p.wparams + p.w_off[0] + static_cast<size_t>(k0) * H1, sb + kXsW1, nk1 * 8 * H1 * 4);
+      if (kMid) {
+        bulk_red_add_f32(p.wparams + p.w_off[1] + static_cast<size_t>(S1 * j) * H2, sb + kXsW2, S1 * H2 * 4);
+        bulk_red_add_f32(p.wparams + p.b_off[1] + S2 * j, sb + kXsB2, S2 * 4);
+      }
+      bulk_red_add_f32(p.wparams + p.w_off[LAST] + static_cast<size_t>(SL * j) * 16, sb + kXsWL, SL * 16 * 4);
+      bulk_red_add_f32(p.wparams + p.b_off[0] + S1 * j, sb + kXsB1, S1 * 4);
+      if (j == 0) bulk_red_add_f32(p.wparams + p.b_off[LAST], sb + kXsBL, 64);
+      bulk_commit();
+      bulk_wait_all();  // performed before the end-of-step barrier lets the next step load the weights
+    }
+  }
   if (xmode) {
     // ---------------------------------------------------------------- gradient exchange (data parallel)
     // This CTA's gradient slices sit in a staging image in shared memory. The bulk copy engine pushes the image
@@ -1045,6 +1074,10 @@ extern "C" int dmlp_mlp_fused_plan_create(const dmlp_mlp_fused_desc_t* d, dmlp_m
   }
   p.nsteps = 1;
   p.slot0 = 0;
+  {
+    const char* e = getenv("DMLP_FUSED_BULK");
+    p.bulk_update = e ? atoi(e) : 0;  // measured: 22.3 us/step with bulk reduce-adds vs 21.3 with red.global (default)
+  }
   *out = reinterpret_cast<dmlp_mlp_fused_plan_t>(pl);
   return DMLP_OK;
 }
