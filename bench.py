@@ -141,6 +141,7 @@ def main() -> int:
     ap.add_argument("--allreduce", default="auto")
     ap.add_argument("--overlap", type=int, default=-1, help="layer-by-layer all-reduce overlap (default: on for multi-GPU wide)")
     ap.add_argument("--no-graph", action="store_true")
+    ap.add_argument("--fused", type=int, default=-1, help="TrainerConfig.fused (-1 auto; 2/3/4 select variants of the fused path)")
     ap.add_argument("--host-batches", type=int, default=0, help="host dataset size in batches per rank")
     a = ap.parse_args()
     if a.impl == "reference":
@@ -172,7 +173,7 @@ def main() -> int:
     batch = a.batch or m["batch"]
     overlap = (a.model == "wide" and multi) if a.overlap < 0 else bool(a.overlap)
     cfg = TrainerConfig(dims=m["dims"], batch=batch, lr=0.01, precision=m["precision"], allreduce=a.allreduce,
-                        overlap=overlap, use_graph=not a.no_graph)
+                        overlap=overlap, use_graph=not a.no_graph, fused=a.fused)
     trainer = Trainer(cfg, device=local_rank, process_group=multi)
 
     # ---- synthetic data: a pinned host dataset (e2e) and a device dataset larger than L2 (kernel timing)
@@ -246,7 +247,7 @@ def main() -> int:
         "data": "synthetic MNIST-shaped (28x28 float32, 10 classes), random-init weights U(-0.05,0.05)",
         "config": {"model": m["name"], "global_batch": gbatch, "per_gpu_batch": batch, "seq_len": None,
                    "parallelism": f"dp{world}", "optimizer": "SGD lr=0.01 fused into all-reduce",
-                   "allreduce": algo, "overlap": overlap, "cuda_graph": not a.no_graph,
+                   "allreduce": algo, "fused_mode": a.fused, "overlap": overlap, "cuda_graph": not a.no_graph,
                    "l2_policy": f"inputs streamed from a {dset.nbytes >> 20} MiB device-resident dataset (> 126 MiB L2), "
                                 f"{dev_batches} distinct batches; weights stay resident by design"},
         "e2e": {"value": e2e_value, "unit": "samples/s", "ms_per_step": max(ms_e2e, wall_e2e) / a.steps,

@@ -821,6 +821,15 @@ extern "C" int dmlp_comm_internal_view(dmlp_comm_t h, int local_idx, uint32_t* p
   return DMLP_OK;
 }
 
+// 1 when all ranks of the communicator sit on one device (collectives then run as ONE cooperative launch; anything
+// that would make separate per-rank launches wait on each other must not be used).
+extern "C" int dmlp_comm_is_emulated(dmlp_comm_t h, int* emulated) {
+  Comm* c = reinterpret_cast<Comm*>(h);
+  DMLP_REQUIRE(c && emulated, "dmlp_comm_is_emulated: bad arguments");
+  *emulated = c->emulated ? 1 : 0;
+  return DMLP_OK;
+}
+
 extern "C" int dmlp_allreduce_pick_algo(int world, size_t bytes) {
   if (world <= 1) return DMLP_ALGO_ONESHOT;
   // Latency-bound sizes: one rendezvous, (n-1) x bytes pulled per rank. Above that two-shot moves

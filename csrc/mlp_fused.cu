@@ -60,6 +60,13 @@ struct FusedParams {
   uint32_t* xstatus;        // host-mapped failure record {code, rank, peer, phase} (watchdog), may be null
   unsigned long long xtimeout_ns;
   unsigned long long total;  // floats in the flat parameter vector
+  // ---- persistent data-parallel mode (red_ctas > 0): the grid is [1 compute cluster | red_ctas reducer CTAs]. The compute
+  // cluster writes its gradients to xgrads[parity][rank] and raises local flags; the reducers (spinning since launch)
+  // rendezvous with the same reducer CTA on every rank, pull all ranks' gradients over NVLink, apply w -= lr/world * sum
+  // and raise a local counter the compute cluster waits on before the next step's weight loads. No kernel boundary
+  // between step and all-reduce, several steps per launch.
+  int red_ctas;
+  float* xgrads[2][8];
   int bulk_update; // single GPU: apply the update with bulk reduce-adds from a staged image (else red.global per thread)
   int nsteps;      // steps this launch performs back to back (> 1 only with in-place SGD: wparams != null)
   int slot0;       // first input slot: step s reads rows [(slot0+s)*B, +B) of the X maps, labels + s*B, metrics + 2*s
@@ -187,8 +194,10 @@ __device__ __forceinline__ uint64_t mdesc(uint32_t tile, int kstep, uint32_t col
 // Exchange mode (xs != 0): the gradient goes to this CTA's staging image in shared memory (byte offset soff); the bulk
 // copy engine pushes the image to the peers afterwards.
 __device__ __forceinline__ void emit_grad4(const FusedParams& p, float step, size_t off, uint32_t xs, uint32_t soff, float a,
-                                           float b, float c, float d) {
-  if (xs != 0u) {
+                                           float b, float c, float d, float* gdst = nullptr) {
+  if (gdst != nullptr) {  // persistent data-parallel mode: this rank's peer-visible gradient buffer
+    *reinterpret_cast<float4*>(gdst + off) = make_float4(a, b, c, d);
+  } else if (xs != 0u) {
     // staged: raw gradients (exchange mode) or -lr*g (single GPU: one bulk reduce-add per range applies them)
     const float gs = p.world > 1 ? 1.f : -step;
     sts128(xs + soff, gs * a, gs * b, gs * c, gs * d);
@@ -226,6 +235,102 @@ __device__ __forceinline__ void worker_colsum(const float (&v)[N], float* red, i
   asm volatile("bar.sync 1, 128;" ::: "memory");
 }
 
+// Pad words of the persistent data-parallel mode (relative to kPadFusedFlags; all but the last group are only used locally)
+constexpr int kPfEpoch = 64;        // steps completed (shared with the in-kernel exchange mode)
+constexpr int kPfWeights = 80;      // counter: reducer CTAs that finished applying an update (red_ctas per step)
+constexpr int kPfRedFlags = 128;    // [source rank][compute CTA]: epoch whose gradient slices are complete (written by every rank)
+constexpr int kMaxRedCtas = 136;  // 8 + 136 CTAs <= 148 SMs: every CTA of the launch must be resident (the roles wait on each other)
+
+__device__ __forceinline__ float4 ld_volatile_f4(const float* p) {
+  float4 v;
+  asm volatile("ld.volatile.global.v4.f32 {%0, %1, %2, %3}, [%4];" : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "l"(p) : "memory");
+  return v;
+}
+
+// Spin until *flag >= target (wrap-safe) with the communicator's watchdog; false on abort / deadline (status recorded).
+__device__ __forceinline__ bool pf_wait(const uint32_t* flag, uint32_t target, const FusedParams& p, int peer, uint32_t phase,
+                                        unsigned long long deadline) {
+  uint32_t spins = 0;
+  while (static_cast<int32_t>(ld_relaxed_sys(flag) - target) < 0) {
+    if ((++spins & 0x3F) == 0) {
+      if (ld_relaxed_sys(p.xpad[p.rank] + kPadAbortWord) != 0u) return false;
+      if (globaltimer_ns() > deadline) {
+        if (p.xstatus != nullptr) {
+          p.xstatus[1] = static_cast<uint32_t>(p.rank);
+          p.xstatus[2] = static_cast<uint32_t>(peer);
+          p.xstatus[3] = phase;
+          __threadfence_system();
+          p.xstatus[0] = DMLP_ERR_TIMEOUT;
+        }
+        for (int q = 0; q < p.world; ++q) st_relaxed_sys(p.xpad[q] + kPadAbortWord, 1u);
+        return false;
+      }
+    }
+  }
+  return true;
+}
+
+// Reducer CTA of the persistent data-parallel mode: one-shot all-reduce + average + SGD per step, fed by local flags.
+__device__ void fused_reducer_loop(const FusedParams& p) {
+  __shared__ int s_fail;
+  __shared__ uint32_t s_epoch0;
+  const int b = static_cast<int>(blockIdx.x) - kFC, nb = p.red_ctas;
+  uint32_t* mypad = p.xpad[p.rank] + kPadFusedFlags;
+  asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
+  asm volatile("griddepcontrol.wait;" ::: "memory");
+  if (threadIdx.x == 0) { s_fail = 0; s_epoch0 = __ldcg(mypad + kPfEpoch); }
+  __syncthreads();
+  const uint32_t epoch0 = s_epoch0;
+  const int nsteps = p.nsteps > 0 ? p.nsteps : 1;
+  const size_t npacks = p.total / 4;  // the flat parameter vector is padded to 64-float multiples
+  for (int st = 0; st < nsteps; ++st) {
+    const uint32_t epoch = epoch0 + static_cast<uint32_t>(st) + 1u;
+    const uint32_t par = epoch & 1u;
+    const unsigned long long deadline = globaltimer_ns() + p.xtimeout_ns;
+    // every rank's compute CTAs raise [rank][cta] in every rank's pad once their gradient slices are complete:
+    // (world x 8) flags to poll locally, no relay through this rank's own flags
+    if (threadIdx.x < p.world * kFC) {
+      if (!pf_wait(mypad + kPfRedFlags + threadIdx.x, epoch, p, threadIdx.x / kFC, 7u, deadline)) s_fail = 1;
+    }
+    __syncthreads();
+    if (s_fail == 0) {
+      const float sc = __ldcg(p.lr) / static_cast<float>(p.world);
+      // kRedPk packs per thread and pass, every load of a pass issued before the first add: one NVLink round trip per pass
+      constexpr int kRedPk = 4;
+      const size_t stride = static_cast<size_t>(nb) * blockDim.x;
+      for (size_t i0 = static_cast<size_t>(b) * blockDim.x + threadIdx.x; i0 < npacks; i0 += stride * kRedPk) {
+        float4 g[kRedPk][8];
+        float4 w[kRedPk];
+#pragma unroll
+        for (int k = 0; k < kRedPk; ++k) {
+          const size_t i = i0 + k * stride;
+          if (i < npacks) {
+#pragma unroll
+            for (int r = 0; r < 8; ++r)
+              if (r < p.world) g[k][r] = ld_volatile_f4(p.xgrads[par][r] + 4 * i);  // rank order: identical sums everywhere
+            w[k] = __ldcg(reinterpret_cast<const float4*>(p.wparams + 4 * i));
+          }
+        }
+#pragma unroll
+        for (int k = 0; k < kRedPk; ++k) {
+          const size_t i = i0 + k * stride;
+          if (i < npacks) {
+            float4 acc = g[k][0];
+#pragma unroll
+            for (int r = 1; r < 8; ++r)
+              if (r < p.world) { acc.x += g[k][r].x; acc.y += g[k][r].y; acc.z += g[k][r].z; acc.w += g[k][r].w; }
+            w[k].x -= sc * acc.x; w[k].y -= sc * acc.y; w[k].z -= sc * acc.z; w[k].w -= sc * acc.w;
+            *reinterpret_cast<float4*>(p.wparams + 4 * i) = w[k];
+          }
+        }
+      }
+    }
+    __threadfence();
+    __syncthreads();
+    if (threadIdx.x == 0) atomicAdd(mypad + kPfWeights, 1u);  // (also on failure: the compute cluster must not hang)
+  }
+}
+
 template <int S1, int S2>  // slice widths: H1/8 and H2/8 (S2 == 0: two-layer model)
 __global__ void __cluster_dims__(kFC, 1, 1) __launch_bounds__(kFThreads, 1)
 mlp_fused_step_kernel(const __grid_constant__ CUtensorMap tmXA, const __grid_constant__ CUtensorMap tmXT,
@@ -259,6 +364,11 @@ mlp_fused_step_kernel(const __grid_constant__ CUtensorMap tmXA, const __grid_con
   const int ngroups = p.in0 / 8;
   const int g0 = (ngroups * j) / kFC, g1 = (ngroups * (j + 1)) / kFC;
   const int k0 = g0 * 8, nk1 = g1 - g0;  // layer-1 K slice: floats [k0, k0 + 8*nk1)
+  if (p.red_ctas > 0 && blockIdx.x >= kFC) {  // persistent data-parallel mode: everything past the first cluster reduces
+    fused_reducer_loop(p);
+    return;
+  }
+  const bool pmode = p.red_ctas > 0;
   const bool worker = warp >= 1;
   const int wwarp = warp - 1;
   const int row = (warp & 3) * 32 + lane;  // TMEM lane == batch row handled by this worker thread
@@ -310,7 +420,7 @@ mlp_fused_step_kernel(const __grid_constant__ CUtensorMap tmXA, const __grid_con
   // launch gap, TMEM allocation and barrier set-up are paid once; steps are separated by one cluster barrier
   // that also publishes the weight updates (red.global + __threadfence) to the next step's loads.
   const int nsteps = p.nsteps > 0 ? p.nsteps : 1;
-  const bool xmode = p.world > 1;
+  const bool xmode = p.world > 1 && !pmode;
   uint32_t xr_phase = 0;  // bit s: parity the next wait on receive stage s expects
   uint32_t epoch0 = 0;  // steps this rank completed before this launch (every rank holds the same count)
   __shared__ int s_xfail;
@@ -331,13 +441,24 @@ mlp_fused_step_kernel(const __grid_constant__ CUtensorMap tmXA, const __grid_con
   }
   if (st == 0) {
     asm volatile("griddepcontrol.wait;" ::: "memory");
-    if (xmode) epoch0 = __ldcg(p.xpad[p.rank] + kPadFusedEpoch);
+    if (xmode || pmode) epoch0 = __ldcg(p.xpad[p.rank] + kPadFusedEpoch);
   }
   const uint32_t epoch = epoch0 + static_cast<uint32_t>(st) + 1u;
   const uint32_t xpar = epoch & 1u;  // receive areas are double-buffered by step parity
   // gradients are staged in shared memory in exchange mode and (single GPU) when the update is applied by bulk reduce-adds
-  const bool bmode = !xmode && p.wparams != nullptr && p.bulk_update != 0;
+  const bool bmode = !xmode && !pmode && p.wparams != nullptr && p.bulk_update != 0;
   const uint32_t xs = (xmode || bmode) ? sb : 0u;
+  float* gdst = pmode ? p.xgrads[xpar][p.rank] : nullptr;
+  if (pmode && st > 0) {
+    // the reducers have applied the previous step's update (red_ctas increments per step) before any weight is loaded
+    if (threadIdx.x == 0) {
+      const unsigned long long deadline = globaltimer_ns() + p.xtimeout_ns;
+      if (!pf_wait(p.xpad[p.rank] + kPadFusedFlags + kPfWeights, (epoch - 1u) * static_cast<uint32_t>(p.red_ctas), p, p.rank, 8u, deadline))
+        s_xfail = 1;
+      fence_proxy_async_all();  // the weights the reducers wrote are re-read by TMA (async proxy)
+    }
+    __syncthreads();
+  }
   if (warp == 0) {
     if (elect_one()) {
     for (int a = 0; a < H1 / 32; ++a) tma_load_2d(smem + oW1B + a * kW1Col, &tmW1, &bar_tma0, 32 * a, k0);
@@ -741,7 +862,7 @@ mlp_fused_step_kernel(const __grid_constant__ CUtensorMap tmXA, const __grid_con
         const size_t off = p.w_off[LAST] + static_cast<size_t>(SL * j + row) * 16;
 #pragma unroll
         for (int c = 0; c < 16; c += 4)
-          emit_grad4(p, step, off + c, xs, kXsWL + row * 64 + c * 4, __uint_as_float(r[c]), __uint_as_float(r[c + 1]), __uint_as_float(r[c + 2]), __uint_as_float(r[c + 3]));
+          emit_grad4(p, step, off + c, xs, kXsWL + row * 64 + c * 4, __uint_as_float(r[c]), __uint_as_float(r[c + 1]), __uint_as_float(r[c + 2]), __uint_as_float(r[c + 3]), gdst);
       }
       if (row == SL) {  // the ones row: column sums of dZ_last = gradient of the last bias
 #pragma unroll
@@ -760,7 +881,7 @@ mlp_fused_step_kernel(const __grid_constant__ CUtensorMap tmXA, const __grid_con
           const size_t off = p.w_off[1] + static_cast<size_t>(S1 * j + row) * H2 + cc;
 #pragma unroll
           for (int c = 0; c < 16; c += 4)
-            emit_grad4(p, step, off + c, xs, kXsW2 + row * (H2 * 4) + (cc + c) * 4, __uint_as_float(r[c]), __uint_as_float(r[c + 1]), __uint_as_float(r[c + 2]), __uint_as_float(r[c + 3]));
+            emit_grad4(p, step, off + c, xs, kXsW2 + row * (H2 * 4) + (cc + c) * 4, __uint_as_float(r[c]), __uint_as_float(r[c + 1]), __uint_as_float(r[c + 2]), __uint_as_float(r[c + 3]), gdst);
         }
         if (row == S1 && (S2 * j) / 16 == cc / 16) {  // ones row: db2; this CTA owns b2[S2*j, S2*j+S2)
           const int c0 = (S2 * j) % 16;
@@ -768,7 +889,7 @@ mlp_fused_step_kernel(const __grid_constant__ CUtensorMap tmXA, const __grid_con
 #pragma unroll
           for (int c = 0; c < 16; c += 4)
             if (c >= c0 && c < c0 + S2)
-              emit_grad4(p, step, off + (c - c0), xs, kXsB2 + (c - c0) * 4, __uint_as_float(r[c]), __uint_as_float(r[c + 1]), __uint_as_float(r[c + 2]), __uint_as_float(r[c + 3]));
+              emit_grad4(p, step, off + (c - c0), xs, kXsB2 + (c - c0) * 4, __uint_as_float(r[c]), __uint_as_float(r[c + 1]), __uint_as_float(r[c + 2]), __uint_as_float(r[c + 3]), gdst);
         }
       }
     }
@@ -784,13 +905,13 @@ mlp_fused_step_kernel(const __grid_constant__ CUtensorMap tmXA, const __grid_con
         const size_t off = p.w_off[0] + static_cast<size_t>(k0 + row) * H1 + cc;
 #pragma unroll
         for (int c = 0; c < 16; c += 4)
-          emit_grad4(p, step, off + c, xs, kXsW1 + row * (H1 * 4) + (cc + c) * 4, __uint_as_float(r[c]), __uint_as_float(r[c + 1]), __uint_as_float(r[c + 2]), __uint_as_float(r[c + 3]));
+          emit_grad4(p, step, off + c, xs, kXsW1 + row * (H1 * 4) + (cc + c) * 4, __uint_as_float(r[c]), __uint_as_float(r[c + 1]), __uint_as_float(r[c + 2]), __uint_as_float(r[c + 3]), gdst);
       }
       if (row == 127 && cc == S1 * j) {  // ones row: db1; this CTA owns b1[S1*j, S1*j+S1)
         const size_t off = p.b_off[0] + S1 * j;
 #pragma unroll
         for (int c = 0; c < 16; c += 4)
-          emit_grad4(p, step, off + c, xs, kXsB1 + c * 4, __uint_as_float(r[c]), __uint_as_float(r[c + 1]), __uint_as_float(r[c + 2]), __uint_as_float(r[c + 3]));
+          emit_grad4(p, step, off + c, xs, kXsB1 + c * 4, __uint_as_float(r[c]), __uint_as_float(r[c + 1]), __uint_as_float(r[c + 2]), __uint_as_float(r[c + 3]), gdst);
       }
     }
   }
@@ -800,9 +921,18 @@ mlp_fused_step_kernel(const __grid_constant__ CUtensorMap tmXA, const __grid_con
   if (j == 0 && worker && row == SL) {
     const size_t off = p.b_off[LAST];
 #pragma unroll
-    for (int c = 0; c < 16; c += 4) emit_grad4(p, step, off + c, xs, kXsBL + c * 4, dbl[c], dbl[c + 1], dbl[c + 2], dbl[c + 3]);
+    for (int c = 0; c < 16; c += 4) emit_grad4(p, step, off + c, xs, kXsBL + c * 4, dbl[c], dbl[c + 1], dbl[c + 2], dbl[c + 3], gdst);
   }
   FPROF(12);
+  if (pmode) {
+    // gradients performed at GPU scope (they sit in this GPU's L2, which is where peer reads are served from) before the
+    // flag: one fence by one thread after the CTA barrier (cumulative), not a MEMBAR.SYS per thread (~4 us)
+    __syncthreads();
+    if (threadIdx.x < p.world) {  // one thread per rank (own included): that rank's reducers poll [my rank][my CTA] locally
+      __threadfence();
+      st_relaxed_sys(p.xpad[threadIdx.x] + kPadFusedFlags + kPfRedFlags + p.rank * kFC + j, epoch);
+    }
+  }
   if (bmode) {
     // Single GPU: the staged -lr*g images are added to the weights by the bulk copy engine
     // (cp.reduce.async.bulk ... add.f32): one instruction per range instead of ~3,300 red.global.add.v4 from the
@@ -987,7 +1117,7 @@ mlp_fused_step_kernel(const __grid_constant__ CUtensorMap tmXA, const __grid_con
   tc_fence_after_sync();
   FPROF(14);
   }  // step loop
-  if (xmode && j == 0 && threadIdx.x == 0) p.xpad[p.rank][kPadFusedEpoch] = epoch0 + static_cast<uint32_t>(nsteps);
+  if ((xmode || pmode) && j == 0 && threadIdx.x == 0) p.xpad[p.rank][kPadFusedEpoch] = epoch0 + static_cast<uint32_t>(nsteps);
   if (warp == 0) {
     tc_fence_after_sync();
     tmem_dealloc(tm, 512);
@@ -1064,13 +1194,24 @@ extern "C" int dmlp_mlp_fused_plan_create(const dmlp_mlp_fused_desc_t* d, dmlp_m
     p.world = d->xchg_world;
     p.rank = d->xchg_rank;
     for (int r = 0; r < d->xchg_world; ++r) {
-      DMLP_REQUIRE(d->xchg_recv_dev[r] && d->xchg_pad_dev[r], "fused step: rank %d's receive area / signal pad is not mapped", r);
+      DMLP_REQUIRE((d->xchg_recv_dev[r] || d->xchg_reducer_ctas > 0) && d->xchg_pad_dev[r], "fused step: rank %d's receive area / signal pad is not mapped", r);
       p.xrecv[r] = d->xchg_recv_dev[r];
       p.xpad[r] = d->xchg_pad_dev[r];
     }
     p.xstatus = d->xchg_status;
     p.xtimeout_ns = d->xchg_timeout_ns ? d->xchg_timeout_ns : 10ull * 1000 * 1000 * 1000;
     p.total = d->param_count;
+    if (d->xchg_reducer_ctas > 0) {
+      DMLP_REQUIRE(d->xchg_reducer_ctas % kFC == 0 && d->xchg_reducer_ctas <= kMaxRedCtas && d->param_count % 4 == 0,
+                   "fused step: reducer CTAs must come in clusters of %d (<= %d) and the parameter count be a multiple of 4", kFC,
+                   kMaxRedCtas);
+      p.red_ctas = d->xchg_reducer_ctas;
+      for (int par = 0; par < 2; ++par)
+        for (int r = 0; r < d->xchg_world; ++r) {
+          DMLP_REQUIRE(d->xchg_grads_dev[par][r] != nullptr, "fused step: rank %d's gradient buffer is not mapped", r);
+          p.xgrads[par][r] = d->xchg_grads_dev[par][r];
+        }
+    }
   }
   p.nsteps = 1;
   p.slot0 = 0;
@@ -1099,7 +1240,7 @@ static int launch_fused(const FusedPlan* pl, const FusedParams& prm, cudaStream_
   }
   cudaLaunchConfig_t cfg;
   memset(&cfg, 0, sizeof(cfg));
-  cfg.gridDim = dim3(kFC);
+  cfg.gridDim = dim3(kFC + (prm.red_ctas > 0 ? prm.red_ctas : 0));
   cfg.blockDim = dim3(kFThreads);
   cfg.dynamicSmemBytes = kFusedSmem;
   cfg.stream = st;
@@ -1108,6 +1249,18 @@ static int launch_fused(const FusedPlan* pl, const FusedParams& prm, cudaStream_
   attr[0].val.programmaticStreamSerializationAllowed = 1;
   cfg.attrs = attr;
   cfg.numAttrs = 1;
+  if (prm.red_ctas > 0) {
+    // The compute cluster and the reducer CTAs wait on each other: every cluster of the launch must be resident at once.
+    static int max_clusters[64] = {0};
+    if (dev < 64 && max_clusters[dev] == 0) {
+      int n = 0;
+      DMLP_CUDA_CHECK(cudaOccupancyMaxActiveClusters(&n, kern, &cfg));
+      max_clusters[dev] = n > 0 ? n : -1;
+    }
+    const int need = 1 + prm.red_ctas / kFC;
+    DMLP_REQUIRE(dev >= 64 || max_clusters[dev] >= need, "fused step: %d clusters of %d CTAs cannot be co-resident on this device (max %d)",
+                 need, kFC, dev < 64 ? max_clusters[dev] : 0);
+  }
   DMLP_CUDA_CHECK(cudaLaunchKernelEx(&cfg, kern, pl->tmXA, pl->tmXT, pl->tmW1, pl->tmW2B, pl->tmW2K, pl->tmWLB, pl->tmWLK, prm));
   DMLP_CUDA_CHECK(cudaGetLastError());
   return DMLP_OK;

@@ -70,6 +70,7 @@ struct Trainer {
   float* peer_grads[2][DMLP_MAX_RANKS];
   float* peer_recv[DMLP_MAX_RANKS];  // fused step with in-kernel gradient exchange: [2][world][total] receive areas
   unsigned long long* fused_prof = nullptr;  // DMLP_FUSED_PROF=1: [8 CTAs][16] phase stamps of the ring plan's last step
+  bool pdp = false;                   // persistent data-parallel launches (fused == 4): compute cluster + reducer CTAs
   bool xchg = false;                  // ... is in use (multi-GPU, fused step, fused != 2, no NVLS arena)
   bool owns_params = false;
   bool nvls = false;  // params/grads live in multicast-bound memory; all-reduce by multimem
@@ -230,7 +231,7 @@ static int build_plans(Trainer* t) {
       if (t->comm == nullptr && t->cfg.fused != 2) { f.sgd_params_dev = t->params; f.lr_dev = t->lr_dev; }
       TRY(dmlp_mlp_fused_plan_create(&f, &t->rplan[slot]));
     }
-    if ((t->comm == nullptr && t->cfg.fused != 2) || t->xchg) {
+    if ((t->comm == nullptr && t->cfg.fused != 2) || t->xchg || t->pdp) {
       dmlp_mlp_fused_desc_t f;
       memset(&f, 0, sizeof(f));
       f.num_layers = L.L;
@@ -254,7 +255,7 @@ static int build_plans(Trainer* t) {
           f.prof_dev = pp;
         }
       }
-      if (t->xchg) {
+      if (t->xchg || t->pdp) {
         uint32_t* pads[DMLP_MAX_RANKS];
         uint32_t *state = nullptr, *host_flags = nullptr, dead = 0;
         unsigned long long timeout_ns = 0;
@@ -266,6 +267,13 @@ static int build_plans(Trainer* t) {
         f.xchg_status = host_flags + 4;
         f.xchg_timeout_ns = timeout_ns;
         f.param_count = L.total;
+        if (t->pdp) {
+          static int red_env = -1;
+          if (red_env < 0) { const char* e = getenv("DMLP_FUSED_REDUCERS"); red_env = (e && atoi(e) > 0) ? atoi(e) : 56; }
+          f.xchg_reducer_ctas = red_env / 8 * 8;
+          for (int par = 0; par < 2; ++par)
+            for (int r = 0; r < t->world; ++r) f.xchg_grads_dev[par][r] = t->peer_grads[par][r];
+        }
       }
       TRY(dmlp_mlp_fused_plan_create(&f, &t->ring_plan));
     }
@@ -621,7 +629,7 @@ extern "C" int dmlp_trainer_create(const dmlp_trainer_config_t* cfg, int device,
   const int B = cfg->batch;
   t->fused_ce = L.out_pad[L.L - 1] <= 32;
   t->fused_step = !t->bf16 && cfg->fused != 0 && dmlp_mlp_fused_supported(cfg->num_layers, cfg->dims, cfg->batch) != 0;
-  if ((cfg->fused == 1 || cfg->fused == 3) && !t->fused_step) {
+  if ((cfg->fused == 1 || cfg->fused == 3 || cfg->fused == 4) && !t->fused_step) {
     set_error(DMLP_ERR_UNSUPPORTED, "fused step kernel does not support this shape / precision");
     delete t;
     return DMLP_ERR_UNSUPPORTED;
@@ -672,6 +680,12 @@ extern "C" int dmlp_trainer_create(const dmlp_trainer_config_t* cfg, int device,
       if (t->bf16) t->peer_shadow[r] = b + 3 * pbytes;
       if (want_x) t->peer_recv[r] = reinterpret_cast<float*>(b + 3 * pbytes);
     }
+    // Persistent data-parallel launches (compute cluster + reducer CTAs in one kernel, several steps per launch) are the
+    // default for the cluster-fused shapes on real multi-GPU communicators; fused == 1 keeps the two-kernel chain.
+    int emulated = 0;
+    TRYF(dmlp_comm_is_emulated(t->comm, &emulated));
+    t->pdp = t->fused_step && !emulated && (cfg->fused == 4 || cfg->fused == -1);
+    for (int r = 0; r < world; ++r) t->pdp = t->pdp && t->peer_grads[0][r] != nullptr;
     t->xchg = t->fused_step && cfg->fused == 3;
     for (int r = 0; r < world; ++r) t->xchg = t->xchg && t->peer_recv[r] != nullptr;
     t->params = t->peer_params[rank];

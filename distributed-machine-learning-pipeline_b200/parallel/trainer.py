@@ -44,7 +44,8 @@ class TrainerConfig:
     overlap: bool = False                      # per-layer buckets reduced during backward
     use_graph: bool = True
     fused: int = -1                            # cluster-fused step kernel: -1 auto, 0 off, 1 require, 2 require + separate
-                                               # update kernel, 3 require + gradient exchange inside the step kernel (world > 1)
+                                               # update kernel, 3 require + gradient exchange inside the step kernel (world > 1),
+                                               # 4 require + persistent launch: compute cluster + reducer CTAs (world > 1)
     schedule: str = "constant"
     seed: int = 0
     watchdog_ms: int = 10000

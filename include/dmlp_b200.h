@@ -183,6 +183,7 @@ int dmlp_comm_arena_ptr(dmlp_comm_t comm, int local_idx, int rank, void** ptr_de
 int dmlp_comm_set_timeout_ms(dmlp_comm_t comm, uint64_t ms); /* in-kernel watchdog, default 10 s */
 int dmlp_comm_abort(dmlp_comm_t comm);                       /* releases every spinning kernel */
 /* out = {failure code, reporting rank, awaited peer, phase, abort flag}; code 0 = healthy. */
+int dmlp_comm_is_emulated(dmlp_comm_t comm, int* emulated);  /* all ranks on one device (single cooperative launches) */
 int dmlp_comm_status(dmlp_comm_t comm, uint32_t out[5]);
 int dmlp_comm_inject_dead_ranks(dmlp_comm_t comm, uint32_t rank_mask); /* fault injection */
 
@@ -312,6 +313,12 @@ typedef struct {
   uint32_t* xchg_status;                    /* host-mapped {code, rank, peer, phase} failure record (nullable) */
   unsigned long long xchg_timeout_ns;       /* watchdog for the flag wait */
   size_t param_count;                       /* floats in the flat parameter vector (slot size) */
+  /* Persistent data-parallel mode (xchg_reducer_ctas > 0, multiple of 8, <= 64): the launch is one compute cluster plus
+   * that many reducer CTAs. The compute cluster writes gradients to xchg_grads_dev[parity][rank]; the reducers run the
+   * one-shot all-reduce + average + SGD over peer memory inside the same launch (local flags both ways), so several
+   * steps per launch work on several GPUs too. xchg_recv_dev is not used in this mode. */
+  int xchg_reducer_ctas;
+  float* xchg_grads_dev[2][DMLP_MAX_RANKS];
 } dmlp_mlp_fused_desc_t;
 typedef struct dmlp_mlp_fused_opaque* dmlp_mlp_fused_plan_t;
 int dmlp_mlp_fused_supported(int num_layers, const int* dims, int batch);

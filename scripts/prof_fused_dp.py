@@ -26,8 +26,8 @@ def main():
     if multi:
         dist.init_process_group("nccl", device_id=torch.device(f"cuda:{local}"))
     rank = dist.get_rank() if multi else 0
-    t = Trainer(TrainerConfig(dims=(784, 128, 64, 10), batch=64, lr=0.01, fused=3 if multi else -1), device=local,
-                process_group=multi)
+    t = Trainer(TrainerConfig(dims=(784, 128, 64, 10), batch=64, lr=0.01, fused=(int(os.environ.get('DMLP_PROF_FUSED_MODE', '3')) if multi else -1)),
+                device=local, process_group=multi)
     x, y = synthetic_mnist(64 * 64, seed=rank)
     acc = np.zeros((8, 16))
     n = 0
@@ -39,7 +39,8 @@ def main():
             n += 1
     acc /= n
     mean = acc.mean(axis=0)
-    order = [i for i in ORDER if (multi or i not in (15, 0, 1))]
+    mode = int(os.environ.get('DMLP_PROF_FUSED_MODE', '3'))
+    order = [i for i in ORDER if ((multi and mode == 3) or i not in (15, 0, 1))]
     out = {"rank": rank, "world": dist.get_world_size() if multi else 1,
            "phase_end_us": {NAMES[i]: round(mean[i] / 1e3, 2) for i in order},
            "phase_us": {NAMES[order[k]]: round((mean[order[k]] - mean[order[k - 1]]) / 1e3, 2) for k in range(1, len(order))}}
