@@ -70,6 +70,21 @@ class AllReduceDesc(C.Structure):
     ]
 
 
+class MlpFusedDesc(C.Structure):
+    """dmlp_mlp_fused_desc_t (include/dmlp_b200.h): the cluster-fused step kernel's plan descriptor."""
+    _fields_ = [
+        ("num_layers", C.c_int), ("dims", C.c_int * 4), ("batch", C.c_int),
+        ("x", C.c_void_p), ("labels", C.c_void_p), ("params", C.c_void_p), ("grads", C.c_void_p),
+        ("w_off", C.c_size_t * 3), ("b_off", C.c_size_t * 3),
+        ("metrics", C.c_void_p), ("debug", C.c_void_p), ("prof", C.c_void_p),
+        ("sgd_params", C.c_void_p), ("lr", C.c_void_p), ("x_slots", C.c_int),
+        ("xchg_world", C.c_int), ("xchg_rank", C.c_int),
+        ("xchg_recv", C.c_void_p * MAX_RANKS), ("xchg_pad", C.c_void_p * MAX_RANKS),
+        ("xchg_status", C.c_void_p), ("xchg_timeout_ns", C.c_ulonglong), ("param_count", C.c_size_t),
+        ("xchg_reducer_ctas", C.c_int), ("xchg_grads", (C.c_void_p * MAX_RANKS) * 2),
+    ]
+
+
 _lib = None
 _lock = threading.Lock()
 

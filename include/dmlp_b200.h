@@ -313,7 +313,7 @@ typedef struct {
   uint32_t* xchg_status;                    /* host-mapped {code, rank, peer, phase} failure record (nullable) */
   unsigned long long xchg_timeout_ns;       /* watchdog for the flag wait */
   size_t param_count;                       /* floats in the flat parameter vector (slot size) */
-  /* Persistent data-parallel mode (xchg_reducer_ctas > 0, multiple of 8, <= 64): the launch is one compute cluster plus
+  /* Persistent data-parallel mode (xchg_reducer_ctas > 0, multiple of 8, <= 136; all 8 + n CTAs must be co-resident): the launch is one compute cluster plus
    * that many reducer CTAs. The compute cluster writes gradients to xchg_grads_dev[parity][rank]; the reducers run the
    * one-shot all-reduce + average + SGD over peer memory inside the same launch (local flags both ways), so several
    * steps per launch work on several GPUs too. xchg_recv_dev is not used in this mode. */

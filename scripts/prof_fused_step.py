@@ -13,11 +13,7 @@ from dmlp_b200.models.layout import ParamLayout  # noqa: E402
 from dmlp_b200.runtime import native  # noqa: E402
 
 
-class Desc(C.Structure):
-    _fields_ = [("num_layers", C.c_int), ("dims", C.c_int * 4), ("batch", C.c_int), ("x", C.c_void_p), ("labels", C.c_void_p),
-                ("params", C.c_void_p), ("grads", C.c_void_p), ("w_off", C.c_size_t * 3), ("b_off", C.c_size_t * 3),
-                ("metrics", C.c_void_p), ("debug", C.c_void_p), ("prof", C.c_void_p),
-                ("sgd_params", C.c_void_p), ("lr", C.c_void_p), ("x_slots", C.c_int)]
+Desc = native.MlpFusedDesc
 
 
 def multi_step_profile(lib, dims, lay, B, slots=8):
