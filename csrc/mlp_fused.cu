@@ -1,11 +1,11 @@
 // Cluster-fused training step for the reference-sized MLP (sm_100a): the whole forward, loss and
 // backward of one batch in ONE launch of one 8-CTA thread-block cluster.
 //
-// Why: at batch 64 every layer is latency bound. A tcgen05.mma costs ~200 cycles no matter how
-// narrow N is (profiles/r1_gemm_kloop_probe.md), the layer-1 forward is 98 of them back to back,
-// and each per-layer kernel pays ~3.3 us of fixed cost. Here the K dimension of every layer is
-// split over the 8 CTAs of a cluster; partial sums travel through distributed shared memory
-// (st.shared::cluster) and the output slice a CTA owns after the reduce-scatter is exactly the K
+// Why: at batch 64 every layer is latency bound: the layer-1 forward is 98 dependent tcgen05.mma in a
+// row and each per-layer kernel pays ~3.3 us of fixed cost (profiles/r1_gemm_kloop_probe.md). Here the K
+// dimension of every layer is split over the 8 CTAs of a cluster; partial sums travel through
+// distributed shared memory (st.async: the bytes complete on an mbarrier of the DESTINATION CTA, no
+// cluster barrier on the chain) and the output slice a CTA owns after the reduce-scatter is exactly the K
 // slice it needs for the next layer:
 //
 //   P0  TMA: X[:, k-slice], W1[k-slice, :]            F1: P1 = X_j . W1_j            -> reduce-scatter
@@ -18,8 +18,14 @@
 //
 // Every product is a tcgen05.mma (kind::tf32, M=128, accumulator in TMEM); weights and inputs come
 // in by TMA, activations / gradients are written to shared memory by the epilogue threads in the
-// canonical swizzled layouts the MMA descriptors expect. Gradients leave in the flat parameter
-// layout; the all-reduce + average + SGD kernel (collectives.cu) follows as usual.
+// canonical swizzled layouts the MMA descriptors expect.
+//
+// What happens to the gradients (FusedParams):
+//   * wparams set, world 1      : w -= lr*g in place (red.global.add.v4.f32); a launch loops over several steps
+//   * wparams null              : gradients are stored in the flat layout; a separate all-reduce+SGD kernel follows
+//   * red_ctas > 0 (world > 1)  : persistent data-parallel launch - this cluster computes, the other CTAs of the grid
+//                                 run the one-shot all-reduce + average + SGD over peer memory (fused_reducer_loop)
+//   * world > 1, red_ctas == 0  : gradient exchange inside the cluster (bulk-copy push, rank-ordered reduce): opt-in
 //
 // Reference math: DSML/client/client.go:112-202 (forward, softmax-CE, backward).
 // Supported shapes: batch <= 64 (multiple of 8), in0 % 8 == 0 and <= 832, H1 = 128, H2 in {64, none},
@@ -30,6 +36,7 @@
 #include <stdlib.h>
 #include <string.h>
 
+#include <memory>
 #include <new>
 
 namespace dmlp {
@@ -1149,13 +1156,14 @@ extern "C" int dmlp_mlp_fused_plan_create(const dmlp_mlp_fused_desc_t* d, dmlp_m
   DMLP_REQUIRE(d && out, "dmlp_mlp_fused_plan_create: null argument");
   DMLP_REQUIRE(dmlp_mlp_fused_supported(d->num_layers, d->dims, d->batch),
                "fused step supports batch<=64 (x8), in<=832 (x8), hidden 128[,64], classes<=16");
-  FusedPlan* pl = new (std::nothrow) FusedPlan();
+  std::unique_ptr<FusedPlan> owner(new (std::nothrow) FusedPlan());  // freed on every early return below
+  FusedPlan* pl = owner.get();
   if (!pl) return set_error(DMLP_ERR_CUDA, "out of host memory");
   const int L = d->num_layers, in0 = d->dims[0], H1 = d->dims[1], H2 = L == 3 ? d->dims[2] : 0;
   const int SL = L == 3 ? H2 / 8 : H1 / 8;
   const float* P = d->params_dev;
   int rc = 0;
-#define MK(expr) do { rc = (expr); if (rc) { delete pl; return rc; } } while (0)
+#define MK(expr) do { rc = (expr); if (rc) return rc; } while (0)
   // X as K-major A (forward) and as MN-major A (layer-1 weight gradient)
   const int slots = d->x_slots > 1 ? d->x_slots : 1;
   DMLP_REQUIRE(slots == 1 || d->sgd_params_dev != nullptr, "multi-step launches need in-place SGD (sgd_params_dev)");
@@ -1219,7 +1227,7 @@ extern "C" int dmlp_mlp_fused_plan_create(const dmlp_mlp_fused_desc_t* d, dmlp_m
     const char* e = getenv("DMLP_FUSED_BULK");
     p.bulk_update = e ? atoi(e) : 0;  // measured: 22.3 us/step with bulk reduce-adds vs 21.3 with red.global (default)
   }
-  *out = reinterpret_cast<dmlp_mlp_fused_plan_t>(pl);
+  *out = reinterpret_cast<dmlp_mlp_fused_plan_t>(owner.release());
   return DMLP_OK;
 }
 
