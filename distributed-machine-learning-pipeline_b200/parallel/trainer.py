@@ -223,6 +223,21 @@ class Trainer:
         with open(path, "rb") as f:
             self.set_params(self.layout.from_reference_bytes(f.read()))
 
+    def save_checkpoint(self, path: str, epoch: int = 0, schedule: str = "constant", **extra) -> None:
+        """Weight blob in the reference layout + ``<path>.json`` (step counter, epoch, lr, schedule, shape)."""
+        from ..utils import checkpoint as ck
+        ck.write_checkpoint(path, self.layout.to_reference_bytes(self.get_params()), dims=self.cfg.dims,
+                            batch=self.cfg.batch, global_step=self.global_step, epoch=epoch, lr=self.cfg.lr,
+                            schedule=schedule, world=self.world, extra=extra or None)
+
+    def load_checkpoint(self, path: str) -> dict:
+        """Restores weights and the step counter (LR schedules are functions of it); returns the sidecar dict."""
+        from ..utils import checkpoint as ck
+        blob, meta = ck.read_checkpoint(path, expect_dims=self.cfg.dims)
+        self.set_params(self.layout.from_reference_bytes(blob))
+        self.global_step = int(meta.get("global_step", self.global_step))
+        return meta
+
     def set_lr(self, lr: float) -> None:
         native.check(self.lib.dmlp_trainer_set_lr(self._h, float(lr)))
 

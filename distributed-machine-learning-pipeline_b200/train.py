@@ -27,6 +27,8 @@ def main(argv=None) -> int:
     ap = argparse.ArgumentParser(description=__doc__)
     Config.add_arguments(ap)
     ap.add_argument("--steps-per-epoch", type=int, default=0)
+    ap.add_argument("--checkpoint", default="", help="write <path> (reference weight blob) + <path>.json after every epoch")
+    ap.add_argument("--resume", default="", help="checkpoint to continue from (weights, step counter, epoch)")
     cfg = Config.from_args(ap.parse_args(argv))
     ns = ap.parse_args(argv)
     setup_logging()
@@ -60,18 +62,26 @@ def main(argv=None) -> int:
     trainer = Trainer(tcfg, device=local, process_group=world > 1)
     if cfg.weights_in:
         trainer.load_weights(cfg.weights_in)
+    first_epoch = 1
+    if ns.resume:
+        meta = trainer.load_checkpoint(ns.resume)  # every rank reads the same file: replicas start identical
+        first_epoch = int(meta.get("epoch", 0)) + 1
+        if rank == 0:
+            log.info("resumed from %s: epoch %d, step %d", ns.resume, first_epoch - 1, trainer.global_step)
     px, py = pin(xtr), pin(ytr)
     spe = ns.steps_per_epoch or xtr.shape[0] // (cfg.batch * world)
     sched = S.make(cfg.schedule, cfg.lr, total_steps=spe * cfg.epochs)
     mw = MetricsWriter(cfg.metrics_jsonl if rank == 0 else None)
     if rank == 0:
         log.info("Starting MLP training...")
-    for ep in range(1, cfg.epochs + 1):
+    for ep in range(first_epoch, cfg.epochs + 1):
         st = trainer.fit(px, py, spe, lr_schedule=sched, device_timing=True)
         if rank == 0:
             log.info("Epoch %d complete: Avg Loss: %.4f, Accuracy: %.2f%%", ep, st["loss"], 100 * st["accuracy"])
             mw.write("epoch", epoch=ep, loss=st["loss"], accuracy=st["accuracy"], steps=spe,
                      device_ms_per_step=st["device_ms"] / spe, samples_per_s=spe * cfg.batch * world / (st["device_ms"] / 1e3))
+            if ns.checkpoint:
+                trainer.save_checkpoint(ns.checkpoint, epoch=ep, schedule=cfg.schedule)
     if rank == 0:
         log.info("Training complete.")
     ev = trainer.evaluate(xte, yte)

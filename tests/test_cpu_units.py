@@ -125,3 +125,31 @@ def test_schedules():
     w = schedule.warmup(schedule.constant(1.0), 4)
     assert w(0) == 0.25 and w(3) == 1.0 and w(10) == 1.0
     assert schedule.make("warmup-cosine", 0.1, 100)(0) < 0.1
+
+
+def test_checkpoint_sidecar_roundtrip(tmp_path):
+    """Checkpoint = reference weight blob + JSON sidecar (step counter, epoch, schedule, shape); SURVEY 5.4."""
+    import numpy as np
+    from dmlp_b200.models.layout import ParamLayout
+    from dmlp_b200.utils import checkpoint as ck
+    lay = ParamLayout((784, 128, 64, 10))
+    flat = lay.init_reference(3)
+    blob = lay.to_reference_bytes(flat)
+    path = str(tmp_path / "w.bin")
+    ck.write_checkpoint(path, blob, dims=(784, 128, 64, 10), batch=64, global_step=1874, epoch=2, lr=0.01,
+                        schedule="cosine", world=8)
+    got, meta = ck.read_checkpoint(path, expect_dims=(784, 128, 64, 10))
+    assert got == blob and meta["global_step"] == 1874 and meta["epoch"] == 2 and meta["schedule"] == "cosine"
+    assert np.array_equal(lay.from_reference_bytes(got), lay.from_reference_bytes(blob))
+    import pytest
+    with pytest.raises(ValueError):
+        ck.read_checkpoint(path, expect_dims=(784, 128, 10))
+    # a bare blob (what the reference client would produce) loads with empty metadata
+    bare = str(tmp_path / "bare.bin")
+    open(bare, "wb").write(blob)
+    got2, meta2 = ck.read_checkpoint(bare)
+    assert got2 == blob and meta2 == {}
+    # truncated blob against its sidecar is refused
+    open(path, "wb").write(blob[:-4])
+    with pytest.raises(ValueError):
+        ck.read_checkpoint(path)

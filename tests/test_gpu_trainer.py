@@ -90,6 +90,25 @@ def test_checkpoint_roundtrip_reference_layout(tmp_path):
     t.close()
 
 
+def test_resume_from_checkpoint_continues_identically(tmp_path):
+    """weights + step counter from the sidecar: a resumed run follows the uninterrupted one bit for bit."""
+    from dmlp_b200.parallel import schedule
+    sched = schedule.warmup(schedule.cosine(0.05, 40), 3)
+    a, x, y = _setup()
+    a.fit(x, y, 8, lr_schedule=sched)
+    path = os.path.join(tmp_path, "ck.bin")
+    a.save_checkpoint(path, epoch=1, schedule="cosine")
+    b, _, _ = _setup()
+    meta = b.load_checkpoint(path)
+    assert meta["global_step"] == 8 and meta["epoch"] == 1 and b.global_step == a.global_step == 8
+    assert np.array_equal(a.get_params(), b.get_params())
+    a.fit(x, y, 8, first_batch=8, lr_schedule=sched)
+    b.fit(x, y, 8, first_batch=8, lr_schedule=sched)
+    assert np.array_equal(a.get_params(), b.get_params())
+    a.close()
+    b.close()
+
+
 def test_wide_shape_smoke_bf16():
     """Scaled-down wide model (same code path as 784-8192-8192-10): multi-tile GEMMs, bf16 shadow."""
     from dmlp_b200.models import oracle
