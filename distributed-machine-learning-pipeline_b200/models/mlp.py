@@ -10,7 +10,6 @@ from __future__ import annotations
 
 from typing import Callable, List, Optional, Sequence
 
-import numpy as np
 import torch
 from torch import nn
 

@@ -15,7 +15,7 @@ from __future__ import annotations
 import ctypes as C
 import logging
 import time
-from dataclasses import dataclass, field
+from dataclasses import dataclass
 from typing import Dict, List, Optional, Sequence, Tuple
 
 import numpy as np

@@ -16,7 +16,7 @@ import os
 import socket
 import tempfile
 import time
-from typing import Dict, List, Optional, Sequence
+from typing import Dict, Optional, Sequence
 
 from . import native
 from .comm import ArenaAllocator

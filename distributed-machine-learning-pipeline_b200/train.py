@@ -14,8 +14,6 @@ import logging
 import os
 import sys
 
-import numpy as np
-
 from .utils import data as D
 from .utils.config import Config
 from .utils.metrics import MetricsWriter, setup_logging

@@ -1,6 +1,5 @@
 """Per-tile timeline of CTA 0 of the persistent GEMM kernel (DMLP_GEMM_PROF=1)."""
 import ctypes as C
-import json
 import os
 import sys
 

@@ -1,7 +1,5 @@
 """CPU-only unit tests: layout/checkpoint, oracle identities, data readers, schedules."""
-import gzip
 import os
-import struct
 
 import numpy as np
 import pytest

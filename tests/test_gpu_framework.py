@@ -1,5 +1,4 @@
 """PyTorch framework layer (autograd functions / MLP module / DataParallel) vs torch autograd."""
-import numpy as np
 import pytest
 import torch
 
