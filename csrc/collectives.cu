@@ -600,8 +600,7 @@ static int launch_coll(K kern, const CollArgs& args, int blocks, int world_y, cu
   } else {
     // Programmatic stream serialization: the kernel may be scheduled while its predecessor drains; it
     // executes griddepcontrol.wait before touching any data.
-    cudaLaunchConfig_t cfg;
-    memset(&cfg, 0, sizeof(cfg));
+    cudaLaunchConfig_t cfg = {};
     cfg.gridDim = grid;
     cfg.blockDim = dim3(kCollThreads);
     cfg.stream = st;

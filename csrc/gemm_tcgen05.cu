@@ -711,8 +711,7 @@ static int launch_gemm(const CUtensorMap& tmA, const CUtensorMap& tmB, const Gem
     attr_mask |= 1ull << dev;
   }
   if (p.pdl || TWO) {
-    cudaLaunchConfig_t cfg;
-    memset(&cfg, 0, sizeof(cfg));
+    cudaLaunchConfig_t cfg = {};
     cfg.gridDim = grid;
     cfg.blockDim = dim3(kGemmThreads);
     cfg.dynamicSmemBytes = smem_bytes;

@@ -1246,8 +1246,7 @@ static int launch_fused(const FusedPlan* pl, const FusedParams& prm, cudaStream_
     DMLP_CUDA_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, kFusedSmem));
     attr_mask |= 1ull << dev;
   }
-  cudaLaunchConfig_t cfg;
-  memset(&cfg, 0, sizeof(cfg));
+  cudaLaunchConfig_t cfg = {};
   cfg.gridDim = dim3(kFC + (prm.red_ctas > 0 ? prm.red_ctas : 0));
   cfg.blockDim = dim3(kFThreads);
   cfg.dynamicSmemBytes = kFusedSmem;

@@ -495,8 +495,7 @@ extern "C" int dmlp_allreduce_nvls(dmlp_comm_t comm, int local_idx, const dmlp_n
   DeviceGuard guard(dev);
   {
     // Programmatic stream serialization: may be scheduled while its predecessor drains (griddepcontrol.wait inside)
-    cudaLaunchConfig_t cfg;
-    memset(&cfg, 0, sizeof(cfg));
+    cudaLaunchConfig_t cfg = {};
     cfg.gridDim = dim3(blocks);
     cfg.blockDim = dim3(kNvlsThreads);
     cfg.stream = as_stream(stream);

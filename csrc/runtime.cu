@@ -29,7 +29,7 @@ extern "C" int dmlp_device_info(int dev, dmlp_device_info_t* out) {
   cudaDeviceProp p;
   DMLP_CUDA_CHECK(cudaGetDeviceProperties(&p, dev));
   memset(out, 0, sizeof(*out));
-  strncpy(out->name, p.name, sizeof(out->name) - 1);
+  snprintf(out->name, sizeof(out->name), "%s", p.name);  // (truncates a longer name, always terminated)
   const unsigned char* u = reinterpret_cast<const unsigned char*>(p.uuid.bytes);
   snprintf(out->uuid, sizeof(out->uuid),
            "GPU-%02x%02x%02x%02x-%02x%02x-%02x%02x-%02x%02x-%02x%02x%02x%02x%02x%02x", u[0], u[1],
