@@ -44,8 +44,10 @@ def main():
             rows.append((fname, 0, "(kernel not found)"))
             continue
         body = [l for l in funcs[name] if re.search(r"/\*[0-9a-f]{4,}\*/", l)]
+        # keep the instruction lines only, without the 128-bit encodings (the listings are evidence, not input)
+        lean = [re.sub(r"\s*/\* 0x[0-9a-f]{16} \*/\s*$", "", l).rstrip() for l in body]
         with open(os.path.join(OUT, fname), "w") as f:
-            f.write(f"// {name}\n" + "\n".join(funcs[name]) + "\n")
+            f.write(f"// {name}\n" + "\n".join(lean) + "\n")
         census = collections.Counter()
         for l in body:
             for op in NOTABLE:
