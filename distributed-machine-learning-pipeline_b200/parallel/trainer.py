@@ -28,6 +28,16 @@ from . import schedule as sched
 log = logging.getLogger("dmlp.trainer")
 
 
+def shard_schedule(global_step: int, rank: int, world: int, batch_stride: Optional[int] = None) -> Tuple[int, int]:
+    """(first batch, stride) of a rank at ``global_step``: step s of rank r consumes batch ``(global_step + s) * world + r``
+    of the shared host dataset, i.e. the ranks split every group of ``world`` consecutive batches (sequential, no
+    shuffle, like the reference's single stream of batches, client.go:596-647). ``batch_stride`` overrides the stride
+    for rank-private datasets that are walked densely (then every rank starts at ``global_step * stride``)."""
+    if batch_stride is None:
+        return global_step * world + rank, world
+    return global_step * int(batch_stride), int(batch_stride)
+
+
 class _NativeCfg(C.Structure):
     _fields_ = [("num_layers", C.c_int), ("dims", C.c_int * 9), ("batch", C.c_int), ("dtype", C.c_int),
                 ("lr", C.c_float), ("allreduce_algo", C.c_int), ("overlap", C.c_int),
@@ -279,8 +289,9 @@ class Trainer:
         nb = n // self.cfg.batch
         if nb == 0:
             raise ValueError("dataset smaller than one batch")
-        stride = self.world if batch_stride is None else int(batch_stride)
-        first = self.global_step * stride + (self.rank if batch_stride is None else 0) if first_batch is None else first_batch
+        first, stride = shard_schedule(self.global_step, self.rank, self.world, batch_stride)
+        if first_batch is not None:
+            first = first_batch
         lrs = None
         if lr_schedule is not None:
             lrs = np.array([lr_schedule(self.global_step + s) for s in range(steps)], dtype=np.float32)

@@ -13,13 +13,11 @@ from __future__ import annotations
 
 import ctypes as C
 import os
-import socket
-import tempfile
-import time
 from typing import Dict, Optional, Sequence
 
 from . import native
 from .comm import ArenaAllocator
+from .fdpass import broadcast_fd
 
 
 class NvlsUnavailable(RuntimeError):
@@ -108,44 +106,19 @@ class NvlsArena:
         if not all(flags):
             raise NvlsUnavailable("a rank's device does not support multicast")
         h = C.c_void_p()
-        status = "ok"
-        path = [None]
-        srv = None
+        fd, err = C.c_int(-1), None
         if rank == 0:
-            fd = C.c_int(-1)
-            rc = lib.dmlp_nvls_create(world, nbytes, C.byref(fd), C.byref(h))
-            if rc != 0:
-                status = native.lib().dmlp_last_error().decode()
-            else:
-                path[0] = os.path.join(tempfile.gettempdir(), f"dmlp_nvls_{os.getpid()}_{int(time.time() * 1e6)}.sock")
-                srv = socket.socket(socket.AF_UNIX, socket.SOCK_STREAM)
-                srv.bind(path[0])
-                srv.listen(world)
-        box = [status, path[0]]
-        dist.broadcast_object_list(box, src=0, group=group)
-        if box[0] != "ok":
-            raise NvlsUnavailable(box[0])
-        if rank == 0:
-            for _ in range(world - 1):
-                conn, _ = srv.accept()
-                socket.send_fds(conn, [b"mc"], [fd.value])
-                conn.recv(1)  # peer has imported; safe to move on
-                conn.close()
-            srv.close()
-            os.unlink(box[1])
-        else:
-            c = socket.socket(socket.AF_UNIX, socket.SOCK_STREAM)
-            for _ in range(200):
-                try:
-                    c.connect(box[1])
-                    break
-                except (FileNotFoundError, ConnectionRefusedError):
-                    time.sleep(0.01)
-            _, fds, _, _ = socket.recv_fds(c, 16, 1)
-            _check(lib.dmlp_nvls_import(world, nbytes, fds[0], C.byref(h)))
-            os.close(fds[0])
-            c.send(b"k")
-            c.close()
+            if lib.dmlp_nvls_create(world, nbytes, C.byref(fd), C.byref(h)) != 0:
+                err = native.lib().dmlp_last_error().decode()
+        try:
+            got = broadcast_fd(fd.value if rank == 0 else None, group=group, tag="dmlp_nvls", error=err)
+        except RuntimeError as e:
+            raise NvlsUnavailable(str(e)) from None
+        if rank != 0:
+            try:
+                _check(lib.dmlp_nvls_import(world, nbytes, got, C.byref(h)))
+            finally:
+                os.close(got)
         _check(lib.dmlp_nvls_add_device(h, device))
         dist.barrier(group=group)  # every device is part of the object before anyone binds
         u, m = C.c_void_p(), C.c_void_p()
