@@ -34,6 +34,7 @@ class DeviceBackend:
         self.min_addr = MIN_ADDR
         self.max_addr = MIN_ADDR + int(mem_size)
         self.dead = False  # fault injection: a dead device stops answering (services check this)
+        self.model_dims = None  # RunForward/RunBackward: model shape; None = inferred from the weight blob's size
 
     def check_addr(self, addr: int) -> None:
         if addr < self.min_addr or addr >= self.max_addr:
@@ -99,6 +100,19 @@ class SimBackend(DeviceBackend):
             buf = self._mem.setdefault(addr, bytearray())
             if len(buf) < nbytes:
                 buf.extend(b"\x00" * (nbytes - len(buf)))
+
+    # -- RunForward / RunBackward (services/compute.py): NumPy oracle ------------------------
+    def _compute(self):
+        if getattr(self, "_oracle", None) is None:
+            from .compute import OracleCompute
+            self._oracle = OracleCompute(self)
+        return self._oracle
+
+    def run_forward(self, input_addr: int, output_addr: int) -> None:
+        self._compute().run_forward(input_addr, output_addr)
+
+    def run_backward(self, gradient_addr: int) -> None:
+        self._compute().run_backward(gradient_addr)
 
 
 def make_backend(kind: str, device_id: int, mem_size: int, cuda_ordinal: Optional[int] = None) -> DeviceBackend:

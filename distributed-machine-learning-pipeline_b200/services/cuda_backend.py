@@ -160,6 +160,79 @@ class CudaBackend(DeviceBackend):
 
         return poll
 
+    # ------------------------------------------------------------------ RunForward / RunBackward
+    # (semantics: services/compute.py). Everything stays on the device: the weight blob, the batch and the result
+    # buffers are wrapped as torch tensors over the backend's allocations, the math runs on the tcgen05 layer
+    # (models.MLP: fused bias+ReLU GEMMs, softmax-CE in the last GEMM's epilogue, dgrad / wgrad GEMMs).
+    def _tensor(self, addr: int, n_floats: int):
+        from ..parallel.data_parallel import arena_tensor
+        return arena_tensor(self.pointer(addr), n_floats, self.ordinal)
+
+    def _model(self):
+        import torch
+        from ..models.mlp import MLP
+        from .compute import WEIGHT_ADDR, infer_dims
+        nbytes = self.size(WEIGHT_ADDR)
+        dims = infer_dims(nbytes, self.model_dims)
+        mlp = getattr(self, "_mlp", None)
+        if mlp is None or mlp.dims != dims:
+            mlp = self._mlp = MLP(dims, device=f"cuda:{self.ordinal}")
+        src = self._tensor(WEIGHT_ADDR, nbytes // 4)
+        cur = 0
+        with torch.no_grad():  # W1|b1|W2|b2|... (unpadded) -> the padded flat layout the kernels use
+            for sl, w, b in zip(mlp.layout.layers, mlp.weights, mlp.biases):
+                w[:, :sl.fan_out].copy_(src[cur:cur + sl.fan_in * sl.fan_out].view(sl.fan_in, sl.fan_out))
+                cur += sl.fan_in * sl.fan_out
+                b[:sl.fan_out].copy_(src[cur:cur + sl.fan_out])
+                cur += sl.fan_out
+        return mlp
+
+    def run_forward(self, input_addr: int, output_addr: int) -> None:
+        import torch
+        from .compute import batch_of
+        with self._lock, torch.cuda.device(self.ordinal):
+            mlp = self._model()
+            in0, classes = mlp.dims[0], mlp.dims[-1]
+            B = batch_of(self.size(input_addr), in0)
+            x = self._tensor(input_addr, B * in0).view(B, in0)
+            with torch.no_grad():
+                logits = mlp(x)[:, :classes]
+            self.check_addr(output_addr)
+            self._reserve(output_addr, B * classes * 4, keep=False)
+            self._bufs[output_addr] = (self._bufs[output_addr][0], B * classes * 4, self._bufs[output_addr][2])
+            self._tensor(output_addr, B * classes).view(B, classes).copy_(logits)
+            torch.cuda.synchronize()
+            self._last_input = input_addr
+
+    def run_backward(self, gradient_addr: int) -> None:
+        import torch
+        from .compute import LABEL_ADDR, batch_of, labels_from_bytes
+        with self._lock, torch.cuda.device(self.ordinal):
+            if getattr(self, "_last_input", None) is None:
+                raise ValueError("RunBackward needs a preceding RunForward")
+            mlp = self._model()
+            in0, classes = mlp.dims[0], mlp.dims[-1]
+            B = batch_of(self.size(self._last_input), in0)
+            x = self._tensor(self._last_input, B * in0).view(B, in0)
+            y = torch.from_numpy(labels_from_bytes(self.read(LABEL_ADDR), B, classes)).to(x.device)
+            mlp.flat_grad.zero_()
+            loss, _ = mlp.loss(x, y)
+            loss.backward()
+            lay = mlp.layout
+            self.check_addr(gradient_addr)
+            nbytes = lay.reference_count * 4
+            self._reserve(gradient_addr, nbytes, keep=False)
+            self._bufs[gradient_addr] = (self._bufs[gradient_addr][0], nbytes, self._bufs[gradient_addr][2])
+            dst = self._tensor(gradient_addr, lay.reference_count)
+            cur = 0
+            for sl in lay.layers:  # padded flat gradients -> the client's blob order
+                gw = mlp.flat_grad[sl.w_off:sl.w_off + sl.fan_in * sl.out_pad].view(sl.fan_in, sl.out_pad)[:, :sl.fan_out]
+                dst[cur:cur + sl.fan_in * sl.fan_out].view(sl.fan_in, sl.fan_out).copy_(gw)
+                cur += sl.fan_in * sl.fan_out
+                dst[cur:cur + sl.fan_out].copy_(mlp.flat_grad[sl.b_off:sl.b_off + sl.fan_out])
+                cur += sl.fan_out
+            torch.cuda.synchronize()
+
     def close(self) -> None:
         with self._lock:
             for ptr, _, _ in self._bufs.values():

@@ -209,18 +209,32 @@ class GPUDeviceService:
             return pb.MemcpyResponse(deviceToHost=pb.MemcpyDeviceToHostResponse(dstData=data))
         context.abort(grpc.StatusCode.INVALID_ARGUMENT, "Invalid Memcpy request: specify hostToDevice or deviceToHost")
 
-    # The reference's stale stubs declare these; here they run the MLP on the device when the
-    # backend provides compute hooks, else answer UNIMPLEMENTED like the reference.
+    # The reference's stale stubs declare these and no server implements them. Here they run the MLP on the
+    # device that holds the buffers (semantics: services/compute.py); a backend without compute hooks
+    # answers UNIMPLEMENTED like the reference.
     def RunForward(self, request, context):
         hook = getattr(self.backend, "run_forward", None)
         if hook is None:
             context.abort(grpc.StatusCode.UNIMPLEMENTED, "method RunForward not implemented")
-        hook(request.inputAddr, request.outputAddr)
+        self._guard_alive(context)
+        self._run_compute(context, "RunForward", hook, request.inputAddr, request.outputAddr)
         return pb.RunForwardResponse(success=True)
 
     def RunBackward(self, request, context):
         hook = getattr(self.backend, "run_backward", None)
         if hook is None:
             context.abort(grpc.StatusCode.UNIMPLEMENTED, "method RunBackward not implemented")
-        hook(request.gradientAddr)
+        self._guard_alive(context)
+        self._run_compute(context, "RunBackward", hook, request.gradientAddr)
         return pb.RunBackwardResponse(success=True)
+
+    @staticmethod
+    def _run_compute(context, what, hook, *addrs) -> None:
+        """Same status codes as Memcpy: address outside the device range / malformed buffers -> InvalidArgument,
+        a buffer that was never written -> Internal."""
+        try:
+            hook(*addrs)
+        except (AddressError, ValueError) as e:
+            context.abort(grpc.StatusCode.INVALID_ARGUMENT, f"{what}: {e}")
+        except MissingBufferError as e:
+            context.abort(grpc.StatusCode.INTERNAL, f"{what}: {e}")

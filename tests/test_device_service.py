@@ -113,7 +113,67 @@ def test_payload_free_stream_send_is_a_device_to_device_copy():
     assert b.backend.read(0x2000) == b"012345"
 
 
-def test_run_forward_is_unimplemented_on_sim_like_the_reference_stub():
+def test_backend_without_compute_hooks_answers_unimplemented_like_the_reference_stub():
+    from dmlp_b200.services.backend import DeviceBackend
+
+    class Bare(DeviceBackend):
+        kind = "bare"
+
     with pytest.raises(RpcAbort) as e:
-        make().RunForward(pb.RunForwardRequest(deviceId=1), FakeContext())
+        GPUDeviceService(Bare(1, 1 << 20)).RunForward(pb.RunForwardRequest(deviceId=1), FakeContext())
     assert e.value.code == grpc.StatusCode.UNIMPLEMENTED
+
+
+@pytest.mark.parametrize("dims,onehot", [((784, 128, 10), True), ((784, 128, 64, 10), False)])
+def test_run_forward_and_backward_compute_on_the_device(dims, onehot):
+    """RunForward / RunBackward (stale stub RPCs of the reference) with the client's memory map: weights blob at
+    0x2000, data at 0x3000, labels at 0x4000, gradients to 0x1000 (services/compute.py)."""
+    import numpy as np
+    from dmlp_b200.models import oracle
+    from dmlp_b200.models.layout import ParamLayout
+    from dmlp_b200.utils.data import synthetic_mnist
+    svc = make(mem=1 << 20)
+    ctx = FakeContext()
+    lay = ParamLayout(dims)
+    flat = lay.init_reference(11)
+    x, y = synthetic_mnist(24, seed=4)
+
+    def h2d(addr, data):
+        svc.Memcpy(pb.MemcpyRequest(hostToDevice=pb.MemcpyHostToDeviceRequest(
+            hostSrcData=data, dstDeviceId=pb.DeviceId(value=1001), dstMemAddr=pb.MemAddr(value=addr))), ctx)
+
+    def d2h(addr):
+        return svc.Memcpy(pb.MemcpyRequest(deviceToHost=pb.MemcpyDeviceToHostRequest(
+            srcDeviceId=pb.DeviceId(value=1001), srcMemAddr=pb.MemAddr(value=addr))), ctx).deviceToHost.dstData
+
+    h2d(0x2000, lay.to_reference_bytes(flat))
+    h2d(0x3000, x.astype("<f4").tobytes())
+    h2d(0x4000, np.eye(10, dtype="<f4")[y].tobytes() if onehot else y.astype("<i4").tobytes())
+    assert svc.RunForward(pb.RunForwardRequest(deviceId=1001, inputAddr=0x3000, outputAddr=0x5000), ctx).success
+    params = [(w.astype(np.float64), b.astype(np.float64)) for w, b in lay.views(flat)]
+    logits, _ = oracle.forward(params, x.astype(np.float64))
+    got = np.frombuffer(d2h(0x5000), "<f4").reshape(24, 10)
+    assert np.abs(got - logits).max() < 1e-5
+    assert svc.RunBackward(pb.RunBackwardRequest(deviceId=1001, gradientAddr=0x1000), ctx).success
+    _, _, grads = oracle.loss_and_grads(params, x.astype(np.float64), y)
+    blob = d2h(0x1000)
+    assert len(blob) == lay.reference_count * 4  # same size as the weight blob: ready for AllReduceRing
+    gflat = lay.from_reference_bytes(blob)
+    for (gw, gb), (rw, rb) in zip(lay.views(gflat), grads):
+        assert np.abs(gw - rw).max() < 1e-6 and np.abs(gb - rb).max() < 1e-6
+
+
+def test_run_forward_error_codes():
+    svc = make(mem=1 << 20)
+    ctx = FakeContext()
+    with pytest.raises(RpcAbort) as e:  # no weights yet
+        svc.RunForward(pb.RunForwardRequest(deviceId=1001, inputAddr=0x3000, outputAddr=0x5000), ctx)
+    assert e.value.code == grpc.StatusCode.INTERNAL
+    svc.backend.write(0x2000, b"\x00" * 100)  # not a known model shape
+    svc.backend.write(0x3000, b"\x00" * 784 * 4)
+    with pytest.raises(RpcAbort) as e:
+        svc.RunForward(pb.RunForwardRequest(deviceId=1001, inputAddr=0x3000, outputAddr=0x5000), ctx)
+    assert e.value.code == grpc.StatusCode.INVALID_ARGUMENT
+    with pytest.raises(RpcAbort) as e:  # backward before any forward
+        svc.RunBackward(pb.RunBackwardRequest(deviceId=1001, gradientAddr=0x1000), ctx)
+    assert e.value.code == grpc.StatusCode.INVALID_ARGUMENT

@@ -143,3 +143,53 @@ def test_gpu_failure_mid_allreduce_is_surfaced(cuda_cluster):
     with pytest.raises(grpc.RpcError) as e:
         client.AllReduceRing(pb.AllReduceRingRequest(commId=init.commId, count=16384))
     assert e.value.code() == grpc.StatusCode.FAILED_PRECONDITION
+
+
+@pytest.mark.parametrize("dims", [(784, 128, 10), (784, 128, 64, 10)])
+def test_run_forward_backward_on_the_gpu_match_the_oracle(dims):
+    """RunForward / RunBackward (the reference's never-implemented device RPCs) on ``backend=cuda``: buffers stay in
+    GPU memory, the math runs on the tcgen05 layer; logits and the gradient blob match the fp64 oracle."""
+    from dmlp_b200.models import oracle
+    from dmlp_b200.models.layout import ParamLayout
+    from dmlp_b200.proto import gpu_sim as pb
+    from dmlp_b200.services.backend import make_backend
+    from dmlp_b200.services.device import GPUDeviceService
+    from dmlp_b200.services.testing import FakeContext
+    from dmlp_b200.utils.data import synthetic_mnist
+    backend = make_backend("cuda", 7, 1 << 20, 0)
+    svc, ctx = GPUDeviceService(backend), FakeContext()
+    try:
+        lay = ParamLayout(dims)
+        flat = lay.init_reference(11)
+        B = 40
+        x, y = synthetic_mnist(B, seed=4)
+
+        def h2d(addr, data):
+            svc.Memcpy(pb.MemcpyRequest(hostToDevice=pb.MemcpyHostToDeviceRequest(
+                hostSrcData=data, dstDeviceId=pb.DeviceId(value=7), dstMemAddr=pb.MemAddr(value=addr))), ctx)
+
+        def d2h(addr):
+            return svc.Memcpy(pb.MemcpyRequest(deviceToHost=pb.MemcpyDeviceToHostRequest(
+                srcDeviceId=pb.DeviceId(value=7), srcMemAddr=pb.MemAddr(value=addr))), ctx).deviceToHost.dstData
+
+        h2d(0x2000, lay.to_reference_bytes(flat))
+        h2d(0x3000, x.astype("<f4").tobytes())
+        h2d(0x4000, np.eye(10, dtype="<f4")[y].tobytes())
+        assert svc.RunForward(pb.RunForwardRequest(deviceId=7, inputAddr=0x3000, outputAddr=0x5000), ctx).success
+        params = [(w.astype(np.float64), b.astype(np.float64)) for w, b in lay.views(flat)]
+        logits, _ = oracle.forward(params, x.astype(np.float64))
+        got = np.frombuffer(d2h(0x5000), "<f4").reshape(B, 10)
+        assert np.abs(got - logits).max() < 5e-3 * max(1.0, np.abs(logits).max())  # tf32 operands
+        assert svc.RunBackward(pb.RunBackwardRequest(deviceId=7, gradientAddr=0x1000), ctx).success
+        _, _, grads = oracle.loss_and_grads(params, x.astype(np.float64), y)
+        blob = d2h(0x1000)
+        assert len(blob) == lay.reference_count * 4
+        for (gw, gb), (rw, rb) in zip(lay.views(lay.from_reference_bytes(blob)), grads):
+            assert np.abs(gw - rw).max() < 2e-2 * max(1e-3, np.abs(rw).max())
+            assert np.abs(gb - rb).max() < 2e-2 * max(1e-3, np.abs(rb).max())
+        # weights updated through Memcpy are picked up by the next call (no stale copy on the device side)
+        h2d(0x2000, lay.to_reference_bytes(np.zeros_like(flat)))
+        assert svc.RunForward(pb.RunForwardRequest(deviceId=7, inputAddr=0x3000, outputAddr=0x5000), ctx).success
+        assert np.abs(np.frombuffer(d2h(0x5000), "<f4")).max() == 0.0
+    finally:
+        backend.close()
