@@ -403,7 +403,7 @@ class GPUCoordinatorService:
             if comm.native is not None and len(comm.native.local_devs) == n:
                 self._allreduce_native(comm, devices, addrs, count, dtype, op, algo, md)
             else:
-                self._allreduce_portable(comm, devices, addrs, count, dtype, op)
+                self._allreduce_portable(comm, devices, addrs, count, dtype, op, md)
 
         if grouped:
             with comm.mu:
@@ -480,7 +480,7 @@ class GPUCoordinatorService:
                 raise RuntimeError(f"rank {dst.rank}: stream failed")
             time.sleep(0.001)
 
-    def _allreduce_portable(self, comm, devices, addrs, count, dtype, op) -> None:
+    def _allreduce_portable(self, comm, devices, addrs, count, dtype, op, md=None) -> None:
         n = len(devices)
         np_dt = _NP_DTYPES[dtype]
         if np_dt is None:
@@ -501,6 +501,15 @@ class GPUCoordinatorService:
             have = min(len(raw) // esz, nelem)
             arr[:have] = np.frombuffer(raw[:have * esz], dtype=np_dt)
             bufs.append(arr)
+        sgd = bool(md) and "dmlp-sgd-lr" in md
+        weights = []
+        if sgd:
+            # The ring below receives into RECV_ADDR (0x2000) on every device like the reference (:427-516), which is
+            # also where the weights live: take them out first.
+            if dtype != "f32":
+                raise ValueError("dmlp-sgd-lr needs f32 gradients")
+            waddr = int(md.get("dmlp-sgd-weights", hex(RECV_ADDR)), 0)
+            weights = [self._dev_read(d, waddr) for d in devices]
         seg = -(-nelem // n)
         red = _NP_OPS[op]
         bounds = [(min(s * seg, nelem), min((s + 1) * seg, nelem)) for s in range(n)]
@@ -527,6 +536,16 @@ class GPUCoordinatorService:
             for r, (s, data) in staged.items():
                 lo, hi = bounds[s]
                 bufs[r][lo:hi] = data
+        if sgd:
+            # same contract as the native path's fused kernel: the gradients stay as they are, the weights at
+            # dmlp-sgd-weights become w - lr * mean(g) on every device
+            lr = float(md["dmlp-sgd-lr"])
+            for d, arr, raw in zip(devices, bufs, weights):
+                w = np.zeros(max(nelem, len(raw) // 4), dtype=np.float32)
+                w[:len(raw) // 4] = np.frombuffer(raw[:len(raw) // 4 * 4], dtype="<f4")
+                w[:nelem] -= np.float32(lr / n) * arr
+                self._dev_write(d, waddr, w.tobytes())
+            return
         for d, arr, tail in zip(devices, bufs, tails):
             self._dev_write(d, addrs[d.rank], arr.tobytes() + tail)
 

@@ -251,3 +251,29 @@ def test_concurrent_rpcs_do_not_corrupt_state(cluster):
     [t.start() for t in ts]
     [t.join() for t in ts]
     assert not errors
+
+
+def test_grpc_client_trains_data_parallel_over_the_contract(cluster):
+    """The reference client's loop with every number produced on the devices: Memcpy shards, RunForward/RunBackward,
+    AllReduceRing with the fused average+SGD metadata. 3 sim devices; must equal the oracle's DP steps."""
+    from dmlp_b200.grpc_client import GrpcTrainer
+    from dmlp_b200.models import oracle
+    from dmlp_b200.models.layout import ParamLayout
+    from dmlp_b200.utils.data import synthetic_mnist
+    dims, batch, lr, steps, n = (784, 128, 64, 10), 16, 0.1, 3, 3
+    _, devs, coord = cluster(n, mem_size=1 << 20)
+    t = GrpcTrainer(coord.addr, [d.addr for d in devs], dims=dims, batch=batch, lr=lr, seed=5)
+    x, y = synthetic_mnist(batch * n * steps, seed=2)
+    lay = ParamLayout(dims)
+    ref = [(w.astype(np.float64), b.astype(np.float64)) for w, b in lay.views(lay.init_reference(5))]
+    stats = t.fit(x, y, steps)
+    for s in range(steps):
+        shards = [(x[(s * n + d) * batch:(s * n + d + 1) * batch].astype(np.float64),
+                   y[(s * n + d) * batch:(s * n + d + 1) * batch]) for d in range(n)]
+        ref, _, _ = oracle.dp_train_step(ref, shards, lr)
+    blobs = [t.weights_blob(d) for d in range(n)]
+    assert blobs[0] == blobs[1] == blobs[2], "replicas diverged"
+    for (w, b), (rw, rb) in zip(lay.views(lay.from_reference_bytes(blobs[0])), ref):
+        assert np.abs(w - rw).max() < 1e-5 and np.abs(b - rb).max() < 1e-5
+    assert all(np.isfinite(s["loss"]) for s in stats) and 0.0 <= stats[-1]["accuracy"] <= 1.0
+    t.close()

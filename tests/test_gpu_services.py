@@ -193,3 +193,30 @@ def test_run_forward_backward_on_the_gpu_match_the_oracle(dims):
         assert np.abs(np.frombuffer(d2h(0x5000), "<f4")).max() == 0.0
     finally:
         backend.close()
+
+
+def test_grpc_client_trains_on_cuda_devices(cuda_cluster):
+    """dmlp_b200.grpc_client against 3 logical devices in GPU memory: shards by Memcpy, RunForward/RunBackward on the
+    tcgen05 layer, AllReduceRing with the fused average+SGD kernel. Must follow the oracle's data-parallel steps."""
+    from dmlp_b200.grpc_client import GrpcTrainer
+    from dmlp_b200.models import oracle
+    from dmlp_b200.models.layout import ParamLayout
+    from dmlp_b200.utils.data import synthetic_mnist
+    dims, batch, lr, steps, n = (784, 128, 64, 10), 32, 0.1, 3, 3
+    _, devs, coord = cuda_cluster(n, mem_size=1 << 20)
+    t = GrpcTrainer(coord.addr, [d.addr for d in devs], dims=dims, batch=batch, lr=lr, seed=5)
+    assert coord.service.communicators[t.comm_id].native is not None
+    x, y = synthetic_mnist(batch * n * steps, seed=2)
+    lay = ParamLayout(dims)
+    ref = [(w.astype(np.float64), b.astype(np.float64)) for w, b in lay.views(lay.init_reference(5))]
+    stats = t.fit(x, y, steps)
+    for s in range(steps):
+        shards = [(x[(s * n + d) * batch:(s * n + d + 1) * batch].astype(np.float64),
+                   y[(s * n + d) * batch:(s * n + d + 1) * batch]) for d in range(n)]
+        ref, _, _ = oracle.dp_train_step(ref, shards, lr)
+    blobs = [t.weights_blob(d) for d in range(n)]
+    assert blobs[0] == blobs[1] == blobs[2], "replicas diverged"
+    for (w, b), (rw, rb) in zip(lay.views(lay.from_reference_bytes(blobs[0])), ref):
+        assert np.abs(w - rw).max() < 3e-3 and np.abs(b - rb).max() < 3e-3
+    assert all(np.isfinite(s["loss"]) for s in stats)
+    t.close()
