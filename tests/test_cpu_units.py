@@ -151,3 +151,43 @@ def test_checkpoint_sidecar_roundtrip(tmp_path):
     open(path, "wb").write(blob[:-4])
     with pytest.raises(ValueError):
         ck.read_checkpoint(path)
+
+
+def test_compute_helpers_shapes_and_labels():
+    """services/compute.py: model shape from the blob size, batch from the buffer size, both label encodings."""
+    import numpy as np
+    import pytest
+    from dmlp_b200.services import compute as cp
+    assert cp.infer_dims(407080) == (784, 128, 10)          # the reference's weight blob (client.go:204-218)
+    assert cp.infer_dims(437544) == (784, 128, 64, 10)      # the README's three-layer shape
+    assert cp.infer_dims(4 * (8 * 16 + 16 + 16 * 4 + 4), hint=(8, 16, 4)) == (8, 16, 4)
+    with pytest.raises(ValueError):
+        cp.infer_dims(1000)
+    assert cp.batch_of(64 * 784 * 4, 784) == 64
+    with pytest.raises(ValueError):
+        cp.batch_of(100, 784)
+    y = np.array([3, 0, 9, 1], dtype=np.int32)
+    assert np.array_equal(cp.labels_from_bytes(np.eye(10, dtype="<f4")[y].tobytes(), 4, 10), y)
+    assert np.array_equal(cp.labels_from_bytes(y.astype("<i4").tobytes(), 4, 10), y)
+    with pytest.raises(ValueError):
+        cp.labels_from_bytes(b"\x00" * 12, 4, 10)
+    with pytest.raises(ValueError):
+        cp.labels_from_bytes(np.array([0, 1, 2, 10], dtype="<i4").tobytes(), 4, 10)
+
+
+def test_grpc_client_cli_against_in_process_servers():
+    """`python -m dmlp_b200.grpc_client` main(): coordinator + 2 sim devices in this process, two short epochs."""
+    from dmlp_b200 import grpc_client
+    from dmlp_b200.services import server as srv
+    from dmlp_b200.services.backend import SimBackend
+    devs = [srv.start_device_server(SimBackend(i + 1, 1 << 20)) for i in range(2)]
+    coord = srv.start_coordinator_server()
+    try:
+        rc = grpc_client.main(["--coordinator", coord.addr, "--devices", ",".join(d.addr for d in devs), "--batch", "8",
+                               "--steps-per-epoch", "2", "--epochs", "2", "--samples", "64", "--dims", "784,128,10"])
+        assert rc == 0
+        assert not coord.service.communicators  # CommDestroy at the end of the run
+    finally:
+        coord.stop()
+        for d in devs:
+            d.stop()
