@@ -31,6 +31,7 @@ CASES = [
     (128, 256, 256), (200, 104, 72), (512, 1024, 384), (1024, 512, 1024),
     # >= 74 tiles of 256 x 256: the CTA-pair (tcgen05.mma.cta_group::2) path, ragged in M, N and K
     (2304, 200, 2320), (2200, 328, 2560), (2304, 2320, 200), (200, 2304, 2320),
+    (2100, 200, 2320),  # the second CTA of the last pair lies entirely past M (scripts/check_gemm_pair_edges.py has more)
 ]
 
 
