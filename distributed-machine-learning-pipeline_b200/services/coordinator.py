@@ -103,6 +103,28 @@ class Communicator:
         self.failure_reason = ""
 
 
+class _InProcessAbort(RuntimeError):
+    def __init__(self, code, details):
+        super().__init__(f"{code.name}: {details}")
+        self._code = code
+
+    def code(self):
+        return self._code
+
+
+class _InProcessContext:
+    """Servicer context for calling a device service that lives in this process (no channel in between)."""
+
+    def abort(self, code, details):
+        raise _InProcessAbort(code, details)
+
+    def invocation_metadata(self):
+        return ()
+
+    def set_trailing_metadata(self, md):
+        pass
+
+
 class GPUCoordinatorService:
     def __init__(self, health_interval: float = 5.0, probe_timeout: float = 2.0,
                  watchdog_ms: int = 10000, start_monitor: bool = True):
@@ -463,17 +485,24 @@ class GPUCoordinatorService:
         """One P2P hop delivered through BeginSend/BeginReceive/StreamSend/GetStreamStatus on the
         receiving device (the reference drives the same five calls, :427-516)."""
         n = len(payload)
-        s = dst.stub.BeginSend(pb.BeginSendRequest(sendBuffAddr=pb.MemAddr(value=DEFAULT_ADDR), numBytes=n,
-                                                   dstRank=pb.Rank(value=dst.rank)), timeout=30)
-        r = dst.stub.BeginReceive(pb.BeginReceiveRequest(streamId=s.streamId, recvBuffAddr=pb.MemAddr(value=recv_addr),
-                                                         numBytes=n, srcRank=pb.Rank(value=src_rank)), timeout=30)
+        if dst.local is not None:
+            # device served by this very process: same five calls on the same state machine, minus the loopback
+            # serialisation (a device that was marked dead still answers UNAVAILABLE through _guard_alive)
+            ctx = _InProcessContext()
+            call = lambda name, req: getattr(dst.local, name)(req, ctx)  # noqa: E731
+        else:
+            call = lambda name, req: getattr(dst.stub, name)(req, timeout=60)  # noqa: E731
+        s = call("BeginSend", pb.BeginSendRequest(sendBuffAddr=pb.MemAddr(value=DEFAULT_ADDR), numBytes=n,
+                                                  dstRank=pb.Rank(value=dst.rank)))
+        r = call("BeginReceive", pb.BeginReceiveRequest(streamId=s.streamId, recvBuffAddr=pb.MemAddr(value=recv_addr),
+                                                        numBytes=n, srcRank=pb.Rank(value=src_rank)))
         if not r.initiated:
             raise RuntimeError(f"rank {dst.rank}: BeginReceive not initiated")
         chunk = 2 << 20
         it = (pb.DataChunk(data=payload[o:o + chunk], streamId=s.streamId.value) for o in range(0, max(n, 1), chunk))
-        dst.stub.StreamSend(it, timeout=60)
+        call("StreamSend", it)
         while True:
-            st = dst.stub.GetStreamStatus(pb.GetStreamStatusRequest(streamId=s.streamId), timeout=30).status
+            st = call("GetStreamStatus", pb.GetStreamStatusRequest(streamId=s.streamId)).status
             if st == pb.SUCCESS:
                 return
             if st == pb.FAILED:
