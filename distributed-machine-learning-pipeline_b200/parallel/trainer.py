@@ -339,7 +339,7 @@ class Trainer:
             log.info("Training complete.")
         return hist
 
-    def evaluate(self, x, y) -> Dict[str, float]:
+    def evaluate(self, x, y, label: str = "Final Test Accuracy") -> Dict[str, float]:
         """Forward-only pass over all full batches (reference ``testModel``, client.go:462-502)."""
         xp, yp, n = self._host_ptrs(x, y)
         nb = n // self.cfg.batch
@@ -348,7 +348,7 @@ class Trainer:
         tot = nb * self.cfg.batch
         acc = correct.value / max(tot, 1)
         if self.rank == 0:
-            log.info("Final Test Accuracy: %.2f%%", 100 * acc)
+            log.info("%s: %.2f%%", label, 100 * acc)  # client.go:501
         return {"loss": loss.value / max(tot, 1), "accuracy": acc, "samples": tot}
 
     # ------------------------------------------------------------------ kernel-only timing helpers

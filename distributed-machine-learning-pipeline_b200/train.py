@@ -85,8 +85,12 @@ def main(argv=None) -> int:
     ev = trainer.evaluate(xte, yte)
     if rank == 0:
         mw.write("eval", **ev)
-        if not cfg.synthetic or ("test_images" in found and cfg.dims[0] == 784):
-            pass
+    if "test_images" in found and "test_labels" in found and cfg.dims[0] == 784 and cfg.dims[-1] == 10:
+        # the reference ships the real t10k split: evaluate on it too (meaningful when the run trained on real data)
+        xr, yr = D.load_idx_images(found["test_images"]), D.load_idx_labels(found["test_labels"])
+        evr = trainer.evaluate(xr, yr, label="Accuracy on the reference's t10k images")
+        if rank == 0:
+            mw.write("eval_t10k", **evr)
         if cfg.weights_out:
             trainer.save_weights(cfg.weights_out)
             log.info("weights saved to %s (reference client layout, %d bytes)", cfg.weights_out,

@@ -191,3 +191,31 @@ def test_grpc_client_cli_against_in_process_servers():
         coord.stop()
         for d in devs:
             d.stop()
+
+
+def test_real_mnist_t10k_convergence_with_the_oracle_if_mounted():
+    """Real data sanity: the reference ships only the t10k split. Train the reference-shaped MLP
+    on 8 000 of its images with the NumPy oracle (the same math the kernels are tested against: client.go:112-267,
+    batch 64, SGD) and evaluate on the other 2 000."""
+    import numpy as np
+    import pytest
+    from dmlp_b200.models import oracle
+    from dmlp_b200.models.layout import ParamLayout
+    from dmlp_b200.utils import data
+    found = data.find_reference_data()
+    if not found or "test_images" not in found or "test_labels" not in found:
+        pytest.skip("reference data not mounted")
+    x = data.load_idx_images(found["test_images"]).astype(np.float64)
+    y = data.load_idx_labels(found["test_labels"])
+    xtr, ytr, xte, yte = x[:8000], y[:8000], x[8000:], y[8000:]
+    lay = ParamLayout((784, 128, 10))  # the shape the reference's code trains (client.go:22-33)
+    params = [(w.astype(np.float64), b.astype(np.float64)) for w, b in lay.views(lay.init_reference(0))]
+    lr, B = 0.1, 64
+    first = None
+    for epoch in range(3):
+        for s in range(8000 // B):
+            params, loss, _ = oracle.train_step(params, xtr[s * B:(s + 1) * B], ytr[s * B:(s + 1) * B], lr)
+            first = loss if first is None else first
+    logits, _ = oracle.forward(params, xte)
+    acc = float((logits.argmax(1) == yte).mean())
+    assert loss < 0.6 * first and acc > 0.85, (first, loss, acc)
