@@ -91,10 +91,10 @@ def main(argv=None) -> int:
         evr = trainer.evaluate(xr, yr, label="Accuracy on the reference's t10k images")
         if rank == 0:
             mw.write("eval_t10k", **evr)
-        if cfg.weights_out:
-            trainer.save_weights(cfg.weights_out)
-            log.info("weights saved to %s (reference client layout, %d bytes)", cfg.weights_out,
-                     os.path.getsize(cfg.weights_out))
+    if rank == 0 and cfg.weights_out:
+        trainer.save_weights(cfg.weights_out)
+        log.info("weights saved to %s (reference client layout, %d bytes)", cfg.weights_out,
+                 os.path.getsize(cfg.weights_out))
     mw.close()
     trainer.close()
     if world > 1:
