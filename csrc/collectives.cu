@@ -11,9 +11,9 @@
 // separate elementwise kernel runs:  w -= lr * scale * sum_r g_r   (lr read from device memory).
 //
 // Synchronisation is a flag protocol in peer-visible "signal pads": same-index CTAs of all ranks
-// meet at barriers using monotonically increasing epochs (st.release.sys / ld.acquire.sys). The
+// meet at barriers using monotonically increasing epochs (relaxed sys-scope flags, see wait_flag). The
 // epochs live in device memory, so a captured CUDA graph can be replayed. Every spin-wait has a
-// globaltimer deadline and also polls a host-mapped abort flag: a dead peer makes the kernel
+// globaltimer deadline and also polls the rank's abort word (device memory): a dead peer makes the kernel
 // record {rank, peer, phase} in a host-mapped status block and exit instead of hanging the GPU.
 //
 // "Emulation": when all ranks of a communicator live on ONE device the same kernels are launched
