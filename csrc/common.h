@@ -48,4 +48,8 @@ namespace dmlp {
 constexpr int kPadAbortWord = 1280;          // abort word (== kPadAbort in collectives.cu)
 constexpr int kPadFusedFlags = 8192;         // fused step kernel: [source rank][cta] arrival epochs (64 words)
 constexpr int kPadFusedEpoch = 8192 + 64;    // fused step kernel: this rank's step epoch (local use)
+// global-batch mode of the fused step (mlp_fused.cu) and its input copy kernel (input_exchange.cu)
+constexpr int kXPushCtas = 16;               // CTAs of the input copy kernel (one ready word each)
+constexpr int kPadXReady = 8192 + 256;       // [source rank][copy CTA]: steps whose inputs that rank has delivered to this rank
+constexpr int kPadXDone = 8192 + 512;        // [source rank]: steps that rank has finished (its input slots may be overwritten)
 }  // namespace dmlp

@@ -26,6 +26,9 @@
 //   * red_ctas > 0 (world > 1)  : persistent data-parallel launch - this cluster computes, the other CTAs of the grid
 //                                 run the one-shot all-reduce + average + SGD over peer memory (fused_reducer_loop)
 //   * world > 1, red_ctas == 0  : gradient exchange inside the cluster (bulk-copy push, rank-ordered reduce): opt-in
+//   * gx (world > 1)            : global-batch weight gradients - the ranks exchange dZ1 (32 KB) and their inputs instead of
+//                                 dW1 (401 KB); every rank computes the layer-1 gradient of the GLOBAL batch itself, in rank
+//                                 order, and applies it in place. See the "global-batch" block below (default on real GPUs).
 //
 // Reference math: DSML/client/client.go:112-202 (forward, softmax-CE, backward).
 // Supported shapes: batch <= 64 (multiple of 8), in0 % 8 == 0 and <= 832, H1 = 128, H2 in {64, none},
@@ -59,7 +62,7 @@ struct FusedParams {
   float* wparams;  // non-null: single-GPU mode, apply w -= lr*g in place instead of writing gradients
   const float* lr;
   float* dbg;      // optional dump of intermediates (tests)
-  unsigned long long* prof;  // optional [8 CTAs][16] globaltimer stamps at phase boundaries
+  unsigned long long* prof;  // optional [8 CTAs][64] globaltimer stamps at phase boundaries
   // ---- in-kernel data-parallel gradient exchange (world > 1), see the "gradient exchange" block in the kernel
   int world, rank;
   float* xrecv[8];          // rank r's receive area as mapped here: [2 parities][world sources][total floats]
@@ -77,11 +80,29 @@ struct FusedParams {
   int bulk_update; // single GPU: apply the update with bulk reduce-adds from a staged image (else red.global per thread)
   int nsteps;      // steps this launch performs back to back (> 1 only with in-place SGD: wparams != null)
   int slot0;       // first input slot: step s reads rows [(slot0+s)*B, +B) of the X maps, labels + s*B, metrics + 2*s
+  // ---- global-batch mode (gx != 0, world > 1, wparams != null). The mean gradient of data-parallel SGD is the gradient of
+  // the global batch: dW1 = sum_r X_r^T dZ1_r. For this model the factors are far smaller than the product (64 x (784 + 128)
+  // floats per rank against 784 x 128), so the ranks exchange the factors: inputs are all-gathered ahead of time by a copy
+  // kernel (input_exchange.cu), dZ1 slices are pushed into every peer's receive area the moment they exist, and every rank
+  // accumulates the K = world x batch product itself in rank order - bit-identical replicas by construction, no reducers,
+  // no rendezvous. The small tensors (W2, W3, b2, b3: 36 KB) are all-reduced inside the kernel: each CTA pushes its slices
+  // to every rank and sums the arrivals in rank order. Arrival is detected on the data itself (the receive areas hold a
+  // NaN pattern no arithmetic produces until real values land), so a transfer costs one NVLink traversal: no flag, no fence.
+  int gx;
+  int xslots;                   // input ring slots per rank: rank r's batch of ring slot s starts at row (r*xslots + s)*B of the X maps
+  unsigned long long g0;        // global index of this launch's first step (parity of the receive areas)
+  long long fault_step;         // fault injection: from this global step on this rank sends nothing and waits for nothing (-1: never)
+  unsigned int xneed;           // the peers' inputs for this launch are in place once their ready words reach this step count
 };
 
 #define FPROF(slot)                                                                                   \
   do {                                                                                                \
-    if (p.prof != nullptr && threadIdx.x == 32) p.prof[j * 16 + (slot)] = globaltimer_ns();             \
+    if (p.prof != nullptr && threadIdx.x == 32) p.prof[j * 64 + (slot)] = globaltimer_ns();             \
+  } while (0)
+// fine-grained stamps of the global-batch tail (slots 16..63): thread `tid` only
+#define FPROFT(tid, slot)                                                                             \
+  do {                                                                                                \
+    if (GX && p.prof != nullptr && threadIdx.x == (tid)) p.prof[j * 64 + (slot)] = globaltimer_ns();    \
   } while (0)
 
 // ---- shared-memory map (bytes). A-operand tiles are written for 64 rows (8 KiB per 128-byte-wide
@@ -124,6 +145,20 @@ constexpr uint32_t oH2K = oRS1;
 constexpr uint32_t oDZ3K = oRS1 + 8192;
 constexpr uint32_t oH2M = oRS1 + 16384;
 constexpr uint32_t oDZ3M = oRS1 + 24576;
+// Global-batch mode: two stages for the peers' operands of the layer-1 weight gradient (X_r^T tile + dZ1_r image, 32 KiB
+// each), in regions whose last readers are the weight-gradient GEMMs that run beside the chain (complete before P5).
+constexpr uint32_t oGX0 = oXA;               // stage 0 X^T (three-layer model; the two-layer model keeps its dZ1 in XA ...
+constexpr uint32_t oGX0b = oW1B;             // ... and uses the W1 region instead)
+constexpr uint32_t oGD0 = oRS1;              // stage 0 dZ1
+constexpr uint32_t oGX1 = oH1K;              // stage 1 X^T: H1K, H1M, W2B, W2K, WLB
+constexpr uint32_t oGD1 = oH1K + 32768;      // stage 1 dZ1: WLK, RED and 24 KiB of the over-read slack
+static_assert(oGD1 == oWLK && oGD1 + 32768 <= kFusedSmem - 1024, "stage 1 runs past the shared-memory map");
+// Staging for pushes over NVLink (the last 8 KiB of the over-read slack: MMAs only ever READ there, into accumulator rows
+// nobody uses). An SM gets a remote write out every ~11 ns whatever its size, so what is pushed is first laid out
+// contiguously here and then stored with full-line, lane-contiguous 16-byte stores: 32 transactions per 4 KiB, not 512.
+constexpr uint32_t oSTG = oEND + 24576;     // [0, 4K): dZ1 slice, 2 KiB per warp holding rows < 64 (later: last-layer dW slice)
+constexpr uint32_t oSTG2 = oSTG + 4096;     // [4K, 8K): dW2 slice
+static_assert(oSTG2 + 4096 <= kFusedSmem - 1024, "push staging runs past the shared-memory map");
 static_assert(kFusedSmem <= 227 * 1024, "fused step does not fit in shared memory");
 
 // TMEM columns
@@ -196,13 +231,23 @@ __device__ __forceinline__ uint64_t mdesc(uint32_t tile, int kstep, uint32_t col
   return make_smem_desc(tile + kstep * 1024, col_bytes, 512, 1);
 }
 
+// Store that is performed at system scope right away (peer-visible data whose arrival the receiver polls for)
+__device__ __forceinline__ void st_volatile_f4(float* p, float a, float b, float c, float d) {
+  asm volatile("st.volatile.global.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(p), "f"(a), "f"(b), "f"(c), "f"(d) : "memory");
+}
 // Emits 4 consecutive gradient values: either into the gradient buffer (multi-GPU: the all-reduce
 // kernel consumes it) or straight into the weights as w -= lr*g (single GPU).
 // Exchange mode (xs != 0): the gradient goes to this CTA's staging image in shared memory (byte offset soff); the bulk
 // copy engine pushes the image to the peers afterwards.
 __device__ __forceinline__ void emit_grad4(const FusedParams& p, float step, size_t off, uint32_t xs, uint32_t soff, float a,
-                                           float b, float c, float d, float* gdst = nullptr) {
-  if (gdst != nullptr) {  // persistent data-parallel mode: this rank's peer-visible gradient buffer
+                                           float b, float c, float d, float* gdst = nullptr, long long gpush = -1) {
+  if (gpush >= 0) {
+    // global-batch mode, small tensors: this rank's contribution goes to slot [parity][my rank] of EVERY rank's receive
+    // area (own included: the reduction then reads all contributions the same way); gpush = float offset of that slot
+#pragma unroll
+    for (int q = 0; q < 8; ++q)
+      if (q < p.world) st_volatile_f4(p.xrecv[q] + gpush + off, a, b, c, d);
+  } else if (gdst != nullptr) {  // persistent data-parallel mode: this rank's peer-visible gradient buffer
     *reinterpret_cast<float4*>(gdst + off) = make_float4(a, b, c, d);
   } else if (xs != 0u) {
     // staged: raw gradients (exchange mode) or -lr*g (single GPU: one bulk reduce-add per range applies them)
@@ -246,8 +291,22 @@ __device__ __forceinline__ void worker_colsum(const float (&v)[N], float* red, i
 constexpr int kPfEpoch = 64;        // steps completed (shared with the in-kernel exchange mode)
 constexpr int kPfWeights = 80;      // counter: reducer CTAs that finished applying an update (red_ctas per step)
 constexpr int kPfRedFlags = 128;    // [source rank][compute CTA]: epoch whose gradient slices are complete (written by every rank)
+constexpr uint32_t kGxEmpty = 0xFFFFFFFFu;  // "nothing has arrived": a NaN pattern that arithmetic never produces (canonical NaN is 0x7FFFFFFF)
 constexpr int kMaxRedCtas = 136;  // 8 + 136 CTAs <= 148 SMs: every CTA of the launch must be resident (the roles wait on each other)
 
+// 16-byte asynchronous copy global -> shared that bypasses L1 (LDGSTS), and the wait for all of this thread's copies
+__device__ __forceinline__ void cp_async16(uint32_t dst_s, const float* src) {
+  asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(dst_s), "l"(src) : "memory");
+}
+__device__ __forceinline__ void cp_async_wait_all() { asm volatile("cp.async.wait_all;" ::: "memory"); }
+// Polling load for data a peer writes into THIS GPU's memory: served by L2 (where incoming NVLink writes land), never by
+// L1. A plain .cg load coalesces like any other load; system-scope strong loads (ld.volatile) were measured at ~13 GB/s
+// per SM here. `asm volatile` keeps the compiler from hoisting it out of the polling loop.
+__device__ __forceinline__ float4 ld_poll_f4(const float* p) {
+  float4 v;
+  asm volatile("ld.global.cg.v4.f32 {%0, %1, %2, %3}, [%4];" : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "l"(p) : "memory");
+  return v;
+}
 __device__ __forceinline__ float4 ld_volatile_f4(const float* p) {
   float4 v;
   asm volatile("ld.volatile.global.v4.f32 {%0, %1, %2, %3}, [%4];" : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "l"(p) : "memory");
@@ -275,6 +334,39 @@ __device__ __forceinline__ bool pf_wait(const uint32_t* flag, uint32_t target, c
     }
   }
   return true;
+}
+
+// Global-batch mode: waits until the 16 bytes at `src` (this GPU's memory, written by a peer) hold data, i.e. no word is the
+// "empty" pattern any more. Watchdog as in pf_wait; `fail` (shared) short-cuts every later wait of a failed launch.
+__device__ __forceinline__ bool gx_valid(const float4& v) {
+  return __float_as_uint(v.x) != kGxEmpty && __float_as_uint(v.y) != kGxEmpty && __float_as_uint(v.z) != kGxEmpty &&
+         __float_as_uint(v.w) != kGxEmpty;
+}
+__device__ __forceinline__ bool gx_timeout(const FusedParams& p, int peer, uint32_t phase, unsigned long long deadline) {
+  if (ld_relaxed_sys(p.xpad[p.rank] + kPadAbortWord) != 0u) return true;
+  if (globaltimer_ns() > deadline) {
+    if (p.xstatus != nullptr) {
+      p.xstatus[1] = static_cast<uint32_t>(p.rank);
+      p.xstatus[2] = static_cast<uint32_t>(peer);
+      p.xstatus[3] = phase;
+      __threadfence_system();
+      p.xstatus[0] = DMLP_ERR_TIMEOUT;
+    }
+    for (int q = 0; q < p.world; ++q) st_relaxed_sys(p.xpad[q] + kPadAbortWord, 1u);
+    return true;
+  }
+  return false;
+}
+__device__ __forceinline__ float4 gx_wait4(const float* src, const FusedParams& p, int peer, uint32_t phase,
+                                           unsigned long long deadline, volatile int* fail) {
+  float4 v = ld_volatile_f4(src);
+  if (*fail != 0) return v;
+  uint32_t spins = 0;
+  while (!gx_valid(v)) {
+    if ((++spins & 0x3F) == 0 && (*fail != 0 || gx_timeout(p, peer, phase, deadline))) { *fail = 1; break; }
+    v = ld_volatile_f4(src);
+  }
+  return v;
 }
 
 // Reducer CTA of the persistent data-parallel mode: one-shot all-reduce + average + SGD per step, fed by local flags.
@@ -338,7 +430,9 @@ __device__ void fused_reducer_loop(const FusedParams& p) {
   }
 }
 
-template <int S1, int S2>  // slice widths: H1/8 and H2/8 (S2 == 0: two-layer model)
+// S1, S2: slice widths H1/8 and H2/8 (S2 == 0: two-layer model). GX: compiled with the global-batch data-parallel mode
+// (a separate instantiation, so the single-GPU kernel carries none of its registers or code).
+template <int S1, int S2, bool GX>
 __global__ void __cluster_dims__(kFC, 1, 1) __launch_bounds__(kFThreads, 1)
 mlp_fused_step_kernel(const __grid_constant__ CUtensorMap tmXA, const __grid_constant__ CUtensorMap tmXT,
                       const __grid_constant__ CUtensorMap tmW1, const __grid_constant__ CUtensorMap tmW2B,
@@ -359,6 +453,8 @@ mlp_fused_step_kernel(const __grid_constant__ CUtensorMap tmXA, const __grid_con
   // bar_wgl / bar_wg2: weight-gradient GEMMs that run beside the chain; bar_ex[k]: arrival of exchange k
   // (remote st.async stores complete transaction bytes on the DESTINATION's barrier: no cluster-wide barrier).
   __shared__ __align__(8) uint64_t bar_tma0, bar_tma1, bar_mma, bar_wgl, bar_wg2, bar_ex[5], bar_xr[4];
+  // global-batch mode, two peer stages: X^T tile landed (TMA) / stage complete (128 workers) / stage consumed (MMA commit)
+  __shared__ __align__(8) uint64_t bar_gx[2], bar_gf[2], bar_ge[2];
   __shared__ uint32_t tmem_slot;
 
   // Warp index through a shuffle: the role branches are then provably warp-uniform and the control warp's
@@ -371,11 +467,11 @@ mlp_fused_step_kernel(const __grid_constant__ CUtensorMap tmXA, const __grid_con
   const int ngroups = p.in0 / 8;
   const int g0 = (ngroups * j) / kFC, g1 = (ngroups * (j + 1)) / kFC;
   const int k0 = g0 * 8, nk1 = g1 - g0;  // layer-1 K slice: floats [k0, k0 + 8*nk1)
-  if (p.red_ctas > 0 && blockIdx.x >= kFC) {  // persistent data-parallel mode: everything past the first cluster reduces
+  if (!GX && p.red_ctas > 0 && blockIdx.x >= kFC) {  // persistent data-parallel mode: everything past the first cluster reduces
     fused_reducer_loop(p);
     return;
   }
-  const bool pmode = p.red_ctas > 0;
+  const bool pmode = !GX && p.red_ctas > 0;  // (the global-batch instantiation carries none of the other exchange modes)
   const bool worker = warp >= 1;
   const int wwarp = warp - 1;
   const int row = (warp & 3) * 32 + lane;  // TMEM lane == batch row handled by this worker thread
@@ -401,6 +497,7 @@ mlp_fused_step_kernel(const __grid_constant__ CUtensorMap tmXA, const __grid_con
     mbar_init(&bar_wg2, 1);
     for (int k = 0; k < 5; ++k) mbar_init(&bar_ex[k], 1);
     for (int k = 0; k < 4; ++k) mbar_init(&bar_xr[k], 1);
+    for (int k = 0; k < 2; ++k) { mbar_init(&bar_gx[k], 1); mbar_init(&bar_gf[k], 128); mbar_init(&bar_ge[k], 1); }
     fence_mbar_init();
     arm_exchanges();
   }
@@ -427,16 +524,22 @@ mlp_fused_step_kernel(const __grid_constant__ CUtensorMap tmXA, const __grid_con
   // launch gap, TMEM allocation and barrier set-up are paid once; steps are separated by one cluster barrier
   // that also publishes the weight updates (red.global + __threadfence) to the next step's loads.
   const int nsteps = p.nsteps > 0 ? p.nsteps : 1;
-  const bool xmode = p.world > 1 && !pmode;
+  constexpr bool gmode = GX;  // (launch_fused<.., true> is only reached through plans with gx set and world > 1)
+  const bool xmode = !GX && p.world > 1 && !pmode;
+  const int W = p.world > 1 ? p.world : 1;
+  const int npeer = gmode ? W - 1 : 0;
+  uint32_t guse0 = 0, guse1 = 0;  // global-batch mode: uses of peer stage 0 / 1 so far (barrier parity = use & 1)
+  uint32_t gmma0 = 0, gmma1 = 0;  // ... as counted by the MMA issuer (warp 0 fills ahead of its own consumption)
   uint32_t xr_phase = 0;  // bit s: parity the next wait on receive stage s expects
   uint32_t epoch0 = 0;  // steps this rank completed before this launch (every rank holds the same count)
   __shared__ int s_xfail;
   if (threadIdx.x == 0) s_xfail = 0;
+  volatile int* xfail = &s_xfail;
   for (int st = 0; st < nsteps; ++st) {
   const uint32_t sp = st & 1;  // parity of the barriers that complete once per step
   FPROF(13);
   if (warp == 0 && elect_one()) {
-    const int xr = (p.slot0 + st) * B;
+    const int xr = ((gmode ? p.rank * p.xslots : 0) + p.slot0 + st) * B;
     mbar_arrive_expect_tx(&bar_tma0, 4 * kTileK + (H1 / 32) * kW1Col);
     for (int b = 0; b < 4; ++b) tma_load_2d(smem + oXA + b * kTileK, &tmXA, &bar_tma0, k0 + 32 * b, xr);
     uint32_t bytes1 = 4 * kColM + 2 * SL * 128;
@@ -449,13 +552,17 @@ mlp_fused_step_kernel(const __grid_constant__ CUtensorMap tmXA, const __grid_con
   if (st == 0) {
     asm volatile("griddepcontrol.wait;" ::: "memory");
     if (xmode || pmode) epoch0 = __ldcg(p.xpad[p.rank] + kPadFusedEpoch);
+    if (gmode) epoch0 = static_cast<uint32_t>(p.g0);
   }
   const uint32_t epoch = epoch0 + static_cast<uint32_t>(st) + 1u;
+  // fault injection: a "dead" rank sends nothing and waits for nothing from its fault step on (its peers' watchdogs fire)
+  const bool gdead = gmode && p.fault_step >= 0 && static_cast<long long>(p.g0) + st >= p.fault_step;
   const uint32_t xpar = epoch & 1u;  // receive areas are double-buffered by step parity
   // gradients are staged in shared memory in exchange mode and (single GPU) when the update is applied by bulk reduce-adds
-  const bool bmode = !xmode && !pmode && p.wparams != nullptr && p.bulk_update != 0;
+  const bool bmode = !GX && !xmode && !pmode && p.wparams != nullptr && p.bulk_update != 0;
   const uint32_t xs = (xmode || bmode) ? sb : 0u;
   float* gdst = pmode ? p.xgrads[xpar][p.rank] : nullptr;
+  if (gdead && threadIdx.x == 0) s_xfail = 1;  // (published by the barriers that precede the first cross-GPU wait)
   if (pmode && st > 0) {
     // the reducers have applied the previous step's update (red_ctas increments per step) before any weight is loaded
     if (threadIdx.x == 0) {
@@ -489,7 +596,25 @@ mlp_fused_step_kernel(const __grid_constant__ CUtensorMap tmXA, const __grid_con
     }
     __syncwarp();
   }
-  const float step = p.wparams != nullptr ? __ldcg(p.lr) : 0.f;  // (after griddepcontrol.wait)
+  // (after griddepcontrol.wait) global-batch mode: the in-place update applies the gradient of the global batch, lr / world
+  const float step = p.wparams != nullptr ? __ldcg(p.lr) / static_cast<float>(gmode ? W : 1) : 0.f;
+  // slot [parity][my rank] of a receive area, in floats (the small tensors keep their offsets of the flat parameter vector,
+  // the dZ1 image sits where W1 would be)
+  const long long gslot = gmode ? static_cast<long long>((static_cast<size_t>(xpar) * W + p.rank) * p.total) : -1;
+  const long long gpush = (gmode && !gdead) ? gslot : -1;
+  const unsigned long long gdeadline = gmode ? globaltimer_ns() + p.xtimeout_ns : 0ull;
+  if (gmode && worker) {
+    // The dZ1 images of the other parity were consumed by all 8 CTAs in the previous step (its end-of-step barrier is
+    // behind us) and are written again by the peers at the end of the NEXT step: mark them empty. Each CTA clears an eighth.
+    const float4 e4 = make_float4(__uint_as_float(kGxEmpty), __uint_as_float(kGxEmpty), __uint_as_float(kGxEmpty), __uint_as_float(kGxEmpty));
+    for (int q = 0; q < W; ++q) {
+      if (q == p.rank) continue;
+      float* img = p.xrecv[p.rank] + (static_cast<size_t>(xpar ^ 1u) * W + q) * p.total + p.w_off[0];
+      const int wt = threadIdx.x - 32;
+      *reinterpret_cast<float4*>(img + 4 * (j * 256 + wt)) = e4;
+      *reinterpret_cast<float4*>(img + 4 * (j * 256 + 128 + wt)) = e4;
+    }
+  }
   // Biases of this CTA's slices and this row's label: requested now, consumed phases later (a cold global load
   // on the critical chain costs ~0.6 us each time).
   float b1r[S1], b2r[kMid ? S2 : 1], blr[16];
@@ -562,7 +687,7 @@ mlp_fused_step_kernel(const __grid_constant__ CUtensorMap tmXA, const __grid_con
       }
       // "ones" column: row S1 of H1_j^T . dZ is then the column sum of dZ = a bias gradient, for free
       *reinterpret_cast<float*>(smem + oH1M + moff(row, S1)) = 1.f;
-      if (p.dbg)
+      if (!GX && p.dbg)
         for (int c = 0; c < S1; ++c) p.dbg[row * H1 + S1 * j + c] = h1[c];
     }
     // X^T tile: column 127 lies outside every CTA's K slice (<= 104 wide) -> make it the ones column
@@ -626,7 +751,7 @@ mlp_fused_step_kernel(const __grid_constant__ CUtensorMap tmXA, const __grid_con
           *reinterpret_cast<float4*>(smem + oH2M + moff(row, c)) = make_float4(h2[c], h2[c + 1], h2[c + 2], h2[c + 3]);
         }
         *reinterpret_cast<float*>(smem + oH2M + moff(row, S2)) = 1.f;
-        if (p.dbg)
+        if (!GX && p.dbg)
           for (int c = 0; c < S2; ++c) p.dbg[64 * H1 + row * H2 + S2 * j + c] = h2[c];
       }
       fence_proxy_async_smem();
@@ -718,7 +843,7 @@ mlp_fused_step_kernel(const __grid_constant__ CUtensorMap tmXA, const __grid_con
         *reinterpret_cast<float4*>(smem + oDZ3K + koff(row, c)) = make_float4(dz3[c], dz3[c + 1], dz3[c + 2], dz3[c + 3]);
         *reinterpret_cast<float4*>(smem + oDZ3M + moff(row, c)) = make_float4(dz3[c], dz3[c + 1], dz3[c + 2], dz3[c + 3]);
       }
-      if (p.dbg && j == 0)
+      if (!GX && p.dbg && j == 0)
         for (int c = 0; c < 16; ++c) p.dbg[64 * H1 + 64 * (kMid ? H2 : 0) + row * 16 + c] = dz3[c];
     } else {
 #pragma unroll
@@ -787,7 +912,7 @@ mlp_fused_step_kernel(const __grid_constant__ CUtensorMap tmXA, const __grid_con
         st_async_f4(dm, bar, dzl[0], dzl[1], dzl[2], dzl[3]);
         st_async_f4(dm + 16, bar, dzl[4], dzl[5], dzl[6], dzl[7]);
       }
-      if (p.dbg)
+      if (!GX && p.dbg)
         for (int c = 0; c < S2; ++c) p.dbg[64 * H1 + 64 * H2 + 64 * 16 + row * H2 + S2 * j + c] = dzl[c];
     }
     FPROF(8);
@@ -825,6 +950,37 @@ mlp_fused_step_kernel(const __grid_constant__ CUtensorMap tmXA, const __grid_con
 #pragma unroll
     for (int c = 0; c < S1; ++c) dz1[c] = dzl[kMid ? 0 : c];
   }
+  // global-batch mode: the slice goes to every peer first (longest way to travel), as block j of the peers' dZ1 receive
+  // image: [8 source CTAs][64 rows][16 columns], 4 KiB contiguous per CTA. Rows of a warp are transposed through shared
+  // memory so that each store instruction covers 512 contiguous bytes (see oSTG).
+  FPROFT(32, 16);
+  FPROFT(128, 32);
+  if (gmode && worker && (warp & 3) < 2) {  // the two warps that hold batch rows 0..63
+    const uint32_t stg = sb + oSTG + (warp & 3) * 2048;
+    if (lane == 0) bulk_wait_read();  // (the previous step's copies out of this warp's staging half)
+    __syncwarp();
+    if (rok) {
+      sts128(stg + lane * 64, dz1[0], dz1[1], dz1[2], dz1[3]);
+      sts128(stg + lane * 64 + 16, dz1[4], dz1[5], dz1[6], dz1[7]);
+      sts128(stg + lane * 64 + 32, dz1[8], dz1[9], dz1[10], dz1[11]);
+      sts128(stg + lane * 64 + 48, dz1[12], dz1[13], dz1[14], dz1[15]);
+    }
+    fence_proxy_async_smem();  // staged with ordinary stores, read by the bulk copy engine
+    __syncwarp();
+    if (gpush >= 0 && lane == 0) {
+      // one bulk copy per peer: the copy engine moves it, this SM's load/store path stays free (SM-issued stores to a
+      // peer stall the issuing warp for about a microsecond)
+      const int rows = B - (warp & 3) * 32 < 32 ? B - (warp & 3) * 32 : 32;
+      if (rows > 0) {
+        const size_t o = static_cast<size_t>(gslot) + p.w_off[0] + j * 1024 + (warp & 3) * 512;
+        for (int q = 0; q < W; ++q)
+          if (q != p.rank) bulk_s2g(p.xrecv[q] + o, stg, rows * 64);
+        bulk_commit();
+      }
+    }
+  }
+  FPROFT(32, 17);
+  FPROFT(128, 33);
   // all-gather dZ1_j into every CTA (MN-major: B operand of the layer-1 weight gradient)
   if (rok) {
 #pragma unroll
@@ -837,13 +993,78 @@ mlp_fused_step_kernel(const __grid_constant__ CUtensorMap tmXA, const __grid_con
       st_async_f4(dm2, bar, dz1[8], dz1[9], dz1[10], dz1[11]);
       st_async_f4(dm2 + 16, bar, dz1[12], dz1[13], dz1[14], dz1[15]);
     }
-    if (p.dbg)
+    if (!GX && p.dbg)
       for (int c = 0; c < S1; ++c) p.dbg[64 * H1 + 128 * (kMid ? H2 : 0) + 64 * 16 + row * H1 + S1 * j + c] = dz1[c];
   }
   FPROF(10);
 
   // ------------------------------------------------------------------ P5: dW1_j = X_j^T . dZ1
-  if (warp == 0) {
+  if (warp == 0 && gmode) {
+    // Global batch: dW1_j = sum over ranks r (in rank order, own rank in its place) of X_{r,j}^T . dZ1_r, accumulated in
+    // ONE TMEM accumulator. Peers' operands pass through two shared-memory stages: this warp loads the X^T tile (TMA from
+    // the gathered input buffer in this GPU's memory), the workers copy the dZ1 image out of the receive area.
+    // The stage regions are free once the weight-gradient GEMMs issued after the last dgrad have completed.
+    mbar_wait(&bar_wgl, sp);
+    if (kMid) mbar_wait(&bar_wg2, sp);
+    if (st == 0 && !gdead) {
+      // the peers' inputs for every step of this launch have been delivered (one ready word per copy CTA and source rank)
+      for (int i = lane; i < W * kXPushCtas; i += 32) {
+        const int src = i / kXPushCtas;
+        if (src != p.rank && !pf_wait(p.xpad[p.rank] + kPadXReady + i, p.xneed, p, src, 11u, gdeadline)) s_xfail = 1;
+      }
+      __threadfence_system();
+      __syncwarp();
+      fence_proxy_async_all();  // written by the peers with ordinary stores, read here by TMA (async proxy)
+    }
+    const uint32_t gx0 = sb + (kMid ? oGX0 : oGX0b);
+    auto fill = [&](int q) {
+      const int s = q & 1;
+      const uint32_t u = s ? guse1 : guse0;
+      if (u > 0) mbar_wait_long(&bar_ge[s], (u - 1) & 1);  // the stage's previous MMAs have read it
+      if (elect_one()) {
+        const int r = q < p.rank ? q : q + 1;
+        const int xrow = (r * p.xslots + p.slot0 + st) * B;
+        mbar_arrive_expect_tx(&bar_gx[s], 4 * kColM);
+        uint8_t* dst = smem + (s ? oGX1 : (kMid ? oGX0 : oGX0b));
+        for (int a = 0; a < 4; ++a) tma_load_2d(dst + a * kColM, &tmXT, &bar_gx[s], k0 + 32 * a, xrow);
+      }
+      __syncwarp();
+      if (s) ++guse1; else ++guse0;
+    };
+    for (int q = 0; q < npeer && q < 2; ++q) fill(q);
+    const uint32_t idw = make_instr_desc(4, true, true, H1);
+    int pending = -1;
+    for (int r = 0; r < W; ++r) {
+      uint32_t xt, dzt;
+      int q = -1, s = 0;
+      if (r == p.rank) {
+        mbar_wait(&bar_ex[4], sp);
+        xt = sb + oXT;
+        dzt = sb + oDZ1;
+      } else {
+        q = r < p.rank ? r : r - 1;
+        s = q & 1;
+        mbar_wait_long(&bar_gf[s], (s ? gmma1 : gmma0) & 1u);
+        xt = s ? sb + oGX1 : gx0;
+        dzt = sb + (s ? oGD1 : oGD0);
+      }
+      fence_proxy_async_smem();
+      tc_fence_after_sync();
+      if (elect_one()) {
+#pragma unroll
+        for (int t = 0; t < 8; ++t)
+          if (t < nb8) tc_mma<4>(tm + cWG1, mdesc(xt, t, kColM), mdesc(dzt, t, kColM), idw, (r | t) != 0);
+        if (q >= 0) tc_commit(&bar_ge[s]);
+        if (r == W - 1) tc_commit(&bar_mma);
+      }
+      __syncwarp();
+      if (pending >= 0) { fill(pending); pending = -1; }  // (after this rank's MMAs are queued: the wait inside overlaps them)
+      if (q >= 0) {
+        if (s) ++gmma1; else ++gmma0;
+        if (q + 2 < npeer) pending = q + 2;
+      }
+    }
+  } else if (warp == 0) {
     mbar_wait(&bar_ex[4], sp);
     fence_proxy_async_smem();
     tc_fence_after_sync();
@@ -859,46 +1080,211 @@ mlp_fused_step_kernel(const __grid_constant__ CUtensorMap tmXA, const __grid_con
   float dbl[16];  // last-layer bias gradient (valid in the thread that owns accumulator row SL)
   if (worker) {
     // while dW1 runs on the tensor core: drain the weight-gradient GEMMs that ran beside the chain
+    FPROFT(32, 18);
+    FPROFT(128, 34);
     mbar_wait(&bar_wgl, sp);
+    FPROFT(128, 35);
     tc_fence_after_sync();
     {
       uint32_t r[16];
       tmem_ld_x16(tm + tq + cWGL, r);
       tmem_ld_wait();
-      if (row < SL) {
+      if (gmode) {
+        // pushed as one contiguous SL x 64 B block (rows < SL sit in the lanes of the warp that owns TMEM lanes 0..31)
+        if ((warp & 3) == 0) {
+          if (lane == 0) bulk_wait_read();  // this warp's dZ1 copies have left the staging half
+          __syncwarp();
+          if (row <= SL) {  // rows < SL: the dW slice; row SL (the ones row): the last bias gradient
+#pragma unroll
+            for (int c = 0; c < 16; c += 4)
+              sts128(sb + oSTG + row * 64 + c * 4, __uint_as_float(r[c]), __uint_as_float(r[c + 1]), __uint_as_float(r[c + 2]), __uint_as_float(r[c + 3]));
+          }
+          fence_proxy_async_smem();
+          __syncwarp();
+          if (gpush >= 0 && lane == 0) {
+            const size_t o = static_cast<size_t>(gpush) + p.w_off[LAST] + static_cast<size_t>(SL * j) * 16;
+            for (int q = 0; q < W; ++q) {
+              bulk_s2g(p.xrecv[q] + o, sb + oSTG, SL * 64);
+              if (j == 0) bulk_s2g(p.xrecv[q] + gpush + p.b_off[LAST], sb + oSTG + SL * 64, 64);
+            }
+            bulk_commit();
+          }
+        }
+      } else if (row < SL) {
         const size_t off = p.w_off[LAST] + static_cast<size_t>(SL * j + row) * 16;
 #pragma unroll
         for (int c = 0; c < 16; c += 4)
-          emit_grad4(p, step, off + c, xs, kXsWL + row * 64 + c * 4, __uint_as_float(r[c]), __uint_as_float(r[c + 1]), __uint_as_float(r[c + 2]), __uint_as_float(r[c + 3]), gdst);
+          emit_grad4(p, step, off + c, xs, kXsWL + row * 64 + c * 4, __uint_as_float(r[c]), __uint_as_float(r[c + 1]), __uint_as_float(r[c + 2]), __uint_as_float(r[c + 3]), gdst, gpush);
       }
       if (row == SL) {  // the ones row: column sums of dZ_last = gradient of the last bias
 #pragma unroll
         for (int c = 0; c < 16; ++c) dbl[c] = __uint_as_float(r[c]);
+        // (global-batch mode: pushed with the dW slice above - a push changes no weight, so it need not wait for wgrad1)
       }
     }
+    FPROFT(128, 36);
     if (kMid) {
       mbar_wait(&bar_wg2, sp);
+      FPROFT(128, 37);
       tc_fence_after_sync();
 #pragma unroll
       for (int cc = 0; cc < H2; cc += 16) {
         uint32_t r[16];
         tmem_ld_x16(tm + tq + cWG2 + cc, r);
         tmem_ld_wait();
-        if (row < S1) {
+        if (gmode) {
+          if (row < S1) {  // staged: the slice is pushed as one contiguous block after the loop
+#pragma unroll
+            for (int c = 0; c < 16; c += 4)
+              sts128(sb + oSTG2 + row * (H2 * 4) + (cc + c) * 4, __uint_as_float(r[c]), __uint_as_float(r[c + 1]), __uint_as_float(r[c + 2]), __uint_as_float(r[c + 3]));
+          }
+        } else if (row < S1) {
           const size_t off = p.w_off[1] + static_cast<size_t>(S1 * j + row) * H2 + cc;
 #pragma unroll
           for (int c = 0; c < 16; c += 4)
-            emit_grad4(p, step, off + c, xs, kXsW2 + row * (H2 * 4) + (cc + c) * 4, __uint_as_float(r[c]), __uint_as_float(r[c + 1]), __uint_as_float(r[c + 2]), __uint_as_float(r[c + 3]), gdst);
+            emit_grad4(p, step, off + c, xs, kXsW2 + row * (H2 * 4) + (cc + c) * 4, __uint_as_float(r[c]), __uint_as_float(r[c + 1]), __uint_as_float(r[c + 2]), __uint_as_float(r[c + 3]), gdst, gpush);
         }
         if (row == S1 && (S2 * j) / 16 == cc / 16) {  // ones row: db2; this CTA owns b2[S2*j, S2*j+S2)
           const int c0 = (S2 * j) % 16;
           const size_t off = p.b_off[1] + S2 * j;
 #pragma unroll
           for (int c = 0; c < 16; c += 4)
-            if (c >= c0 && c < c0 + S2)
-              emit_grad4(p, step, off + (c - c0), xs, kXsB2 + (c - c0) * 4, __uint_as_float(r[c]), __uint_as_float(r[c + 1]), __uint_as_float(r[c + 2]), __uint_as_float(r[c + 3]), gdst);
+            if (c >= c0 && c < c0 + S2) {
+              if (gmode)  // staged behind the last-layer block of this warp's staging half, pushed with the dW2 slice
+                sts128(sb + oSTG + 1280 + (c - c0) * 4, __uint_as_float(r[c]), __uint_as_float(r[c + 1]), __uint_as_float(r[c + 2]), __uint_as_float(r[c + 3]));
+              else
+                emit_grad4(p, step, off + (c - c0), xs, kXsB2 + (c - c0) * 4, __uint_as_float(r[c]), __uint_as_float(r[c + 1]), __uint_as_float(r[c + 2]), __uint_as_float(r[c + 3]), gdst, gpush);
+            }
         }
       }
+    }
+    if (gmode && kMid && (warp & 3) == 0) {
+      fence_proxy_async_smem();
+      __syncwarp();
+      if (gpush >= 0 && lane == 0) {
+        for (int q = 0; q < W; ++q) {
+          bulk_s2g(p.xrecv[q] + gpush + p.w_off[1] + static_cast<size_t>(S1 * j) * H2, sb + oSTG2, S1 * H2 * 4);
+          bulk_s2g(p.xrecv[q] + gpush + p.b_off[1] + S2 * j, sb + oSTG + 1280, S2 * 4);
+        }
+        bulk_commit();
+      }
+    }
+    FPROFT(128, 38);
+    if (gmode) {
+      FPROF(15);
+      const int wt = static_cast<int>(threadIdx.x) - 32;
+      const float4 e4 = make_float4(__uint_as_float(kGxEmpty), __uint_as_float(kGxEmpty), __uint_as_float(kGxEmpty), __uint_as_float(kGxEmpty));
+      // ---- peers' dZ1 images -> stages (the control warp loads the matching X^T tiles and issues the MMAs)
+      for (int q = 0; q < npeer; ++q) {
+        const int s = q & 1, r = q < p.rank ? q : q + 1;
+        const uint32_t u = s ? guse1 : guse0;
+        if (u > 0) mbar_wait_long(&bar_ge[s], (u - 1) & 1);
+        if (q == 0) { FPROFT(32, 19); FPROFT(128, 39); }
+        const float* img = p.xrecv[p.rank] + (static_cast<size_t>(xpar) * W + r) * p.total + p.w_off[0];
+        const uint32_t dzt = sb + (s ? oGD1 : oGD0);
+        // 16 chunks of 16 bytes per thread, copied global -> shared asynchronously (no registers, all in flight at once,
+        // rolled loops: the code executed per step is refetched from L2 every time, so its size counts) straight into
+        // their place in the operand image, then validated there; chunks that were still empty are copied again.
+        {
+          uint32_t pend = 0;
+          for (int k = 0; k < 16; ++k)
+            if ((((wt + 128 * k) & 255) >> 2) < B) pend |= 1u << k;  // rows >= B are never sent
+          uint32_t spins = 0;
+          while (pend != 0u) {
+            for (int k = 0; k < 16; ++k) {
+              // chunk c of the receive image = source CTA c / 256, batch row (c % 256) / 4, columns 4 * (c % 4) ..
+              const int c = wt + 128 * k;
+              if ((pend >> k) & 1u) cp_async16(dzt + moff((c & 255) >> 2, S1 * (c >> 8) + 4 * (c & 3)), img + 4 * c);
+            }
+            cp_async_wait_all();
+            for (int k = 0; k < 16; ++k) {
+              const int c = wt + 128 * k;
+              if ((pend >> k) & 1u) {
+                const float4 v = lds128(dzt + moff((c & 255) >> 2, S1 * (c >> 8) + 4 * (c & 3)));
+                if (gx_valid(v)) pend &= ~(1u << k);
+              }
+            }
+            if (*xfail != 0) break;
+            if (pend != 0u && (++spins & 0xF) == 0 && gx_timeout(p, r, 9u, gdeadline)) *xfail = 1;
+          }
+          if (q == 0) { FPROFT(32, 20); FPROFT(128, 40); }
+        }
+        mbar_wait_long(&bar_gx[s], u & 1);  // the X^T tile has landed: its (unused) column 127 becomes the ones column
+        if (q == 0) { FPROFT(32, 22); FPROFT(128, 42); }
+        if (wt < 64) {
+          const uint32_t xt = sb + (s ? oGX1 : (kMid ? oGX0 : oGX0b));
+          asm volatile("st.shared.f32 [%0], %1;" ::"r"(xt + moff(wt, 127)), "f"(1.f) : "memory");
+        }
+        fence_proxy_async_smem();
+        mbar_arrive(&bar_gf[s]);
+        if (s) ++guse1; else ++guse0;
+      }
+      FPROF(0);
+      // ---- small tensors: sum every rank's contribution (own included) in rank order, apply, mark the slots empty
+      {
+        constexpr int nW2 = kMid ? S1 * H2 / 4 : 0, nWL = SL * 16 / 4, nB2 = kMid ? S2 / 4 : 0;
+        const int n_items = nW2 + nWL + nB2 + (j == 0 ? 4 : 0);
+        float* rb = p.xrecv[p.rank] + static_cast<size_t>(xpar) * W * p.total;
+        static_assert(nW2 + nWL + nB2 + 4 <= 3 * 128, "more than three small-tensor items per worker thread");
+        // up to three items per thread, all of them in flight at once; ranks in groups of four (rank order is kept:
+        // the groups are added one after the other)
+        size_t offs[3];
+        float4 w[3], acc[3];
+#pragma unroll
+        for (int i = 0; i < 3; ++i) {
+          const int it = wt + 128 * i;
+          int k = it;
+          size_t off;
+          if (k < nW2) off = p.w_off[1] + static_cast<size_t>(S1 * j) * H2;
+          else if ((k -= nW2) < nWL) off = p.w_off[LAST] + static_cast<size_t>(SL * j) * 16;
+          else if ((k -= nWL) < nB2) off = p.b_off[1] + S2 * j;
+          else { k -= nB2; off = p.b_off[LAST]; }
+          offs[i] = off + static_cast<size_t>(k) * 4;
+          acc[i] = make_float4(0.f, 0.f, 0.f, 0.f);
+          if (it < n_items) w[i] = __ldcg(reinterpret_cast<const float4*>(p.wparams + offs[i]));
+        }
+        FPROFT(32, 23); FPROFT(128, 43);
+        for (int r0 = 0; r0 < W; r0 += 4) {
+          uint32_t pend = 0;
+#pragma unroll
+          for (int i = 0; i < 3; ++i)
+#pragma unroll
+            for (int rr = 0; rr < 4; ++rr)
+              if (wt + 128 * i < n_items && r0 + rr < W) pend |= 1u << (i * 4 + rr);
+          float4 v[3][4];
+          uint32_t spins = 0;
+          while (pend != 0u) {
+#pragma unroll
+            for (int i = 0; i < 3; ++i)
+#pragma unroll
+              for (int rr = 0; rr < 4; ++rr)
+                if ((pend >> (i * 4 + rr)) & 1u) v[i][rr] = ld_poll_f4(rb + static_cast<size_t>(r0 + rr) * p.total + offs[i]);
+#pragma unroll
+            for (int i = 0; i < 3; ++i)
+#pragma unroll
+              for (int rr = 0; rr < 4; ++rr)
+                if (((pend >> (i * 4 + rr)) & 1u) && (gx_valid(v[i][rr]) || *xfail != 0)) pend &= ~(1u << (i * 4 + rr));
+            if (pend != 0u && (++spins & 0xF) == 0 && gx_timeout(p, r0, 10u, gdeadline)) *xfail = 1;
+            if (p.prof != nullptr && threadIdx.x == 32) p.prof[j * 64 + 50] = spins + 1;
+          }
+          FPROFT(32, 24); FPROFT(128, 44);
+#pragma unroll
+          for (int rr = 0; rr < 4; ++rr)
+#pragma unroll
+            for (int i = 0; i < 3; ++i)
+              if (wt + 128 * i < n_items && r0 + rr < W) {
+                acc[i].x += v[i][rr].x; acc[i].y += v[i][rr].y; acc[i].z += v[i][rr].z; acc[i].w += v[i][rr].w;
+                *reinterpret_cast<float4*>(rb + static_cast<size_t>(r0 + rr) * p.total + offs[i]) = e4;
+              }
+        }
+#pragma unroll
+        for (int i = 0; i < 3; ++i)
+          if (wt + 128 * i < n_items) {
+            w[i].x -= step * acc[i].x; w[i].y -= step * acc[i].y; w[i].z -= step * acc[i].z; w[i].w -= step * acc[i].w;
+            *reinterpret_cast<float4*>(p.wparams + offs[i]) = w[i];
+          }
+      }
+      FPROF(1);
     }
     mbar_wait(&bar_mma, mma_phase);
     FPROF(11);
@@ -925,7 +1311,7 @@ mlp_fused_step_kernel(const __grid_constant__ CUtensorMap tmXA, const __grid_con
   mma_phase ^= 1;
   // Last-layer bias: every CTA consumed its copy before delivering dZ1, and wgrad1 (just waited for) was issued
   // after all dZ1 arrived -> CTA 0 may update it now; the end-of-step barrier publishes it.
-  if (j == 0 && worker && row == SL) {
+  if (!gmode && j == 0 && worker && row == SL) {
     const size_t off = p.b_off[LAST];
 #pragma unroll
     for (int c = 0; c < 16; c += 4) emit_grad4(p, step, off + c, xs, kXsBL + c * 4, dbl[c], dbl[c + 1], dbl[c + 2], dbl[c + 3], gdst);
@@ -1124,7 +1510,13 @@ mlp_fused_step_kernel(const __grid_constant__ CUtensorMap tmXA, const __grid_con
   tc_fence_after_sync();
   FPROF(14);
   }  // step loop
+  if (gmode && worker && lane == 0) bulk_wait_read();  // pushes still reading this CTA's staging area
   if ((xmode || pmode) && j == 0 && threadIdx.x == 0) p.xpad[p.rank][kPadFusedEpoch] = epoch0 + static_cast<uint32_t>(nsteps);
+  // global-batch mode: this rank no longer reads the input slots of these steps (every CTA is past the last barrier):
+  // the peers' copy kernels may overwrite them
+  if (gmode && j == 0 && threadIdx.x < W && static_cast<int>(threadIdx.x) != p.rank &&
+      !(p.fault_step >= 0 && static_cast<long long>(p.g0) + nsteps > p.fault_step))
+    st_relaxed_sys(p.xpad[threadIdx.x] + kPadXDone + p.rank, static_cast<uint32_t>(p.g0) + static_cast<uint32_t>(nsteps));
   if (warp == 0) {
     tc_fence_after_sync();
     tmem_dealloc(tm, 512);
@@ -1167,8 +1559,10 @@ extern "C" int dmlp_mlp_fused_plan_create(const dmlp_mlp_fused_desc_t* d, dmlp_m
   // X as K-major A (forward) and as MN-major A (layer-1 weight gradient)
   const int slots = d->x_slots > 1 ? d->x_slots : 1;
   DMLP_REQUIRE(slots == 1 || d->sgd_params_dev != nullptr, "multi-step launches need in-place SGD (sgd_params_dev)");
-  MK(make_tensor_map_2d(&pl->tmXA, d->x_dev, 4, false, in0, d->batch * slots, in0, 32, kFBK, 1));
-  MK(make_tensor_map_2d(&pl->tmXT, d->x_dev, 4, false, in0, d->batch * slots, in0, 32, kFBK, 2));
+  // global-batch mode: x_dev is the gathered input buffer [world][slots][batch][in0] (own rank's ring at its rank index)
+  const int xranks = (d->gx_enable && d->xchg_world > 1) ? d->xchg_world : 1;
+  MK(make_tensor_map_2d(&pl->tmXA, d->x_dev, 4, false, in0, static_cast<uint64_t>(d->batch) * slots * xranks, in0, 32, kFBK, 1));
+  MK(make_tensor_map_2d(&pl->tmXT, d->x_dev, 4, false, in0, static_cast<uint64_t>(d->batch) * slots * xranks, in0, 32, kFBK, 2));
   MK(make_tensor_map_2d(&pl->tmW1, P + d->w_off[0], 4, false, H1, in0, H1, 32, kKGroupsMax * 8, 2));
   const int last = L - 1;
   if (L == 3) {
@@ -1202,13 +1596,18 @@ extern "C" int dmlp_mlp_fused_plan_create(const dmlp_mlp_fused_desc_t* d, dmlp_m
     p.world = d->xchg_world;
     p.rank = d->xchg_rank;
     for (int r = 0; r < d->xchg_world; ++r) {
-      DMLP_REQUIRE((d->xchg_recv_dev[r] || d->xchg_reducer_ctas > 0) && d->xchg_pad_dev[r], "fused step: rank %d's receive area / signal pad is not mapped", r);
+      DMLP_REQUIRE((d->xchg_recv_dev[r] || (d->xchg_reducer_ctas > 0 && !d->gx_enable)) && d->xchg_pad_dev[r], "fused step: rank %d's receive area / signal pad is not mapped", r);
       p.xrecv[r] = d->xchg_recv_dev[r];
       p.xpad[r] = d->xchg_pad_dev[r];
     }
     p.xstatus = d->xchg_status;
     p.xtimeout_ns = d->xchg_timeout_ns ? d->xchg_timeout_ns : 10ull * 1000 * 1000 * 1000;
     p.total = d->param_count;
+    if (d->gx_enable) {
+      DMLP_REQUIRE(d->xchg_reducer_ctas == 0, "fused step: the global-batch mode has no reducer CTAs");
+      p.gx = 1;
+      p.xslots = slots;
+    }
     if (d->xchg_reducer_ctas > 0) {
       DMLP_REQUIRE(d->xchg_reducer_ctas % kFC == 0 && d->xchg_reducer_ctas <= kMaxRedCtas && d->param_count % 4 == 0,
                    "fused step: reducer CTAs must come in clusters of %d (<= %d) and the parameter count be a multiple of 4", kFC,
@@ -1223,6 +1622,7 @@ extern "C" int dmlp_mlp_fused_plan_create(const dmlp_mlp_fused_desc_t* d, dmlp_m
   }
   p.nsteps = 1;
   p.slot0 = 0;
+  p.fault_step = -1;
   {
     const char* e = getenv("DMLP_FUSED_BULK");
     p.bulk_update = e ? atoi(e) : 0;  // measured: 22.3 us/step with bulk reduce-adds vs 21.3 with red.global (default)
@@ -1236,9 +1636,9 @@ extern "C" int dmlp_mlp_fused_plan_destroy(dmlp_mlp_fused_plan_t h) {
   return DMLP_OK;
 }
 
-template <int S1, int S2>
+template <int S1, int S2, bool GX>
 static int launch_fused(const FusedPlan* pl, const FusedParams& prm, cudaStream_t st) {
-  auto kern = mlp_fused_step_kernel<S1, S2>;
+  auto kern = mlp_fused_step_kernel<S1, S2, GX>;
   static unsigned long long attr_mask = 0;
   int dev = 0;
   DMLP_CUDA_CHECK(cudaGetDevice(&dev));
@@ -1276,8 +1676,38 @@ static int launch_fused(const FusedPlan* pl, const FusedParams& prm, cudaStream_
 extern "C" int dmlp_mlp_fused_step(dmlp_mlp_fused_plan_t h, void* stream) {
   const FusedPlan* pl = reinterpret_cast<const FusedPlan*>(h);
   DMLP_REQUIRE(pl, "null fused plan");
-  if (pl->layers == 3) return launch_fused<16, 8>(pl, pl->p, as_stream(stream));
-  return launch_fused<16, 0>(pl, pl->p, as_stream(stream));
+  if (pl->layers == 3) return launch_fused<16, 8, false>(pl, pl->p, as_stream(stream));
+  return launch_fused<16, 0, false>(pl, pl->p, as_stream(stream));
+}
+
+// Global-batch data-parallel mode (plan created with gx_enable): `global_step` is the index of the first of these steps
+// since the trainer started (identical on every rank; it selects the parity of the receive areas) and `inputs_ready` the
+// step count the peers' input-ready words must have reached (dmlp_input_exchange) before their inputs are read.
+extern "C" int dmlp_mlp_fused_steps_gx(dmlp_mlp_fused_plan_t h, int slot0, int nsteps, unsigned long long global_step,
+                                       unsigned int inputs_ready, void* stream) {
+  const FusedPlan* pl = reinterpret_cast<const FusedPlan*>(h);
+  DMLP_REQUIRE(pl && pl->p.gx, "dmlp_mlp_fused_steps_gx: the plan was not created for the global-batch mode");
+  DMLP_REQUIRE(nsteps >= 1 && slot0 >= 0 && slot0 + nsteps <= pl->slots, "dmlp_mlp_fused_steps_gx: slots [%d, %d) outside the plan's %d",
+               slot0, slot0 + nsteps, pl->slots);
+  FusedParams prm = pl->p;
+  prm.nsteps = nsteps;
+  prm.slot0 = slot0;
+  prm.g0 = global_step;
+  prm.xneed = inputs_ready;
+  prm.labels = pl->p.labels + static_cast<size_t>(slot0) * pl->p.B;
+  prm.metrics = pl->p.metrics + 2 * static_cast<size_t>(slot0);
+  if (pl->layers == 3) return launch_fused<16, 8, true>(pl, prm, as_stream(stream));
+  return launch_fused<16, 0, true>(pl, prm, as_stream(stream));
+}
+
+// Fault injection for the global-batch mode: from global step `step` on this rank behaves as if it had died (sends
+// nothing, waits for nothing); its peers' watchdogs then fire. -1 switches it off. Also refreshes the watchdog budget.
+extern "C" int dmlp_mlp_fused_set_fault(dmlp_mlp_fused_plan_t h, long long step, unsigned long long timeout_ns) {
+  FusedPlan* pl = reinterpret_cast<FusedPlan*>(h);
+  DMLP_REQUIRE(pl, "null fused plan");
+  pl->p.fault_step = step;
+  if (timeout_ns) pl->p.xtimeout_ns = timeout_ns;
+  return DMLP_OK;
 }
 
 extern "C" int dmlp_mlp_fused_steps(dmlp_mlp_fused_plan_t h, int slot0, int nsteps, void* stream) {
@@ -1291,6 +1721,6 @@ extern "C" int dmlp_mlp_fused_steps(dmlp_mlp_fused_plan_t h, int slot0, int nste
   prm.slot0 = slot0;
   prm.labels = pl->p.labels + static_cast<size_t>(slot0) * pl->p.B;
   prm.metrics = pl->p.metrics + 2 * static_cast<size_t>(slot0);
-  if (pl->layers == 3) return launch_fused<16, 8>(pl, prm, as_stream(stream));
-  return launch_fused<16, 0>(pl, prm, as_stream(stream));
+  if (pl->layers == 3) return launch_fused<16, 8, false>(pl, prm, as_stream(stream));
+  return launch_fused<16, 0, false>(pl, prm, as_stream(stream));
 }

@@ -78,15 +78,38 @@ __device__ __forceinline__ bool mbar_try_wait(uint64_t* bar, uint32_t parity) {
   return ok != 0;
 }
 // Blocks until the phase with the given parity has completed. Traps on timeout.
-__device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
-  if (mbar_try_wait(bar, parity)) return;
+// The slow path is one out-of-line function: inlined at every wait it was ~7 % of the fused kernel's code, and a
+// kernel that runs its whole body once per step pays for code size in instruction fetches from L2.
+static __device__ __noinline__ void mbar_wait_slow(uint32_t bar_s, uint32_t parity) {
   const long long t0 = clock64();
-  while (!mbar_try_wait(bar, parity)) {
+  for (;;) {
+    uint32_t ok;
+    asm volatile(
+        "{\n"
+        ".reg .pred p;\n"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n"
+        "selp.u32 %0, 1, 0, p;\n"
+        "}\n"
+        : "=r"(ok)
+        : "r"(bar_s), "r"(parity)
+        : "memory");
+    if (ok) return;
     if (clock64() - t0 > DMLP_MBAR_TIMEOUT_CYCLES) {
       printf("dmlp: mbarrier wait timed out (block %d,%d thread %d)\n", blockIdx.x, blockIdx.y,
              threadIdx.x);
       __trap();
     }
+  }
+}
+__device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
+  if (mbar_try_wait(bar, parity)) return;
+  mbar_wait_slow(smem_u32(bar), parity);
+}
+
+// Same without the trap: for barriers whose completion depends on ANOTHER GPU (the waits that feed them carry the
+// communicator's own watchdog, which may be set longer than the trap budget above).
+__device__ __forceinline__ void mbar_wait_long(uint64_t* bar, uint32_t parity) {
+  while (!mbar_try_wait(bar, parity)) {
   }
 }
 

@@ -69,7 +69,15 @@ struct Trainer {
   void* peer_shadow[DMLP_MAX_RANKS];
   float* peer_grads[2][DMLP_MAX_RANKS];
   float* peer_recv[DMLP_MAX_RANKS];  // fused step with in-kernel gradient exchange: [2][world][total] receive areas
-  unsigned long long* fused_prof = nullptr;  // DMLP_FUSED_PROF=1: [8 CTAs][16] phase stamps of the ring plan's last step
+  unsigned long long* fused_prof = nullptr;  // DMLP_FUSED_PROF=1: [8 CTAs][64] phase stamps of the ring plan's last step
+  bool gx = false;                    // global-batch mode (default on real GPUs): dZ1 / input exchange, see mlp_fused.cu
+  float* peer_xall[DMLP_MAX_RANKS];   // rank r's gathered input buffer [world][kRingSlots][batch][in0] as mapped here
+  unsigned long long gsteps = 0;      // steps run in global-batch mode (identical on every rank)
+  unsigned long long ring_end[2] = {0, 0};  // gsteps at the end of the chunk that last used ring chunk c
+  uint32_t* gx_pads[DMLP_MAX_RANKS];
+  uint32_t* gx_status = nullptr;
+  long long fault_step = -1;          // fault injection: this rank goes silent from this global step on
+  bool failed = false;                // a collective watchdog fired: the trainer refuses further steps
   bool pdp = false;                   // persistent data-parallel launches (fused == 4): compute cluster + reducer CTAs
   bool xchg = false;                  // ... is in use (multi-GPU, fused step, fused != 2, no NVLS arena)
   bool owns_params = false;
@@ -231,13 +239,13 @@ static int build_plans(Trainer* t) {
       if (t->comm == nullptr && t->cfg.fused != 2) { f.sgd_params_dev = t->params; f.lr_dev = t->lr_dev; }
       TRY(dmlp_mlp_fused_plan_create(&f, &t->rplan[slot]));
     }
-    if ((t->comm == nullptr && t->cfg.fused != 2) || t->xchg || t->pdp) {
+    if ((t->comm == nullptr && t->cfg.fused != 2) || t->xchg || t->pdp || t->gx) {
       dmlp_mlp_fused_desc_t f;
       memset(&f, 0, sizeof(f));
       f.num_layers = L.L;
       for (int l = 0; l <= L.L; ++l) f.dims[l] = t->cfg.dims[l];
       f.batch = B;
-      f.x_dev = t->x_ring;
+      f.x_dev = t->gx ? t->peer_xall[t->rank] : t->x_ring;
       f.labels_dev = t->y_ring;
       f.params_dev = t->params;
       f.grads_dev = t->grads[0];
@@ -250,12 +258,12 @@ static int build_plans(Trainer* t) {
         const char* e = getenv("DMLP_FUSED_PROF");
         if (e && atoi(e) > 0) {
           void* pp = nullptr;
-          TRY(dev_alloc(t, 8 * 16 * 8, &pp));
+          TRY(dev_alloc(t, 8 * 64 * 8, &pp));
           t->fused_prof = static_cast<unsigned long long*>(pp);
           f.prof_dev = pp;
         }
       }
-      if (t->xchg || t->pdp) {
+      if (t->xchg || t->pdp || t->gx) {
         uint32_t* pads[DMLP_MAX_RANKS];
         uint32_t *state = nullptr, *host_flags = nullptr, dead = 0;
         unsigned long long timeout_ns = 0;
@@ -267,6 +275,11 @@ static int build_plans(Trainer* t) {
         f.xchg_status = host_flags + 4;
         f.xchg_timeout_ns = timeout_ns;
         f.param_count = L.total;
+        if (t->gx) {
+          f.gx_enable = 1;
+          for (int r = 0; r < t->world; ++r) t->gx_pads[r] = pads[r];
+          t->gx_status = host_flags + 4;
+        }
         if (t->pdp) {
           static int red_env = -1;
           if (red_env < 0) { const char* e = getenv("DMLP_FUSED_REDUCERS"); red_env = (e && atoi(e) > 0) ? atoi(e) : 56; }
@@ -434,6 +447,17 @@ static int run_fused_ring(Trainer* t, const float* x_host, const int32_t* y_host
     }
     chunk_first_step[c] = -1;
   };
+  unsigned long long gx_timeout_ns = 0;
+  if (t->gx) {
+    // the watchdog budget and the fault-injection step are read at every run (dmlp_comm_set_timeout_ms may have changed)
+    uint32_t* pads[DMLP_MAX_RANKS];
+    uint32_t *state = nullptr, *host_flags = nullptr, dead = 0;
+    int crank = 0, cworld = 0, cdev = 0;
+    TRY(dmlp_comm_internal_view(t->comm, t->local_idx, pads, &state, &host_flags, &gx_timeout_ns, &dead, &crank, &cworld, &cdev));
+    long long fs = t->fault_step;
+    if (fs < 0 && ((dead >> t->rank) & 1u)) fs = 0;  // dmlp_comm_inject_dead_ranks: dead from now on
+    TRY(dmlp_mlp_fused_set_fault(t->ring_plan, fs, gx_timeout_ns));
+  }
   if (start_event) DMLP_CUDA_CHECK(cudaEventRecord(reinterpret_cast<cudaEvent_t>(start_event), t->s_main));
   // Gradient buffers alternate with the GLOBAL step parity (slot parity == step parity), also across
   // calls: a call that starts on an odd step begins at slot 1 of its first chunk.
@@ -463,6 +487,18 @@ static int run_fused_ring(Trainer* t, const float* x_host, const int32_t* y_host
     }
     DMLP_CUDA_CHECK(cudaEventRecord(t->ev_ring_h2d[c], t->s_copy));
     DMLP_CUDA_CHECK(cudaStreamWaitEvent(t->s_main, t->ev_ring_h2d[c], 0));
+    const unsigned long long g_chunk0 = t->gsteps, g_chunk1 = t->gsteps + static_cast<unsigned long long>(n);
+    if (t->gx) {
+      // all-gather the chunk's inputs: into the same ring slots of every peer, once the peers are done with the steps
+      // that last used them; the step kernels wait for the peers' ready words (= g_chunk1) before reading peer inputs
+      void* dsts[DMLP_MAX_RANKS];
+      const size_t ring_off = static_cast<size_t>(t->rank) * kRingSlots * B * xin + static_cast<size_t>(c * kRingChunk + off) * B * xin;
+      for (int r = 0; r < t->world; ++r) dsts[r] = t->peer_xall[r] + ring_off;
+      TRY(dmlp_input_exchange(xdst, dsts, sizeof(float) * n * B * xin, t->gx_pads, t->rank, t->world,
+                              static_cast<uint32_t>(t->ring_end[c]), static_cast<uint32_t>(g_chunk1), gx_timeout_ns, t->gx_status,
+                              t->s_copy));
+      t->ring_end[c] = g_chunk1;
+    }
     static int per_launch_env = -1;  // experiment knob: cap on steps per launch (default: the whole chunk)
     if (per_launch_env < 0) { const char* e = getenv("DMLP_FUSED_STEPS_PER_LAUNCH"); per_launch_env = (e && atoi(e) > 0) ? atoi(e) : kRingChunk; }
     for (int i = 0; i < n;) {
@@ -477,7 +513,12 @@ static int run_fused_ring(Trainer* t, const float* x_host, const int32_t* y_host
         // as many steps as share this learning rate, in one launch
         int m = 1;
         while (i + m < n && m < per_launch_env && (!lr_schedule || lr_schedule[s + m] == t->lr_host[0])) ++m;
-        TRY(dmlp_mlp_fused_steps(t->ring_plan, slot, m, t->s_main));
+        if (t->gx) {
+          TRY(dmlp_mlp_fused_steps_gx(t->ring_plan, slot, m, g_chunk0 + static_cast<unsigned long long>(i),
+                                      static_cast<unsigned int>(g_chunk1), t->s_main));
+        } else {
+          TRY(dmlp_mlp_fused_steps(t->ring_plan, slot, m, t->s_main));
+        }
         ++launches;
         i += m;
       } else {
@@ -497,6 +538,7 @@ static int run_fused_ring(Trainer* t, const float* x_host, const int32_t* y_host
     last_c = c;
     s0 += n;
     ++ci;
+    if (t->gx) t->gsteps = g_chunk1;
   }
   if (stop_event) DMLP_CUDA_CHECK(cudaEventRecord(reinterpret_cast<cudaEvent_t>(stop_event), t->s_main));
   DMLP_CUDA_CHECK(cudaStreamSynchronize(t->s_main));
@@ -508,8 +550,10 @@ static int run_fused_ring(Trainer* t, const float* x_host, const int32_t* y_host
   if (t->comm) {
     uint32_t st[5];
     TRY(dmlp_comm_status(t->comm, st));
-    if (st[0] != 0)
+    if (st[0] != 0) {
+      t->failed = true;  // sticky, like a FAILED communicator of the reference (gpu_coordinator_server.go:281-285)
       return set_error(DMLP_ERR_TIMEOUT, "collective watchdog: rank %u waited for rank %u (phase %u)", st[1], st[2], st[3]);
+    }
   }
   return DMLP_OK;
 }
@@ -533,8 +577,11 @@ extern "C" int dmlp_trainer_arena_bytes(const dmlp_trainer_config_t* cfg, size_t
   size_t b = 3 * align_up(n * 4, 256);
   if (cfg->dtype == DMLP_BF16) b += align_up(n * 2, 256);
   // fused step with in-kernel gradient exchange: receive slots [2 parities][up to 8 ranks][params]
-  if (cfg->dtype == DMLP_F32 && cfg->fused == 3 && dmlp_mlp_fused_supported(cfg->num_layers, cfg->dims, cfg->batch))
-    b += 2 * DMLP_MAX_RANKS * align_up(n * 4, 256);
+  const bool fused_ok = cfg->dtype == DMLP_F32 && dmlp_mlp_fused_supported(cfg->num_layers, cfg->dims, cfg->batch);
+  if (fused_ok && (cfg->fused == 3 || cfg->fused == 5 || cfg->fused == -1)) b += 2 * DMLP_MAX_RANKS * align_up(n * 4, 256);
+  // global-batch mode: the gathered input buffer [ranks][ring slots][batch][in0]
+  if (fused_ok && (cfg->fused == 5 || cfg->fused == -1))
+    b += align_up(static_cast<size_t>(DMLP_MAX_RANKS) * kRingSlots * cfg->batch * cfg->dims[0] * 4, 256);
   *bytes = b;
   return DMLP_OK;
 }
@@ -617,6 +664,8 @@ extern "C" int dmlp_trainer_create(const dmlp_trainer_config_t* cfg, int device,
   memset(t->peer_shadow, 0, sizeof(t->peer_shadow));
   memset(t->peer_grads, 0, sizeof(t->peer_grads));
   memset(t->peer_recv, 0, sizeof(t->peer_recv));
+  memset(t->peer_xall, 0, sizeof(t->peer_xall));
+  memset(t->gx_pads, 0, sizeof(t->gx_pads));
   t->cfg = *cfg;
   t->dev = device;
   t->comm = (world > 1) ? comm : nullptr;
@@ -629,7 +678,7 @@ extern "C" int dmlp_trainer_create(const dmlp_trainer_config_t* cfg, int device,
   const int B = cfg->batch;
   t->fused_ce = L.out_pad[L.L - 1] <= 32;
   t->fused_step = !t->bf16 && cfg->fused != 0 && dmlp_mlp_fused_supported(cfg->num_layers, cfg->dims, cfg->batch) != 0;
-  if ((cfg->fused == 1 || cfg->fused == 3 || cfg->fused == 4) && !t->fused_step) {
+  if ((cfg->fused == 1 || cfg->fused == 3 || cfg->fused == 4 || cfg->fused == 5) && !t->fused_step) {
     set_error(DMLP_ERR_UNSUPPORTED, "fused step kernel does not support this shape / precision");
     delete t;
     return DMLP_ERR_UNSUPPORTED;
@@ -670,8 +719,13 @@ extern "C" int dmlp_trainer_create(const dmlp_trainer_config_t* cfg, int device,
       size_t cap = 0;
       int e = dmlp_comm_arena_ptr(t->comm, local_idx, r, &base, &cap);
       if (e != DMLP_OK) { if (r == rank) return fail(e); continue; }  // peers unmapped: ring still works
-      const bool want_x = t->fused_step && cfg->fused == 3;
-      size_t need = arena_offset + 3 * pbytes + (t->bf16 ? sbytes : 0) + (want_x ? 2 * static_cast<size_t>(world) * pbytes : 0);
+      // fused == -1 (auto) takes the global-batch mode when the arena was sized for it (dmlp_trainer_arena_bytes)
+      const size_t xall_bytes = align_up(static_cast<size_t>(world) * kRingSlots * B * L.in[0] * 4, 256);
+      const size_t base_need = arena_offset + 3 * pbytes + (t->bf16 ? sbytes : 0);
+      const size_t recv_bytes = 2 * static_cast<size_t>(world) * pbytes;
+      const bool want_g = t->fused_step && (cfg->fused == 5 || (cfg->fused == -1 && cap >= base_need + recv_bytes + xall_bytes));
+      const bool want_x = t->fused_step && (cfg->fused == 3 || want_g);
+      size_t need = base_need + (want_x ? recv_bytes : 0) + (want_g ? xall_bytes : 0);
       if (cap < need) { set_error(DMLP_ERR_INVALID, "communicator arena too small: %zu < %zu", cap, need); return fail(DMLP_ERR_INVALID); }
       uint8_t* b = static_cast<uint8_t*>(base) + arena_offset;
       t->peer_params[r] = reinterpret_cast<float*>(b);
@@ -679,6 +733,7 @@ extern "C" int dmlp_trainer_create(const dmlp_trainer_config_t* cfg, int device,
       t->peer_grads[1][r] = reinterpret_cast<float*>(b + 2 * pbytes);
       if (t->bf16) t->peer_shadow[r] = b + 3 * pbytes;
       if (want_x) t->peer_recv[r] = reinterpret_cast<float*>(b + 3 * pbytes);
+      if (want_g) t->peer_xall[r] = reinterpret_cast<float*>(b + 3 * pbytes + recv_bytes);
     }
     // Persistent data-parallel launches (compute cluster + reducer CTAs in one kernel, several steps per launch) are the
     // default for the cluster-fused shapes on real multi-GPU communicators; fused == 1 keeps the two-kernel chain.
@@ -688,6 +743,15 @@ extern "C" int dmlp_trainer_create(const dmlp_trainer_config_t* cfg, int device,
     for (int r = 0; r < world; ++r) t->pdp = t->pdp && t->peer_grads[0][r] != nullptr;
     t->xchg = t->fused_step && cfg->fused == 3;
     for (int r = 0; r < world; ++r) t->xchg = t->xchg && t->peer_recv[r] != nullptr;
+    // Global-batch mode: the default for the cluster-fused shapes on real multi-GPU communicators (fused == 4 keeps the
+    // persistent compute-cluster + reducer launch, fused == 1 the two-kernel chain).
+    t->gx = t->fused_step && !emulated && (cfg->fused == 5 || cfg->fused == -1);
+    for (int r = 0; r < world; ++r) t->gx = t->gx && t->peer_recv[r] != nullptr && t->peer_xall[r] != nullptr;
+    if (cfg->fused == 5 && !t->gx) {
+      set_error(DMLP_ERR_UNSUPPORTED, "global-batch mode needs one GPU per rank and every rank's arena mapped");
+      return fail(DMLP_ERR_UNSUPPORTED);
+    }
+    if (t->gx) t->pdp = false;
     t->params = t->peer_params[rank];
     t->grads[0] = t->peer_grads[0][rank];
     t->grads[1] = t->peer_grads[1][rank];
@@ -734,7 +798,22 @@ extern "C" int dmlp_trainer_create(const dmlp_trainer_config_t* cfg, int device,
   for (int l = 0; l < L.L; ++l) CUF(cudaEventCreateWithFlags(&t->ev_dz[l], cudaEventDisableTiming));
   for (int l = 0; l < L.L; ++l) CUF(cudaEventCreateWithFlags(&t->ev_bucket[l], cudaEventDisableTiming));
   if (t->fused_step) {
-    TRYF(dev_alloc(t, static_cast<size_t>(kRingSlots) * B * L.in[0] * 4, &p)); t->x_ring = static_cast<float*>(p);
+    if (t->gx) {
+      // own ring = this rank's part of its gathered input buffer; receive areas start out "empty" (0xFF bytes), the
+      // exchange words of the signal pad at zero. Python barriers across the ranks before the first step.
+      t->x_ring = t->peer_xall[rank] + static_cast<size_t>(rank) * kRingSlots * B * L.in[0];
+      CUF(cudaMemset(t->peer_recv[rank], 0xFF, 2 * static_cast<size_t>(world) * pbytes));
+      uint32_t* pads[DMLP_MAX_RANKS];
+      uint32_t *state = nullptr, *host_flags = nullptr, dead = 0;
+      unsigned long long timeout_ns = 0;
+      int crank = 0, cworld = 0, cdev = 0;
+      TRYF(dmlp_comm_internal_view(t->comm, t->local_idx, pads, &state, &host_flags, &timeout_ns, &dead, &crank, &cworld, &cdev));
+      CUF(cudaMemset(pads[rank] + kPadXReady, 0, 4 * DMLP_MAX_RANKS * kXPushCtas));
+      CUF(cudaMemset(pads[rank] + kPadXDone, 0, 4 * DMLP_MAX_RANKS));
+      CUF(cudaDeviceSynchronize());
+    } else {
+      TRYF(dev_alloc(t, static_cast<size_t>(kRingSlots) * B * L.in[0] * 4, &p)); t->x_ring = static_cast<float*>(p);
+    }
     TRYF(dev_alloc(t, static_cast<size_t>(kRingSlots) * B * 4, &p)); t->y_ring = static_cast<int*>(p);
     TRYF(dev_alloc(t, static_cast<size_t>(kRingSlots) * 8, &p)); t->metrics_ring = static_cast<float*>(p);
     for (int c = 0; c < kRingChunks; ++c) {
@@ -778,6 +857,27 @@ extern "C" int dmlp_trainer_set_lr(dmlp_trainer_t h, float lr) {
   return DMLP_OK;
 }
 
+// Fault injection (BASELINE config 5): this rank stops taking part in the exchange from global step `step` on
+// (counted from the trainer's creation; -1 = never), as if its GPU had died mid-run. Its peers' in-kernel watchdogs
+// fire after the communicator's timeout, dmlp_trainer_run returns DMLP_ERR_TIMEOUT there and the trainer turns FAILED.
+// Mirrors the reference's device-failure test (gpu_coordinator_server_test.go:370-429).
+extern "C" int dmlp_trainer_set_fault(dmlp_trainer_t h, long long step) {
+  Trainer* t = reinterpret_cast<Trainer*>(h);
+  DMLP_REQUIRE(t, "null trainer");
+  t->fault_step = step;
+  return DMLP_OK;
+}
+
+// 0 = usable, 1 = FAILED (sticky). mode: 0 single GPU / per-layer, 1 two-kernel chain, 3 in-cluster exchange,
+// 4 persistent compute + reducer launch, 5 global-batch mode.
+extern "C" int dmlp_trainer_state(dmlp_trainer_t h, int* failed, int* mode) {
+  Trainer* t = reinterpret_cast<Trainer*>(h);
+  DMLP_REQUIRE(t, "null trainer");
+  if (failed) *failed = t->failed ? 1 : 0;
+  if (mode) *mode = t->gx ? 5 : t->pdp ? 4 : t->xchg ? 3 : (t->fused_step && t->comm) ? 1 : 0;
+  return DMLP_OK;
+}
+
 extern "C" int dmlp_trainer_launches_last_run(dmlp_trainer_t h, long long* n) {
   Trainer* t = reinterpret_cast<Trainer*>(h);
   DMLP_REQUIRE(t && n, "bad arguments");
@@ -804,6 +904,8 @@ extern "C" int dmlp_trainer_run(dmlp_trainer_t h, const float* x_host, const int
                                 float* metrics_out, int use_graph, void* start_event, void* stop_event) {
   Trainer* t = reinterpret_cast<Trainer*>(h);
   DMLP_REQUIRE(t && x_host && y_host && num_batches > 0 && steps >= 0, "dmlp_trainer_run: bad arguments");
+  if (t->failed)
+    return set_error(DMLP_ERR_ABORTED, "the trainer's communicator is FAILED (a collective watchdog fired earlier); create a new one");
   DeviceGuard g(t->dev);
   const int B = t->cfg.batch;
   const size_t xin = t->lay.in[0];

@@ -55,7 +55,9 @@ class TrainerConfig:
     use_graph: bool = True
     fused: int = -1                            # cluster-fused step kernel: -1 auto, 0 off, 1 require, 2 require + separate
                                                # update kernel, 3 require + gradient exchange inside the step kernel (world > 1),
-                                               # 4 require + persistent launch: compute cluster + reducer CTAs (world > 1)
+                                               # 4 require + persistent launch: compute cluster + reducer CTAs (world > 1),
+                                               # 5 require + global-batch mode: dZ1 / input exchange instead of the dW1
+                                               #   all-reduce (world > 1; what -1 picks on real GPUs)
     schedule: str = "constant"
     seed: int = 0
     watchdog_ms: int = 10000
@@ -99,6 +101,8 @@ def _declare(lib) -> None:
         "dmlp_trainer_run_resident": [vp, i32, i32, vp, vp],
         "dmlp_trainer_eval": [vp, vp, vp, sz, C.POINTER(C.c_double), C.POINTER(C.c_longlong)],
         "dmlp_trainer_buffer": [vp, i32, i32, C.POINTER(vp)],
+        "dmlp_trainer_set_fault": [vp, C.c_longlong],
+        "dmlp_trainer_state": [vp, C.POINTER(i32), C.POINTER(i32)],
     }
     for name, args in sigs.items():
         fn = getattr(lib, name)
@@ -199,6 +203,11 @@ class Trainer:
         self.global_step = 0
         self._pinned: Dict[int, Tuple[PinnedArray, PinnedArray]] = {}
         self.set_params(self.layout.init_reference(cfg.seed))
+        if process_group and self.world > 1:
+            # every rank's receive areas / signal words are initialised before anybody's first step writes into them
+            import torch.distributed as dist
+            native.check(self.lib.dmlp_device_sync(self.device))
+            dist.barrier()
 
     # ------------------------------------------------------------------ parameters
     def _param_ptr(self) -> Tuple[int, int]:
@@ -247,6 +256,28 @@ class Trainer:
         self.set_params(self.layout.from_reference_bytes(blob))
         self.global_step = int(meta.get("global_step", self.global_step))
         return meta
+
+    # ------------------------------------------------------------------ failure handling
+    def inject_fault(self, step: int) -> None:
+        """Fault injection: this rank stops taking part in the gradient exchange from global step ``step`` on (counted
+        from this trainer's creation; -1 switches it off), as if its GPU had died. The peers' in-kernel watchdogs fire
+        after ``watchdog_ms``; their ``fit`` raises ``native.DmlpError`` (TIMEOUT) and the trainer turns FAILED — the
+        training-path analogue of the reference's device-failure test (gpu_coordinator_server_test.go:370-429)."""
+        native.check(self.lib.dmlp_trainer_set_fault(self._h, int(step)))
+
+    @property
+    def failed(self) -> bool:
+        f, m = C.c_int(), C.c_int()
+        native.check(self.lib.dmlp_trainer_state(self._h, C.byref(f), C.byref(m)))
+        return bool(f.value)
+
+    @property
+    def dp_mode(self) -> int:
+        """Data-parallel variant in use: 0 none/per-layer, 1 two-kernel chain, 3 in-cluster exchange, 4 persistent
+        compute + reducer launch, 5 global-batch mode."""
+        f, m = C.c_int(), C.c_int()
+        native.check(self.lib.dmlp_trainer_state(self._h, C.byref(f), C.byref(m)))
+        return m.value
 
     def set_lr(self, lr: float) -> None:
         native.check(self.lib.dmlp_trainer_set_lr(self._h, float(lr)))

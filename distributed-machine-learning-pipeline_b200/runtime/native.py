@@ -82,6 +82,7 @@ class MlpFusedDesc(C.Structure):
         ("xchg_recv", C.c_void_p * MAX_RANKS), ("xchg_pad", C.c_void_p * MAX_RANKS),
         ("xchg_status", C.c_void_p), ("xchg_timeout_ns", C.c_ulonglong), ("param_count", C.c_size_t),
         ("xchg_reducer_ctas", C.c_int), ("xchg_grads", (C.c_void_p * MAX_RANKS) * 2),
+        ("gx_enable", C.c_int),
     ]
 
 

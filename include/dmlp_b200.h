@@ -319,10 +319,31 @@ typedef struct {
    * steps per launch work on several GPUs too. xchg_recv_dev is not used in this mode. */
   int xchg_reducer_ctas;
   float* xchg_grads_dev[2][DMLP_MAX_RANKS];
+  /* Global-batch mode (gx_enable != 0 with xchg_world > 1 and xchg_reducer_ctas == 0; the default on real GPUs): the
+   * ranks exchange the FACTORS of the layer-1 weight gradient instead of the gradient: inputs are all-gathered ahead of
+   * time (dmlp_input_exchange; x_dev is then [world][x_slots][batch][dims[0]], own ring at index xchg_rank), every CTA
+   * pushes its dZ1 slice into all peers' receive areas (xchg_recv_dev, pre-filled with 0xFF bytes) and each rank
+   * accumulates dW1 = sum_r X_r^T dZ1_r itself in rank order; W2/W3/biases are all-reduced in the kernel by push +
+   * rank-ordered sum. Arrival is detected on the data, no flags. Launch with dmlp_mlp_fused_steps_gx. */
+  int gx_enable;
 } dmlp_mlp_fused_desc_t;
 typedef struct dmlp_mlp_fused_opaque* dmlp_mlp_fused_plan_t;
 int dmlp_mlp_fused_supported(int num_layers, const int* dims, int batch);
 int dmlp_mlp_fused_plan_create(const dmlp_mlp_fused_desc_t* desc, dmlp_mlp_fused_plan_t* out);
+/* Global-batch mode launches: global_step = index of the first step (same on every rank), inputs_ready = value the
+ * peers' input-ready words must have reached. dmlp_mlp_fused_set_fault: fault injection (rank goes silent from that
+ * global step on; -1 = off) and watchdog budget (0 keeps it). Reference for the failure semantics:
+ * DSML/gpu_coordinator_service/gpu_coordinator_server.go:339-346. */
+int dmlp_mlp_fused_steps_gx(dmlp_mlp_fused_plan_t plan, int slot0, int nsteps, unsigned long long global_step,
+                            unsigned int inputs_ready, void* stream);
+int dmlp_mlp_fused_set_fault(dmlp_mlp_fused_plan_t plan, long long step, unsigned long long timeout_ns);
+/* Input all-gather for the global-batch mode (csrc/input_exchange.cu): writes `bytes` (x16) from src_local into the
+ * same place of every peer's gathered input buffer (dst_peers[r], r != rank, peer-mapped) once all peers' "done"
+ * words in this rank's signal pad reached need_done, then publishes ready_value in the peers' "ready" words.
+ * No counterpart in the reference (inputs never leave the client there, DSML/client/client.go:596-608). */
+int dmlp_input_exchange(const void* src_local, void* const* dst_peers, size_t bytes, uint32_t* const* pads, int rank,
+                        int world, uint32_t need_done, uint32_t ready_value, unsigned long long timeout_ns,
+                        uint32_t* status, void* stream);
 /* Runs `nsteps` consecutive optimisation steps on ring slots slot0 .. slot0+nsteps-1 in ONE launch (plan created with
  * x_slots > 1 and sgd_params_dev: the weights are updated in place between the steps inside the kernel). */
 int dmlp_mlp_fused_steps(dmlp_mlp_fused_plan_t plan, int slot0, int nsteps, void* stream);
@@ -374,6 +395,12 @@ int dmlp_trainer_kernels_per_step(dmlp_trainer_t t, int* n);
 /* Kernel launches issued by the most recent dmlp_trainer_run on the fused path (a launch may cover several steps);
  * 0 when the per-layer path ran (use kernels_per_step * steps there). */
 int dmlp_trainer_launches_last_run(dmlp_trainer_t t, long long* n);
+/* Fault injection on the training path (BASELINE config 5; reference test: gpu_coordinator_server_test.go:370-429):
+ * this rank goes silent from global step `step` on (-1: never). dmlp_trainer_state: failed = 1 once a collective
+ * watchdog fired (sticky: dmlp_trainer_run then returns DMLP_ERR_ABORTED, like AllReduceRing on a FAILED communicator,
+ * gpu_coordinator_server.go:281-285); mode = data-parallel variant in use (5 = global-batch mode). */
+int dmlp_trainer_set_fault(dmlp_trainer_t trainer, long long step);
+int dmlp_trainer_state(dmlp_trainer_t trainer, int* failed, int* mode);
 int dmlp_trainer_run(dmlp_trainer_t t, const float* x_host, const int32_t* y_host, size_t num_batches,
                      size_t first_batch, size_t batch_stride, int steps, const float* lr_schedule,
                      float* metrics_out, int use_graph, void* start_event, void* stop_event);

@@ -115,16 +115,17 @@ def main():
 
     # ---- 2. data-parallel trainer vs oracle
     # (fused=3: the step kernel exchanges the gradients itself - push over NVLink, rank-ordered reduce + SGD;
-    #  fused=4: persistent launch = compute cluster + reducer CTAs running the one-shot all-reduce+SGD)
+    #  fused=4: persistent launch = compute cluster + reducer CTAs running the one-shot all-reduce+SGD;
+    #  fused=5 / -1: global-batch mode, covered in depth by mp_gx_worker.py)
     for overlap, algo, fused in ((False, "auto", -1), (True, "auto", -1), (False, "nvls" if nvls_ok else "twoshot", -1),
-                                 (False, "auto", 3), (False, "auto", 4), (False, "auto", 1)):
+                                 (False, "auto", 3), (False, "auto", 4), (False, "auto", 1), (False, "auto", 5)):
         cfg = TrainerConfig(dims=(784, 128, 64, 10), batch=64, lr=0.1, overlap=overlap, seed=7, allreduce=algo, fused=fused)
         t = Trainer(cfg, device=local, process_group=True)
         x, y = synthetic_mnist(64 * world * 6, seed=3)
         params = [(w.astype(np.float64), b.astype(np.float64)) for w, b in t.weights()]
         steps = 6
         st = t.fit(x, y, steps)
-        if fused in (3, 4) or (fused == -1 and algo == "auto"):  # (-1 picks the persistent data-parallel launch)
+        if fused in (3, 4, 5) or (fused == -1 and algo == "auto"):  # (-1 picks the global-batch mode)
             assert t.kernels_per_step == 1 and t.launches_last_run == 1, (t.kernels_per_step, t.launches_last_run)
         if fused == 1:
             assert t.kernels_per_step == 2, t.kernels_per_step

@@ -20,7 +20,7 @@ STRUCTS = [
     ("dmlp_device_info_t", "l2_bytes", "dmlp_b200.runtime.native:DeviceInfo", "l2_bytes"),
     ("dmlp_allreduce_desc_t", "prof_dev", "dmlp_b200.runtime.native:AllReduceDesc", "prof"),
     ("dmlp_nvls_allreduce_desc_t", "oneshot", "dmlp_b200.runtime.nvls:NvlsAllReduceDesc", "oneshot"),
-    ("dmlp_mlp_fused_desc_t", "xchg_grads_dev", "dmlp_b200.runtime.native:MlpFusedDesc", "xchg_grads"),
+    ("dmlp_mlp_fused_desc_t", "gx_enable", "dmlp_b200.runtime.native:MlpFusedDesc", "gx_enable"),
     ("dmlp_trainer_config_t", "fused", "dmlp_b200.parallel.trainer:_NativeCfg", "fused"),
 ]
 

@@ -65,11 +65,22 @@ def test_single_process_dead_gpu_rank_times_out():
 
 @needs2
 def test_torchrun_ipc_collectives_and_dp_trainer():
-    n = 2 if _ngpu() < 4 else 4
+    n = min(_ngpu(), 8)
     cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", f"--nproc-per-node={n}",
            "--master-addr", "127.0.0.1", "--master-port", "29617", os.path.join(ROOT, "tests", "mp_worker.py")]
     r = subprocess.run(cmd, capture_output=True, text=True, timeout=600, cwd=ROOT)
     assert r.returncode == 0 and "MP_WORKER_OK" in r.stdout, r.stdout[-3000:] + r.stderr[-3000:]
+
+
+@needs2
+def test_torchrun_global_batch_mode_oracle_soak_and_rank_failure():
+    """The default data-parallel path of the fused step on every GPU of the box (2..8 ranks): oracle equality, replica
+    bit-equality over a long run, and a rank that dies mid-run (watchdog -> TIMEOUT -> FAILED trainer)."""
+    n = min(_ngpu(), 8)
+    cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", f"--nproc-per-node={n}",
+           "--master-addr", "127.0.0.1", "--master-port", "29619", os.path.join(ROOT, "tests", "mp_gx_worker.py")]
+    r = subprocess.run(cmd, capture_output=True, text=True, timeout=900, cwd=ROOT)
+    assert r.returncode == 0 and "MP_GX_OK" in r.stdout, r.stdout[-3000:] + r.stderr[-3000:]
 
 
 @needs2
