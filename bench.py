@@ -236,6 +236,45 @@ def main() -> int:
     wall_e2e = max_over_ranks(st_e2e["seconds"] * 1e3)
     clocks = sampler.stop(t_start, t_stop)
 
+    # ---- correctness of what was just timed, outside the timed regions: (1) every replica holds bit-identical
+    # parameters after all those steps, (2) the loss is finite and fell, (3) a fresh trainer of the same configuration
+    # follows the NumPy fp64 oracle (mean-gradient SGD over the ranks' shards) for a few steps.
+    import hashlib
+    flat = trainer.get_params()
+    digest = hashlib.sha256(flat.tobytes()).hexdigest()[:16]
+    digests = [digest]
+    if multi:
+        digests = [None] * world
+        dist.all_gather_object(digests, digest)
+    losses = st_e2e.get("per_step_loss")
+    verified = {"replicas_equal": all(d == digests[0] for d in digests), "param_sha256_16": digests[0],
+                "params_finite": bool(np.isfinite(flat).all()),
+                "loss_finite": bool(np.isfinite(st_dev["loss"]) and np.isfinite(st_e2e["loss"])),
+                "loss_first_last": [float(st_dev["per_step_loss"][0]), float(losses[-1])] if losses is not None else None}
+    if a.model != "wide":
+        from dmlp_b200.models import oracle
+        k = 4
+        vcfg = TrainerConfig(dims=m["dims"], batch=batch, lr=0.05, precision=m["precision"], allreduce=a.allreduce,
+                             overlap=overlap, use_graph=not a.no_graph, fused=a.fused, seed=7)
+        vt = Trainer(vcfg, device=local_rank, process_group=multi)
+        vx, vy = synthetic_mnist(batch * world * k, seed=3, features=feat, num_classes=m["dims"][-1])
+        ref = [(w.astype(np.float64), b.astype(np.float64)) for w, b in vt.weights()]
+        vt.fit(vx, vy, k)  # rank r consumes batch s * world + r of the shared set
+        for s_ in range(k):
+            shards = [(vx[(s_ * world + r) * batch:(s_ * world + r + 1) * batch].astype(np.float64),
+                       vy[(s_ * world + r) * batch:(s_ * world + r + 1) * batch]) for r in range(world)]
+            ref, _, _ = oracle.dp_train_step(ref, shards, 0.05)
+        err = max(max(np.abs(w - rw).max(), np.abs(b - rb).max()) for (w, b), (rw, rb) in zip(vt.weights(), ref))
+        errs = [float(err)]
+        if multi:
+            errs = [None] * world
+            dist.all_gather_object(errs, float(err))
+        verified.update({"oracle_steps": k, "oracle_max_abs_err": max(errs), "oracle_tol": 2e-3,
+                         "oracle_ok": bool(max(errs) < 2e-3), "dp_mode": vt.dp_mode})
+        vt.close()
+        if multi:
+            dist.barrier()
+
     gbatch = batch * world
     value = a.steps * gbatch / (ms_dev / 1e3)
     e2e_value = a.steps * gbatch / (max(ms_e2e, wall_e2e) / 1e3)
@@ -262,6 +301,7 @@ def main() -> int:
         "kernels_per_step": trainer.kernels_per_step,
         "steps_per_launch": round(a.steps / max(launches_dev, 1), 2),
         "clocks": clocks,
+        "verified": verified,
         "impl": "ours",
     }
     sys.stdout.flush()

@@ -236,7 +236,7 @@ __device__ __forceinline__ bool coll_barrier(const CollArgs& a, int rank, uint32
   __syncthreads();
   if (threadIdx.x < a.world) {
     const int p = threadIdx.x;
-    if (release) __threadfence_system();
+    if (release || a.strict) __threadfence_system();  // (strict mode: every barrier releases, entry barriers included)
     st_relaxed_sys(a.pad[p] + kPadBarrier + blockIdx.x * kMaxRanks + rank, epoch);
     if (!wait_flag(a.pad[rank] + kPadBarrier + blockIdx.x * kMaxRanks + p, epoch, a, rank, p, phase, deadline))
       *s_fail = 1;
@@ -1058,6 +1058,18 @@ extern "C" int dmlp_allreduce_sum_f32_noalloc(int world, const float* const* in_
   unsigned char* base = nullptr;
   int rc = noalloc_scratch_ptr(&base);
   if (rc) return rc;
+  {
+    // the kernel runs on the current device and dereferences every rank's buffers there
+    int dev = -1;
+    DMLP_CUDA_CHECK(cudaGetDevice(&dev));
+    for (int r = 0; r < world; ++r) {
+      cudaPointerAttributes at;
+      if (cudaPointerGetAttributes(&at, in_dev[r]) == cudaSuccess && at.type == cudaMemoryTypeDevice && at.device != dev)
+        return set_error(DMLP_ERR_INVALID, "dmlp_allreduce_sum_f32_noalloc: rank %d's input lives on device %d, the call runs on device %d",
+                         r, at.device, dev);
+      cudaGetLastError();
+    }
+  }
   cudaStream_t st = as_stream(stream);
   // The array keeps whatever the previous call left behind. Flags, epochs, sequence numbers and
   // the watchdog words must start from zero; staging slots are always written before they are read.
@@ -1090,4 +1102,17 @@ extern "C" int dmlp_allreduce_sum_f32_noalloc(int world, const float* const* in_
   if (blocks > 16) blocks = 16;
   if (world == 1) return launch_coll(allreduce_oneshot_kernel<float, false>, a, blocks, 1, st);
   return launch_coll(allreduce_ring_kernel<float, false>, a, blocks, world, st);
+}
+
+// The allocation-free all-reduce keeps its watchdog record {code, rank, peer, phase} in the static array, where the
+// host cannot see it: without this getter a kernel that gave up (10 s without a peer, or an abort) would still look
+// like a success. Call it after synchronising the stream the all-reduce ran on; out[0] == 0 means the last call on the
+// current device completed. Performs one small synchronous device-to-host copy, no allocation.
+extern "C" int dmlp_allreduce_noalloc_status(uint32_t out[4]) {
+  DMLP_REQUIRE(out != nullptr, "dmlp_allreduce_noalloc_status: null output");
+  unsigned char* base = nullptr;
+  int rc = noalloc_scratch_ptr(&base);
+  if (rc) return rc;
+  DMLP_CUDA_CHECK(cudaMemcpy(out, reinterpret_cast<uint32_t*>(base) + 4, 4 * sizeof(uint32_t), cudaMemcpyDeviceToHost));
+  return DMLP_OK;
 }

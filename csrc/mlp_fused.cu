@@ -93,6 +93,11 @@ struct FusedParams {
   unsigned long long g0;        // global index of this launch's first step (parity of the receive areas)
   long long fault_step;         // fault injection: from this global step on this rank sends nothing and waits for nothing (-1: never)
   unsigned int xneed;           // the peers' inputs for this launch are in place once their ready words reach this step count
+  // DMLP_COLL_STRICT=1 (same switch as collectives.cu): every cross-GPU flag is published behind a system-scope fence
+  // and every flag wait is followed by a system-scope acquire fence - the conservative protocol the default is compared
+  // against. The default relies on this GPU's L2 being the point of coherence for its own memory (peer reads of it are
+  // served there), so a gpu-scope fence before a flag and no fence after a poll suffice; docs/FUSED_STEP.md, section 6.
+  int strict;
 };
 
 #define FPROF(slot)                                                                                   \
@@ -333,6 +338,7 @@ __device__ __forceinline__ bool pf_wait(const uint32_t* flag, uint32_t target, c
       }
     }
   }
+  if (p.strict) __threadfence_system();  // acquire side of the conservative protocol
   return true;
 }
 
@@ -386,6 +392,12 @@ __device__ void fused_reducer_loop(const FusedParams& p) {
     const uint32_t epoch = epoch0 + static_cast<uint32_t>(st) + 1u;
     const uint32_t par = epoch & 1u;
     const unsigned long long deadline = globaltimer_ns() + p.xtimeout_ns;
+    // fault injection: a "dead" rank neither reduces nor waits (its own compute cluster is still released below)
+    if (p.fault_step >= 0 && static_cast<long long>(p.g0) + st >= p.fault_step) {
+      __syncthreads();
+      if (threadIdx.x == 0) { s_fail = 1; atomicAdd(mypad + kPfWeights, 1u); }
+      continue;
+    }
     // every rank's compute CTAs raise [rank][cta] in every rank's pad once their gradient slices are complete:
     // (world x 8) flags to poll locally, no relay through this rank's own flags
     if (threadIdx.x < p.world * kFC) {
@@ -424,6 +436,7 @@ __device__ void fused_reducer_loop(const FusedParams& p) {
         }
       }
     }
+    if (p.strict) __threadfence_system(); else
     __threadfence();
     __syncthreads();
     if (threadIdx.x == 0) atomicAdd(mypad + kPfWeights, 1u);  // (also on failure: the compute cluster must not hang)
@@ -497,7 +510,7 @@ mlp_fused_step_kernel(const __grid_constant__ CUtensorMap tmXA, const __grid_con
     mbar_init(&bar_wg2, 1);
     for (int k = 0; k < 5; ++k) mbar_init(&bar_ex[k], 1);
     for (int k = 0; k < 4; ++k) mbar_init(&bar_xr[k], 1);
-    for (int k = 0; k < 2; ++k) { mbar_init(&bar_gx[k], 1); mbar_init(&bar_gf[k], 128); mbar_init(&bar_ge[k], 1); }
+    for (int k = 0; k < 2; ++k) { mbar_init(&bar_gx[k], 1); mbar_init(&bar_gf[k], 96); mbar_init(&bar_ge[k], 1); }
     fence_mbar_init();
     arm_exchanges();
   }
@@ -645,7 +658,7 @@ mlp_fused_step_kernel(const __grid_constant__ CUtensorMap tmXA, const __grid_con
     mbar_wait(&bar_mma, mma_phase);
     tc_fence_after_sync();
     // reduce-scatter: columns [S1*i, S1*i+S1) of my partial go to CTA i
-#pragma unroll
+#pragma unroll 1
     for (int i = 0; i < kFC; ++i) {
       uint32_t r[16];
       tmem_ld_x16(tm + tq + cF1 + S1 * i, r);
@@ -670,6 +683,7 @@ mlp_fused_step_kernel(const __grid_constant__ CUtensorMap tmXA, const __grid_con
 #pragma unroll
     for (int c = 0; c < S1; ++c) h1[c] = 0.f;
     if (rok) {
+      #pragma unroll 1
       for (int s = 0; s < kFC; ++s) {  // fixed order: deterministic sums
         const float4* src = reinterpret_cast<const float4*>(smem + oRS1 + (s * 64 + row) * (S1 * 4));
 #pragma unroll
@@ -713,7 +727,7 @@ mlp_fused_step_kernel(const __grid_constant__ CUtensorMap tmXA, const __grid_con
     if (worker) {
       mbar_wait(&bar_mma, mma_phase);
       tc_fence_after_sync();
-#pragma unroll
+#pragma unroll 1
       for (int i = 0; i < kFC; ++i) {
         uint32_t r[8];
         tmem_ld_x8(tm + tq + cF2 + S2 * i, r);
@@ -735,7 +749,9 @@ mlp_fused_step_kernel(const __grid_constant__ CUtensorMap tmXA, const __grid_con
 #pragma unroll
       for (int c = 0; c < S2; ++c) h2[c] = 0.f;
       if (rok) {
-        for (int s = 0; s < kFC; ++s) {
+        #pragma unroll 1
+        #pragma unroll 1
+      for (int s = 0; s < kFC; ++s) {
           const float4* src = reinterpret_cast<const float4*>(smem + oRS2 + (s * 64 + row) * (S2 * 4));
 #pragma unroll
           for (int c = 0; c < S2; c += 4) {
@@ -782,7 +798,7 @@ mlp_fused_step_kernel(const __grid_constant__ CUtensorMap tmXA, const __grid_con
     tmem_ld_x16(tm + tq + cF3, r);
     tmem_ld_wait();
     if (rok) {
-#pragma unroll
+#pragma unroll 1
       for (int i = 0; i < kFC; ++i) {
         const uint32_t dst = mapa(sb + oAR3 + (j * 64 + row) * 64, i);
         const uint32_t bar = mapa(smem_u32(&bar_ex[2]), i);
@@ -807,6 +823,7 @@ mlp_fused_step_kernel(const __grid_constant__ CUtensorMap tmXA, const __grid_con
     float loss = 0.f;
     int hit = 0;
     if (rok) {
+      #pragma unroll 1
       for (int s = 0; s < kFC; ++s) {
         const float4* src = reinterpret_cast<const float4*>(smem + oAR3 + (s * 64 + row) * 64);
 #pragma unroll
@@ -903,7 +920,7 @@ mlp_fused_step_kernel(const __grid_constant__ CUtensorMap tmXA, const __grid_con
   if (kMid) {
     // all-gather dZ2_j (= dzl) into every CTA: K-major (A of dgrad2) and MN-major (B of wgrad2)
     if (rok) {
-#pragma unroll
+#pragma unroll 1
       for (int i = 0; i < kFC; ++i) {
         const uint32_t bar = mapa(smem_u32(&bar_ex[3]), i);
         const uint32_t dm = mapa(sb + oDZ2M + moff(row, S2 * j), i);
@@ -973,6 +990,7 @@ mlp_fused_step_kernel(const __grid_constant__ CUtensorMap tmXA, const __grid_con
       const int rows = B - (warp & 3) * 32 < 32 ? B - (warp & 3) * 32 : 32;
       if (rows > 0) {
         const size_t o = static_cast<size_t>(gslot) + p.w_off[0] + j * 1024 + (warp & 3) * 512;
+        #pragma unroll 1
         for (int q = 0; q < W; ++q)
           if (q != p.rank) bulk_s2g(p.xrecv[q] + o, stg, rows * 64);
         bulk_commit();
@@ -983,7 +1001,7 @@ mlp_fused_step_kernel(const __grid_constant__ CUtensorMap tmXA, const __grid_con
   FPROFT(128, 33);
   // all-gather dZ1_j into every CTA (MN-major: B operand of the layer-1 weight gradient)
   if (rok) {
-#pragma unroll
+#pragma unroll 1
     for (int i = 0; i < kFC; ++i) {
       const uint32_t bar = mapa(smem_u32(&bar_ex[4]), i);
       const uint32_t dm = mapa(sb + oDZ1 + moff(row, S1 * j), i);
@@ -1078,7 +1096,9 @@ mlp_fused_step_kernel(const __grid_constant__ CUtensorMap tmXA, const __grid_con
     __syncwarp();
   }
   float dbl[16];  // last-layer bias gradient (valid in the thread that owns accumulator row SL)
-  if (worker) {
+  // Global-batch mode: the worker warps split up. The warp that owns TMEM lanes 0..31 (the only one whose rows of the side
+  // weight gradients are real) drains and pushes them; the other three stage the peers' dZ1 at once.
+  if (worker && (!gmode || (warp & 3) == 0)) {
     // while dW1 runs on the tensor core: drain the weight-gradient GEMMs that ran beside the chain
     FPROFT(32, 18);
     FPROFT(128, 34);
@@ -1103,6 +1123,7 @@ mlp_fused_step_kernel(const __grid_constant__ CUtensorMap tmXA, const __grid_con
           __syncwarp();
           if (gpush >= 0 && lane == 0) {
             const size_t o = static_cast<size_t>(gpush) + p.w_off[LAST] + static_cast<size_t>(SL * j) * 16;
+            #pragma unroll 1
             for (int q = 0; q < W; ++q) {
               bulk_s2g(p.xrecv[q] + o, sb + oSTG, SL * 64);
               if (j == 0) bulk_s2g(p.xrecv[q] + gpush + p.b_off[LAST], sb + oSTG + SL * 64, 64);
@@ -1127,7 +1148,7 @@ mlp_fused_step_kernel(const __grid_constant__ CUtensorMap tmXA, const __grid_con
       mbar_wait(&bar_wg2, sp);
       FPROFT(128, 37);
       tc_fence_after_sync();
-#pragma unroll
+#pragma unroll 1
       for (int cc = 0; cc < H2; cc += 16) {
         uint32_t r[16];
         tmem_ld_x16(tm + tq + cWG2 + cc, r);
@@ -1162,6 +1183,7 @@ mlp_fused_step_kernel(const __grid_constant__ CUtensorMap tmXA, const __grid_con
       fence_proxy_async_smem();
       __syncwarp();
       if (gpush >= 0 && lane == 0) {
+        #pragma unroll 1
         for (int q = 0; q < W; ++q) {
           bulk_s2g(p.xrecv[q] + gpush + p.w_off[1] + static_cast<size_t>(S1 * j) * H2, sb + oSTG2, S1 * H2 * 4);
           bulk_s2g(p.xrecv[q] + gpush + p.b_off[1] + S2 * j, sb + oSTG + 1280, S2 * 4);
@@ -1170,10 +1192,11 @@ mlp_fused_step_kernel(const __grid_constant__ CUtensorMap tmXA, const __grid_con
       }
     }
     FPROFT(128, 38);
-    if (gmode) {
+  }
+  if (worker) {
+    if (gmode && (warp & 3) != 0) {
       FPROF(15);
-      const int wt = static_cast<int>(threadIdx.x) - 32;
-      const float4 e4 = make_float4(__uint_as_float(kGxEmpty), __uint_as_float(kGxEmpty), __uint_as_float(kGxEmpty), __uint_as_float(kGxEmpty));
+      const int wt = static_cast<int>(threadIdx.x) - 32;  // 0..95: warps 1..3
       // ---- peers' dZ1 images -> stages (the control warp loads the matching X^T tiles and issues the MMAs)
       for (int q = 0; q < npeer; ++q) {
         const int s = q & 1, r = q < p.rank ? q : q + 1;
@@ -1182,23 +1205,25 @@ mlp_fused_step_kernel(const __grid_constant__ CUtensorMap tmXA, const __grid_con
         if (q == 0) { FPROFT(32, 19); FPROFT(128, 39); }
         const float* img = p.xrecv[p.rank] + (static_cast<size_t>(xpar) * W + r) * p.total + p.w_off[0];
         const uint32_t dzt = sb + (s ? oGD1 : oGD0);
-        // 16 chunks of 16 bytes per thread, copied global -> shared asynchronously (no registers, all in flight at once,
+        // 21-22 chunks of 16 bytes per thread, copied global -> shared asynchronously (no registers, all in flight at once,
         // rolled loops: the code executed per step is refetched from L2 every time, so its size counts) straight into
         // their place in the operand image, then validated there; chunks that were still empty are copied again.
         {
           uint32_t pend = 0;
-          for (int k = 0; k < 16; ++k)
-            if ((((wt + 128 * k) & 255) >> 2) < B) pend |= 1u << k;  // rows >= B are never sent
+          for (int k = 0; k < 22; ++k) {
+            const int c = wt + 96 * k;  // 2048 chunks over 96 threads
+            if (c < 2048 && ((c & 255) >> 2) < B) pend |= 1u << k;  // rows >= B are never sent
+          }
           uint32_t spins = 0;
           while (pend != 0u) {
-            for (int k = 0; k < 16; ++k) {
+            for (int k = 0; k < 22; ++k) {
               // chunk c of the receive image = source CTA c / 256, batch row (c % 256) / 4, columns 4 * (c % 4) ..
-              const int c = wt + 128 * k;
+              const int c = wt + 96 * k;
               if ((pend >> k) & 1u) cp_async16(dzt + moff((c & 255) >> 2, S1 * (c >> 8) + 4 * (c & 3)), img + 4 * c);
             }
             cp_async_wait_all();
-            for (int k = 0; k < 16; ++k) {
-              const int c = wt + 128 * k;
+            for (int k = 0; k < 22; ++k) {
+              const int c = wt + 96 * k;
               if ((pend >> k) & 1u) {
                 const float4 v = lds128(dzt + moff((c & 255) >> 2, S1 * (c >> 8) + 4 * (c & 3)));
                 if (gx_valid(v)) pend &= ~(1u << k);
@@ -1220,76 +1245,76 @@ mlp_fused_step_kernel(const __grid_constant__ CUtensorMap tmXA, const __grid_con
         if (s) ++guse1; else ++guse0;
       }
       FPROF(0);
-      // ---- small tensors: sum every rank's contribution (own included) in rank order, apply, mark the slots empty
-      {
-        constexpr int nW2 = kMid ? S1 * H2 / 4 : 0, nWL = SL * 16 / 4, nB2 = kMid ? S2 / 4 : 0;
-        const int n_items = nW2 + nWL + nB2 + (j == 0 ? 4 : 0);
-        float* rb = p.xrecv[p.rank] + static_cast<size_t>(xpar) * W * p.total;
-        static_assert(nW2 + nWL + nB2 + 4 <= 3 * 128, "more than three small-tensor items per worker thread");
-        // up to three items per thread, all of them in flight at once; ranks in groups of four (rank order is kept:
-        // the groups are added one after the other)
-        size_t offs[3];
-        float4 w[3], acc[3];
+    }
+  }
+  if (gmode) {
+    // ---- small tensors (W2 / last-layer W slices, b2, last bias): summed while the last wgrad1 MMAs run, by ALL 160
+    // threads (the control warp has issued everything, the staging warps are done, the pushing warp too): at most two
+    // 16-byte items per thread, every rank's contribution (own included) of both in flight at once, ranks in groups of
+    // four added one group after the other (rank order). Applied with a fire-and-forget reduction, w += -(lr/world)*sum:
+    // every element is touched by one thread, so the result equals w - (lr/world)*sum bit for bit on every rank.
+    constexpr int nW2 = kMid ? S1 * H2 / 4 : 0, nWL = SL * 16 / 4, nB2 = kMid ? S2 / 4 : 0;
+    static_assert(nW2 + nWL + nB2 + 4 <= 2 * kFThreads, "more than two small-tensor items per thread");
+    const int n_items = nW2 + nWL + nB2 + (j == 0 ? 4 : 0);
+    const int tid = static_cast<int>(threadIdx.x);
+    float* rb = p.xrecv[p.rank] + static_cast<size_t>(xpar) * W * p.total;
+    const float4 e4 = make_float4(__uint_as_float(kGxEmpty), __uint_as_float(kGxEmpty), __uint_as_float(kGxEmpty), __uint_as_float(kGxEmpty));
+    size_t offs[2];
+    float4 acc[2];
 #pragma unroll
-        for (int i = 0; i < 3; ++i) {
-          const int it = wt + 128 * i;
-          int k = it;
-          size_t off;
-          if (k < nW2) off = p.w_off[1] + static_cast<size_t>(S1 * j) * H2;
-          else if ((k -= nW2) < nWL) off = p.w_off[LAST] + static_cast<size_t>(SL * j) * 16;
-          else if ((k -= nWL) < nB2) off = p.b_off[1] + S2 * j;
-          else { k -= nB2; off = p.b_off[LAST]; }
-          offs[i] = off + static_cast<size_t>(k) * 4;
-          acc[i] = make_float4(0.f, 0.f, 0.f, 0.f);
-          if (it < n_items) w[i] = __ldcg(reinterpret_cast<const float4*>(p.wparams + offs[i]));
-        }
-        FPROFT(32, 23); FPROFT(128, 43);
-        for (int r0 = 0; r0 < W; r0 += 4) {
-          uint32_t pend = 0;
+    for (int i = 0; i < 2; ++i) {
+      int k = tid + kFThreads * i;
+      size_t off;
+      if (k < nW2) off = p.w_off[1] + static_cast<size_t>(S1 * j) * H2;
+      else if ((k -= nW2) < nWL) off = p.w_off[LAST] + static_cast<size_t>(SL * j) * 16;
+      else if ((k -= nWL) < nB2) off = p.b_off[1] + S2 * j;
+      else { k -= nB2; off = p.b_off[LAST]; }
+      offs[i] = off + static_cast<size_t>(k) * 4;
+      acc[i] = make_float4(0.f, 0.f, 0.f, 0.f);
+    }
+    for (int r0 = 0; r0 < W; r0 += 4) {
+      uint32_t pend = 0;
 #pragma unroll
-          for (int i = 0; i < 3; ++i)
+      for (int i = 0; i < 2; ++i)
 #pragma unroll
-            for (int rr = 0; rr < 4; ++rr)
-              if (wt + 128 * i < n_items && r0 + rr < W) pend |= 1u << (i * 4 + rr);
-          float4 v[3][4];
-          uint32_t spins = 0;
-          while (pend != 0u) {
+        for (int rr = 0; rr < 4; ++rr)
+          if (tid + kFThreads * i < n_items && r0 + rr < W) pend |= 1u << (i * 4 + rr);
+      float4 v[2][4];
+      uint32_t spins = 0;
+      while (pend != 0u) {
 #pragma unroll
-            for (int i = 0; i < 3; ++i)
-#pragma unroll
-              for (int rr = 0; rr < 4; ++rr)
-                if ((pend >> (i * 4 + rr)) & 1u) v[i][rr] = ld_poll_f4(rb + static_cast<size_t>(r0 + rr) * p.total + offs[i]);
-#pragma unroll
-            for (int i = 0; i < 3; ++i)
-#pragma unroll
-              for (int rr = 0; rr < 4; ++rr)
-                if (((pend >> (i * 4 + rr)) & 1u) && (gx_valid(v[i][rr]) || *xfail != 0)) pend &= ~(1u << (i * 4 + rr));
-            if (pend != 0u && (++spins & 0xF) == 0 && gx_timeout(p, r0, 10u, gdeadline)) *xfail = 1;
-            if (p.prof != nullptr && threadIdx.x == 32) p.prof[j * 64 + 50] = spins + 1;
-          }
-          FPROFT(32, 24); FPROFT(128, 44);
+        for (int i = 0; i < 2; ++i)
 #pragma unroll
           for (int rr = 0; rr < 4; ++rr)
+            if ((pend >> (i * 4 + rr)) & 1u) v[i][rr] = ld_poll_f4(rb + static_cast<size_t>(r0 + rr) * p.total + offs[i]);
 #pragma unroll
-            for (int i = 0; i < 3; ++i)
-              if (wt + 128 * i < n_items && r0 + rr < W) {
-                acc[i].x += v[i][rr].x; acc[i].y += v[i][rr].y; acc[i].z += v[i][rr].z; acc[i].w += v[i][rr].w;
-                *reinterpret_cast<float4*>(rb + static_cast<size_t>(r0 + rr) * p.total + offs[i]) = e4;
-              }
-        }
+        for (int i = 0; i < 2; ++i)
 #pragma unroll
-        for (int i = 0; i < 3; ++i)
-          if (wt + 128 * i < n_items) {
-            w[i].x -= step * acc[i].x; w[i].y -= step * acc[i].y; w[i].z -= step * acc[i].z; w[i].w -= step * acc[i].w;
-            *reinterpret_cast<float4*>(p.wparams + offs[i]) = w[i];
-          }
+          for (int rr = 0; rr < 4; ++rr)
+            if (((pend >> (i * 4 + rr)) & 1u) && (gx_valid(v[i][rr]) || *xfail != 0)) pend &= ~(1u << (i * 4 + rr));
+        if (pend != 0u && (++spins & 0xF) == 0 && gx_timeout(p, r0, 10u, gdeadline)) *xfail = 1;
       }
-      FPROF(1);
+#pragma unroll
+      for (int rr = 0; rr < 4; ++rr)
+#pragma unroll
+        for (int i = 0; i < 2; ++i)
+          if (tid + kFThreads * i < n_items && r0 + rr < W) {
+            acc[i].x += v[i][rr].x; acc[i].y += v[i][rr].y; acc[i].z += v[i][rr].z; acc[i].w += v[i][rr].w;
+            *reinterpret_cast<float4*>(rb + static_cast<size_t>(r0 + rr) * p.total + offs[i]) = e4;
+          }
     }
+#pragma unroll
+    for (int i = 0; i < 2; ++i)
+      if (tid + kFThreads * i < n_items)
+        asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(p.wparams + offs[i]), "f"(-step * acc[i].x),
+                     "f"(-step * acc[i].y), "f"(-step * acc[i].z), "f"(-step * acc[i].w) : "memory");
+    FPROF(1);
+  }
+  if (worker) {
     mbar_wait(&bar_mma, mma_phase);
     FPROF(11);
     tc_fence_after_sync();
-#pragma unroll
+#pragma unroll 1
     for (int cc = 0; cc < H1; cc += 16) {
       uint32_t r[16];
       tmem_ld_x16(tm + tq + cWG1 + cc, r);
@@ -1321,7 +1346,9 @@ mlp_fused_step_kernel(const __grid_constant__ CUtensorMap tmXA, const __grid_con
     // gradients performed at GPU scope (they sit in this GPU's L2, which is where peer reads are served from) before the
     // flag: one fence by one thread after the CTA barrier (cumulative), not a MEMBAR.SYS per thread (~4 us)
     __syncthreads();
-    if (threadIdx.x < p.world) {  // one thread per rank (own included): that rank's reducers poll [my rank][my CTA] locally
+    const bool pdead = p.fault_step >= 0 && static_cast<long long>(p.g0) + st >= p.fault_step;  // fault injection
+    if (threadIdx.x < p.world && !pdead) {  // one thread per rank (own included): that rank's reducers poll [my rank][my CTA] locally
+      if (p.strict) __threadfence_system(); else
       __threadfence();
       st_relaxed_sys(p.xpad[threadIdx.x] + kPadFusedFlags + kPfRedFlags + p.rank * kFC + j, epoch);
     }
@@ -1424,6 +1451,7 @@ mlp_fused_step_kernel(const __grid_constant__ CUtensorMap tmXA, const __grid_con
           }
         }
       }
+      if (p.strict) __threadfence_system();
       __syncwarp();
     }
     __syncthreads();
@@ -1624,6 +1652,10 @@ extern "C" int dmlp_mlp_fused_plan_create(const dmlp_mlp_fused_desc_t* d, dmlp_m
   p.slot0 = 0;
   p.fault_step = -1;
   {
+    const char* e = getenv("DMLP_COLL_STRICT");
+    p.strict = e ? atoi(e) : 0;
+  }
+  {
     const char* e = getenv("DMLP_FUSED_BULK");
     p.bulk_update = e ? atoi(e) : 0;  // measured: 22.3 us/step with bulk reduce-adds vs 21.3 with red.global (default)
   }
@@ -1686,7 +1718,7 @@ extern "C" int dmlp_mlp_fused_step(dmlp_mlp_fused_plan_t h, void* stream) {
 extern "C" int dmlp_mlp_fused_steps_gx(dmlp_mlp_fused_plan_t h, int slot0, int nsteps, unsigned long long global_step,
                                        unsigned int inputs_ready, void* stream) {
   const FusedPlan* pl = reinterpret_cast<const FusedPlan*>(h);
-  DMLP_REQUIRE(pl && pl->p.gx, "dmlp_mlp_fused_steps_gx: the plan was not created for the global-batch mode");
+  DMLP_REQUIRE(pl && (pl->p.gx || pl->p.red_ctas > 0), "dmlp_mlp_fused_steps_gx: the plan has no data-parallel mode with a global step");
   DMLP_REQUIRE(nsteps >= 1 && slot0 >= 0 && slot0 + nsteps <= pl->slots, "dmlp_mlp_fused_steps_gx: slots [%d, %d) outside the plan's %d",
                slot0, slot0 + nsteps, pl->slots);
   FusedParams prm = pl->p;
@@ -1696,6 +1728,10 @@ extern "C" int dmlp_mlp_fused_steps_gx(dmlp_mlp_fused_plan_t h, int slot0, int n
   prm.xneed = inputs_ready;
   prm.labels = pl->p.labels + static_cast<size_t>(slot0) * pl->p.B;
   prm.metrics = pl->p.metrics + 2 * static_cast<size_t>(slot0);
+  if (!pl->p.gx) {  // persistent compute + reducer launch: the global step only feeds the fault injection
+    if (pl->layers == 3) return launch_fused<16, 8, false>(pl, prm, as_stream(stream));
+    return launch_fused<16, 0, false>(pl, prm, as_stream(stream));
+  }
   if (pl->layers == 3) return launch_fused<16, 8, true>(pl, prm, as_stream(stream));
   return launch_fused<16, 0, true>(pl, prm, as_stream(stream));
 }

@@ -112,7 +112,10 @@ extern "C" int dmlp_malloc(int dev, size_t bytes, void** ptr) {
   if (!g.ok) return set_error(DMLP_ERR_CUDA, "cannot select device %d", dev);
   if (bytes == 0) bytes = 16;
   DMLP_CUDA_CHECK(cudaMalloc(ptr, bytes));
-  DMLP_CUDA_CHECK(cudaMemset(*ptr, 0, bytes));
+  // The zero-fill runs on the legacy default stream, which does not order against the library's non-blocking streams
+  // (or other devices): it must have finished before anybody can touch the buffer. Allocation is not a hot path.
+  DMLP_CUDA_CHECK(cudaMemsetAsync(*ptr, 0, bytes, nullptr));
+  DMLP_CUDA_CHECK(cudaStreamSynchronize(nullptr));
   return DMLP_OK;
 }
 

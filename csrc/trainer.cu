@@ -448,7 +448,7 @@ static int run_fused_ring(Trainer* t, const float* x_host, const int32_t* y_host
     chunk_first_step[c] = -1;
   };
   unsigned long long gx_timeout_ns = 0;
-  if (t->gx) {
+  if (t->gx || t->pdp) {
     // the watchdog budget and the fault-injection step are read at every run (dmlp_comm_set_timeout_ms may have changed)
     uint32_t* pads[DMLP_MAX_RANKS];
     uint32_t *state = nullptr, *host_flags = nullptr, dead = 0;
@@ -513,7 +513,7 @@ static int run_fused_ring(Trainer* t, const float* x_host, const int32_t* y_host
         // as many steps as share this learning rate, in one launch
         int m = 1;
         while (i + m < n && m < per_launch_env && (!lr_schedule || lr_schedule[s + m] == t->lr_host[0])) ++m;
-        if (t->gx) {
+        if (t->gx || t->pdp) {
           TRY(dmlp_mlp_fused_steps_gx(t->ring_plan, slot, m, g_chunk0 + static_cast<unsigned long long>(i),
                                       static_cast<unsigned int>(g_chunk1), t->s_main));
         } else {
@@ -538,7 +538,7 @@ static int run_fused_ring(Trainer* t, const float* x_host, const int32_t* y_host
     last_c = c;
     s0 += n;
     ++ci;
-    if (t->gx) t->gsteps = g_chunk1;
+    if (t->gx || t->pdp) t->gsteps = g_chunk1;
   }
   if (stop_event) DMLP_CUDA_CHECK(cudaEventRecord(reinterpret_cast<cudaEvent_t>(stop_event), t->s_main));
   DMLP_CUDA_CHECK(cudaStreamSynchronize(t->s_main));
@@ -578,9 +578,9 @@ extern "C" int dmlp_trainer_arena_bytes(const dmlp_trainer_config_t* cfg, size_t
   if (cfg->dtype == DMLP_BF16) b += align_up(n * 2, 256);
   // fused step with in-kernel gradient exchange: receive slots [2 parities][up to 8 ranks][params]
   const bool fused_ok = cfg->dtype == DMLP_F32 && dmlp_mlp_fused_supported(cfg->num_layers, cfg->dims, cfg->batch);
-  if (fused_ok && (cfg->fused == 3 || cfg->fused == 5 || cfg->fused == -1)) b += 2 * DMLP_MAX_RANKS * align_up(n * 4, 256);
+  if (fused_ok && (cfg->fused == 3 || cfg->fused == 5)) b += 2 * DMLP_MAX_RANKS * align_up(n * 4, 256);
   // global-batch mode: the gathered input buffer [ranks][ring slots][batch][in0]
-  if (fused_ok && (cfg->fused == 5 || cfg->fused == -1))
+  if (fused_ok && cfg->fused == 5)
     b += align_up(static_cast<size_t>(DMLP_MAX_RANKS) * kRingSlots * cfg->batch * cfg->dims[0] * 4, 256);
   *bytes = b;
   return DMLP_OK;
@@ -719,11 +719,10 @@ extern "C" int dmlp_trainer_create(const dmlp_trainer_config_t* cfg, int device,
       size_t cap = 0;
       int e = dmlp_comm_arena_ptr(t->comm, local_idx, r, &base, &cap);
       if (e != DMLP_OK) { if (r == rank) return fail(e); continue; }  // peers unmapped: ring still works
-      // fused == -1 (auto) takes the global-batch mode when the arena was sized for it (dmlp_trainer_arena_bytes)
       const size_t xall_bytes = align_up(static_cast<size_t>(world) * kRingSlots * B * L.in[0] * 4, 256);
       const size_t base_need = arena_offset + 3 * pbytes + (t->bf16 ? sbytes : 0);
       const size_t recv_bytes = 2 * static_cast<size_t>(world) * pbytes;
-      const bool want_g = t->fused_step && (cfg->fused == 5 || (cfg->fused == -1 && cap >= base_need + recv_bytes + xall_bytes));
+      const bool want_g = t->fused_step && cfg->fused == 5;
       const bool want_x = t->fused_step && (cfg->fused == 3 || want_g);
       size_t need = base_need + (want_x ? recv_bytes : 0) + (want_g ? xall_bytes : 0);
       if (cap < need) { set_error(DMLP_ERR_INVALID, "communicator arena too small: %zu < %zu", cap, need); return fail(DMLP_ERR_INVALID); }
@@ -743,9 +742,9 @@ extern "C" int dmlp_trainer_create(const dmlp_trainer_config_t* cfg, int device,
     for (int r = 0; r < world; ++r) t->pdp = t->pdp && t->peer_grads[0][r] != nullptr;
     t->xchg = t->fused_step && cfg->fused == 3;
     for (int r = 0; r < world; ++r) t->xchg = t->xchg && t->peer_recv[r] != nullptr;
-    // Global-batch mode: the default for the cluster-fused shapes on real multi-GPU communicators (fused == 4 keeps the
-    // persistent compute-cluster + reducer launch, fused == 1 the two-kernel chain).
-    t->gx = t->fused_step && !emulated && (cfg->fused == 5 || cfg->fused == -1);
+    // Global-batch mode (fused == 5, opt-in): measured against the persistent launch in profiles/r2_dp_modes_scaling.md
+    // (level at 2 GPUs, slower from 4 GPUs on: its per-peer staging is serial inside each CTA).
+    t->gx = t->fused_step && !emulated && cfg->fused == 5;
     for (int r = 0; r < world; ++r) t->gx = t->gx && t->peer_recv[r] != nullptr && t->peer_xall[r] != nullptr;
     if (cfg->fused == 5 && !t->gx) {
       set_error(DMLP_ERR_UNSUPPORTED, "global-batch mode needs one GPU per rank and every rank's arena mapped");

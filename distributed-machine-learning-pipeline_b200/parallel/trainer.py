@@ -57,7 +57,7 @@ class TrainerConfig:
                                                # update kernel, 3 require + gradient exchange inside the step kernel (world > 1),
                                                # 4 require + persistent launch: compute cluster + reducer CTAs (world > 1),
                                                # 5 require + global-batch mode: dZ1 / input exchange instead of the dW1
-                                               #   all-reduce (world > 1; what -1 picks on real GPUs)
+                                               #   all-reduce (world > 1; opt-in, see profiles/r2_dp_modes_scaling.md)
     schedule: str = "constant"
     seed: int = 0
     watchdog_ms: int = 10000

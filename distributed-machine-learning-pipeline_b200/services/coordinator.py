@@ -55,6 +55,10 @@ _NP_OPS = {pb.SUM: np.add, pb.PROD: np.multiply, pb.MIN: np.minimum, pb.MAX: np.
 # devices here and drives the GPUs directly; gRPC to them is then only used for health probes.
 LOCAL_DEVICES: Dict[str, GPUDeviceService] = {}
 _LOCAL_LOCK = threading.Lock()
+# Native collectives are per-rank launches on the devices' streams: two of them interleaved by concurrent RPC handlers
+# (same or different communicators over the same GPUs) would rendezvous with each other. One process-wide lock is held
+# from the first per-rank launch of a collective (or of a whole group) until its completion has been checked.
+_NATIVE_LOCK = threading.RLock()
 
 
 def register_local_device(addr: str, svc: GPUDeviceService) -> None:
@@ -86,7 +90,7 @@ class DeviceInfo:
 
 @dataclass
 class QueuedOp:
-    run: Callable[[], None]
+    run: Callable[[bool], None]  # run(deferred): deferred = launch only, GroupEnd waits once for the whole group
     name: str
 
 
@@ -382,14 +386,21 @@ class GPUCoordinatorService:
         with comm.mu:
             comm.group_active = False
             queued, comm.queue = comm.queue, []
-        for op in queued:
+        with _NATIVE_LOCK:
+            name = "GroupEnd"
             try:
-                op.run()
+                for op in queued:  # launched back to back on the communicator's streams, no wait in between
+                    name = op.name
+                    op.run(True)
+                if queued and comm.native is not None:
+                    name = "GroupEnd"
+                    comm.native.sync()   # ONE wait for the whole group ...
+                    comm.native.check()  # ... and one look at the watchdog words
             except Exception as e:
                 with comm.mu:
                     comm.status = pb.FAILED
-                    comm.failure_reason = f"{op.name}: {e}"
-                context.abort(grpc.StatusCode.UNKNOWN, f"{op.name} failed at GroupEnd: {e}")
+                    comm.failure_reason = f"{name}: {e}"
+                context.abort(grpc.StatusCode.UNKNOWN, f"{name} failed at GroupEnd: {e}")
         if queued:
             with comm.mu:
                 if comm.status != pb.FAILED:
@@ -421,9 +432,9 @@ class GPUCoordinatorService:
                 addrs[rank] = ma.value
         op = request.op
 
-        def run():
+        def run(deferred: bool = False):
             if comm.native is not None and len(comm.native.local_devs) == n:
-                self._allreduce_native(comm, devices, addrs, count, dtype, op, algo, md)
+                self._allreduce_native(comm, devices, addrs, count, dtype, op, algo, md, deferred)
             else:
                 self._allreduce_portable(comm, devices, addrs, count, dtype, op, md)
 
@@ -448,8 +459,12 @@ class GPUCoordinatorService:
         return pb.AllReduceRingResponse(success=True)
 
     # -- native path: one kernel per rank over peer memory -------------------------------------
-    def _allreduce_native(self, comm, devices, addrs, count, dtype, op, algo, md) -> None:
+    def _allreduce_native(self, comm, devices, addrs, count, dtype, op, algo, md, deferred: bool = False) -> None:
         from ..runtime import native
+        with _NATIVE_LOCK:
+            self._allreduce_native_locked(comm, devices, addrs, count, dtype, op, algo, md, deferred, native)
+
+    def _allreduce_native_locked(self, comm, devices, addrs, count, dtype, op, algo, md, deferred, native) -> None:
         ndt = {"u8": native.U8, "i32": native.I32, "f32": native.F32, "bf16": native.BF16}[dtype]
         esz = native.DTYPE_SIZE[ndt]
         if count % esz:
@@ -471,12 +486,14 @@ class GPUCoordinatorService:
                 be.check_addr(waddr)
                 be.ensure(waddr, count)
                 outs.append(be.pointer(waddr))
-                lrs.append(be.scalar_f32("lr", float(md["dmlp-sgd-lr"])))
+                lrs.append(be.scalar_f32(None, float(md["dmlp-sgd-lr"])))  # a slot of its own: earlier launches may still read theirs
             kwargs = dict(fuse_sgd=True, lr=lrs, scale=1.0 / len(devices))
         else:
             outs = ptrs
         comm.native.allreduce(ptrs, outs, count // esz, dtype=ndt, op=int(op),
                               algo=native.ALGO_BY_NAME.get(algo, native.ALGO_AUTO), **kwargs)
+        if deferred:
+            return  # part of a group: GroupEnd waits once after the last launch
         comm.native.sync()
         comm.native.check()  # raises CommFailure when a watchdog fired (dead peer mid-collective)
 
@@ -604,10 +621,13 @@ class GPUCoordinatorService:
         comm = self._get(request.commId, context)
         with comm.mu:
             queued, comm.queue = comm.queue, []
-        for op in queued:
-            op.run()
-        if comm.native is not None:
-            comm.native.sync()
+        with _NATIVE_LOCK:
+            for op in queued:
+                op.run(True)
+            if comm.native is not None:
+                comm.native.sync()
+                if queued:
+                    comm.native.check()
         with comm.mu:
             comm.finalized = True
         return pb.CommFinalizeResponse(success=True)
@@ -635,7 +655,8 @@ class GPUCoordinatorService:
         moved = 0
         try:
             if native_ok and all(d.local is not None for d in devices):
-                moved = self._naive_native(devices, size, latency)
+                with _NATIVE_LOCK:
+                    moved = self._naive_native(devices, size, latency)
             else:
                 gathered = []
                 for d in devices:

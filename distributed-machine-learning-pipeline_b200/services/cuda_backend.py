@@ -12,7 +12,7 @@ from __future__ import annotations
 import ctypes as C
 import struct
 import threading
-from typing import Callable, Dict, Tuple
+from typing import Optional, Callable, Dict, Tuple
 
 from ..runtime import native
 from .backend import DeviceBackend, MissingBufferError
@@ -119,9 +119,13 @@ class CudaBackend(DeviceBackend):
                 self._scratch[name] = ent
             return ent[0]
 
-    def scalar_f32(self, name: str, value: float) -> int:
-        """Device-resident fp32 scalar (e.g. the learning rate read by the fused SGD kernels)."""
+    def scalar_f32(self, name: Optional[str], value: float) -> int:
+        """Device-resident fp32 scalar (e.g. the learning rate read by the fused SGD kernels). ``name=None`` takes the
+        next of 64 rotating slots, so that launches still in flight (a group submitted without waits) keep theirs."""
         with self._lock:
+            if name is None:
+                self._scalar_seq = (getattr(self, "_scalar_seq", -1) + 1) % 64
+                name = f"_rot{self._scalar_seq}"
             ptr = self._scalars.get(name)
             if ptr is None:
                 ptr = self._alloc(16)

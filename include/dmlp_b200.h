@@ -280,6 +280,13 @@ int dmlp_allreduce_nvls(dmlp_comm_t comm, int local_idx, const dmlp_nvls_allredu
  */
 int dmlp_allreduce_sum_f32_noalloc(int world, const float* const* in_dev, float* const* out_dev,
                                    size_t count, void* stream);
+/* Watchdog record {code, rank, peer, phase} of the most recent dmlp_allreduce_sum_f32_noalloc on the current device
+ * (it lives in the static array, out of the host's sight). Call after synchronising that call's stream: out[0] == 0
+ * means it completed; DMLP_ERR_TIMEOUT means a rank gave up after 10 s and `out_dev` holds garbage. One small
+ * synchronous device-to-host copy, no allocation. Make the first call on a device (either entry point) at start-up,
+ * before the GPU's memory is handed to a pool and outside stream capture: with lazy module loading that first call is
+ * what materialises the 4.1 MiB array. No counterpart in the reference. */
+int dmlp_allreduce_noalloc_status(uint32_t out[4]);
 
 /* ------------------------------------------------------------------ cluster-fused MLP step
  * Forward + softmax-CE + backward of one batch of the reference-sized MLP in ONE launch of an 8-CTA

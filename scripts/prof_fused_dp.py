@@ -13,7 +13,7 @@ sys.path.insert(0, ROOT)
 from dmlp_b200.parallel.trainer import Trainer, TrainerConfig  # noqa: E402
 from dmlp_b200.utils.data import synthetic_mnist  # noqa: E402
 
-NAMES_GX = {15: "side wgrads drained + pushed", 0: "peers' dZ1 staged", 1: "small tensors reduced", 11: "wgrad1 (all ranks) done",
+NAMES_GX = {15: "stage loop entered", 0: "peers' dZ1 staged", 1: "small tensors reduced", 11: "wgrad1 (all ranks) done",
             12: "dW1 applied in place", 14: "fence + end-of-step barrier"}
 NAMES = {13: "step start", 2: "F1 mma+scatter", 3: "RS1 arrived", 4: "H1+F2+scatter", 5: "RS2 arrived", 6: "H2+F3+allreduce",
          7: "logits arrived", 8: "CE+dgL+gather dZ2", 9: "dgrad2 done", 10: "gather dZ1", 11: "wgrads drained + wg1 done",

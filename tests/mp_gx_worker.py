@@ -64,7 +64,7 @@ def main():
         dist.barrier()
 
     # ---- 2. soak: replicas stay bit-identical, loss finite and falling
-    cfg = TrainerConfig(dims=(784, 128, 64, 10), batch=64, lr=0.05, seed=11)  # fused=-1: the default must pick mode 5
+    cfg = TrainerConfig(dims=(784, 128, 64, 10), batch=64, lr=0.05, seed=11, fused=5)
     t = Trainer(cfg, device=local, process_group=True)
     assert t.dp_mode == 5, t.dp_mode
     x, y = synthetic_mnist(64 * world * 64, seed=5)
@@ -79,34 +79,36 @@ def main():
     t.close()
     dist.barrier()
 
-    # ---- 3. a rank dies mid-run
-    cfg = TrainerConfig(dims=(784, 128, 64, 10), batch=64, lr=0.05, seed=11, watchdog_ms=400)
-    t = Trainer(cfg, device=local, process_group=True)
-    x, y = synthetic_mnist(64 * world * 16, seed=5)
-    t.fit(x, y, 8)
-    dead = world - 1
-    if rank == dead:
-        t.inject_fault(8 + 5)  # goes silent at the 6th step of the next call
-    t0 = time.time()
-    err = None
-    try:
-        t.fit(x, y, 16)
-    except native.NativeError as e:
-        err = e
-    dt = time.time() - t0
-    if rank != dead:
-        assert err is not None and err.code == native.ERR_TIMEOUT, err
-        assert f"waited for rank {dead}" in str(err), str(err)
-        assert dt < 0.4 + 1.0, f"survivor returned after {dt:.2f} s"
-        assert t.failed
+    # ---- 3. a rank dies mid-run: the default path (persistent compute + reducer launch, mode 4) and the global-batch mode
+    for fused, want_mode in ((-1, 4), (5, 5)):
+        cfg = TrainerConfig(dims=(784, 128, 64, 10), batch=64, lr=0.05, seed=11, watchdog_ms=400, fused=fused)
+        t = Trainer(cfg, device=local, process_group=True)
+        assert t.dp_mode == want_mode, (t.dp_mode, want_mode)
+        x, y = synthetic_mnist(64 * world * 16, seed=5)
+        t.fit(x, y, 8)
+        dead = world - 1
+        if rank == dead:
+            t.inject_fault(8 + 5)  # goes silent at the 6th step of the next call
+        t0 = time.time()
+        err = None
         try:
-            t.fit(x, y, 1)
-            raise AssertionError("a FAILED trainer accepted more steps")
+            t.fit(x, y, 16)
         except native.NativeError as e:
-            assert e.code == native.ERR_ABORTED, e
-        print(f"gx failure ok on rank {rank}: {err} after {dt * 1e3:.0f} ms", flush=True)
-    t.close()
-    dist.barrier()
+            err = e
+        dt = time.time() - t0
+        if rank != dead:
+            assert err is not None and err.code == native.ERR_TIMEOUT, err
+            assert f"waited for rank {dead}" in str(err), str(err)
+            assert dt < 0.4 + 1.0, f"survivor returned after {dt:.2f} s"
+            assert t.failed
+            try:
+                t.fit(x, y, 1)
+                raise AssertionError("a FAILED trainer accepted more steps")
+            except native.NativeError as e:
+                assert e.code == native.ERR_ABORTED, e
+            print(f"failure ok (mode {want_mode}) on rank {rank}: {err} after {dt * 1e3:.0f} ms", flush=True)
+        t.close()
+        dist.barrier()
     if rank == 0:
         print("MP_GX_OK", flush=True)
     dist.destroy_process_group()

@@ -125,7 +125,7 @@ def main():
         params = [(w.astype(np.float64), b.astype(np.float64)) for w, b in t.weights()]
         steps = 6
         st = t.fit(x, y, steps)
-        if fused in (3, 4, 5) or (fused == -1 and algo == "auto"):  # (-1 picks the global-batch mode)
+        if fused in (3, 4, 5) or (fused == -1 and algo == "auto"):  # (-1 picks the persistent data-parallel launch)
             assert t.kernels_per_step == 1 and t.launches_last_run == 1, (t.kernels_per_step, t.launches_last_run)
         if fused == 1:
             assert t.kernels_per_step == 2, t.kernels_per_step

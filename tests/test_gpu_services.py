@@ -103,6 +103,68 @@ def test_ring_f32_padding_case_and_fused_sgd(cuda_cluster):
         assert np.abs(np.frombuffer(_d2h(pb, client, md.deviceId.value, 0x1000), np.float32) - s).max() < 1e-4
 
 
+def test_concurrent_allreduce_on_two_communicators_over_the_same_gpus(cuda_cluster):
+    """Two communicators over the same logical devices, hammered from two threads at once (the gRPC server has 16
+    workers): native collectives are serialised per process, so neither mixes buffers nor starves the other into
+    its watchdog (coordinator.py native collectives were not serialised)."""
+    import threading
+    from dmlp_b200.proto import gpu_sim as pb
+    client, devs, coord = cuda_cluster(3)
+    addrs = [d.addr for d in devs]
+    c1 = client.CommInit(pb.CommInitRequest(numDevices=3, device_addresses=addrs))
+    c2 = client.CommInit(pb.CommInitRequest(numDevices=3, device_addresses=addrs))
+    n = 64 * 1024
+    errs = []
+
+    def worker(comm, addr, val, lr):
+        try:
+            for it in range(12):
+                for k, md in enumerate(comm.devices):
+                    _h2d(pb, client, md.deviceId.value, addr, np.full(n, val * (k + 1), np.float32).tobytes())
+                    _h2d(pb, client, md.deviceId.value, addr + 0x100, np.ones(n, np.float32).tobytes())
+                memaddrs = {k: pb.MemAddr(value=addr) for k in range(3)}
+                r = client.AllReduceRing(pb.AllReduceRingRequest(commId=comm.commId, count=4 * n, memAddrs=memaddrs),
+                                         metadata=(("dmlp-dtype", "f32"), ("dmlp-sgd-lr", str(lr)),
+                                                   ("dmlp-sgd-weights", hex(addr + 0x100))))
+                assert r.success
+                want = 1.0 - lr * (val * 6) / 3
+                for md in comm.devices:
+                    got = np.frombuffer(_d2h(pb, client, md.deviceId.value, addr + 0x100), np.float32)
+                    assert np.allclose(got, want, rtol=1e-5), (it, got[:4], want)
+        except Exception as e:  # noqa: BLE001
+            errs.append(e)
+
+    t1 = threading.Thread(target=worker, args=(c1, 0x1000, 1.0, 0.5))
+    t2 = threading.Thread(target=worker, args=(c2, 0x1400, 3.0, 0.125))
+    t1.start(); t2.start(); t1.join(); t2.join()
+    assert not errs, errs
+    for c in (c1, c2):
+        assert client.GetCommStatus(pb.GetCommStatusRequest(commId=c.commId)).status == pb.SUCCESS
+
+
+def test_group_end_submits_the_queue_with_one_wait(cuda_cluster):
+    """GroupStart .. GroupEnd: the queued collectives are launched back to back and waited for once; each
+    keeps its own learning-rate scalar."""
+    from dmlp_b200.proto import gpu_sim as pb
+    client, devs, coord = cuda_cluster(2)
+    init = client.CommInit(pb.CommInitRequest(numDevices=2, device_addresses=[d.addr for d in devs]))
+    n = 4096
+    for k, md in enumerate(init.devices):
+        _h2d(pb, client, md.deviceId.value, 0x1000, np.full(n, float(k + 1), np.float32).tobytes())
+        _h2d(pb, client, md.deviceId.value, 0x1400, np.ones(n, np.float32).tobytes())
+    assert client.GroupStart(pb.GroupStartRequest(commId=init.commId)).success
+    for lr in (0.5, 0.25):  # two fused updates of the same weights, queued
+        memaddrs = {k: pb.MemAddr(value=0x1000) for k in range(2)}
+        assert client.AllReduceRing(pb.AllReduceRingRequest(commId=init.commId, count=4 * n, memAddrs=memaddrs),
+                                    metadata=(("dmlp-dtype", "f32"), ("dmlp-sgd-lr", str(lr)),
+                                              ("dmlp-sgd-weights", hex(0x1400)))).success
+    assert client.GroupEnd(pb.GroupEndRequest(commId=init.commId)).success
+    for md in init.devices:
+        got = np.frombuffer(_d2h(pb, client, md.deviceId.value, 0x1400), np.float32)
+        assert np.allclose(got, 1.0 - (0.5 + 0.25) * 1.5), got[:4]
+    assert client.GetCommStatus(pb.GetCommStatusRequest(commId=init.commId)).status == pb.SUCCESS
+
+
 def test_p2p_stream_is_a_device_copy_kernel(cuda_cluster):
     """BeginSend/BeginReceive + payload-free StreamSend → P2P copy kernel; status follows its CUDA event."""
     from dmlp_b200.proto import gpu_sim as pb
