@@ -1292,7 +1292,8 @@ mlp_fused_step_kernel(const __grid_constant__ CUtensorMap tmXA, const __grid_con
 #pragma unroll
           for (int rr = 0; rr < 4; ++rr)
             if (((pend >> (i * 4 + rr)) & 1u) && (gx_valid(v[i][rr]) || *xfail != 0)) pend &= ~(1u << (i * 4 + rr));
-        if (pend != 0u && (++spins & 0xF) == 0 && gx_timeout(p, r0, 10u, gdeadline)) *xfail = 1;
+        // (on a timeout the record names the rank whose contribution is still missing: bit i*4+rr = rank r0+rr)
+        if (pend != 0u && (++spins & 0xF) == 0 && gx_timeout(p, r0 + ((__ffs(pend) - 1) & 3), 10u, gdeadline)) *xfail = 1;
       }
 #pragma unroll
       for (int rr = 0; rr < 4; ++rr)
