@@ -145,6 +145,9 @@ def main() -> int:
     ap.add_argument("--no-graph", action="store_true")
     ap.add_argument("--fused", type=int, default=-1, help="TrainerConfig.fused (-1 auto; 2/3/4 select variants of the fused path)")
     ap.add_argument("--host-batches", type=int, default=0, help="host dataset size in batches per rank")
+    ap.add_argument("--fault", default="", help="after the timed regions: failure drill 'dead-rank:<r>@step:<s>' (s counted "
+                    "from the drill's start); reports how long the survivors need to notice (BASELINE config 5)")
+    ap.add_argument("--watchdog-ms", type=int, default=10000)
     a = ap.parse_args()
     if a.impl == "reference":
         return run_reference(a)
@@ -175,7 +178,7 @@ def main() -> int:
     batch = a.batch or m["batch"]
     overlap = (a.model == "wide" and multi) if a.overlap < 0 else bool(a.overlap)
     cfg = TrainerConfig(dims=m["dims"], batch=batch, lr=0.01, precision=m["precision"], allreduce=a.allreduce,
-                        overlap=overlap, use_graph=not a.no_graph, fused=a.fused)
+                        overlap=overlap, use_graph=not a.no_graph, fused=a.fused, watchdog_ms=a.watchdog_ms)
     trainer = Trainer(cfg, device=local_rank, process_group=multi)
 
     # ---- synthetic data: a pinned host dataset (e2e) and a device dataset larger than L2 (kernel timing)
@@ -275,6 +278,34 @@ def main() -> int:
         if multi:
             dist.barrier()
 
+    # ---- failure drill (optional, last: it leaves the communicator FAILED): one rank goes silent mid-run
+    drill = None
+    if a.fault and multi:
+        from dmlp_b200.parallel.schedule import parse_fault
+        from dmlp_b200.runtime import native
+        dead_rank, dead_step = parse_fault(a.fault)
+        drill_steps = dead_step + 32
+        barrier()
+        if rank == dead_rank:
+            trainer.inject_fault(trainer.global_step + dead_step)
+        t0 = time.perf_counter()
+        err = None
+        try:
+            trainer.fit(px, py, drill_steps, return_metrics=False, batch_stride=1)
+        except native.NativeError as e:
+            err = e
+        dt_ms = (time.perf_counter() - t0) * 1e3
+        rec = {"rank": rank, "error": (err.message if err else None), "code": (err.code if err else 0),
+               "returned_after_ms": dt_ms, "failed_state": trainer.failed}
+        recs = [None] * world
+        dist.all_gather_object(recs, rec)
+        surv = [r_ for r_ in recs if r_["rank"] != dead_rank]
+        drill = {"spec": a.fault, "watchdog_ms": a.watchdog_ms, "dead_rank": dead_rank,
+                 "survivors_detected": all(r_["code"] == native.ERR_TIMEOUT and r_["failed_state"] for r_ in surv),
+                 "survivor_return_ms_max": max(r_["returned_after_ms"] for r_ in surv),
+                 "detect_overhead_ms": max(r_["returned_after_ms"] for r_ in surv) - a.watchdog_ms,
+                 "example": surv[0]["error"]}
+
     gbatch = batch * world
     value = a.steps * gbatch / (ms_dev / 1e3)
     e2e_value = a.steps * gbatch / (max(ms_e2e, wall_e2e) / 1e3)
@@ -302,6 +333,7 @@ def main() -> int:
         "steps_per_launch": round(a.steps / max(launches_dev, 1), 2),
         "clocks": clocks,
         "verified": verified,
+        "failure_drill": drill,
         "impl": "ours",
     }
     sys.stdout.flush()

@@ -972,8 +972,10 @@ extern "C" int dmlp_trainer_run(dmlp_trainer_t h, const float* x_host, const int
   if (t->comm) {
     uint32_t st[5];
     TRY(dmlp_comm_status(t->comm, st));
-    if (st[0] != 0)
+    if (st[0] != 0) {
+      t->failed = true;  // sticky: further runs are refused with DMLP_ERR_ABORTED
       return set_error(DMLP_ERR_TIMEOUT, "collective watchdog: rank %u waited for rank %u (phase %u)", st[1], st[2], st[3]);
+    }
   }
   return DMLP_OK;
 }

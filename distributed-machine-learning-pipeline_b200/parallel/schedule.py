@@ -36,3 +36,19 @@ def make(name: str, lr: float, total_steps: int = 0, **kw) -> Schedule:
     if name == "warmup-cosine":
         return warmup(cosine(lr, total_steps, kw.get("min_lr", 0.0)), kw.get("warmup_steps", max(total_steps // 20, 1)))
     raise ValueError(f"unknown schedule {name!r}")
+
+
+def parse_fault(spec: str):
+    """``"dead-rank:<r>@step:<s>"`` -> (r, s); empty / None -> (-1, -1). The fault-injection syntax of ``Config.fault``
+    (utils/config.py), ``train.py`` and ``bench.py --fault``."""
+    if not spec:
+        return -1, -1
+    try:
+        left, right = spec.split("@")
+        kind, r = left.split(":")
+        what, s = right.split(":")
+        if kind != "dead-rank" or what != "step":
+            raise ValueError(spec)
+        return int(r), int(s)
+    except Exception as e:  # noqa: BLE001
+        raise ValueError(f"fault spec {spec!r} is not of the form dead-rank:<r>@step:<s>") from e

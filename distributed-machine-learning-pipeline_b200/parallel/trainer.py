@@ -264,6 +264,7 @@ class Trainer:
         after ``watchdog_ms``; their ``fit`` raises ``native.DmlpError`` (TIMEOUT) and the trainer turns FAILED — the
         training-path analogue of the reference's device-failure test (gpu_coordinator_server_test.go:370-429)."""
         native.check(self.lib.dmlp_trainer_set_fault(self._h, int(step)))
+        self._fault_step = int(step)  # (per-layer / two-kernel paths: applied by fit() through the communicator's dead mask)
 
     @property
     def failed(self) -> bool:
@@ -316,6 +317,20 @@ class Trainer:
         """Runs ``steps`` optimisation steps. Rank r consumes batches r, r+world, r+2·world, … of the
         host dataset (sequential, no shuffle, partial last batch dropped — like the reference).
         ``batch_stride=1`` walks a rank-private dataset densely instead."""
+        fs = getattr(self, "_fault_step", -1)
+        if (fs >= 0 and self.comm is not None and self.world > 1 and self.dp_mode in (0, 1)
+                and self.global_step <= fs < self.global_step + steps and first_batch is None):
+            # Fault injection on the paths whose collectives are separate kernels (per-layer buckets, two-kernel chain):
+            # run up to the fault step, then mark this rank dead in its communicator - its all-reduce kernels return
+            # at once from then on and the peers' watchdogs fire. (The fused data-parallel kernels take the step natively.)
+            k = fs - self.global_step
+            self._fault_step = -1
+            if k > 0:
+                self.fit(x, y, k, lr_schedule=lr_schedule, return_metrics=return_metrics, batch_stride=batch_stride)
+            self.comm.inject_dead_ranks(1 << self.rank)
+            self.cfg.use_graph = False  # captured graphs froze the collectives' arguments: the dead rank runs eagerly
+            return self.fit(x, y, steps - k, lr_schedule=lr_schedule, return_metrics=return_metrics,
+                            device_timing=device_timing, batch_stride=batch_stride)
         xp, yp, n = self._host_ptrs(x, y)
         nb = n // self.cfg.batch
         if nb == 0:

@@ -13,6 +13,7 @@ import argparse
 import logging
 import os
 import sys
+import time
 
 from .utils import data as D
 from .utils.config import Config
@@ -34,6 +35,7 @@ def main(argv=None) -> int:
     import torch.distributed as dist
     from .parallel import schedule as S
     from .parallel.trainer import Trainer, TrainerConfig, pin
+    from .runtime import native
 
     rank, world = int(os.environ.get("RANK", 0)), int(os.environ.get("WORLD_SIZE", 1))
     local = int(os.environ.get("LOCAL_RANK", 0))
@@ -66,6 +68,11 @@ def main(argv=None) -> int:
         first_epoch = int(meta.get("epoch", 0)) + 1
         if rank == 0:
             log.info("resumed from %s: epoch %d, step %d", ns.resume, first_epoch - 1, trainer.global_step)
+    # fault injection (BASELINE config 5): "dead-rank:<r>@step:<s>" - rank r stops taking part in the gradient exchange
+    # at global step s, as if its GPU had died (reference test: gpu_coordinator_server_test.go:370-429)
+    dead_rank, dead_step = S.parse_fault(cfg.fault)
+    if dead_rank == rank:
+        trainer.inject_fault(dead_step)
     px, py = pin(xtr), pin(ytr)
     spe = ns.steps_per_epoch or xtr.shape[0] // (cfg.batch * world)
     sched = S.make(cfg.schedule, cfg.lr, total_steps=spe * cfg.epochs)
@@ -73,7 +80,25 @@ def main(argv=None) -> int:
     if rank == 0:
         log.info("Starting MLP training...")
     for ep in range(first_epoch, cfg.epochs + 1):
-        st = trainer.fit(px, py, spe, lr_schedule=sched, device_timing=True)
+        try:
+            st = trainer.fit(px, py, spe, lr_schedule=sched, device_timing=True)
+        except native.NativeError as e:
+            if e.code not in (native.ERR_TIMEOUT, native.ERR_ABORTED):
+                raise
+            # A peer stopped answering mid-all-reduce: the in-kernel watchdog fired, the communicator is FAILED (sticky,
+            # like the reference's, gpu_coordinator_server.go:339-346). Log it, leave no GPU work behind, exit non-zero.
+            log.error("rank %d: communicator FAILED in epoch %d: %s", rank, ep, e.message)
+            mw.write("failure", rank=rank, epoch=ep, error=e.message, global_step=trainer.global_step)
+            mw.close()
+            trainer.close()
+            return 3
+        if dead_rank == rank and trainer.global_step > dead_step >= 0:
+            # the "dead" rank: its kernels went silent at the fault step. Give the survivors their watchdog budget to
+            # notice before this process disappears (a launcher that sees a child exit tears the others down).
+            log.error("rank %d: simulated device failure at step %d, exiting", rank, dead_step)
+            time.sleep(cfg.watchdog_ms / 1000.0 + 1.0)
+            mw.close()
+            return 17
         if rank == 0:
             log.info("Epoch %d complete: Avg Loss: %.4f, Accuracy: %.2f%%", ep, st["loss"], 100 * st["accuracy"])
             mw.write("epoch", epoch=ep, loss=st["loss"], accuracy=st["accuracy"], steps=spe,

@@ -80,8 +80,10 @@ def main():
     dist.barrier()
 
     # ---- 3. a rank dies mid-run: the default path (persistent compute + reducer launch, mode 4) and the global-batch mode
-    for fused, want_mode in ((-1, 4), (5, 5)):
-        cfg = TrainerConfig(dims=(784, 128, 64, 10), batch=64, lr=0.05, seed=11, watchdog_ms=400, fused=fused)
+    # ... and the per-layer path with its bucketed all-reduce overlapped with backward (mode 0: what the wide model runs)
+    for fused, want_mode in ((-1, 4), (5, 5), (0, 0)):
+        cfg = TrainerConfig(dims=(784, 128, 64, 10), batch=64, lr=0.05, seed=11, watchdog_ms=400, fused=fused,
+                            overlap=(fused == 0))
         t = Trainer(cfg, device=local, process_group=True)
         assert t.dp_mode == want_mode, (t.dp_mode, want_mode)
         x, y = synthetic_mnist(64 * world * 16, seed=5)

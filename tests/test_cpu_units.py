@@ -219,3 +219,15 @@ def test_real_mnist_t10k_convergence_with_the_oracle_if_mounted():
     logits, _ = oracle.forward(params, xte)
     acc = float((logits.argmax(1) == yte).mean())
     assert loss < 0.6 * first and acc > 0.85, (first, loss, acc)
+
+
+def test_fault_spec_parsing():
+    """``Config.fault`` / ``bench.py --fault`` syntax (BASELINE config 5: a rank dies at a given step)."""
+    import pytest
+    from dmlp_b200.parallel.schedule import parse_fault
+    assert parse_fault("") == (-1, -1)
+    assert parse_fault(None) == (-1, -1)
+    assert parse_fault("dead-rank:3@step:40") == (3, 40)
+    for bad in ("dead-rank:3", "rank:1@step:2", "dead-rank:x@step:2", "dead-rank:1@epoch:2"):
+        with pytest.raises(ValueError):
+            parse_fault(bad)
