@@ -1,0 +1,151 @@
+"""The fair library bar (NOT the product path): the same MLP step built from stock parts and captured in ONE CUDA graph.
+
+    forward / backward : torch autograd over cuBLAS (TF32 allowed - the precision our tensor-core path uses)
+    gradient sync      : ONE torch.distributed.all_reduce (NCCL) on the flat gradient vector
+    optimizer          : one fused axpy on the flat parameter vector (w += -(lr/world) * g)
+    launch overhead    : none - the whole step (zero-grad, fwd, bwd, all-reduce, update) replays as a CUDA graph
+
+This replaces the eager DistributedDataParallel comparison of round 1 (0.7 ms of Python per step): the number this
+script prints is what a careful PyTorch + NCCL user gets on the same box. Batch 64 per GPU, inputs copied from a
+device-resident set each step, device-timed with CUDA events, max over ranks.
+
+    python baseline/nccl_graph_mlp.py --steps 2000
+    python -m torch.distributed.run --nproc-per-node N --master-addr 127.0.0.1 --master-port 29531 \
+        baseline/nccl_graph_mlp.py --steps 2000
+"""
+import argparse
+import json
+import os
+import signal
+
+import torch
+import torch.distributed as dist
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--steps", type=int, default=2000)
+    ap.add_argument("--warmup", type=int, default=200)
+    ap.add_argument("--dims", default="784,128,64,10")
+    ap.add_argument("--batch", type=int, default=64)
+    ap.add_argument("--lr", type=float, default=0.01)
+    ap.add_argument("--time-limit", type=int, default=90, help="seconds before the run reports an error and exits")
+    a = ap.parse_args()
+    rank, world = int(os.environ.get("RANK", 0)), int(os.environ.get("WORLD_SIZE", 1))
+    local = int(os.environ.get("LOCAL_RANK", 0))
+    torch.cuda.set_device(local)
+    if world > 1:
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    torch.backends.cuda.matmul.allow_tf32 = True
+    torch.backends.cudnn.allow_tf32 = True
+    dims = [int(d) for d in a.dims.split(",")]
+
+    # flat parameter / gradient vectors; the per-layer tensors are views (their .grad are views of the flat gradient)
+    sizes = [(fi * fo, fo) for fi, fo in zip(dims[:-1], dims[1:])]
+    total = sum(w + b for w, b in sizes)
+    flat_w = torch.empty(total, device="cuda").uniform_(-0.05, 0.05)
+    flat_g = torch.zeros(total, device="cuda")
+    if world > 1:
+        dist.broadcast(flat_w, 0)
+    params, off = [], 0
+    for (nw, nb), fi, fo in zip(sizes, dims[:-1], dims[1:]):
+        w = flat_w[off:off + nw].view(fi, fo).requires_grad_(True)
+        w.grad = flat_g[off:off + nw].view(fi, fo)
+        off += nw
+        b = flat_w[off:off + nb].requires_grad_(True)
+        b.grad = flat_g[off:off + nb]
+        off += nb
+        params.append((w, b))
+    nbatches = 1024
+    xs = torch.rand(nbatches, a.batch, dims[0], device="cuda")
+    ys = torch.randint(0, dims[-1], (nbatches, a.batch), device="cuda")
+    sx, sy = xs[0].clone(), ys[0].clone()
+    alpha = -a.lr / world
+
+    def step_body():
+        flat_g.zero_()
+        h = sx
+        for l, (w, b) in enumerate(params):
+            h = torch.addmm(b, h, w)
+            if l < len(params) - 1:
+                h = torch.relu(h)
+        loss = torch.nn.functional.cross_entropy(h, sy)
+        loss.backward()  # accumulates into the .grad views = the flat gradient
+        if world > 1:
+            dist.all_reduce(flat_g)
+        with torch.no_grad():
+            flat_w.add_(flat_g, alpha=alpha)
+        return loss
+
+    def timed(fn, steps):
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for i in range(steps):
+            fn(i)
+        e1.record()
+        torch.cuda.synchronize()
+        t = torch.tensor([e0.elapsed_time(e1)], device="cuda", dtype=torch.float64)
+        if world > 1:
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return t.item()
+
+    def eager(i):
+        sx.copy_(xs[i % nbatches])
+        sy.copy_(ys[i % nbatches])
+        step_body()
+
+    results = {}
+
+    def give_up(signum, frame):  # a wedged NCCL capture must not hold the GPUs: report what we have and leave
+        results.setdefault("cuda_graph", {"error": f"no progress within {a.time_limit} s (NCCL under graph capture?)"})
+        if rank == 0:
+            print(json.dumps({"impl": "torch + cuBLAS + NCCL all_reduce, CUDA graph", "n_gpus": world, **results}), flush=True)
+        os._exit(3)
+
+    signal.signal(signal.SIGALRM, give_up)
+    signal.alarm(a.time_limit)
+    for i in range(max(a.warmup // 4, 11)):
+        eager(i)
+    ms = timed(eager, max(a.steps // 4, 50))
+    n_eager = max(a.steps // 4, 50)
+    results["eager"] = {"ms_per_step": ms / n_eager, "samples_per_s": n_eager * a.batch * world / (ms / 1e3)}
+    try:
+        s = torch.cuda.Stream()
+        s.wait_stream(torch.cuda.current_stream())
+        with torch.cuda.stream(s):
+            for _ in range(11):
+                step_body()
+        torch.cuda.current_stream().wait_stream(s)
+        g = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(g, capture_error_mode="thread_local"):  # (NCCL's watchdog thread may touch CUDA meanwhile)
+            step_body()
+
+        def gstep(i):
+            sx.copy_(xs[i % nbatches])
+            sy.copy_(ys[i % nbatches])
+            g.replay()
+
+        for i in range(max(a.warmup, 20)):
+            gstep(i)
+        ms = timed(gstep, a.steps)
+        results["cuda_graph"] = {"ms_per_step": ms / a.steps, "samples_per_s": a.steps * a.batch * world / (ms / 1e3)}
+        # replicas must agree (same init, same summed gradient)
+        if world > 1:
+            ref = flat_w.clone()
+            dist.broadcast(ref, 0)
+            results["replicas_equal"] = bool(torch.equal(ref, flat_w))
+    except Exception as e:  # graph capture of NCCL can be refused by some stacks
+        results["cuda_graph"] = {"error": str(e)[:300]}
+    if rank == 0:
+        print(json.dumps({"impl": "torch autograd + cuBLAS + ONE NCCL all_reduce on the flat gradient + fused axpy, CUDA graph",
+                          "n_gpus": world, "dims": dims, "per_gpu_batch": a.batch, "tf32": True, **results}))
+    if world > 1:
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

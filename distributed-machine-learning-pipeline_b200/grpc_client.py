@@ -19,6 +19,7 @@ from __future__ import annotations
 import argparse
 import logging
 import time
+from concurrent.futures import ThreadPoolExecutor
 from typing import List, Optional, Sequence
 
 import numpy as np
@@ -48,6 +49,9 @@ class GrpcTrainer:
         self.comm_id = init.commId
         self.device_ids = [m.deviceId.value for m in init.devices]
         self._stub = dict(zip(self.device_ids, self.dev_stubs))
+        # the per-device halves of a step are independent RPC sequences: issue them concurrently (gRPC releases the GIL
+        # while it waits; the reference client walks its devices one after the other, client.go:596-647)
+        self._pool = ThreadPoolExecutor(max_workers=max(len(self.device_ids), 1), thread_name_prefix="dmlp-dev")
         self.blob_bytes = self.layout.reference_count * 4
         blob = self.layout.to_reference_bytes(self.layout.init_reference(seed))
         for did in self.device_ids:  # identical replicas (client.go:642-644)
@@ -68,27 +72,50 @@ class GrpcTrainer:
         return self._d2h(self.device_ids[device_index], WEIGHT_ADDR)
 
     # ------------------------------------------------------------------ one optimisation step
+    def _device_half(self, did: int, stub, x, y, backward: bool = True):
+        """Everything one device does for one batch: upload its shard, RunForward (+ RunBackward), read the logits."""
+        classes = self.dims[-1]
+        self._h2d(did, DATA_ADDR, np.ascontiguousarray(x, dtype="<f4").tobytes())
+        if backward:
+            self._h2d(did, LABEL_ADDR, np.eye(classes, dtype="<f4")[np.asarray(y)].tobytes())  # one-hot like client.go:315-350
+        stub.RunForward(pb.RunForwardRequest(deviceId=did, inputAddr=DATA_ADDR, outputAddr=LOGIT_ADDR))
+        if backward:
+            stub.RunBackward(pb.RunBackwardRequest(deviceId=did, gradientAddr=GRAD_ADDR))
+        logits = np.frombuffer(self._d2h(did, LOGIT_ADDR), dtype="<f4").reshape(len(y), classes).astype(np.float64)
+        z = logits - logits.max(1, keepdims=True)
+        p = np.exp(z) / np.exp(z).sum(1, keepdims=True)
+        loss = float(-np.log(p[np.arange(len(y)), y] + 1e-10).sum())
+        return loss, int((logits.argmax(1) == np.asarray(y)).sum()), len(y)
+
     def step(self, shards) -> dict:
         """``shards[d] = (x float32 [B][in], y int [B])`` for device d."""
-        classes = self.dims[-1]
-        loss_sum, correct, seen = 0.0, 0, 0
-        for did, stub, (x, y) in zip(self.device_ids, self.dev_stubs, shards):
-            self._h2d(did, DATA_ADDR, np.ascontiguousarray(x, dtype="<f4").tobytes())
-            self._h2d(did, LABEL_ADDR, np.eye(classes, dtype="<f4")[np.asarray(y)].tobytes())  # one-hot like client.go:315-350
-            stub.RunForward(pb.RunForwardRequest(deviceId=did, inputAddr=DATA_ADDR, outputAddr=LOGIT_ADDR))
-            stub.RunBackward(pb.RunBackwardRequest(deviceId=did, gradientAddr=GRAD_ADDR))
-            logits = np.frombuffer(self._d2h(did, LOGIT_ADDR), dtype="<f4").reshape(len(y), classes).astype(np.float64)
-            z = logits - logits.max(1, keepdims=True)
-            p = np.exp(z) / np.exp(z).sum(1, keepdims=True)
-            loss_sum += float(-np.log(p[np.arange(len(y)), y] + 1e-10).sum())
-            correct += int((logits.argmax(1) == np.asarray(y)).sum())
-            seen += len(y)
+        futs = [self._pool.submit(self._device_half, did, stub, x, y)
+                for did, stub, (x, y) in zip(self.device_ids, self.dev_stubs, shards)]
+        parts = [f.result() for f in futs]
+        loss_sum, correct, seen = (sum(p[i] for p in parts) for i in range(3))
         r = self.coord.AllReduceRing(pb.AllReduceRingRequest(commId=self.comm_id, count=self.blob_bytes),
                                      metadata=(("dmlp-dtype", "f32"), ("dmlp-sgd-lr", repr(self.lr)),
                                                ("dmlp-sgd-weights", hex(WEIGHT_ADDR))))
         if not r.success:
             raise RuntimeError("AllReduceRing failed")
         return {"loss": loss_sum / seen, "accuracy": correct / seen}
+
+    def evaluate(self, x: np.ndarray, y: np.ndarray) -> dict:
+        """Forward-only pass over all full batches, spread over the devices (the reference's ``testModel``,
+        client.go:462-502: softmax + argmax accuracy, "Final Test Accuracy")."""
+        B, n = self.batch, len(self.device_ids)
+        nb = x.shape[0] // B
+        loss_sum, correct, seen = 0.0, 0, 0
+        for b0 in range(0, nb, n):
+            futs = [self._pool.submit(self._device_half, self.device_ids[d], self.dev_stubs[d],
+                                      x[(b0 + d) * B:(b0 + d + 1) * B], y[(b0 + d) * B:(b0 + d + 1) * B], False)
+                    for d in range(min(n, nb - b0))]
+            for f in futs:
+                ls, c, m = f.result()
+                loss_sum, correct, seen = loss_sum + ls, correct + c, seen + m
+        acc = correct / max(seen, 1)
+        log.info("Final Test Accuracy: %.2f%%", 100 * acc)  # client.go:501
+        return {"loss": loss_sum / max(seen, 1), "accuracy": acc, "samples": seen}
 
     def fit(self, x: np.ndarray, y: np.ndarray, steps: int, first_batch: int = 0) -> List[dict]:
         n, B = len(self.device_ids), self.batch
@@ -103,19 +130,22 @@ class GrpcTrainer:
         return out
 
     def close(self) -> None:
+        self._pool.shutdown(wait=True)
         self.coord.CommDestroy(pb.CommDestroyRequest(commId=self.comm_id))
 
 
 def main(argv: Optional[Sequence[str]] = None) -> int:
     ap = argparse.ArgumentParser(description=__doc__)
-    ap.add_argument("--coordinator", default="127.0.0.1:50050")
-    ap.add_argument("--devices", default="127.0.0.1:50051,127.0.0.1:50052,127.0.0.1:50053")
+    # the reference client's endpoints (client.go:518,527) = this repo's launchers' defaults (services/server.py)
+    ap.add_argument("--coordinator", default="127.0.0.1:50051")
+    ap.add_argument("--devices", default="127.0.0.1:5003,127.0.0.1:5004,127.0.0.1:5005")
     ap.add_argument("--dims", default="784,128,64,10")
     ap.add_argument("--batch", type=int, default=64)
     ap.add_argument("--lr", type=float, default=0.01)
     ap.add_argument("--epochs", type=int, default=1)
     ap.add_argument("--steps-per-epoch", type=int, default=50)
     ap.add_argument("--samples", type=int, default=60000)
+    ap.add_argument("--test-samples", type=int, default=10000)
     a = ap.parse_args(argv)
     logging.basicConfig(level=logging.INFO, format="%(asctime)s %(message)s")
     dims = tuple(int(v) for v in a.dims.split(","))
@@ -132,6 +162,8 @@ def main(argv: Optional[Sequence[str]] = None) -> int:
                  float(np.mean([s["loss"] for s in st])), 100 * float(np.mean([s["accuracy"] for s in st])),
                  a.steps_per_epoch / (time.time() - t0))
     log.info("Training complete.")
+    xte, yte = D.synthetic_mnist(a.test_samples, seed=1, features=dims[0], num_classes=dims[-1])
+    t.evaluate(xte, yte)  # testModel (client.go:658 -> :462-502)
     t.close()
     return 0
 

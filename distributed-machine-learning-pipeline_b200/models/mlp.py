@@ -46,25 +46,35 @@ class MLP(nn.Module):
         hook = self.layer_ready_hook
         return (lambda: hook(l)) if hook is not None else None
 
-    def features(self, x: torch.Tensor) -> torch.Tensor:
-        """All layers but the last (ReLU after each)."""
+    def _chain(self, l: int) -> dict:
+        """Layer l > 0 consumes the ReLU output of layer l-1: its dgrad epilogue applies that ReLU's mask and writes
+        layer l-1's bias gradient (no eager mask / column-sum kernels in backward)."""
+        return dict(mask_input=l > 0, prev_grad_b=self._gb[l - 1] if l > 0 else None)
+
+    def features(self, x: torch.Tensor, head_follows: bool = False) -> torch.Tensor:
+        """All layers but the last (ReLU after each). A layer that is consumed by the next layer of this module gets
+        its gradient masked and its bias gradient produced there (``pre_masked``); the last of them only when the
+        module's own head follows (``forward`` / ``loss``) - a caller that puts its own head on ``features(x)`` gets an
+        ordinary autograd tensor."""
         h = x
-        for l in range(len(self.weights) - 1):
-            h = F.fused_linear(h, self.weights[l], self.biases[l], True, self._gw[l], self._gb[l], self._ready(l))
+        n = len(self.weights)
+        for l in range(n - 1):
+            h = F.fused_linear(h, self.weights[l], self.biases[l], True, self._gw[l], self._gb[l], self._ready(l),
+                               pre_masked=(l < n - 2) or head_follows, **self._chain(l))
         return h
 
     def forward(self, x: torch.Tensor) -> torch.Tensor:
         """Logits ``[B, out_pad]`` (columns >= num_classes are padding and stay zero)."""
         l = len(self.weights) - 1
-        return F.fused_linear(self.features(x), self.weights[l], self.biases[l], False, self._gw[l], self._gb[l],
-                              self._ready(l))
+        return F.fused_linear(self.features(x, head_follows=True), self.weights[l], self.biases[l], False, self._gw[l], self._gb[l],
+                              self._ready(l), **self._chain(l))
 
     def loss(self, x: torch.Tensor, labels: torch.Tensor):
         """Mean cross-entropy and hit count; the last layer and the loss run as one kernel.
         ``loss.backward()`` leaves all gradients in ``flat_grad`` (same layout as ``flat``)."""
         l = len(self.weights) - 1
-        return F.linear_softmax_ce(self.features(x), self.weights[l], self.biases[l], labels.to(torch.int32),
-                                   self.num_classes, self._gw[l], self._gb[l], self._ready(l))
+        return F.linear_softmax_ce(self.features(x, head_follows=True), self.weights[l], self.biases[l], labels.to(torch.int32),
+                                   self.num_classes, self._gw[l], self._gb[l], self._ready(l), **self._chain(l))
 
     # ------------------------------------------------------------------ checkpoints (reference layout)
     def reference_blob(self) -> bytes:

@@ -487,6 +487,7 @@ class GPUCoordinatorService:
                 be.ensure(waddr, count)
                 outs.append(be.pointer(waddr))
                 lrs.append(be.scalar_f32(None, float(md["dmlp-sgd-lr"])))  # a slot of its own: earlier launches may still read theirs
+                be.touched(waddr)
             kwargs = dict(fuse_sgd=True, lr=lrs, scale=1.0 / len(devices))
         else:
             outs = ptrs

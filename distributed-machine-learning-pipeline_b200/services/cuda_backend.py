@@ -32,6 +32,7 @@ class CudaBackend(DeviceBackend):
         s = C.c_void_p()
         native.check(self._lib.dmlp_stream_create(self.ordinal, C.byref(s)))
         self.copy_stream = s.value
+        self._versions: Dict[int, int] = {}  # bumped whenever a buffer's contents change (Memcpy, collectives)
         info = native.DeviceInfo()
         native.check(self._lib.dmlp_device_info(self.ordinal, C.byref(info)))
         self._info = {"cuda-ordinal": str(self.ordinal), "uuid": info.uuid.decode(), "name": info.name.decode(),
@@ -65,13 +66,30 @@ class CudaBackend(DeviceBackend):
         self._bufs[addr] = (ptr, size, cap)
         return ptr
 
+    # Memcpy H2D / D2H (gpu_device_server.go:195-230): through a pinned staging buffer with cudaMemcpyAsync on the
+    # device's copy stream - DMA straight from/to page-locked memory instead of the driver's bounce copy of a pageable
+    # buffer. The stream is drained before returning (an RPC reply promises the bytes are there).
+    def _staging(self, nbytes: int) -> int:
+        if getattr(self, "_pin_cap", 0) < nbytes:
+            if getattr(self, "_pin_ptr", None):
+                self._lib.dmlp_host_free(self._pin_ptr)
+            cap = max(1 << 20, 1 << (nbytes - 1).bit_length())
+            p = C.c_void_p()
+            native.check(self._lib.dmlp_host_alloc(cap, C.byref(p)))
+            self._pin_ptr, self._pin_cap = p.value, cap
+        return self._pin_ptr
+
     def write(self, addr: int, data: bytes) -> None:
         with self._lock:
             n = len(data)
             ptr = self._reserve(addr, n, keep=False)
             self._bufs[addr] = (ptr, n, self._bufs[addr][2])
+            self._versions[addr] = self._versions.get(addr, 0) + 1
             if n:
-                native.check(self._lib.dmlp_memcpy_h2d(self.ordinal, ptr, bytes(data), n, None))
+                pin = self._staging(n)
+                C.memmove(pin, bytes(data), n)
+                native.check(self._lib.dmlp_memcpy_h2d(self.ordinal, ptr, pin, n, self.copy_stream))
+                native.check(self._lib.dmlp_stream_sync(self.ordinal, self.copy_stream))
 
     def read(self, addr: int, nbytes: int = 0) -> bytes:
         with self._lock:
@@ -79,10 +97,17 @@ class CudaBackend(DeviceBackend):
             if ent is None:
                 raise MissingBufferError(f"no data at address 0x{addr:x}")
             n = ent[1] if nbytes <= 0 or nbytes >= ent[1] else nbytes
-            buf = C.create_string_buffer(n)
-            if n:
-                native.check(self._lib.dmlp_memcpy_d2h(self.ordinal, buf, ent[0], n, None))
-            return buf.raw
+            if not n:
+                return b""
+            pin = self._staging(n)
+            native.check(self._lib.dmlp_memcpy_d2h(self.ordinal, pin, ent[0], n, self.copy_stream))
+            native.check(self._lib.dmlp_stream_sync(self.ordinal, self.copy_stream))
+            return C.string_at(pin, n)
+
+    def touched(self, addr: int) -> None:
+        """A kernel wrote the buffer at ``addr`` (e.g. the fused all-reduce+SGD updating the weight blob)."""
+        with self._lock:
+            self._versions[addr] = self._versions.get(addr, 0) + 1
 
     def has(self, addr: int) -> bool:
         with self._lock:
@@ -147,6 +172,7 @@ class CudaBackend(DeviceBackend):
         with dst._lock:
             dptr = dst._reserve(recv_addr, nbytes, keep=False)
             dst._bufs[recv_addr] = (dptr, nbytes, dst._bufs[recv_addr][2])
+            dst._versions[recv_addr] = dst._versions.get(recv_addr, 0) + 1
         if dst.ordinal != self.ordinal:
             devs = (C.c_int * 2)(self.ordinal, dst.ordinal)
             native.check(self._lib.dmlp_enable_peer_access(2, devs))
@@ -181,6 +207,11 @@ class CudaBackend(DeviceBackend):
         mlp = getattr(self, "_mlp", None)
         if mlp is None or mlp.dims != dims:
             mlp = self._mlp = MLP(dims, device=f"cuda:{self.ordinal}")
+            self._mlp_version = None
+        ver = (self._versions.get(WEIGHT_ADDR, 0), self.pointer(WEIGHT_ADDR))
+        if self._mlp_version == ver:
+            return mlp  # the resident padded copy still mirrors the blob (RunForward + RunBackward of one step)
+        self._mlp_version = ver
         src = self._tensor(WEIGHT_ADDR, nbytes // 4)
         cur = 0
         with torch.no_grad():  # W1|b1|W2|b2|... (unpadded) -> the padded flat layout the kernels use
@@ -245,6 +276,9 @@ class CudaBackend(DeviceBackend):
                 self._lib.dmlp_free(self.ordinal, ptr)
             for ptr in self._scalars.values():
                 self._lib.dmlp_free(self.ordinal, ptr)
+            if getattr(self, "_pin_ptr", None):
+                self._lib.dmlp_host_free(self._pin_ptr)
+                self._pin_ptr, self._pin_cap = None, 0
             self._bufs.clear()
             self._scratch.clear()
             self._scalars.clear()

@@ -37,7 +37,12 @@ def test_mlp_loss_and_grads_match_torch(dims, B):
     logits = m(x)
     assert (logits - ref_logits).abs().max().item() < 5e-3 * max(1.0, ref_logits.abs().max().item())
     loss, correct = m.loss(x, y)
-    loss.backward()
+    torch.cuda.synchronize()
+    torch.cuda.set_sync_debug_mode("error")  # loss.backward() must not synchronise with the host anywhere
+    try:
+        loss.backward()
+    finally:
+        torch.cuda.set_sync_debug_mode("default")
     torch.cuda.synchronize()
     assert abs(loss.item() - ref_loss) < 5e-3 * max(1.0, ref_loss)
     assert abs(correct.item() - (ref_logits[:, :dims[-1]].argmax(1) == y.long()).sum().item()) <= 2
