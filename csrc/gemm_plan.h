@@ -41,6 +41,7 @@ struct GemmParams {
   int accumulate;
   int prof;  // debug: CTA 0 stamps a per-tile timeline into g_gemm_prof
   int pdl;  // launched with programmatic stream serialization: the kernel executes griddepcontrol.wait
+  int epi2;  // TMA-store epilogue with eight epilogue warps (E2 kernel instantiations); see gemm_plan_create
   // fused softmax cross-entropy epilogue (last layer): non-null labels switch it on
   const int* ce_labels;
   int ce_classes;
@@ -52,6 +53,7 @@ struct GemmParams {
 
 struct GemmPlan {
   CUtensorMap tmA, tmB;
+  CUtensorMap tmC;  // output tensor (box: 32 rows x 128 bytes, 128B swizzle) of the TMA-store epilogue, when p.epi2
   GemmParams p;
   int grid_x, grid_y;
   int total_tiles;

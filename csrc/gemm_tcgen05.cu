@@ -4,6 +4,9 @@
 //   warp 0      : TMA producer  (cp.async.bulk.tensor, 128B swizzle, mbarrier complete_tx)
 //   warp 1      : TMEM allocator + single-thread tcgen05.mma issuer (accumulator in TMEM)
 //   warps 2..5  : epilogue (tcgen05.ld -> bias / ReLU / ReLU-mask / column-sum -> global)
+//   warps 2..9  : (E2 instantiations: plain / bias / ReLU outputs) eight epilogue warps, two per TMEM lane quadrant,
+//                 each staging 32 rows x 128 B of finished output in shared memory and handing it to the TMA store
+//                 engine (cp.async.bulk.tensor shared -> global): no transposing patch, no per-lane global stores
 // The smem ring has `stages` slots, each holding one 128-byte-wide K slab of A and B
 // (32 tf32 or 64 bf16 elements of K). block_n is a *runtime* value: the instruction
 // descriptor, the TMEM column count and the smem carve-up are all computed at launch.
@@ -18,11 +21,15 @@
 #include <stdlib.h>
 #include <string.h>
 
+#include <atomic>
+
 namespace dmlp {
 
 
 constexpr int kMaxStages = 8;
-constexpr int kGemmThreads = 192;
+constexpr int kGemmThreads = 192;    // producer + MMA + 4 epilogue warps
+constexpr int kGemmThreadsE2 = 320;  // producer + MMA + 8 epilogue warps (TMA-store epilogue)
+constexpr uint32_t kE2StageBytes = 8 * 4096;  // one 32-row x 128 B staging buffer per epilogue warp
 
 // Per-tile timeline of CTA 0 (debug, DMLP_GEMM_PROF=1 at plan creation): 8 globaltimer stamps per tile.
 //  0 producer: first smem slot of the tile acquired   1 producer: last TMA of the tile issued
@@ -38,10 +45,10 @@ __device__ unsigned long long g_gemm_prof[kProfTiles * 16];
 
 // TWO: CTA pairs (cluster of 2) run tcgen05.mma.cta_group::2 on 256 x block_n tiles: each CTA stages its 128 rows of A
 // and HALF of the B tile, which halves the shared-memory fill + read traffic per SM that bounds the 1-CTA mainloop.
-template <int EB, bool A_MN, bool B_MN, bool TWO>
-__global__ void __launch_bounds__(kGemmThreads, 1)
-gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA,
-                    const __grid_constant__ CUtensorMap tmB, const GemmParams p) {
+template <int EB, bool A_MN, bool B_MN, bool TWO, bool E2>
+__global__ void __launch_bounds__(E2 ? kGemmThreadsE2 : kGemmThreads, 1)
+gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
+                    const __grid_constant__ CUtensorMap tmC, const GemmParams p) {
   constexpr int BM = 128;
   constexpr int KS = 128 / EB;            // K elements per pipeline stage (one 128 B swizzle row)
   constexpr int UK = 32 / EB;             // K elements per tcgen05.mma
@@ -64,7 +71,8 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA,
   __shared__ __align__(8) uint64_t tmem_full_bar[2];   // accumulator buffer b holds a finished tile
   __shared__ __align__(8) uint64_t tmem_empty_bar[2];  // the epilogue has drained buffer b
   __shared__ uint32_t tmem_base_slot;
-  __shared__ float s_part[4][256];  // per-epilogue-warp column partials
+  __shared__ float s_part_raw[E2 ? 1 : 4][256];  // per-epilogue-warp column partials (E2 plans have no column sums:
+  auto s_part = [&](int w) -> float* { return s_part_raw[E2 ? 0 : w]; };  // their code is never reached there)
   __shared__ float s_loss[4];
   __shared__ int s_hit[4];
 
@@ -101,13 +109,14 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA,
   if (warp == 0 && lane == 0) {
     tma_prefetch_desc(&tmA);
     tma_prefetch_desc(&tmB);
+    if constexpr (E2) tma_prefetch_desc(&tmC);
     for (int s = 0; s < p.stages; ++s) {
       mbar_init(&full_bar[s], 1);
       mbar_init(&empty_bar[s], 1);
     }
     for (int b = 0; b < 2; ++b) {
       mbar_init(&tmem_full_bar[b], 1);
-      mbar_init(&tmem_empty_bar[b], TWO ? 256 : 128);  // pair: the leader's barrier collects both CTAs' epilogues
+      mbar_init(&tmem_empty_bar[b], (TWO ? 2 : 1) * (E2 ? 256 : 128));  // pair: the leader's barrier collects both CTAs' epilogues
     }
     fence_mbar_init();
   }
@@ -240,6 +249,91 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA,
     const int m = m0 + row;
     const bool m_ok = m < p.M;
     const uint32_t buf = tcount & 1;
+    bool handled = false;
+    if constexpr (E2) {
+      // ---- TMA-store epilogue (plans without mask / column sums / accumulate / softmax-CE, exactly one output).
+      // Interior tiles: warp w drains TMEM lanes 32*(w%4).. of the column half (w-2)/4 in chunks of 128 output bytes
+      // (64 bf16 / 32 fp32 columns): tcgen05.ld -> bias / ReLU in registers -> one 128 B row per lane into a private
+      // 4 KiB staging buffer (128B-swizzled: conflict-free) -> one cp.async.bulk.tensor store per chunk by one lane.
+      const bool fast2 = m0 + BM <= p.M && n0 + p.block_n <= p.N;  // (uniform over the CTA)
+      const uint32_t e2buf = smem_u32(smem + p.epi_stage_off) + static_cast<uint32_t>(warp - 2) * 4096u;
+      if (lane == 0) tma_store_wait_read<0>();  // my previous tile's stores have left the staging buffer
+      __syncwarp();
+      if (!fast2) {
+        // edge tile: the bounds-checked path below, run by warps 2..5 over patches that overlay all staging buffers
+        asm volatile("bar.sync 2, 256;" ::: "memory");
+        handled = warp >= 6;
+      } else {
+        handled = true;
+        constexpr int CH = 128 / 4;                       // fp32 accumulator columns per fp32 chunk ...
+        const bool ob = p.out_bf16 != nullptr;            // ... twice that per bf16 chunk
+        const int chunk = ob ? 2 * CH : CH;
+        const int ncols = p.block_n >> 1;
+        const int cbase = ((warp - 2) >> 2) * ncols;
+        mbar_wait(&tmem_full_bar[buf], (tcount >> 1) & 1);
+        tc_fence_after_sync();
+        if (warp == 2) GPROF(5, tcount);
+        const uint32_t t_row = tmem_base + buf * p.tmem_buf_cols + (static_cast<uint32_t>(q * 32) << 16);
+        const uint32_t wrow = e2buf + lane * 128;
+        const uint32_t sw = static_cast<uint32_t>(lane & 7);
+        for (int c = 0; c < ncols; c += chunk) {
+          const int col = cbase + c;
+          float v[64];
+#pragma unroll
+          for (int g = 0; g < 4; ++g) {
+            if (g < chunk / 16) {
+              uint32_t r[16];
+              tmem_ld_x16(t_row + col + 16 * g, r);
+              tmem_ld_wait();
+#pragma unroll
+              for (int jj = 0; jj < 16; ++jj) v[16 * g + jj] = __uint_as_float(r[jj]);
+            }
+          }
+          if (p.bias != nullptr) {
+#pragma unroll
+            for (int g = 0; g < 16; ++g) {
+              if (4 * g < chunk) {
+                const float4 b4 = __ldg(reinterpret_cast<const float4*>(p.bias + n0 + col) + g);
+                v[4 * g] += b4.x; v[4 * g + 1] += b4.y; v[4 * g + 2] += b4.z; v[4 * g + 3] += b4.w;
+              }
+            }
+          }
+          if (p.relu) {
+#pragma unroll
+            for (int jj = 0; jj < 64; ++jj) v[jj] = fmaxf(v[jj], 0.f);
+          }
+          if (c != 0) {
+            if (lane == 0) tma_store_wait_read<0>();  // the previous chunk's store has read the buffer
+            __syncwarp();
+          }
+          if (ob) {
+#pragma unroll
+            for (int k = 0; k < 8; ++k) {  // 8 x 16 B = this lane's 128 B row: 64 bf16
+              uint32_t pk[4];
+#pragma unroll
+              for (int e = 0; e < 4; ++e) {
+                const __nv_bfloat162 h2 = __floats2bfloat162_rn(v[8 * k + 2 * e], v[8 * k + 2 * e + 1]);
+                pk[e] = *reinterpret_cast<const uint32_t*>(&h2);
+              }
+              asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(wrow + ((static_cast<uint32_t>(k) ^ sw) << 4)), "r"(pk[0]),
+                           "r"(pk[1]), "r"(pk[2]), "r"(pk[3]) : "memory");
+            }
+          } else {
+#pragma unroll
+            for (int k = 0; k < 8; ++k)  // 32 fp32
+              sts128(wrow + ((static_cast<uint32_t>(k) ^ sw) << 4), v[4 * k], v[4 * k + 1], v[4 * k + 2], v[4 * k + 3]);
+          }
+          fence_proxy_async_smem();
+          __syncwarp();
+          if (lane == 0) {
+            tma_store_2d(&tmC, smem + p.epi_stage_off + static_cast<size_t>(warp - 2) * 4096u, n0 + col, m0 + q * 32);
+            tma_store_commit();
+          }
+        }
+        if (warp == 2) GPROF(6, tcount);
+      }
+    }
+    if (!handled) {
     float* stg = reinterpret_cast<float*>(smem + p.epi_stage_off) + q * (32 * kEpiLd);
     const int rsub = lane >> 3, c4 = (lane & 7) * 4;
     const bool vec_f32 = p.out_f32 != nullptr && ((reinterpret_cast<uintptr_t>(p.out_f32) & 15) == 0) && (p.ld_out & 3) == 0;
@@ -248,7 +342,7 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA,
                           ((reinterpret_cast<uintptr_t>(p.mask) & (p.mask_is_bf16 ? 7 : 15)) == 0);
     // Interior tile with vectorisable pointers: straight-line code, no per-element bounds checks, loads
     // batched ahead of their uses. (One epilogue warp per scheduler: nothing hides latency but ILP.)
-    const bool fast = m0 + BM <= p.M && n0 + p.block_n <= p.N && (p.block_n & 31) == 0 &&
+    const bool fast = !E2 && m0 + BM <= p.M && n0 + p.block_n <= p.N && (p.block_n & 31) == 0 &&
                     (p.out_f32 == nullptr || vec_f32) && (p.out_bf16 == nullptr || vec_b16) &&
                     (p.mask == nullptr || vec_mask) && ((reinterpret_cast<uintptr_t>(p.bias) & 15) == 0);
     const uint32_t stg_s = smem_u32(stg);
@@ -355,7 +449,7 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA,
         sj += __shfl_xor_sync(0xffffffffu, sj, 4);
         sj += __shfl_xor_sync(0xffffffffu, sj, 2);
         sj += __shfl_xor_sync(0xffffffffu, sj, 1);
-        if (lane == j) s_part[q][j] = sj;
+        if (lane == j) s_part(q)[j] = sj;
       }
 #pragma unroll
       for (int o = 16; o > 0; o >>= 1) {
@@ -365,7 +459,7 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA,
       if (lane == 0) { s_loss[q] = loss; s_hit[q] = hit; }
       asm volatile("bar.sync 1, 128;" ::: "memory");
       if (etid < p.N && p.colsum != nullptr) {
-        const float t = s_part[0][etid] + s_part[1][etid] + s_part[2][etid] + s_part[3][etid];
+        const float t = s_part(0)[etid] + s_part(1)[etid] + s_part(2)[etid] + s_part(3)[etid];
         if (direct) p.colsum[etid] = t; else atomicAdd(p.colsum + etid, t);
       }
       if (etid == 0) {
@@ -486,7 +580,7 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA,
             }
             if (lane < 8) {
 #pragma unroll
-              for (int k = 0; k < 4; ++k) s_part[q][c + c4 + k] = cs[k];
+              for (int k = 0; k < 4; ++k) s_part(q)[c + c4 + k] = cs[k];
             }
           }
           __syncwarp();  // the patch is rewritten by the next chunk
@@ -614,7 +708,7 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA,
           }
           if (lane < 8) {
 #pragma unroll
-            for (int k = 0; k < 4; ++k) s_part[q][c + c4 + k] = cs[k];
+            for (int k = 0; k < 4; ++k) s_part(q)[c + c4 + k] = cs[k];
           }
         }
         __syncwarp();  // the patch is rewritten by the next chunk
@@ -626,14 +720,24 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA,
         for (int cidx = etid; cidx < cols_done; cidx += 128) {
           const int n = n0 + cidx;
           if (n < p.N) {
-            const float t = s_part[0][cidx] + s_part[1][cidx] + s_part[2][cidx] + s_part[3][cidx];
+            const float t = s_part(0)[cidx] + s_part(1)[cidx] + s_part(2)[cidx] + s_part(3)[cidx];
             if (direct) p.colsum[n] = t; else atomicAdd(p.colsum + n, t);
           }
         }
       }
     }
-    // this tile's accumulator has been read out: hand the TMEM buffer back to the MMA warp
     if (p.colsum != nullptr || p.ce_labels != nullptr) asm volatile("bar.sync 1, 128;" ::: "memory");  // s_part reuse
+    }  // !handled
+    if constexpr (E2) {
+      // an edge tile's patches overlay every warp's staging buffer: nobody stages again before they are all done
+      if (!(m0 + BM <= p.M && n0 + p.block_n <= p.N)) {
+        if (warp >= 6) {  // (sat the tile out: still in step with the accumulator hand-over)
+          mbar_wait(&tmem_full_bar[buf], (tcount >> 1) & 1);
+        }
+        asm volatile("bar.sync 2, 256;" ::: "memory");
+      }
+    }
+    // this tile's accumulator has been read out: hand the TMEM buffer back to the MMA warp
     tc_fence_before_sync();
     if (TWO && crank != 0) mbar_arrive_cluster(cl_mapa(smem_u32(&tmem_empty_bar[buf]), 0));  // the leader's barrier
     else mbar_arrive(&tmem_empty_bar[buf]);
@@ -641,6 +745,9 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA,
     }
   }
 
+  if constexpr (E2) {
+    if (warp >= 2 && lane == 0) tma_store_wait<0>();  // my bulk stores are complete before this CTA's shared memory goes away
+  }
   tc_fence_before_sync();
   __syncthreads();
   if constexpr (TWO) cl_sync();  // the peer may still be signalling my barriers / the pair's MMAs use both TMEMs
@@ -698,22 +805,26 @@ int make_tensor_map_2d(CUtensorMap* out, const void* base, int elem_bytes, bool 
   return DMLP_OK;
 }
 
-template <int EB, bool A_MN, bool B_MN, bool TWO = false>
-static int launch_gemm(const CUtensorMap& tmA, const CUtensorMap& tmB, const GemmParams& p,
-                       dim3 grid, size_t smem_bytes, cudaStream_t stream) {
-  auto kern = gemm_tcgen05_kernel<EB, A_MN, B_MN, TWO>;
-  static unsigned long long attr_mask = 0;  // devices on which the smem opt-in has been applied
+template <int EB, bool A_MN, bool B_MN, bool TWO, bool E2>
+static int launch_gemm_t(const CUtensorMap& tmA, const CUtensorMap& tmB, const CUtensorMap& tmC, const GemmParams& p,
+                         dim3 grid, size_t smem_bytes, cudaStream_t stream) {
+  auto kern = gemm_tcgen05_kernel<EB, A_MN, B_MN, TWO, E2>;
+  constexpr int kThreads = E2 ? kGemmThreadsE2 : kGemmThreads;
+  // devices on which the smem opt-in has been applied (gRPC worker threads launch GEMMs on different devices at once)
+  static std::atomic<unsigned long long> attr_mask{0};
   int dev = 0;
   DMLP_CUDA_CHECK(cudaGetDevice(&dev));
-  if (!(attr_mask & (1ull << dev))) {
+  if (!(attr_mask.load(std::memory_order_acquire) & (1ull << dev))) {
+    cudaFuncAttributes fa;
+    DMLP_CUDA_CHECK(cudaFuncGetAttributes(&fa, kern));  // 227 KiB per CTA = static + dynamic
     DMLP_CUDA_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                         216 * 1024));
-    attr_mask |= 1ull << dev;
+                                         227 * 1024 - static_cast<int>((fa.sharedSizeBytes + 1023) / 1024 * 1024)));
+    attr_mask.fetch_or(1ull << dev, std::memory_order_release);
   }
   if (p.pdl || TWO) {
     cudaLaunchConfig_t cfg = {};
     cfg.gridDim = grid;
-    cfg.blockDim = dim3(kGemmThreads);
+    cfg.blockDim = dim3(kThreads);
     cfg.dynamicSmemBytes = smem_bytes;
     cfg.stream = stream;
     cudaLaunchAttribute attr[2];
@@ -732,12 +843,18 @@ static int launch_gemm(const CUtensorMap& tmA, const CUtensorMap& tmB, const Gem
     }
     cfg.attrs = attr;
     cfg.numAttrs = na;
-    DMLP_CUDA_CHECK(cudaLaunchKernelEx(&cfg, kern, tmA, tmB, p));
+    DMLP_CUDA_CHECK(cudaLaunchKernelEx(&cfg, kern, tmA, tmB, tmC, p));
   } else {
-    kern<<<grid, kGemmThreads, smem_bytes, stream>>>(tmA, tmB, p);
+    kern<<<grid, kThreads, smem_bytes, stream>>>(tmA, tmB, tmC, p);
   }
   DMLP_CUDA_CHECK(cudaGetLastError());
   return DMLP_OK;
+}
+
+template <int EB, bool A_MN, bool B_MN, bool TWO = false>
+static int launch_gemm(const GemmPlan* pl, dim3 grid, cudaStream_t stream) {
+  if (pl->p.epi2) return launch_gemm_t<EB, A_MN, B_MN, TWO, true>(pl->tmA, pl->tmB, pl->tmC, pl->p, grid, pl->smem, stream);
+  return launch_gemm_t<EB, A_MN, B_MN, TWO, false>(pl->tmA, pl->tmB, pl->tmA, pl->p, grid, pl->smem, stream);
 }
 
 static int ceil_div(int a, int b) { return (a + b - 1) / b; }
@@ -804,7 +921,27 @@ int dmlp::gemm_plan_create(const dmlp_gemm_desc_t* d, GemmPlan* plan) {
   p.a_tx_bytes = (d->a_major == 0) ? a_box_rows * 128 : 128 * 128;
   p.b_stage_bytes = d->b_major == 0 ? b_cols * 128 : ceil_div(b_cols, ATOM) * KS * 128;  // per CTA
   const size_t stage_bytes = p.a_stage_bytes + p.b_stage_bytes;
-  const size_t budget = 196 * 1024;  // + 18 KiB of epilogue patches + 1 KiB alignment slack <= the 216 KiB opt-in
+  // TMA-store epilogue with eight epilogue warps (E2 kernels): outputs that are a plain / bias / ReLU function of the
+  // accumulator, one output tensor, tiles whose column halves split into whole 128-byte chunks.
+  {
+    static int e2_env = -1;
+    if (e2_env < 0) { const char* e = getenv("DMLP_GEMM_EPI2"); e2_env = e ? atoi(e) : 1; }
+    const bool one_out = (d->out_f32_dev != nullptr) != (d->out_bf16_dev != nullptr);
+    const void* optr = d->out_f32_dev ? static_cast<const void*>(d->out_f32_dev) : d->out_bf16_dev;
+    const long long old = d->out_f32_dev ? d->ld_out * 4 : d->ld_out_bf16 * 2;  // output row pitch in bytes
+    const int half_bytes = (bn / 2) * (d->out_f32_dev ? 4 : 2);
+    p.epi2 = (e2_env != 0 && one_out && d->mask_dev == nullptr && d->colsum_dev == nullptr && !d->accumulate &&
+              d->ce_labels_dev == nullptr && d->M >= 128 && half_bytes % 128 == 0 && old % 16 == 0 &&
+              (reinterpret_cast<uintptr_t>(optr) & 15) == 0 && (reinterpret_cast<uintptr_t>(d->bias_dev) & 15) == 0) ? 1 : 0;
+    if (p.epi2) {
+      if (d->out_f32_dev) rc = make_tensor_map_2d(&plan->tmC, d->out_f32_dev, 4, false, d->N, d->M, d->ld_out, 32, 32, 1);
+      else rc = make_tensor_map_2d(&plan->tmC, d->out_bf16_dev, 2, true, d->N, d->M, d->ld_out_bf16, 64, 32, 1);
+      if (rc) return rc;
+    }
+  }
+  const size_t epi_bytes = p.epi2 ? kE2StageBytes : kEpiStageBytes;
+  // stages + epilogue staging (E2: 32 KiB, 8 store buffers; else 18 KiB of transposing patches) + 1 KiB alignment slack
+  const size_t budget = (p.epi2 ? 225 : 214) * 1024 - epi_bytes;  // static shared memory: ~1 KiB (E2) / ~5 KiB
   int stages = static_cast<int>(budget / stage_bytes);
   if (stages > kMaxStages) stages = kMaxStages;
   if (stages > p.num_k_blocks) stages = p.num_k_blocks;
@@ -852,7 +989,7 @@ int dmlp::gemm_plan_create(const dmlp_gemm_desc_t* d, GemmPlan* plan) {
     plan->grid_y = 1;
   }
   p.epi_stage_off = static_cast<uint32_t>(stages * stage_bytes);
-  plan->smem = stages * stage_bytes + kEpiStageBytes + 1024;
+  plan->smem = stages * stage_bytes + epi_bytes + 1024;
   plan->key = (two ? 8 : 0) | (bf16 ? 4 : 0) | (d->a_major ? 2 : 0) | (d->b_major ? 1 : 0);
   // PDL only for single-wave grids: an early-launched dependent must never compete with CTAs of
   // this grid that are still waiting for an SM.
@@ -867,22 +1004,22 @@ int dmlp::gemm_plan_create(const dmlp_gemm_desc_t* d, GemmPlan* plan) {
 int dmlp::gemm_plan_run(const GemmPlan* plan, cudaStream_t st) {
   const dim3 grid(plan->grid_x, plan->grid_y);
   switch (plan->key) {
-    case 0: return launch_gemm<4, false, false>(plan->tmA, plan->tmB, plan->p, grid, plan->smem, st);
-    case 1: return launch_gemm<4, false, true>(plan->tmA, plan->tmB, plan->p, grid, plan->smem, st);
-    case 2: return launch_gemm<4, true, false>(plan->tmA, plan->tmB, plan->p, grid, plan->smem, st);
-    case 3: return launch_gemm<4, true, true>(plan->tmA, plan->tmB, plan->p, grid, plan->smem, st);
-    case 4: return launch_gemm<2, false, false>(plan->tmA, plan->tmB, plan->p, grid, plan->smem, st);
-    case 5: return launch_gemm<2, false, true>(plan->tmA, plan->tmB, plan->p, grid, plan->smem, st);
-    case 6: return launch_gemm<2, true, false>(plan->tmA, plan->tmB, plan->p, grid, plan->smem, st);
-    case 7: return launch_gemm<2, true, true>(plan->tmA, plan->tmB, plan->p, grid, plan->smem, st);
-    case 8: return launch_gemm<4, false, false, true>(plan->tmA, plan->tmB, plan->p, grid, plan->smem, st);
-    case 9: return launch_gemm<4, false, true, true>(plan->tmA, plan->tmB, plan->p, grid, plan->smem, st);
-    case 10: return launch_gemm<4, true, false, true>(plan->tmA, plan->tmB, plan->p, grid, plan->smem, st);
-    case 11: return launch_gemm<4, true, true, true>(plan->tmA, plan->tmB, plan->p, grid, plan->smem, st);
-    case 12: return launch_gemm<2, false, false, true>(plan->tmA, plan->tmB, plan->p, grid, plan->smem, st);
-    case 13: return launch_gemm<2, false, true, true>(plan->tmA, plan->tmB, plan->p, grid, plan->smem, st);
-    case 14: return launch_gemm<2, true, false, true>(plan->tmA, plan->tmB, plan->p, grid, plan->smem, st);
-    default: return launch_gemm<2, true, true, true>(plan->tmA, plan->tmB, plan->p, grid, plan->smem, st);
+    case 0: return launch_gemm<4, false, false>(plan, grid, st);
+    case 1: return launch_gemm<4, false, true>(plan, grid, st);
+    case 2: return launch_gemm<4, true, false>(plan, grid, st);
+    case 3: return launch_gemm<4, true, true>(plan, grid, st);
+    case 4: return launch_gemm<2, false, false>(plan, grid, st);
+    case 5: return launch_gemm<2, false, true>(plan, grid, st);
+    case 6: return launch_gemm<2, true, false>(plan, grid, st);
+    case 7: return launch_gemm<2, true, true>(plan, grid, st);
+    case 8: return launch_gemm<4, false, false, true>(plan, grid, st);
+    case 9: return launch_gemm<4, false, true, true>(plan, grid, st);
+    case 10: return launch_gemm<4, true, false, true>(plan, grid, st);
+    case 11: return launch_gemm<4, true, true, true>(plan, grid, st);
+    case 12: return launch_gemm<2, false, false, true>(plan, grid, st);
+    case 13: return launch_gemm<2, false, true, true>(plan, grid, st);
+    case 14: return launch_gemm<2, true, false, true>(plan, grid, st);
+    default: return launch_gemm<2, true, true, true>(plan, grid, st);
   }
 }
 

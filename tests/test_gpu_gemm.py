@@ -110,6 +110,38 @@ def test_forward_explicit_block_n(bn):
     assert (out.double() - ref).abs().max().item() < 1e-3 * ref.abs().max().item()
 
 
+@pytest.mark.parametrize("dtype,out_kind", [(torch.float32, "f32"), (torch.bfloat16, "f32"), (torch.bfloat16, "bf16")])
+@pytest.mark.parametrize("M,K,N,bn", [(640, 192, 768, 256), (300, 160, 512, 128), (384, 96, 640, 64),
+                                      (2304, 200, 2320, 0), (2100, 264, 2560, 0)])
+@pytest.mark.parametrize("bias_relu", [False, True])
+def test_tma_store_epilogue(dtype, out_kind, M, K, N, bn, bias_relu):
+    """One output tensor and nothing but bias / ReLU after the accumulator: the eight-warp TMA-store epilogue
+    (interior tiles) next to the bounds-checked path (edge rows / columns of the same launch), single CTAs and CTA pairs.
+    References: (a) fp64 product of the operands as the tensor core sees them, (b) the plain fp32 PyTorch product."""
+    if out_kind == "f32" and bn == 64 and dtype == torch.bfloat16:
+        pytest.skip("covered by the fp32-operand case")
+    from dmlp_b200.ops import kernels as k
+    torch.manual_seed(5)
+    x = _rand((M, K), dtype, (K + 7) // 8 * 8)
+    w = _rand((K, N), dtype, (N + 7) // 8 * 8) * 0.1
+    b = torch.randn(N, device="cuda") if bias_relu else None
+    out = (torch.full((M, N), float("nan"), device="cuda") if out_kind == "f32"
+           else torch.zeros((M, N), device="cuda", dtype=torch.bfloat16))
+    if out_kind == "f32":
+        k.linear_forward(x, w, b, bias_relu, out=out, block_n=bn)
+    else:
+        k.linear_forward(x, w, b, bias_relu, out_bf16=out, block_n=bn)
+    torch.cuda.synchronize()
+    ref = _operand_ref(x) @ _operand_ref(w)
+    plain = x.float() @ w.float()
+    if bias_relu:
+        ref, plain = torch.relu(ref + b.double()), torch.relu(plain + b)
+    scale = max(1.0, ref.abs().max().item())
+    tol = 2e-3 if out_kind == "f32" else 2e-2
+    assert (out.double() - ref).abs().max().item() < tol * scale
+    assert (out.double() - plain.double()).abs().max().item() < (2e-2 if dtype == torch.float32 or out_kind == "bf16" else 5e-3) * scale
+
+
 @pytest.mark.parametrize("dtype", [torch.float32, torch.bfloat16])
 @pytest.mark.parametrize("B,K,C,N", [(64, 64, 10, 16), (100, 128, 10, 16), (64, 96, 27, 32), (300, 64, 10, 16)])
 def test_fused_linear_softmax_ce(dtype, B, K, C, N):
