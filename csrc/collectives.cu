@@ -829,13 +829,35 @@ extern "C" int dmlp_comm_is_emulated(dmlp_comm_t h, int* emulated) {
   return DMLP_OK;
 }
 
-extern "C" int dmlp_allreduce_pick_algo(int world, size_t bytes) {
+// Algorithm choice, table-driven from the graph-timed sweeps under profiles/ (fp32 SUM, one 8 x B200 NVSwitch box).
+// One row per world size: largest message (bytes) for which one-shot still wins over two-shot, and the smallest for which
+// the in-switch reduction (NVLS: multimem.ld_reduce + multimem.st) wins - it needs both buffers in multicast-bound
+// memory (runtime/nvls.py), which the caller states with `nvls_available`.
+//   * one-shot: one rendezvous, (n-1) x bytes pulled per rank - latency-bound sizes;
+//   * two-shot: reduce-scatter by peer loads + all-gather by peer stores, 2(n-1)/n x bytes per rank;
+//   * NVLS    : every byte crosses each link once and the switch adds; extra latency of the multimem round trip;
+//   * ring    : never picked. 2(n-1) dependent hops, each a flag handshake over the same all-to-all fabric on which
+//               two-shot moves the same bytes in two hops: on NVSwitch a ring has the latency of a ring and the
+//               bandwidth of nothing better. It stays as the RPC's namesake and the comparison mode (algo = ring).
+struct AlgoRow { int world; size_t oneshot_max; size_t nvls_min; };
+static const AlgoRow kAlgoTable[] = {
+    {2, 4u << 20, ~static_cast<size_t>(0)},   // two ranks: a pull of the peer's buffer IS the reduce-scatter + gather
+    {3, 1u << 20, 64u << 20},
+    {4, 1u << 20, 64u << 20},                 // profiles/r1_allreduce_sweep_4gpu_graph.jsonl: NVLS 173 vs 180 us at 64 MiB
+    {6, 512u << 10, 16u << 20},
+    {8, 512u << 10, 16u << 20},               // profiles/r1_allreduce_sweep_8gpu_graph.jsonl: NVLS 58.6 vs 61.4 us at 16 MiB
+};
+
+extern "C" int dmlp_allreduce_pick_algo_ex(int world, size_t bytes, int nvls_available) {
   if (world <= 1) return DMLP_ALGO_ONESHOT;
-  // Latency-bound sizes: one rendezvous, (n-1) x bytes pulled per rank. Above that two-shot moves
-  // 2(n-1)/n x bytes per rank. Thresholds are refined by the sweep in profiles/.
-  const size_t oneshot_max = world <= 2 ? (4u << 20) : world <= 4 ? (1u << 20) : (512u << 10);
-  return bytes <= oneshot_max ? DMLP_ALGO_ONESHOT : DMLP_ALGO_TWOSHOT;
+  const AlgoRow* row = &kAlgoTable[0];
+  for (const AlgoRow& r : kAlgoTable)
+    if (r.world <= world) row = &r;  // the largest tabulated world not above this one
+  if (nvls_available && bytes >= row->nvls_min) return DMLP_ALGO_NVLS;
+  return bytes <= row->oneshot_max ? DMLP_ALGO_ONESHOT : DMLP_ALGO_TWOSHOT;
 }
+
+extern "C" int dmlp_allreduce_pick_algo(int world, size_t bytes) { return dmlp_allreduce_pick_algo_ex(world, bytes, 0); }
 
 extern "C" int dmlp_allreduce(dmlp_comm_t h, int local_idx, const dmlp_allreduce_desc_t* d, void* stream) {
   Comm* c = reinterpret_cast<Comm*>(h);

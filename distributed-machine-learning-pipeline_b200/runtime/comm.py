@@ -190,8 +190,10 @@ class Communicator:
         d.prof = prof
         native.check(native.lib().dmlp_allreduce(self._h, local_idx, C.byref(d), stream or None))
 
-    def pick_algo(self, nbytes: int) -> int:
-        return native.lib().dmlp_allreduce_pick_algo(self.world, nbytes)
+    def pick_algo(self, nbytes: int, nvls_available: bool = False) -> int:
+        """What ``algo=auto`` runs for a message of ``nbytes`` (table in csrc/collectives.cu, from the sweeps under
+        profiles/); with ``nvls_available`` (buffers in a multicast-bound arena) the table includes NVLS."""
+        return native.lib().dmlp_allreduce_pick_algo_ex(self.world, nbytes, int(nvls_available))
 
     def destroy(self) -> None:
         if getattr(self, "_h", None):

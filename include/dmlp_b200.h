@@ -219,6 +219,9 @@ typedef struct {
  * returns immediately. Failures of peers surface through dmlp_comm_status. */
 int dmlp_allreduce(dmlp_comm_t comm, int local_idx, const dmlp_allreduce_desc_t* desc, void* stream);
 int dmlp_allreduce_pick_algo(int world, size_t bytes);
+/* Same with NVLS in the table: nvls_available = both buffers live in multicast-bound memory (dmlp_nvls_*), then
+ * DMLP_ALGO_NVLS is returned from the size on at which the in-switch reduction wins (run it with dmlp_allreduce_nvls). */
+int dmlp_allreduce_pick_algo_ex(int world, size_t bytes, int nvls_available);
 
 /* P2P push copy kernel (StreamSend on real GPUs, gpu_device_server.go:112-181): launched on
  * src_dev, dst may be peer memory. */

@@ -26,7 +26,7 @@ def main():
     ap.add_argument("--max-bytes", type=int, default=1 << 30)
     ap.add_argument("--factor", type=int, default=4)
     ap.add_argument("--out", default="")
-    ap.add_argument("--algos", default="auto,oneshot,twoshot,ring,nccl")
+    ap.add_argument("--algos", default="auto,oneshot,twoshot,ring,nvls,nccl")
     ap.add_argument("--graph", type=int, default=1, help="time CUDA-graph replays of `iters` launches (default) or eager launches")
     a = ap.parse_args()
     rank, world = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"])
@@ -46,7 +46,7 @@ def main():
     my_in.normal_()
     nccl_buf = torch.empty(maxb // 4, device="cuda")
     nvls = None
-    if "nvls" in a.algos.split(","):
+    if "nvls" in a.algos.split(",") or "auto" in a.algos.split(","):
         from dmlp_b200.runtime.nvls import NvlsArena, NvlsUnavailable
         try:
             nvls = NvlsArena.from_process_group(local, 2 * maxb + 4096)
@@ -71,13 +71,17 @@ def main():
             if algo == "nvls" and (nvls is None or count % 4):
                 continue
 
+            use = algo
+            if algo == "auto":  # the dispatcher's choice, NVLS included when the multicast arena exists
+                use = native.ALGO_NAMES.get(comm.pick_algo(nbytes, nvls is not None and count % 4 == 0), "twoshot")
+
             def launch():
                 if algo == "nccl":
                     dist.all_reduce(nccl_buf[:count])
-                elif algo == "nvls":  # multimem.ld_reduce -> multimem.st through the NVSwitch
+                elif use == "nvls":  # multimem.ld_reduce -> multimem.st through the NVSwitch
                     nvls.allreduce(comm, 0, nv_in, nv_out, count, local, stream=stream.cuda_stream)
                 else:
-                    comm.allreduce(ins, outs, count, algo=native.ALGO_BY_NAME[algo], local_idx=0,
+                    comm.allreduce(ins, outs, count, algo=native.ALGO_BY_NAME[use], local_idx=0,
                                    stream=stream.cuda_stream)
 
             for _ in range(5):
@@ -110,7 +114,7 @@ def main():
                 comm.check()
             us = t.item() * 1e3
             algbw = nbytes / (us * 1e-6) / 1e9
-            picked = native.ALGO_NAMES.get(comm.pick_algo(nbytes), "?") if algo == "auto" else algo
+            picked = use
             row = {"bytes": nbytes, "impl": algo, "picked": picked, "n_gpus": world, "latency_us": round(us, 2),
                    "algbw_GBs": round(algbw, 2), "busbw_GBs": round(algbw * 2 * (world - 1) / world, 2), "iters": iters,
                    "timing": "cuda-graph replay" if a.graph else "eager launches"}

@@ -79,6 +79,32 @@ def main():
     t.close()
     dist.barrier()
 
+    # ---- 2b. soak of the DEFAULT path (persistent compute + reducer launch): 10^5 steps, replicas bit-identical, and the
+    # relaxed flag protocol (gpu-scope fence before a flag, no fence after a poll) against the conservative one
+    # (DMLP_COLL_STRICT=1: system-scope fences both sides) - the two runs must end with the same bits
+    import hashlib
+    pdp_steps = int(os.environ.get("DMLP_PDP_SOAK_STEPS", "100000"))
+    digests = {}
+    for strict in ("0", "1"):
+        os.environ["DMLP_COLL_STRICT"] = strict  # read when the trainer builds its fused-step plan
+        t = Trainer(TrainerConfig(dims=(784, 128, 64, 10), batch=64, lr=0.02, seed=13), device=local, process_group=True)
+        assert t.dp_mode == 4, t.dp_mode
+        x, y = synthetic_mnist(64 * world * 64, seed=9)
+        t0 = time.time()
+        st = t.fit(x, y, pdp_steps, return_metrics=False)
+        dt = time.time() - t0
+        assert replicas_equal(t), f"replicas diverged in the {pdp_steps}-step soak (strict={strict})"
+        flat = t.get_params()
+        assert np.isfinite(flat).all()
+        digests[strict] = hashlib.sha256(flat.tobytes()).hexdigest()
+        if rank == 0:
+            print(f"soak ok (mode 4, strict={strict}): {pdp_steps} steps, {dt * 1e6 / pdp_steps:.1f} us/step wall, "
+                  f"sha256 {digests[strict][:16]}", flush=True)
+        t.close()
+        dist.barrier()
+    os.environ.pop("DMLP_COLL_STRICT", None)
+    assert digests["0"] == digests["1"], "relaxed and strict flag protocols produced different parameters"
+
     # ---- 3. a rank dies mid-run: the default path (persistent compute + reducer launch, mode 4) and the global-batch mode
     # ... and the per-layer path with its bucketed all-reduce overlapped with backward (mode 0: what the wide model runs)
     for fused, want_mode in ((-1, 4), (5, 5), (0, 0)):
