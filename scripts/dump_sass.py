@@ -9,10 +9,13 @@ SO = os.path.join(ROOT, "distributed-machine-learning-pipeline_b200", "_native",
 OUT = os.path.join(ROOT, "profiles", "sass")
 
 PICK = {  # listing name -> regex on the mangled kernel name
-    "gemm_tcgen05_tf32_fwd.sass": r"gemm_tcgen05_kernelILi4ELb0ELb1ELb0E",
-    "gemm_tcgen05_bf16_wgrad.sass": r"gemm_tcgen05_kernelILi2ELb1ELb1ELb0E",
-    "gemm_tcgen05_bf16_fwd_cta_pair.sass": r"gemm_tcgen05_kernelILi2ELb0ELb1ELb1E",
-    "mlp_fused_step_16_8.sass": r"mlp_fused_step_kernelILi16ELi8E",
+    "gemm_tcgen05_tf32_fwd.sass": r"gemm_tcgen05_kernelILi4ELb0ELb1ELb0ELb0E",
+    "gemm_tcgen05_bf16_wgrad.sass": r"gemm_tcgen05_kernelILi2ELb1ELb1ELb0ELb0E",
+    "gemm_tcgen05_bf16_fwd_cta_pair.sass": r"gemm_tcgen05_kernelILi2ELb0ELb1ELb1ELb0E",
+    "gemm_tcgen05_bf16_fwd_cta_pair_tma_store.sass": r"gemm_tcgen05_kernelILi2ELb0ELb1ELb1ELb1E",
+    "mlp_fused_step_16_8.sass": r"mlp_fused_step_kernelILi16ELi8ELb0E",
+    "mlp_fused_step_16_8_global_batch.sass": r"mlp_fused_step_kernelILi16ELi8ELb1E",
+    "input_exchange.sass": r"input_exchange_kernel",
     "allreduce_oneshot_f32_sgd.sass": r"allreduce_oneshot_kernelIfLb1E",
     "allreduce_twoshot_f32_sgd.sass": r"allreduce_twoshot_kernelIfLb1E",
     "allreduce_ring_f32_sgd.sass": r"allreduce_ring_kernelIfLb1E",
@@ -21,7 +24,7 @@ PICK = {  # listing name -> regex on the mangled kernel name
     "sgd.sass": r"sgd_kernel",
     "softmax_ce.sass": r"softmax_ce_kernel",
 }
-NOTABLE = ["UTCHMMA.2CTA", "UTCHMMA", "UTCQMMA", "LDTM", "UTMALDG", "UTMAPF", "UTMASTG", "UBLKCP", "UBLKRED", "UTCBAR", "UTCATOMSWS", "SYNCS", "UCGABAR",
+NOTABLE = ["UTCHMMA.2CTA", "UTCHMMA", "LDGSTS", "UTCQMMA", "LDTM", "UTMALDG", "UTMAPF", "UTMASTG", "UBLKCP", "UBLKRED", "UTCBAR", "UTCATOMSWS", "SYNCS", "UCGABAR",
            "LDGMC", "STG.E.128.MMC", "RED", "ATOM", "LDG", "STG", "LDS", "STS", "MEMBAR", "CCTL", "ERRBAR", "R2UR", "BRA.U.ANY", "ELECT"]
 
 
@@ -59,7 +62,7 @@ def main():
         f.write("# SASS evidence (`cuobjdump -sass` of libdmlp_b200.so, sm_100a) — regenerate with `python scripts/dump_sass.py`\n\n"
                 "Full listings of one instantiation per kernel family are in this directory.\n"
                 "Mnemonics that prove the Blackwell paths: `UTCHMMA` = tcgen05.mma (`.2CTA` = cta_group::2), `LDTM` = tcgen05.ld, "
-                "`UTMALDG` = TMA tensor load, `UTMAPF` = TMA L2 prefetch, `UBLKCP` / `UBLKRED` = cp.async.bulk / cp.reduce.async.bulk, "
+                "`UTMALDG` / `UTMASTG` = TMA tensor load / store, `LDGSTS` = cp.async, `UTMAPF` = TMA L2 prefetch, `UBLKCP` / `UBLKRED` = cp.async.bulk / cp.reduce.async.bulk, "
                 "`UTCBAR` = tcgen05.commit, `UTCATOMSWS` = TMEM alloc/dealloc, `SYNCS` = mbarrier, `UCGABAR` = cluster barrier, "
                 "`LDGMC...ADD` = NVLS multimem.ld_reduce. `BRA.U.ANY` counts per-lane \"waterfall\" loops around uniform-datapath "
                 "instructions (0 in the GEMM / fused kernels since the warp-uniform role dispatch, see ../r1_mma_issue_probe.md).\n\n"
