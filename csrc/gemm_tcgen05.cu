@@ -257,7 +257,7 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
       // 4 KiB staging buffer (128B-swizzled: conflict-free) -> one cp.async.bulk.tensor store per chunk by one lane.
       const bool fast2 = m0 + BM <= p.M && n0 + p.block_n <= p.N;  // (uniform over the CTA)
       const uint32_t e2buf = smem_u32(smem + p.epi_stage_off) + static_cast<uint32_t>(warp - 2) * 4096u;
-      if (lane == 0) tma_store_wait_read<0>();  // my previous tile's stores have left the staging buffer
+      if (elect_one()) tma_store_wait_read<0>();  // my previous tile's stores have left the staging buffer
       __syncwarp();
       if (!fast2) {
         // edge tile: the bounds-checked path below, run by warps 2..5 over patches that overlay all staging buffers
@@ -303,7 +303,7 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
             for (int jj = 0; jj < 64; ++jj) v[jj] = fmaxf(v[jj], 0.f);
           }
           if (c != 0) {
-            if (lane == 0) tma_store_wait_read<0>();  // the previous chunk's store has read the buffer
+            if (elect_one()) tma_store_wait_read<0>();  // the previous chunk's store has read the buffer
             __syncwarp();
           }
           if (ob) {
@@ -325,7 +325,7 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
           }
           fence_proxy_async_smem();
           __syncwarp();
-          if (lane == 0) {
+          if (elect_one()) {  // (converged warp: always the same lane, which also owns the bulk group)
             tma_store_2d(&tmC, smem + p.epi_stage_off + static_cast<size_t>(warp - 2) * 4096u, n0 + col, m0 + q * 32);
             tma_store_commit();
           }
@@ -746,7 +746,7 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
   }
 
   if constexpr (E2) {
-    if (warp >= 2 && lane == 0) tma_store_wait<0>();  // my bulk stores are complete before this CTA's shared memory goes away
+    if (warp >= 2 && elect_one()) tma_store_wait<0>();  // my bulk stores are complete before this CTA's shared memory goes away
   }
   tc_fence_before_sync();
   __syncthreads();

@@ -974,7 +974,7 @@ mlp_fused_step_kernel(const __grid_constant__ CUtensorMap tmXA, const __grid_con
   FPROFT(128, 32);
   if (gmode && worker && (warp & 3) < 2) {  // the two warps that hold batch rows 0..63
     const uint32_t stg = sb + oSTG + (warp & 3) * 2048;
-    if (lane == 0) bulk_wait_read();  // (the previous step's copies out of this warp's staging half)
+    if (elect_one()) bulk_wait_read();  // (the previous step's copies out of this warp's staging half)
     __syncwarp();
     if (rok) {
       sts128(stg + lane * 64, dz1[0], dz1[1], dz1[2], dz1[3]);
@@ -984,7 +984,7 @@ mlp_fused_step_kernel(const __grid_constant__ CUtensorMap tmXA, const __grid_con
     }
     fence_proxy_async_smem();  // staged with ordinary stores, read by the bulk copy engine
     __syncwarp();
-    if (gpush >= 0 && lane == 0) {
+    if (gpush >= 0 && elect_one()) {
       // one bulk copy per peer: the copy engine moves it, this SM's load/store path stays free (SM-issued stores to a
       // peer stall the issuing warp for about a microsecond)
       const int rows = B - (warp & 3) * 32 < 32 ? B - (warp & 3) * 32 : 32;
@@ -1112,7 +1112,7 @@ mlp_fused_step_kernel(const __grid_constant__ CUtensorMap tmXA, const __grid_con
       if (gmode) {
         // pushed as one contiguous SL x 64 B block (rows < SL sit in the lanes of the warp that owns TMEM lanes 0..31)
         if ((warp & 3) == 0) {
-          if (lane == 0) bulk_wait_read();  // this warp's dZ1 copies have left the staging half
+          if (elect_one()) bulk_wait_read();  // this warp's dZ1 copies have left the staging half
           __syncwarp();
           if (row <= SL) {  // rows < SL: the dW slice; row SL (the ones row): the last bias gradient
 #pragma unroll
@@ -1121,7 +1121,7 @@ mlp_fused_step_kernel(const __grid_constant__ CUtensorMap tmXA, const __grid_con
           }
           fence_proxy_async_smem();
           __syncwarp();
-          if (gpush >= 0 && lane == 0) {
+          if (gpush >= 0 && elect_one()) {
             const size_t o = static_cast<size_t>(gpush) + p.w_off[LAST] + static_cast<size_t>(SL * j) * 16;
             #pragma unroll 1
             for (int q = 0; q < W; ++q) {
@@ -1182,7 +1182,7 @@ mlp_fused_step_kernel(const __grid_constant__ CUtensorMap tmXA, const __grid_con
     if (gmode && kMid && (warp & 3) == 0) {
       fence_proxy_async_smem();
       __syncwarp();
-      if (gpush >= 0 && lane == 0) {
+      if (gpush >= 0 && elect_one()) {
         #pragma unroll 1
         for (int q = 0; q < W; ++q) {
           bulk_s2g(p.xrecv[q] + gpush + p.w_off[1] + static_cast<size_t>(S1 * j) * H2, sb + oSTG2, S1 * H2 * 4);
@@ -1539,7 +1539,7 @@ mlp_fused_step_kernel(const __grid_constant__ CUtensorMap tmXA, const __grid_con
   tc_fence_after_sync();
   FPROF(14);
   }  // step loop
-  if (gmode && worker && lane == 0) bulk_wait_read();  // pushes still reading this CTA's staging area
+  if (gmode && worker && elect_one()) bulk_wait_read();  // pushes still reading this CTA's staging area
   if ((xmode || pmode) && j == 0 && threadIdx.x == 0) p.xpad[p.rank][kPadFusedEpoch] = epoch0 + static_cast<uint32_t>(nsteps);
   // global-batch mode: this rank no longer reads the input slots of these steps (every CTA is past the last barrier):
   // the peers' copy kernels may overwrite them
