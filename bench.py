@@ -302,6 +302,7 @@ def main() -> int:
         surv = [r_ for r_ in recs if r_["rank"] != dead_rank]
         drill = {"spec": a.fault, "watchdog_ms": a.watchdog_ms, "dead_rank": dead_rank,
                  "survivors_detected": all(r_["code"] == native.ERR_TIMEOUT and r_["failed_state"] for r_ in surv),
+                 "survivors_naming_dead_rank": sum(1 for r_ in surv if f"waited for rank {dead_rank}" in (r_["error"] or "")),
                  "survivor_return_ms_max": max(r_["returned_after_ms"] for r_ in surv),
                  "detect_overhead_ms": max(r_["returned_after_ms"] for r_ in surv) - a.watchdog_ms,
                  "example": surv[0]["error"]}

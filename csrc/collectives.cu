@@ -198,7 +198,7 @@ __device__ __forceinline__ void report_failure(const CollArgs& a, int rank, int 
   __threadfence_system();
   a.status[0] = DMLP_ERR_TIMEOUT;
   // Release everybody quickly: the abort word sits in each rank's (peer-visible) signal pad.
-  for (int p = 0; p < a.world; ++p) st_relaxed_sys(a.pad[p] + kPadAbort, 1u);
+  for (int p = 0; p < a.world; ++p) st_relaxed_sys(a.pad[p] + kPadAbort, abort_word_for(rank, peer));
   __threadfence_system();
 }
 
@@ -216,7 +216,8 @@ __device__ __forceinline__ bool wait_flag(const uint32_t* flag, uint32_t target,
   uint32_t spins = 0;
   while (static_cast<int32_t>(ld_relaxed_sys(flag) - target) < 0) {
     if ((++spins & 0x3F) == 0) {
-      if (ld_relaxed_sys(a.pad[rank] + kPadAbort) != 0u) return false;
+      const uint32_t ab = ld_relaxed_sys(a.pad[rank] + kPadAbort);
+      if (ab != 0u) { record_abort(a.status, rank, ab, static_cast<uint32_t>(phase)); return false; }
       if (globaltimer_ns() > deadline) {
         report_failure(a, rank, peer, phase);
         return false;
@@ -844,8 +845,9 @@ static const AlgoRow kAlgoTable[] = {
     {2, 4u << 20, ~static_cast<size_t>(0)},   // two ranks: a pull of the peer's buffer IS the reduce-scatter + gather
     {3, 1u << 20, 64u << 20},
     {4, 1u << 20, 64u << 20},                 // profiles/r1_allreduce_sweep_4gpu_graph.jsonl: NVLS 173 vs 180 us at 64 MiB
-    {6, 512u << 10, 16u << 20},
-    {8, 512u << 10, 16u << 20},               // profiles/r1_allreduce_sweep_8gpu_graph.jsonl: NVLS 58.6 vs 61.4 us at 16 MiB
+    {6, 512u << 10, 64u << 20},
+    {8, 512u << 10, 64u << 20},               // profiles/r2_allreduce_sweep_8gpu_graph.jsonl: two-shot 61 vs NVLS 75 us at 16 MiB,
+                                              // NVLS 178 vs 201 us at 64 MiB, 588 vs 761 us at 256 MiB
 };
 
 extern "C" int dmlp_allreduce_pick_algo_ex(int world, size_t bytes, int nvls_available) {

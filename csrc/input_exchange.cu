@@ -38,7 +38,8 @@ __global__ void __launch_bounds__(256) input_exchange_kernel(const XPushParams a
     uint32_t spins = 0;
     while (static_cast<int32_t>(ld_relaxed_sys(f) - a.need_done) < 0) {
       if ((++spins & 0x3F) == 0) {
-        if (ld_relaxed_sys(a.pad[a.rank] + kPadAbortWord) != 0u) { s_fail = 1; break; }
+        const uint32_t ab = ld_relaxed_sys(a.pad[a.rank] + kPadAbortWord);
+        if (ab != 0u) { record_abort(a.status, a.rank, ab, 12u); s_fail = 1; break; }
         if (globaltimer_ns() > deadline) {
           if (a.status != nullptr) {
             a.status[1] = static_cast<uint32_t>(a.rank);
@@ -47,7 +48,7 @@ __global__ void __launch_bounds__(256) input_exchange_kernel(const XPushParams a
             __threadfence_system();
             a.status[0] = DMLP_ERR_TIMEOUT;
           }
-          for (int q = 0; q < a.world; ++q) st_relaxed_sys(a.pad[q] + kPadAbortWord, 1u);
+          for (int q = 0; q < a.world; ++q) st_relaxed_sys(a.pad[q] + kPadAbortWord, abort_word_for(a.rank, static_cast<int>(threadIdx.x)));
           s_fail = 1;
           break;
         }

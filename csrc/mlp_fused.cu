@@ -324,7 +324,8 @@ __device__ __forceinline__ bool pf_wait(const uint32_t* flag, uint32_t target, c
   uint32_t spins = 0;
   while (static_cast<int32_t>(ld_relaxed_sys(flag) - target) < 0) {
     if ((++spins & 0x3F) == 0) {
-      if (ld_relaxed_sys(p.xpad[p.rank] + kPadAbortWord) != 0u) return false;
+      const uint32_t ab = ld_relaxed_sys(p.xpad[p.rank] + kPadAbortWord);
+      if (ab != 0u) { record_abort(p.xstatus, p.rank, ab, phase); return false; }
       if (globaltimer_ns() > deadline) {
         if (p.xstatus != nullptr) {
           p.xstatus[1] = static_cast<uint32_t>(p.rank);
@@ -333,7 +334,7 @@ __device__ __forceinline__ bool pf_wait(const uint32_t* flag, uint32_t target, c
           __threadfence_system();
           p.xstatus[0] = DMLP_ERR_TIMEOUT;
         }
-        for (int q = 0; q < p.world; ++q) st_relaxed_sys(p.xpad[q] + kPadAbortWord, 1u);
+        for (int q = 0; q < p.world; ++q) st_relaxed_sys(p.xpad[q] + kPadAbortWord, abort_word_for(p.rank, peer));
         return false;
       }
     }
@@ -349,7 +350,8 @@ __device__ __forceinline__ bool gx_valid(const float4& v) {
          __float_as_uint(v.w) != kGxEmpty;
 }
 __device__ __forceinline__ bool gx_timeout(const FusedParams& p, int peer, uint32_t phase, unsigned long long deadline) {
-  if (ld_relaxed_sys(p.xpad[p.rank] + kPadAbortWord) != 0u) return true;
+  const uint32_t ab = ld_relaxed_sys(p.xpad[p.rank] + kPadAbortWord);
+  if (ab != 0u) { record_abort(p.xstatus, p.rank, ab, phase); return true; }
   if (globaltimer_ns() > deadline) {
     if (p.xstatus != nullptr) {
       p.xstatus[1] = static_cast<uint32_t>(p.rank);
@@ -358,7 +360,7 @@ __device__ __forceinline__ bool gx_timeout(const FusedParams& p, int peer, uint3
       __threadfence_system();
       p.xstatus[0] = DMLP_ERR_TIMEOUT;
     }
-    for (int q = 0; q < p.world; ++q) st_relaxed_sys(p.xpad[q] + kPadAbortWord, 1u);
+    for (int q = 0; q < p.world; ++q) st_relaxed_sys(p.xpad[q] + kPadAbortWord, abort_word_for(p.rank, peer));
     return true;
   }
   return false;
@@ -1436,7 +1438,8 @@ mlp_fused_step_kernel(const __grid_constant__ CUtensorMap tmXA, const __grid_con
         uint32_t spins = 0;
         while (static_cast<int32_t>(ld_relaxed_sys(f) - epoch) < 0) {
           if ((++spins & 0x3F) == 0) {
-            if (ld_relaxed_sys(p.xpad[p.rank] + kPadAbortWord) != 0u) { s_xfail = 1; break; }
+            const uint32_t ab = ld_relaxed_sys(p.xpad[p.rank] + kPadAbortWord);
+            if (ab != 0u) { record_abort(p.xstatus, p.rank, ab, 5u); s_xfail = 1; break; }
             if (globaltimer_ns() > deadline) {
               if (p.xstatus != nullptr) {
                 p.xstatus[1] = static_cast<uint32_t>(p.rank);
@@ -1445,7 +1448,7 @@ mlp_fused_step_kernel(const __grid_constant__ CUtensorMap tmXA, const __grid_con
                 __threadfence_system();
                 p.xstatus[0] = DMLP_ERR_TIMEOUT;
               }
-              for (int q = 0; q < W; ++q) st_relaxed_sys(p.xpad[q] + kPadAbortWord, 1u);
+              for (int q = 0; q < W; ++q) st_relaxed_sys(p.xpad[q] + kPadAbortWord, abort_word_for(p.rank, peer));
               s_xfail = 1;
               break;
             }

@@ -182,12 +182,13 @@ __device__ __forceinline__ bool nvls_wait(const uint32_t* flag, uint32_t target,
   uint32_t spins = 0;
   while (static_cast<int32_t>(ld_relaxed_sys(flag) - target) < 0) {
     if ((++spins & 0x3F) == 0) {
-      if (ld_relaxed_sys(a.pad[a.rank] + kNvlsPadAbort) != 0u) return false;
+      const uint32_t ab = ld_relaxed_sys(a.pad[a.rank] + kNvlsPadAbort);
+      if (ab != 0u) { record_abort(a.status, a.rank, ab, static_cast<uint32_t>(phase)); return false; }
       if (globaltimer_ns() > deadline) {
         a.status[1] = a.rank; a.status[2] = peer; a.status[3] = phase;
         __threadfence_system();
         a.status[0] = DMLP_ERR_TIMEOUT;
-        for (int p = 0; p < a.world; ++p) st_relaxed_sys(a.pad[p] + kNvlsPadAbort, 1u);
+        for (int p = 0; p < a.world; ++p) st_relaxed_sys(a.pad[p] + kNvlsPadAbort, abort_word_for(a.rank, peer));
         __threadfence_system();
         return false;
       }

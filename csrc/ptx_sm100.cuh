@@ -337,4 +337,25 @@ __device__ __forceinline__ uint64_t globaltimer_ns() {
   return t;
 }
 
+// ---------------------------------------------------------------- watchdog bookkeeping shared by every cross-GPU wait
+// The abort word in each rank's signal pad releases everybody once ONE rank's watchdog has fired. It carries who gave up
+// on whom, so that the ranks that leave through the abort word (they never time out themselves) can still tell the host:
+//   0            : running        1 : aborted by the host (dmlp_comm_abort)
+//   0x10000 | detector << 8 | missing : rank `detector` waited for rank `missing` until its deadline
+__device__ __forceinline__ uint32_t abort_word_for(int detector, int missing) {
+  return 0x10000u | (static_cast<uint32_t>(detector & 0xFF) << 8) | static_cast<uint32_t>(missing & 0xFF);
+}
+// A wait saw the abort word `v`: leave a failure record {code, rank, peer, phase} in this rank's host-mapped status block
+// unless one is there already (4 = DMLP_ERR_TIMEOUT: a named peer went missing; 5 = DMLP_ERR_ABORTED: host abort).
+__device__ __forceinline__ void record_abort(uint32_t* status, int rank, uint32_t v, uint32_t phase) {
+  if (status == nullptr) return;
+  if (*reinterpret_cast<volatile uint32_t*>(status) != 0u) return;
+  const bool named = (v & 0x10000u) != 0u;
+  status[1] = static_cast<uint32_t>(rank);
+  status[2] = named ? (v & 0xFFu) : 0xFFFFFFFFu;
+  status[3] = phase | 0x80u;  // bit 7: learnt through the abort word
+  __threadfence_system();
+  status[0] = named ? 4u : 5u;
+}
+
 }  // namespace dmlp
