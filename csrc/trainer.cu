@@ -718,7 +718,7 @@ extern "C" int dmlp_trainer_create(const dmlp_trainer_config_t* cfg, int device,
       void* base = nullptr;
       size_t cap = 0;
       int e = dmlp_comm_arena_ptr(t->comm, local_idx, r, &base, &cap);
-      if (e != DMLP_OK) { if (r == rank) return fail(e); continue; }  // peers unmapped: ring still works
+      if (e != DMLP_OK) { if (r == rank) return fail(e); continue; }  // (a peer that is not mapped: dmlp_allreduce will refuse later)
       const size_t xall_bytes = align_up(static_cast<size_t>(world) * kRingSlots * B * L.in[0] * 4, 256);
       const size_t base_need = arena_offset + 3 * pbytes + (t->bf16 ? sbytes : 0);
       const size_t recv_bytes = 2 * static_cast<size_t>(world) * pbytes;
@@ -918,7 +918,11 @@ extern "C" int dmlp_trainer_run(dmlp_trainer_t h, const float* x_host, const int
     float saved = t->lr_host[0];
     t->lr_host[0] = 0.f;
     DMLP_CUDA_CHECK(cudaMemcpy(t->lr_dev, t->lr_host, 4, cudaMemcpyHostToDevice));
-    for (int par = 0; par < 2; ++par) {
+    // Parities continue the alternation of the real steps (gradient buffers are double-buffered by step parity and the
+    // one-shot all-reduce skips its trailing rendezvous: reusing the parity of the step just finished would overwrite a
+    // buffer a slower peer may still be reading).
+    for (int i = 0; i < 2; ++i) {
+      const int par = static_cast<int>((t->steps_done + i) & 1);
       DMLP_CUDA_CHECK(cudaMemcpyAsync(t->x[par], x_host, sizeof(float) * B * xin, cudaMemcpyDefault, t->s_main));
       DMLP_CUDA_CHECK(cudaMemcpyAsync(t->labels[par], y_host, sizeof(int) * B, cudaMemcpyDefault, t->s_main));
       TRY(enqueue_step(t, par, true));
@@ -999,7 +1003,7 @@ extern "C" int dmlp_trainer_run_resident(dmlp_trainer_t h, int steps, int use_gr
     float saved = t->lr_host[0];
     t->lr_host[0] = 0.f;
     DMLP_CUDA_CHECK(cudaMemcpy(t->lr_dev, t->lr_host, 4, cudaMemcpyHostToDevice));
-    for (int par = 0; par < 2; ++par) TRY(enqueue_step(t, par, true));
+    for (int i = 0; i < 2; ++i) TRY(enqueue_step(t, static_cast<int>((t->steps_done + i) & 1), true));  // (see dmlp_trainer_run)
     DMLP_CUDA_CHECK(cudaStreamSynchronize(t->s_main));
     t->lr_host[0] = saved;
     DMLP_CUDA_CHECK(cudaMemcpy(t->lr_dev, t->lr_host, 4, cudaMemcpyHostToDevice));

@@ -64,5 +64,30 @@ def test_graft_entry_build_is_importable_and_links():
         pytest.skip("native library not built yet")
     lib = native.lib()
     for sym in ("dmlp_gemm", "dmlp_allreduce", "dmlp_allreduce_nvls", "dmlp_mlp_fused_steps", "dmlp_trainer_run",
-                "dmlp_allreduce_sum_f32_noalloc", "dmlp_comm_is_emulated", "dmlp_gemm_prof_read"):
+                "dmlp_allreduce_sum_f32_noalloc", "dmlp_comm_is_emulated", "dmlp_gemm_prof_read",
+                "dmlp_allreduce_noalloc_status", "dmlp_mlp_fused_steps_gx", "dmlp_mlp_fused_set_fault", "dmlp_input_exchange",
+                "dmlp_trainer_set_fault", "dmlp_trainer_state", "dmlp_allreduce_pick_algo_ex"):
         assert hasattr(lib, sym), sym
+
+
+def test_allreduce_dispatcher_table():
+    """`algo=auto` (csrc/collectives.cu, table from the sweeps under profiles/): one-shot for latency-bound sizes, two-shot
+    above, NVLS only when the caller says the buffers are multicast-bound and only from the size at which it wins; the ring
+    (the RPC's namesake, gpu_coordinator_server.go:272-376) is the comparison mode and never picked."""
+    from dmlp_b200.runtime import native
+    if not native.available():
+        import pytest
+        pytest.skip("native library not built yet")
+    pick = native.lib().dmlp_allreduce_pick_algo_ex
+    one, two, ring, nvls = (native.ALGO_BY_NAME[k] for k in ("oneshot", "twoshot", "ring", "nvls"))
+    assert pick(1, 1 << 20, 1) == one
+    for world in (2, 3, 4, 8):
+        assert pick(world, 1024, 1) == one
+        assert pick(world, 437544, 0) == one          # the small model's gradient
+        assert pick(world, 1 << 30, 0) == two
+        picks = {pick(world, 1 << s, n) for s in range(10, 31) for n in (0, 1)}
+        assert ring not in picks
+    assert pick(2, 4 << 20, 0) == one and pick(2, 16 << 20, 0) == two
+    assert pick(8, 512 << 10, 0) == one and pick(8, 1 << 20, 0) == two
+    assert pick(8, 16 << 20, 1) == two and pick(8, 64 << 20, 1) == nvls and pick(8, 64 << 20, 0) == two
+    assert pick(4, 64 << 20, 1) == nvls and pick(2, 1 << 30, 1) == two  # (no multicast win on two ranks)
