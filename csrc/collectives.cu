@@ -75,7 +75,7 @@ struct CollArgs {
   unsigned long long timeout_ns;
   // optional phase timestamps: [block][4] x u64 globaltimer ns {entry, after barrier-in, after data, exit}
   unsigned long long* prof;
-  uint32_t strict;  // env DMLP_COLL_STRICT=1: add a system-scope acquire fence after every flag wait
+  uint32_t strict;  // env DMLP_COLL_STRICT: 2 (default) flag polls are acquire loads; 1 adds system fences both sides; 0 relaxed polls
 };
 
 #define DMLP_PROF(slot)                                                               \
@@ -210,11 +210,12 @@ __device__ __forceinline__ void report_failure(const CollArgs& a, int rank, int 
 //    acquire fence follows: every read of peer-written data in these kernels is a volatile
 //    (sys-scope, L1-bypassing) load issued after the flag was observed (control dependency +
 //    bar.sync), and data a peer pushed into local memory is only read by later kernels.
-//    DMLP_COLL_STRICT=1 restores the fence.
+//    Since round 2 the poll itself is an acquire load by default (+0.05 us per rendezvous); DMLP_COLL_STRICT=1
+//    restores the fence, =0 the relaxed poll.
 __device__ __forceinline__ bool wait_flag(const uint32_t* flag, uint32_t target, const CollArgs& a,
                                           int rank, int peer, int phase, unsigned long long deadline) {
   uint32_t spins = 0;
-  while (static_cast<int32_t>(ld_relaxed_sys(flag) - target) < 0) {
+  while (static_cast<int32_t>((a.strict == 2 ? ld_acquire_sys(flag) : ld_relaxed_sys(flag)) - target) < 0) {
     if ((++spins & 0x3F) == 0) {
       const uint32_t ab = ld_relaxed_sys(a.pad[rank] + kPadAbort);
       if (ab != 0u) { record_abort(a.status, rank, ab, static_cast<uint32_t>(phase)); return false; }
@@ -224,7 +225,7 @@ __device__ __forceinline__ bool wait_flag(const uint32_t* flag, uint32_t target,
       }
     }
   }
-  if (a.strict) __threadfence_system();
+  if (a.strict == 1) __threadfence_system();
   return true;
 }
 
@@ -237,7 +238,7 @@ __device__ __forceinline__ bool coll_barrier(const CollArgs& a, int rank, uint32
   __syncthreads();
   if (threadIdx.x < a.world) {
     const int p = threadIdx.x;
-    if (release || a.strict) __threadfence_system();  // (strict mode: every barrier releases, entry barriers included)
+    if (release || a.strict == 1) __threadfence_system();  // (strict mode: every barrier releases, entry barriers included)
     st_relaxed_sys(a.pad[p] + kPadBarrier + blockIdx.x * kMaxRanks + rank, epoch);
     if (!wait_flag(a.pad[rank] + kPadBarrier + blockIdx.x * kMaxRanks + p, epoch, a, rank, p, phase, deadline))
       *s_fail = 1;
@@ -902,7 +903,7 @@ extern "C" int dmlp_allreduce(dmlp_comm_t h, int local_idx, const dmlp_allreduce
   a.prof = reinterpret_cast<unsigned long long*>(d->prof_dev);
   {
     static int strict = -1;
-    if (strict < 0) { const char* e = getenv("DMLP_COLL_STRICT"); strict = e ? atoi(e) : 0; }
+    if (strict < 0) { const char* e = getenv("DMLP_COLL_STRICT"); strict = e ? atoi(e) : 2; }  // 2: acquire polls (default)
     a.strict = static_cast<uint32_t>(strict);
   }
   for (int r = 0; r < world; ++r) {

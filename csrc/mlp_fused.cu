@@ -93,10 +93,10 @@ struct FusedParams {
   unsigned long long g0;        // global index of this launch's first step (parity of the receive areas)
   long long fault_step;         // fault injection: from this global step on this rank sends nothing and waits for nothing (-1: never)
   unsigned int xneed;           // the peers' inputs for this launch are in place once their ready words reach this step count
-  // DMLP_COLL_STRICT=1 (same switch as collectives.cu): every cross-GPU flag is published behind a system-scope fence
-  // and every flag wait is followed by a system-scope acquire fence - the conservative protocol the default is compared
-  // against. The default relies on this GPU's L2 being the point of coherence for its own memory (peer reads of it are
-  // served there), so a gpu-scope fence before a flag and no fence after a poll suffice; docs/FUSED_STEP.md, section 6.
+  // DMLP_COLL_STRICT (same switch as collectives.cu). 2 (default): flag polls are ld.acquire.sys; flags are published
+  // behind a gpu-scope fence, which relies on this GPU's L2 being the point of coherence for its own memory (peer reads
+  // of it are served there). 1: the conservative protocol - system-scope fence before every flag published to a peer and
+  // after every flag wait. 0: relaxed polls, no acquire (round 1's protocol). docs/FUSED_STEP.md, section 6a.
   int strict;
 };
 
@@ -322,7 +322,8 @@ __device__ __forceinline__ float4 ld_volatile_f4(const float* p) {
 __device__ __forceinline__ bool pf_wait(const uint32_t* flag, uint32_t target, const FusedParams& p, int peer, uint32_t phase,
                                         unsigned long long deadline) {
   uint32_t spins = 0;
-  while (static_cast<int32_t>(ld_relaxed_sys(flag) - target) < 0) {
+  // (strict == 2: the poll itself is an acquire load - the variant measured against the relaxed default)
+  while (static_cast<int32_t>((p.strict == 2 ? ld_acquire_sys(flag) : ld_relaxed_sys(flag)) - target) < 0) {
     if ((++spins & 0x3F) == 0) {
       const uint32_t ab = ld_relaxed_sys(p.xpad[p.rank] + kPadAbortWord);
       if (ab != 0u) { record_abort(p.xstatus, p.rank, ab, phase); return false; }
@@ -339,7 +340,7 @@ __device__ __forceinline__ bool pf_wait(const uint32_t* flag, uint32_t target, c
       }
     }
   }
-  if (p.strict) __threadfence_system();  // acquire side of the conservative protocol
+  if (p.strict == 1) __threadfence_system();  // acquire side of the conservative protocol
   return true;
 }
 
@@ -438,7 +439,7 @@ __device__ void fused_reducer_loop(const FusedParams& p) {
         }
       }
     }
-    if (p.strict) __threadfence_system(); else
+    if (p.strict == 1) __threadfence_system(); else
     __threadfence();
     __syncthreads();
     if (threadIdx.x == 0) atomicAdd(mypad + kPfWeights, 1u);  // (also on failure: the compute cluster must not hang)
@@ -1351,7 +1352,7 @@ mlp_fused_step_kernel(const __grid_constant__ CUtensorMap tmXA, const __grid_con
     __syncthreads();
     const bool pdead = p.fault_step >= 0 && static_cast<long long>(p.g0) + st >= p.fault_step;  // fault injection
     if (threadIdx.x < p.world && !pdead) {  // one thread per rank (own included): that rank's reducers poll [my rank][my CTA] locally
-      if (p.strict) __threadfence_system(); else
+      if (p.strict == 1) __threadfence_system(); else
       __threadfence();
       st_relaxed_sys(p.xpad[threadIdx.x] + kPadFusedFlags + kPfRedFlags + p.rank * kFC + j, epoch);
     }
@@ -1455,7 +1456,7 @@ mlp_fused_step_kernel(const __grid_constant__ CUtensorMap tmXA, const __grid_con
           }
         }
       }
-      if (p.strict) __threadfence_system();
+      if (p.strict == 1) __threadfence_system();
       __syncwarp();
     }
     __syncthreads();
@@ -1657,7 +1658,7 @@ extern "C" int dmlp_mlp_fused_plan_create(const dmlp_mlp_fused_desc_t* d, dmlp_m
   p.fault_step = -1;
   {
     const char* e = getenv("DMLP_COLL_STRICT");
-    p.strict = e ? atoi(e) : 0;
+    p.strict = e ? atoi(e) : 2;  // default: acquire loads on the flag polls (+0.05 us per rendezvous, measured at 2 GPUs)
   }
   {
     const char* e = getenv("DMLP_FUSED_BULK");

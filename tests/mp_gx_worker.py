@@ -80,12 +80,12 @@ def main():
     dist.barrier()
 
     # ---- 2b. soak of the DEFAULT path (persistent compute + reducer launch): 10^5 steps, replicas bit-identical, and the
-    # relaxed flag protocol (gpu-scope fence before a flag, no fence after a poll) against the conservative one
-    # (DMLP_COLL_STRICT=1: system-scope fences both sides) - the two runs must end with the same bits
+    # default flag protocol (gpu-scope fence before a flag, acquire load on the poll; "0" = round 1's relaxed poll) against
+    # the conservative one (DMLP_COLL_STRICT=1: system-scope fences both sides) - all runs must end with the same bits
     import hashlib
     pdp_steps = int(os.environ.get("DMLP_PDP_SOAK_STEPS", "100000"))
     digests = {}
-    for strict in ("0", "1"):
+    for strict in ("2", "0", "1"):
         os.environ["DMLP_COLL_STRICT"] = strict  # read when the trainer builds its fused-step plan
         t = Trainer(TrainerConfig(dims=(784, 128, 64, 10), batch=64, lr=0.02, seed=13), device=local, process_group=True)
         assert t.dp_mode == 4, t.dp_mode
@@ -103,7 +103,7 @@ def main():
         t.close()
         dist.barrier()
     os.environ.pop("DMLP_COLL_STRICT", None)
-    assert digests["0"] == digests["1"], "relaxed and strict flag protocols produced different parameters"
+    assert digests["2"] == digests["1"] == digests["0"], "the flag protocols produced different parameters"
 
     # ---- 3. a rank dies mid-run: the default path (persistent compute + reducer launch, mode 4) and the global-batch mode
     # ... and the per-layer path with its bucketed all-reduce overlapped with backward (mode 0: what the wide model runs)

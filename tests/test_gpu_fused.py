@@ -11,6 +11,36 @@ def _trainer(dims, fused, batch=64, lr=0.05, use_graph=False):
     return Trainer(TrainerConfig(dims=dims, batch=batch, lr=lr, fused=fused, use_graph=use_graph), device=0)
 
 
+def _tf32(a: np.ndarray) -> np.ndarray:
+    """fp32 -> what kind::tf32 consumes (10-bit mantissa, low 13 bits dropped), as float64 for exact accumulation."""
+    return (np.ascontiguousarray(a, dtype=np.float32).view(np.int32) & ~0x1FFF).view(np.float32).astype(np.float64)
+
+
+def _tf32_chain_oracle(params, x, y):
+    """The reference math (client.go:112-202) with every GEMM operand truncated to tf32 where the kernel feeds it to a
+    tensor core, everything else in float64: pins the kernel's data flow (K slices, exchanges, masks) far tighter than
+    the plain oracle, whose distance to a tf32 kernel is dominated by operand rounding."""
+    B = x.shape[0]
+    acts, h = [x.astype(np.float64)], x.astype(np.float64)
+    for i, (w, b) in enumerate(params):
+        z = _tf32(h) @ _tf32(w) + b
+        h = np.maximum(z, 0) if i < len(params) - 1 else z
+        acts.append(h)
+    logits = acts[-1]
+    e = np.exp(logits - logits.max(1, keepdims=True))
+    p = e / e.sum(1, keepdims=True)
+    onehot = np.zeros_like(p)
+    onehot[np.arange(B), y] = 1
+    loss = float(np.mean(-np.log((p * onehot).sum(1) + 1e-10)))
+    dz = (p - onehot) / B
+    grads = [None] * len(params)
+    for l in range(len(params) - 1, -1, -1):
+        grads[l] = (_tf32(acts[l]).T @ _tf32(dz), _tf32(dz).sum(0))  # (bias gradient = ones column of the same MMA)
+        if l > 0:
+            dz = (_tf32(dz) @ _tf32(params[l][0]).T) * (acts[l] > 0)
+    return loss, grads
+
+
 @pytest.mark.parametrize("dims", [(784, 128, 64, 10), (784, 128, 10)])
 @pytest.mark.parametrize("batch", [64, 32])
 def test_fused_gradients_match_oracle(dims, batch):
@@ -38,6 +68,16 @@ def test_fused_gradients_match_oracle(dims, batch):
         sw, sb = max(1e-4, np.abs(gw).max()), max(1e-4, np.abs(gb).max())
         assert np.abs(kw - gw).max() < 5e-2 * sw, f"dW{l + 1}: {np.abs(kw - gw).max()} vs scale {sw}"
         assert np.abs(kb - gb).max() < 5e-2 * sb, f"db{l + 1}: {np.abs(kb - gb).max()} vs scale {sb}"
+    # against the oracle that truncates operands where the kernel does: an order of magnitude tighter (a wrong K-slice
+    # or exchange contribution of a percent would show)
+    loss_t, grads_t = _tf32_chain_oracle(params, x[:batch], y[:batch])
+    assert abs(st["per_step_loss"][0] - loss_t) < 2e-3 * max(1.0, loss_t), (st["per_step_loss"][0], loss_t)
+    for l, ((gw, gb), s) in enumerate(zip(grads_t, t.layout.layers)):
+        kw = g[s.w_off:s.w_off + s.fan_in * s.out_pad].reshape(s.fan_in, s.out_pad)[:, :s.fan_out]
+        kb = g[s.b_off:s.b_off + s.fan_out]
+        sw, sb = max(1e-4, np.abs(gw).max()), max(1e-4, np.abs(gb).max())
+        assert np.abs(kw - gw).max() < 5e-3 * sw, f"dW{l + 1} vs tf32 oracle: {np.abs(kw - gw).max()} vs scale {sw}"
+        assert np.abs(kb - gb).max() < 5e-3 * sb, f"db{l + 1} vs tf32 oracle: {np.abs(kb - gb).max()} vs scale {sb}"
     t.close()
 
 
