@@ -22,13 +22,14 @@ type comes from gRPC metadata ``dmlp-dtype`` (default ``f32`` when ``count % 4 =
 
 Execution paths for collectives:
   native    all devices are in-process CUDA backends → one fused kernel per rank over peer memory
-            (``runtime.comm.Communicator``); metadata ``dmlp-algo`` picks ring/oneshot/twoshot/auto
+            (``runtime.comm.Communicator``); metadata ``dmlp-algo`` picks ring/oneshot/twoshot/nvls/auto
   portable  anything else (sim devices, remote devices) → the ring schedule is driven through the
             device RPC contract (BeginSend/BeginReceive/StreamSend/GetStreamStatus/Memcpy)
 """
 from __future__ import annotations
 
 import logging
+import os
 import threading
 import time
 from dataclasses import dataclass, field
@@ -105,6 +106,13 @@ class Communicator:
         self.native = None  # runtime.comm.Communicator when every device is an in-process CUDA backend
         self.finalized = False
         self.failure_reason = ""
+        # Symmetric heap (runtime.nvls.NvlsArena: one physical allocation per device, all bound to one multicast
+        # object): created on the first AllReduceRing that can use the switch reduction. Buffers of the devices'
+        # address spaces are moved into slots that have the same offset on every device. None = not tried yet,
+        # False = unavailable on this box / for this device set.
+        self.heap = None
+        self.heap_slots: Dict[tuple, tuple] = {}  # (per-rank addresses) -> (offset, capacity)
+        self.heap_adopted: set = set()  # (backend, addr) pairs living in the heap
 
 
 class _InProcessAbort(RuntimeError):
@@ -159,6 +167,20 @@ class GPUCoordinatorService:
             self._release(c)
 
     def _release(self, comm: Communicator) -> None:
+        if comm.heap:
+            with _NATIVE_LOCK:
+                for be, addr in list(comm.heap_adopted):
+                    try:
+                        be.unadopt(addr)  # contents go back to a private allocation: the devices outlive the communicator
+                    except Exception as e:  # pragma: no cover
+                        log.warning("moving 0x%x out of the symmetric heap: %s", addr, e)
+                comm.heap_adopted.clear()
+                comm.heap_slots.clear()
+                try:
+                    comm.heap.destroy()
+                except Exception as e:  # pragma: no cover
+                    log.warning("releasing the symmetric heap of communicator %d: %s", comm.id, e)
+            comm.heap = False
         if comm.native is not None:
             try:
                 comm.native.abort()
@@ -469,34 +491,104 @@ class GPUCoordinatorService:
         esz = native.DTYPE_SIZE[ndt]
         if count % esz:
             raise ValueError(f"count {count} is not a multiple of the {dtype} element size")
-        ptrs = []
         for d in devices:
             be = d.local.backend
             be.check_addr(addrs[d.rank])
             be.ensure(addrs[d.rank], count)
-            ptrs.append(be.pointer(addrs[d.rank]))
-        kwargs = {}
-        if "dmlp-sgd-lr" in md:
+        sgd = "dmlp-sgd-lr" in md
+        waddr, lrs = None, None
+        if sgd:
             # Fused gradient average + SGD: weights at dmlp-sgd-weights (default 0x2000) are updated
             # in the same kernel; nothing elementwise runs afterwards (client.go:254-267 on device).
             waddr = int(md.get("dmlp-sgd-weights", hex(RECV_ADDR)), 0)
-            outs, lrs = [], []
+            lrs = []
             for d in devices:
                 be = d.local.backend
                 be.check_addr(waddr)
                 be.ensure(waddr, count)
-                outs.append(be.pointer(waddr))
                 lrs.append(be.scalar_f32(None, float(md["dmlp-sgd-lr"])))  # a slot of its own: earlier launches may still read theirs
                 be.touched(waddr)
-            kwargs = dict(fuse_sgd=True, lr=lrs, scale=1.0 / len(devices))
-        else:
-            outs = ptrs
+        if self._allreduce_switch(comm, devices, addrs, count, dtype, op, algo, md, native, lrs, waddr):
+            if deferred:
+                return  # part of a group: GroupEnd waits once after the last launch
+            comm.native.sync()
+            comm.native.check()
+            return
+        # (pointers are read after the attempt above: it may have moved buffers into the symmetric heap)
+        ptrs = [d.local.backend.pointer(addrs[d.rank]) for d in devices]
+        outs = [d.local.backend.pointer(waddr) for d in devices] if sgd else ptrs
+        kwargs = dict(fuse_sgd=True, lr=lrs, scale=1.0 / len(devices)) if sgd else {}
+        if algo == "nvls":
+            algo = "auto"  # asked for the switch path but the heap is full: unicast kernels
         comm.native.allreduce(ptrs, outs, count // esz, dtype=ndt, op=int(op),
                               algo=native.ALGO_BY_NAME.get(algo, native.ALGO_AUTO), **kwargs)
         if deferred:
             return  # part of a group: GroupEnd waits once after the last launch
         comm.native.sync()
         comm.native.check()  # raises CommFailure when a watchdog fired (dead peer mid-collective)
+
+    # -- switch-reduced path: the buffers live in a symmetric, multicast-bound heap ---------------
+    def _service_heap(self, comm):
+        """The communicator's symmetric heap, created on first use (``DMLP_SERVICE_HEAP_MB`` per device, default 64;
+        0 disables). ``False`` when the device set cannot have one (emulated ranks, no multicast support)."""
+        if comm.heap is None:
+            from ..runtime.nvls import NvlsArena, NvlsUnavailable
+            mb = int(os.environ.get("DMLP_SERVICE_HEAP_MB", "64"))
+            comm.heap = False
+            if mb > 0 and not comm.native.emulated:
+                try:
+                    comm.heap = NvlsArena.local(list(comm.native.local_devs), mb << 20)
+                except (NvlsUnavailable, Exception) as e:
+                    log.info("communicator %d: no symmetric heap (%s); collectives stay on unicast peer memory", comm.id, e)
+        return comm.heap
+
+    def _heap_place(self, comm, heap, devices, addr_of, nbytes):
+        """Moves every device's buffer at ``addr_of[rank]`` into one slot of the heap (same offset on every device).
+        Returns the offset, or None when the heap is full (the caller falls back to the unicast kernels)."""
+        key = tuple(addr_of[d.rank] for d in devices)
+        slot = comm.heap_slots.get(key)
+        if slot is None or slot[1] < nbytes:
+            cap = max(4096, (nbytes + 4095) // 4096 * 4096)
+            try:
+                slot = (heap.alloc.alloc(cap), cap)  # (a grown buffer takes a new slot; the old one is not reused)
+            except MemoryError:
+                return None
+            comm.heap_slots[key] = slot
+        for li, d in enumerate(devices):
+            be = d.local.backend
+            be.adopt(addr_of[d.rank], heap.uc[comm.native.local_devs[li]] + slot[0], slot[1])
+            comm.heap_adopted.add((be, addr_of[d.rank]))
+        return slot[0]
+
+    def _allreduce_switch(self, comm, devices, addrs, count, dtype, op, algo, md, native, lrs, waddr) -> bool:
+        """f32 SUM through NVLS (``multimem.ld_reduce`` / ``multimem.st`` on the heap's multicast address) when the
+        caller asks for it (``dmlp-algo: nvls``) or the dispatcher table picks it for this size. Returns False when this
+        call has to take the unicast path instead."""
+        if dtype != "f32" or int(op) != pb.SUM or algo not in ("auto", "nvls") or count < 16:
+            return False
+        if algo == "auto" and comm.native.pick_algo(count, True) != native.ALGO_NVLS:
+            return False
+        heap = self._service_heap(comm)
+        if not heap:
+            if algo == "nvls":
+                raise RuntimeError("dmlp-algo nvls: this communicator has no multicast heap")
+            return False
+        o_in = self._heap_place(comm, heap, devices, addrs, count)
+        if o_in is None:
+            return False
+        o_out = o_in
+        if lrs is not None:
+            o_out = self._heap_place(comm, heap, devices, {d.rank: waddr for d in devices}, count)
+            if o_out is None:
+                return False
+        for li, d in enumerate(devices):
+            dev = comm.native.local_devs[li]
+            if lrs is not None:
+                heap.allreduce(comm.native, li, o_in, o_out, count // 4, dev, fuse_sgd=True, lr=lrs[li],
+                               scale=1.0 / len(devices))
+            else:
+                heap.allreduce(comm.native, li, o_in, o_out, count // 4, dev)
+        return True
 
     # -- portable path: ring schedule driven through the device RPC contract -------------------
     def _transfer(self, dst: DeviceInfo, payload: bytes, recv_addr: int, src_rank: int) -> None:

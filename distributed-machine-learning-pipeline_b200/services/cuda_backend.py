@@ -33,6 +33,7 @@ class CudaBackend(DeviceBackend):
         native.check(self._lib.dmlp_stream_create(self.ordinal, C.byref(s)))
         self.copy_stream = s.value
         self._versions: Dict[int, int] = {}  # bumped whenever a buffer's contents change (Memcpy, collectives)
+        self._external: Dict[int, int] = {}  # address -> capacity of buffers that live in somebody else's allocation
         info = native.DeviceInfo()
         native.check(self._lib.dmlp_device_info(self.ordinal, C.byref(info)))
         self._info = {"cuda-ordinal": str(self.ordinal), "uuid": info.uuid.decode(), "name": info.name.decode(),
@@ -61,7 +62,10 @@ class CudaBackend(DeviceBackend):
         if ent is not None:
             if keep and ent[1] > 0:
                 native.check(self._lib.dmlp_memcpy_d2d(self.ordinal, ptr, ent[0], ent[1], None))
-            native.check(self._lib.dmlp_free(self.ordinal, ent[0]))
+            if addr in self._external:  # lived in a symmetric heap slot: the heap's owner frees it, the slot is left behind
+                self._external.pop(addr)
+            else:
+                native.check(self._lib.dmlp_free(self.ordinal, ent[0]))
         size = nbytes if not keep or ent is None else max(ent[1], nbytes)
         self._bufs[addr] = (ptr, size, cap)
         return ptr
@@ -125,6 +129,40 @@ class CudaBackend(DeviceBackend):
             ent = self._bufs.get(addr)
             if ent is None or ent[1] < nbytes:
                 self._reserve(addr, nbytes, keep=True)  # fresh memory is zeroed by the runtime
+
+    # ------------------------------------------------------------------ symmetric heap slots
+    def adopt(self, addr: int, ptr: int, cap: int) -> None:
+        """Moves the buffer at ``addr`` into caller-owned device memory (a slot of a symmetric, multicast-bound heap that
+        has the same offset on every device of a communicator): contents are copied, the private allocation is freed,
+        and from now on Memcpy / collectives / RunForward see the slot. The backend never frees ``ptr``."""
+        with self._lock:
+            ent = self._bufs.get(addr)
+            if ent is None:
+                raise MissingBufferError(f"no data at address 0x{addr:x}")
+            if ent[0] == ptr:
+                return
+            if ent[1] > cap:
+                raise ValueError(f"buffer at 0x{addr:x} ({ent[1]} bytes) does not fit the {cap}-byte slot")
+            if ent[1]:
+                native.check(self._lib.dmlp_memcpy_d2d(self.ordinal, ptr, ent[0], ent[1], None))
+            if addr not in self._external:
+                native.check(self._lib.dmlp_free(self.ordinal, ent[0]))
+            self._bufs[addr] = (ptr, ent[1], cap)
+            self._external[addr] = cap
+
+    def unadopt(self, addr: int) -> None:
+        """Back into a private allocation (the heap that held the slot is going away)."""
+        with self._lock:
+            ent = self._bufs.get(addr)
+            if ent is None or addr not in self._external:
+                return
+            cap = max(256, (ent[1] + 255) // 256 * 256)
+            ptr = self._alloc(cap)
+            if ent[1]:
+                native.check(self._lib.dmlp_memcpy_d2d(self.ordinal, ptr, ent[0], ent[1], None))
+            native.check(self._lib.dmlp_device_sync(self.ordinal))
+            self._external.pop(addr)
+            self._bufs[addr] = (ptr, ent[1], cap)
 
     def pointer(self, addr: int) -> int:
         with self._lock:
@@ -270,8 +308,10 @@ class CudaBackend(DeviceBackend):
 
     def close(self) -> None:
         with self._lock:
-            for ptr, _, _ in self._bufs.values():
-                self._lib.dmlp_free(self.ordinal, ptr)
+            for a_, (ptr, _, _) in self._bufs.items():
+                if a_ not in self._external:
+                    self._lib.dmlp_free(self.ordinal, ptr)
+            self._external.clear()
             for ptr, _ in self._scratch.values():
                 self._lib.dmlp_free(self.ordinal, ptr)
             for ptr in self._scalars.values():

@@ -114,3 +114,102 @@ def test_single_process_nvls_allreduce():
         assert (o.double().cpu() - ref).abs().max().item() < 1e-4
     arena.destroy()
     comm.destroy()
+
+
+@needs2
+def test_grpc_allreduce_runs_on_the_symmetric_heap():
+    """Devices on distinct GPUs behind the gRPC contract: an f32 SUM AllReduceRing moves the buffers into the
+    communicator's multicast-bound heap (same offset on every GPU) and reduces in the switch; Memcpy, the fused SGD
+    update, the unicast kernels and a larger rewrite of the same address keep working on the moved buffers."""
+    import numpy as np
+    from dmlp_b200.proto import gpu_sim as pb
+    from dmlp_b200.proto import rpc
+    from dmlp_b200.runtime.nvls import supported
+    from dmlp_b200.services import server as srv
+    from dmlp_b200.services.backend import make_backend
+    n = min(_ngpu(), 8)
+    if not all(supported(d) for d in range(n)):
+        pytest.skip("multicast objects are not supported on this box")
+    devs = [srv.start_device_server(make_backend("cuda", i + 1, 0x2000, i)) for i in range(n)]
+    coord = srv.start_coordinator_server()
+    try:
+        client = rpc.CoordinatorStub(rpc.insecure_channel(coord.addr))
+        init = client.CommInit(pb.CommInitRequest(numDevices=n, device_addresses=[d.addr for d in devs]))
+        comm = coord.service.communicators[init.commId]
+        assert comm.native is not None and not comm.native.emulated
+
+        def h2d(dev, addr, data):
+            assert client.Memcpy(pb.MemcpyRequest(hostToDevice=pb.MemcpyHostToDeviceRequest(
+                hostSrcData=data, dstDeviceId=pb.DeviceId(value=dev), dstMemAddr=pb.MemAddr(value=addr)))).hostToDevice.success
+
+        def d2h(dev, addr):
+            return np.frombuffer(client.Memcpy(pb.MemcpyRequest(deviceToHost=pb.MemcpyDeviceToHostRequest(
+                srcDeviceId=pb.DeviceId(value=dev), srcMemAddr=pb.MemAddr(value=addr), numBytes=0))).deviceToHost.dstData,
+                np.float32)
+
+        ids = [md.deviceId.value for md in init.devices]
+        rng = np.random.default_rng(3)
+        nelem = 200003  # odd: the scalar tail of the switch kernel
+        grads = [rng.standard_normal(nelem).astype(np.float32) for _ in ids]
+        w0 = rng.standard_normal(nelem).astype(np.float32)
+        for i, g in zip(ids, grads):
+            h2d(i, 0x1000, g.tobytes())
+            h2d(i, 0x2000, w0.tobytes())
+        before = [d.service.backend.pointer(0x1000) for d in devs]
+        # 1. fused average + SGD in the switch-reduced kernel
+        assert client.AllReduceRing(pb.AllReduceRingRequest(commId=init.commId, count=nelem * 4),
+                                    metadata=(("dmlp-algo", "nvls"), ("dmlp-sgd-lr", "0.05"))).success
+        assert comm.heap, "the symmetric heap was not created"
+        after = [d.service.backend.pointer(0x1000) for d in devs]
+        assert all(a != b for a, b in zip(after, before))
+        offs = {a - comm.heap.uc[i] for i, a in enumerate(after)}
+        assert len(offs) == 1, f"not symmetric: {offs}"
+        ref = w0.astype(np.float64) - 0.05 * np.mean(np.stack(grads).astype(np.float64), axis=0)
+        ws = [d2h(i, 0x2000) for i in ids]
+        for w in ws:
+            assert np.abs(w - ref).max() < 1e-5 and np.array_equal(w, ws[0])
+        for i, g in zip(ids, grads):  # gradients untouched by the fused form
+            assert np.array_equal(d2h(i, 0x1000), g)
+        # 2. plain sum, in place on the heap
+        assert client.AllReduceRing(pb.AllReduceRingRequest(commId=init.commId, count=nelem * 4),
+                                    metadata=(("dmlp-algo", "nvls"),)).success
+        s = np.sum(np.stack(grads).astype(np.float64), axis=0)
+        outs = [d2h(i, 0x1000) for i in ids]
+        for o in outs:
+            assert np.abs(o - s).max() < 1e-4 and np.array_equal(o, outs[0])
+        # 3. the unicast kernels read and write heap memory of the peers too
+        for i, g in zip(ids, grads):
+            h2d(i, 0x1000, g.tobytes())
+        assert client.AllReduceRing(pb.AllReduceRingRequest(commId=init.commId, count=nelem * 4),
+                                    metadata=(("dmlp-algo", "twoshot"),)).success
+        for i in ids:
+            assert np.abs(d2h(i, 0x1000) - s).max() < 1e-4
+        # 4. auto: the dispatcher table decides (same answer either way), a group of two launches, one wait
+        for i, g in zip(ids, grads):
+            h2d(i, 0x1000, g.tobytes())
+        assert client.GroupStart(pb.GroupStartRequest(commId=init.commId)).success
+        for _ in range(2):
+            assert client.AllReduceRing(pb.AllReduceRingRequest(commId=init.commId, count=nelem * 4)).success
+        assert client.GroupEnd(pb.GroupEndRequest(commId=init.commId)).success
+        for i in ids:
+            assert np.abs(d2h(i, 0x1000) - n * s).max() < 1e-3 * n
+        # 5. a larger rewrite of the address leaves the slot; the next collective places it again
+        big = [rng.standard_normal(2 * nelem).astype(np.float32) for _ in ids]
+        for i, g in zip(ids, big):
+            h2d(i, 0x1000, g.tobytes())
+        assert client.AllReduceRing(pb.AllReduceRingRequest(commId=init.commId, count=2 * nelem * 4),
+                                    metadata=(("dmlp-algo", "nvls"),)).success
+        sb = np.sum(np.stack(big).astype(np.float64), axis=0)
+        for i in ids:
+            assert np.abs(d2h(i, 0x1000) - sb).max() < 1e-4
+        # 6. destroying the communicator moves the data back to private memory: still readable through the device
+        assert client.CommDestroy(pb.CommDestroyRequest(commId=init.commId)).success
+        for d in devs:
+            be = d.service.backend
+            got = np.frombuffer(be.read(0x1000), np.float32)
+            assert np.abs(got - sb).max() < 1e-4
+    finally:
+        coord.stop()
+        for d in devs:
+            d.stop()
+            d.service.backend.close()
