@@ -9,6 +9,8 @@
 
 #include "../include/dmlp_b200.h"
 
+#include "wgrad_rs.h"
+
 namespace dmlp {
 
 // Epilogue transpose patch: 32 rows x 32 fp32 columns per epilogue warp, rows padded to 36 floats so that
@@ -49,6 +51,24 @@ struct GemmParams {
   float* ce_logits;
   float* ce_loss_sum;
   int* ce_correct;
+  // reduce-scatter epilogue (data-parallel weight gradients, E2 plans only): instead of storing the tile into out_f32,
+  // every 4 KiB staging chunk is pushed by the bulk copy engine into the slot [my rank][tile / world] of the tile's
+  // OWNER (rank tile % world; peer-mapped memory, own rank included) and the owner's arrival counter of that
+  // (source, tile) is bumped once per epilogue warp. Four more warps of the same CTAs (wgrad_rs.cuh) consume the tiles
+  // this rank owns: rsq.
+  int rs_world;  // 0: off
+  int rs_rank;
+  int rs_tiles_per_owner;
+  float* rs_slot[8];
+  uint32_t* rs_count[8];
+  RsReduceParams rsq;
+};
+
+// Geometry a consumer of the reduce-scatter epilogue needs to find a chunk's place in the output matrix.
+struct GemmRsGeometry {
+  int tm, bn, subs;  // tile rows (128 per CTA of a pair), tile columns, CTAs per tile
+  int tiles_m, tiles_n, raster_g, total_tiles;
+  int grid;          // CTAs of the GEMM launch
 };
 
 struct GemmPlan {
@@ -63,5 +83,12 @@ struct GemmPlan {
 
 int gemm_plan_create(const dmlp_gemm_desc_t* desc, GemmPlan* plan);
 int gemm_plan_run(const GemmPlan* plan, cudaStream_t stream);
+// True when the plan's epilogue can push whole tiles to their owners (TMA-store epilogue, fp32 output, no partial tiles,
+// tiles divisible among the ranks).
+bool gemm_plan_rs_eligible(const GemmPlan* plan, int world);
+// Switches the plan to the reduce-scatter epilogue. slots[r] / counts[r]: rank r's slot area and counters as mapped on
+// this device. Shrinks the shared-memory ring so that a small consumer CTA fits on the same SM.
+int gemm_plan_enable_rs(GemmPlan* plan, int world, int rank, float* const* slots, uint32_t* const* counts,
+                        GemmRsGeometry* geo);
 
 }  // namespace dmlp

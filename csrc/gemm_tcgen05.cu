@@ -16,6 +16,7 @@
 // (:173-175, :197-199).
 #include "common.h"
 #include "gemm_plan.h"
+#include "wgrad_rs.cuh"
 #include "ptx_sm100.cuh"
 
 #include <stdlib.h>
@@ -28,6 +29,7 @@ namespace dmlp {
 
 constexpr int kMaxStages = 8;
 constexpr int kGemmThreads = 192;    // producer + MMA + 4 epilogue warps
+constexpr int kGemmThreadsRS = 448;  // ... + 4 consumer warps (reduce-scatter epilogue, wgrad_rs.cuh)
 constexpr int kGemmThreadsE2 = 320;  // producer + MMA + 8 epilogue warps (TMA-store epilogue)
 constexpr uint32_t kE2StageBytes = 8 * 4096;  // one 32-row x 128 B staging buffer per epilogue warp
 
@@ -45,10 +47,14 @@ __device__ unsigned long long g_gemm_prof[kProfTiles * 16];
 
 // TWO: CTA pairs (cluster of 2) run tcgen05.mma.cta_group::2 on 256 x block_n tiles: each CTA stages its 128 rows of A
 // and HALF of the B tile, which halves the shared-memory fill + read traffic per SM that bounds the 1-CTA mainloop.
-template <int EB, bool A_MN, bool B_MN, bool TWO, bool E2>
-__global__ void __launch_bounds__(E2 ? kGemmThreadsE2 : kGemmThreads, 1)
+// E2M: 0 = four epilogue warps, generic epilogue; 1 = eight epilogue warps, TMA-store epilogue; 2 = eight epilogue warps,
+// reduce-scatter epilogue (fp32 tiles pushed to their owner ranks; a leaner instantiation: see gemm_plan_enable_rs).
+template <int EB, bool A_MN, bool B_MN, bool TWO, int E2M>
+__global__ void __launch_bounds__(E2M == 2 ? kGemmThreadsRS : E2M ? kGemmThreadsE2 : kGemmThreads, 1)
 gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
-                    const __grid_constant__ CUtensorMap tmC, const GemmParams p) {
+                    const __grid_constant__ CUtensorMap tmC, const __grid_constant__ GemmParams p) {
+  constexpr bool E2 = E2M != 0;
+  constexpr bool RS = E2M == 2;
   constexpr int BM = 128;
   constexpr int KS = 128 / EB;            // K elements per pipeline stage (one 128 B swizzle row)
   constexpr int UK = 32 / EB;             // K elements per tcgen05.mma
@@ -74,6 +80,8 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
   __shared__ float s_part_raw[E2 ? 1 : 4][256];  // per-epilogue-warp column partials (E2 plans have no column sums:
   auto s_part = [&](int w) -> float* { return s_part_raw[E2 ? 0 : w]; };  // their code is never reached there)
   __shared__ float s_loss[4];
+  __shared__ int s_rs_fail;
+  __shared__ uint32_t s_rs_epoch;
   __shared__ int s_hit[4];
 
   // Warp index through a shuffle: the compiler then knows the role branches below are warp-uniform and
@@ -232,6 +240,9 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
         }
       }
     }
+  } else if (RS && warp >= 10) {
+    // ------------------------------------------------------------ consumer warps of the reduce-scatter epilogue
+    if constexpr (RS) rs_consume(p.rsq, static_cast<int>(threadIdx.x) - kGemmThreadsE2, &s_rs_fail, &s_rs_epoch);
   } else {
     // ------------------------------------------------------------ epilogue warps
     const int q = warp & 3;  // TMEM lane quadrant this warp may access
@@ -266,7 +277,7 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
       } else {
         handled = true;
         constexpr int CH = 128 / 4;                       // fp32 accumulator columns per fp32 chunk ...
-        const bool ob = p.out_bf16 != nullptr;            // ... twice that per bf16 chunk
+        const bool ob = !RS && p.out_bf16 != nullptr;     // ... twice that per bf16 chunk
         const int chunk = ob ? 2 * CH : CH;
         const int ncols = p.block_n >> 1;
         const int cbase = ((warp - 2) >> 2) * ncols;
@@ -276,6 +287,16 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
         const uint32_t t_row = tmem_base + buf * p.tmem_buf_cols + (static_cast<uint32_t>(q * 32) << 16);
         const uint32_t wrow = e2buf + lane * 128;
         const uint32_t sw = static_cast<uint32_t>(lane & 7);
+        // reduce-scatter epilogue: this CTA's half of slot [my rank][tile / world] at the tile's owner, chunk by chunk
+        // (chunk id = (column half * chunks per half + chunk) * 4 + lane quadrant; 4 KiB each, kept 128B-swizzled)
+        float* rs_dst = nullptr;
+        if constexpr (RS) {
+          const int owner = tile % p.rs_world, jt = tile / p.rs_world;
+          rs_dst = p.rs_slot[owner] +
+                   (static_cast<size_t>(p.rs_rank) * p.rs_tiles_per_owner + jt) * (static_cast<size_t>(TM) * p.block_n) +
+                   static_cast<size_t>(crank) * BM * p.block_n +
+                   (static_cast<size_t>((warp - 2) >> 2) * (ncols / CH) * 4 + q) * 1024;
+        }
         for (int c = 0; c < ncols; c += chunk) {
           const int col = cbase + c;
           float v[64];
@@ -326,9 +347,24 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
           fence_proxy_async_smem();
           __syncwarp();
           if (elect_one()) {  // (converged warp: always the same lane, which also owns the bulk group)
-            tma_store_2d(&tmC, smem + p.epi_stage_off + static_cast<size_t>(warp - 2) * 4096u, n0 + col, m0 + q * 32);
+            if constexpr (RS) {
+              asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], 4096;" ::"l"(rs_dst + static_cast<size_t>(c / CH) * 4096),
+                           "r"(e2buf) : "memory");
+            } else {
+              tma_store_2d(&tmC, smem + p.epi_stage_off + static_cast<size_t>(warp - 2) * 4096u, n0 + col, m0 + q * 32);
+            }
             tma_store_commit();
           }
+        }
+        if constexpr (RS) {
+          if (elect_one()) {
+            tma_store_wait<0>();  // my chunks of this tile have been written ...
+            asm volatile("fence.proxy.async;" ::: "memory");
+            __threadfence_system();  // ... and are ordered before the owner sees the counter move
+            uint32_t* cnt = p.rs_count[tile % p.rs_world] + static_cast<size_t>(p.rs_rank) * p.rs_tiles_per_owner + tile / p.rs_world;
+            asm volatile("red.relaxed.sys.global.add.u32 [%0], 1;" ::"l"(cnt) : "memory");
+          }
+          __syncwarp();
         }
         if (warp == 2) GPROF(6, tcount);
       }
@@ -805,11 +841,11 @@ int make_tensor_map_2d(CUtensorMap* out, const void* base, int elem_bytes, bool 
   return DMLP_OK;
 }
 
-template <int EB, bool A_MN, bool B_MN, bool TWO, bool E2>
+template <int EB, bool A_MN, bool B_MN, bool TWO, int E2>
 static int launch_gemm_t(const CUtensorMap& tmA, const CUtensorMap& tmB, const CUtensorMap& tmC, const GemmParams& p,
                          dim3 grid, size_t smem_bytes, cudaStream_t stream) {
   auto kern = gemm_tcgen05_kernel<EB, A_MN, B_MN, TWO, E2>;
-  constexpr int kThreads = E2 ? kGemmThreadsE2 : kGemmThreads;
+  constexpr int kThreads = E2 == 2 ? kGemmThreadsRS : E2 ? kGemmThreadsE2 : kGemmThreads;
   // devices on which the smem opt-in has been applied (gRPC worker threads launch GEMMs on different devices at once)
   static std::atomic<unsigned long long> attr_mask{0};
   int dev = 0;
@@ -853,8 +889,11 @@ static int launch_gemm_t(const CUtensorMap& tmA, const CUtensorMap& tmB, const C
 
 template <int EB, bool A_MN, bool B_MN, bool TWO = false>
 static int launch_gemm(const GemmPlan* pl, dim3 grid, cudaStream_t stream) {
-  if (pl->p.epi2) return launch_gemm_t<EB, A_MN, B_MN, TWO, true>(pl->tmA, pl->tmB, pl->tmC, pl->p, grid, pl->smem, stream);
-  return launch_gemm_t<EB, A_MN, B_MN, TWO, false>(pl->tmA, pl->tmB, pl->tmA, pl->p, grid, pl->smem, stream);
+  if constexpr (A_MN && B_MN) {  // (weight gradients: both operands MN-major)
+    if (pl->p.rs_world > 0) return launch_gemm_t<EB, A_MN, B_MN, TWO, 2>(pl->tmA, pl->tmB, pl->tmC, pl->p, grid, pl->smem, stream);
+  }
+  if (pl->p.epi2) return launch_gemm_t<EB, A_MN, B_MN, TWO, 1>(pl->tmA, pl->tmB, pl->tmC, pl->p, grid, pl->smem, stream);
+  return launch_gemm_t<EB, A_MN, B_MN, TWO, 0>(pl->tmA, pl->tmB, pl->tmA, pl->p, grid, pl->smem, stream);
 }
 
 static int ceil_div(int a, int b) { return (a + b - 1) / b; }
@@ -1001,6 +1040,41 @@ int dmlp::gemm_plan_create(const dmlp_gemm_desc_t* d, GemmPlan* plan) {
   return DMLP_OK;
 }
 
+bool dmlp::gemm_plan_rs_eligible(const GemmPlan* plan, int world) {
+  const GemmParams& p = plan->p;
+  const int tm = (plan->key & 8) ? 256 : 128;
+  return world >= 2 && world <= 8 && p.epi2 && (plan->key & 3) == 3 && p.out_f32 != nullptr && p.out_bf16 == nullptr && p.M % tm == 0 &&
+         p.N % p.block_n == 0 && (p.block_n / 2) % 32 == 0 && plan->total_tiles % world == 0 &&
+         plan->total_tiles >= plan->grid_x / ((plan->key & 8) ? 2 : 1);
+}
+
+int dmlp::gemm_plan_enable_rs(GemmPlan* plan, int world, int rank, float* const* slots, uint32_t* const* counts,
+                              GemmRsGeometry* geo) {
+  DMLP_REQUIRE(plan && slots && counts && geo && rank >= 0 && rank < world, "gemm_plan_enable_rs: bad arguments");
+  DMLP_REQUIRE(gemm_plan_rs_eligible(plan, world), "gemm_plan_enable_rs: the plan cannot push whole tiles to %d owners", world);
+  GemmParams& p = plan->p;
+  const bool two = (plan->key & 8) != 0;
+  p.rs_world = world;
+  p.rs_rank = rank;
+  p.rs_tiles_per_owner = plan->total_tiles / world;
+  for (int r = 0; r < 8; ++r) {
+    p.rs_slot[r] = r < world ? slots[r] : nullptr;
+    p.rs_count[r] = r < world ? counts[r] : nullptr;
+    DMLP_REQUIRE(r >= world || (p.rs_slot[r] && p.rs_count[r]), "gemm_plan_enable_rs: rank %d is not mapped", r);
+  }
+  p.pdl = 0;
+  { const char* pe = getenv("DMLP_RS_PROF"); if (pe && atoi(pe) > 0) p.prof = 1; }
+  geo->tm = two ? 256 : 128;
+  geo->bn = p.block_n;
+  geo->subs = two ? 2 : 1;
+  geo->tiles_m = p.M / geo->tm;
+  geo->tiles_n = p.N / p.block_n;
+  geo->raster_g = p.raster_g;
+  geo->total_tiles = plan->total_tiles;
+  geo->grid = plan->grid_x;
+  return DMLP_OK;
+}
+
 int dmlp::gemm_plan_run(const GemmPlan* plan, cudaStream_t st) {
   const dim3 grid(plan->grid_x, plan->grid_y);
   switch (plan->key) {
@@ -1028,6 +1102,13 @@ extern "C" int dmlp_gemm(const dmlp_gemm_desc_t* d, void* stream) {
   int rc = gemm_plan_create(d, &plan);
   if (rc) return rc;
   return gemm_plan_run(&plan, as_stream(stream));
+}
+
+// Debug: the consumer warps' per-CTA timeline of the most recent reduce-scatter GEMM (DMLP_RS_PROF=1), 148 x 4 stamps.
+extern "C" int dmlp_wgrad_rs_prof_read(unsigned long long* host, int n_words) {
+  DMLP_REQUIRE(host != nullptr && n_words > 0 && n_words <= 148 * 4, "dmlp_wgrad_rs_prof_read: bad arguments");
+  DMLP_CUDA_CHECK(cudaMemcpyFromSymbol(host, dmlp::g_rs_prof, sizeof(unsigned long long) * n_words));
+  return DMLP_OK;
 }
 
 // Debug: copies the per-tile timeline of CTA 0 of the most recent profiled GEMM (DMLP_GEMM_PROF=1) to the host.

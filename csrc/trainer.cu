@@ -14,6 +14,7 @@
 // backward continues (layer-by-layer overlap).
 #include "common.h"
 #include "gemm_plan.h"
+#include "wgrad_rs.h"
 
 #include <string.h>
 
@@ -120,6 +121,14 @@ struct Trainer {
   bool direct = false;     // batch fits one M tile: reductions are stored, no zeroing needed
   cudaStream_t s_aux = nullptr;  // wgrad branch (runs beside the dgrad chain)
   cudaEvent_t ev_dz[kMaxLayers], ev_aux_done;
+  // wgrad -> reduce-scatter -> SGD -> all-gather pipeline of the large layers (wgrad_rs.cuh): the layer's wgrad GEMM pushes
+  // its tiles to their owners; consumer warps of the same kernel reduce, update and broadcast the tiles this rank owns
+  bool emulated = false;
+  bool rs_on[kMaxLayers] = {};
+  int rs_layers = 0;
+  RsReduceParams rs[2][kMaxLayers];
+  int rs_grid[kMaxLayers] = {};
+  cudaEvent_t ev_rs = nullptr, ev_rs_comm = nullptr;
   int kernels_per_step = 0;
   long long launches_last_run = 0;  // kernel launches of the most recent run (fused path: a launch may cover several steps)
   unsigned long long steps_done = 0;
@@ -137,6 +146,73 @@ static int dev_alloc(Trainer* t, size_t bytes, void** out) {
     int _rc = (expr);    \
     if (_rc) return _rc; \
   } while (0)
+
+// Picks the layers whose weight gradient goes through the fused wgrad -> reduce-scatter -> SGD -> all-gather pipeline
+// (layer-by-layer overlap on a real multi-GPU communicator, big layers whose tiles divide among the ranks) and rewires
+// their wgrad plans. DMLP_WGRAD_RS=0 turns it off, DMLP_WGRAD_RS_MIN_KB moves the size threshold (default 8 MiB).
+static int setup_wgrad_rs(Trainer* t) {
+  const ParamLayout& L = t->lay;
+  t->rs_layers = 0;
+  for (int l = 0; l < kMaxLayers; ++l) t->rs_on[l] = false;
+  if (t->comm == nullptr || t->nvls || t->cfg.overlap == 0 || t->fused_step || t->emulated) return DMLP_OK;
+  const char* e = getenv("DMLP_WGRAD_RS");
+  if (e && atoi(e) == 0) return DMLP_OK;
+  const char* mk = getenv("DMLP_WGRAD_RS_MIN_KB");
+  const size_t min_bytes = (mk ? static_cast<size_t>(atol(mk)) : 8192u) * 1024u;
+  for (int r = 0; r < t->world; ++r)
+    if (!t->peer_grads[0][r] || !t->peer_grads[1][r] || !t->peer_params[r] || (t->bf16 && !t->peer_shadow[r])) return DMLP_OK;
+  uint32_t* pads[DMLP_MAX_RANKS];
+  uint32_t *state = nullptr, *host_flags = nullptr, dead = 0;
+  unsigned long long timeout_ns = 0;
+  int crank = 0, cworld = 0, cdev = 0;
+  TRY(dmlp_comm_internal_view(t->comm, t->local_idx, pads, &state, &host_flags, &timeout_ns, &dead, &crank, &cworld, &cdev));
+  int used = 0;
+  for (int l = 0; l < L.L; ++l) {
+    const size_t wbytes = static_cast<size_t>(L.in[l]) * L.out_pad[l] * 4;
+    if (wbytes < min_bytes || !gemm_plan_rs_eligible(&t->wgrad[0][l], t->world)) continue;
+    const int words = kRsCounts + (t->wgrad[0][l].total_tiles + 15) / 16 * 16;
+    if (used + words > kPadRsWords) continue;
+    for (int par = 0; par < 2; ++par) {
+      float* slots[DMLP_MAX_RANKS];
+      uint32_t* counts[DMLP_MAX_RANKS];
+      for (int r = 0; r < t->world; ++r) {
+        slots[r] = t->peer_grads[par][r] + L.w_off[l];
+        counts[r] = pads[r] + kPadRsBase + used + kRsCounts;
+      }
+      GemmRsGeometry g;
+      TRY(gemm_plan_enable_rs(&t->wgrad[par][l], t->world, t->rank, slots, counts, &g));
+      RsReduceParams& a = t->rs[par][l];
+      memset(&a, 0, sizeof(a));
+      a.world = t->world; a.rank = t->rank;
+      a.ld = L.out_pad[l];
+      a.tm = g.tm; a.bn = g.bn; a.subs = g.subs;
+      a.tiles_m = g.tiles_m; a.tiles_n = g.tiles_n; a.raster_g = g.raster_g;
+      a.tiles_per_owner = g.total_tiles / t->world;
+      a.slots = slots[t->rank];
+      a.counts = counts[t->rank];
+      a.per_tile = 8u * static_cast<uint32_t>(g.subs);
+      for (int r = 0; r < t->world; ++r) {
+        a.w[r] = t->peer_params[r] + L.w_off[l];
+        a.w16[r] = t->bf16 ? static_cast<__nv_bfloat16*>(t->peer_shadow[r]) + L.w_off[l] : nullptr;
+        a.done[r] = pads[r] + kPadRsBase + used + kRsDone;
+        a.pad[r] = pads[r];
+      }
+      a.lr = t->lr_dev;
+      a.scale = 1.f / static_cast<float>(t->world);
+      a.epoch = pads[t->rank] + kPadRsBase + used + kRsEpoch;
+      a.status = host_flags + 4;
+      a.timeout_ns = timeout_ns ? timeout_ns : 10ull * 1000 * 1000 * 1000;
+      { const char* pe = getenv("DMLP_RS_PROF"); a.prof = (pe && atoi(pe) > 0) ? 1 : 0; }
+      t->wgrad[par][l].p.rsq = a;
+    }
+    t->rs_on[l] = true;
+    ++t->rs_layers;
+    used += words;
+  }
+  // counters start from zero for this trainer (the ranks meet in a barrier before the first step)
+  if (t->rs_layers > 0) DMLP_CUDA_CHECK(cudaMemset(pads[t->rank] + kPadRsBase, 0, sizeof(uint32_t) * kPadRsWords));
+  return DMLP_OK;
+}
 
 // Builds every GEMM plan (TMA descriptors included) for both input parities.
 static int build_plans(Trainer* t) {
@@ -191,6 +267,7 @@ static int build_plans(Trainer* t) {
       TRY(gemm_plan_create(&d, &t->wgrad[par][l]));
     }
   }
+  TRY(setup_wgrad_rs(t));
   for (int l = 1; l < L.L; ++l) {
     // ---- dgrad: dZ_{l-1} = (dZ_l . W_l^T) * (act_{l-1} > 0); column sums -> db_{l-1} (set per parity at launch)
     dmlp_gemm_desc_t d;
@@ -374,15 +451,23 @@ static int enqueue_step(Trainer* t, int par, bool count_kernels) {
     // dZ_l is ready on S: the wgrad branch may start
     DMLP_CUDA_CHECK(cudaEventRecord(t->ev_dz[l], S));
     DMLP_CUDA_CHECK(cudaStreamWaitEvent(A, t->ev_dz[l], 0));
-    TRY(gemm_plan_run(&t->wgrad[par][l], A));
-    ++nk;
+    if (!t->rs_on[l]) {  // (the pipelined layers run their wgrad last: see below)
+      TRY(gemm_plan_run(&t->wgrad[par][l], A));
+      ++nk;
+    }
     if (l > 0) {
       GemmPlan pl = t->dgrad[l];
       pl.p.colsum = t->grads[par] + L.b_off[l - 1];
       TRY(gemm_plan_run(&pl, S));
       ++nk;
     }
-    if (overlap) {
+    if (overlap && t->rs_on[l]) {
+      // only the bias goes through the bucket all-reduce (its gradient came from the producer of dZ_l)
+      const size_t hi = (l + 1 < L.L) ? L.w_off[l + 1] : L.total;
+      DMLP_CUDA_CHECK(cudaStreamWaitEvent(t->s_comm, t->ev_dz[l], 0));
+      TRY(enqueue_allreduce(t, par, L.b_off[l], hi - L.b_off[l], t->s_comm));
+      ++nk;
+    } else if (overlap) {
       // bucket l = [W_l | b_l]: needs wgrad_l (A) and dgrad_l (S, it reads W_l which the fused SGD rewrites);
       // b_l came from the producer of dZ_l, which precedes both.
       const size_t lo = L.w_off[l];
@@ -395,6 +480,32 @@ static int enqueue_step(Trainer* t, int par, bool count_kernels) {
       }
       TRY(enqueue_allreduce(t, par, lo, hi - lo, t->s_comm));
       ++nk;
+    }
+  }
+  if (overlap && t->rs_layers > 0) {
+    // Pipelined layers: wgrad GEMM with the reduce-scatter epilogue, then its consumer, after every dgrad of this step
+    // (a pushed tile tells the peers that this rank no longer reads the layer's weights). The GEMMs of one step run one
+    // after the other anyway (each fills the GPU); putting the big weight gradient last lets its whole exchange hide
+    // behind its own tensor-core time.
+    uint32_t* pads[DMLP_MAX_RANKS];
+    uint32_t *state = nullptr, *host_flags = nullptr, dead = 0;
+    unsigned long long timeout_ns = 0;
+    int crank = 0, cworld = 0, cdev = 0;
+    TRY(dmlp_comm_internal_view(t->comm, t->local_idx, pads, &state, &host_flags, &timeout_ns, &dead, &crank, &cworld, &cdev));
+    DMLP_CUDA_CHECK(cudaEventRecord(t->ev_rs, S));
+    DMLP_CUDA_CHECK(cudaStreamWaitEvent(A, t->ev_rs, 0));
+    // ... and after every bucket all-reduce of this step has COMPLETED. Both kinds of kernel wait for their peers: if one
+    // rank's GPU ran the all-reduce first (its CTAs spinning at the entry barrier, keeping some of the GEMM's persistent CTAs
+    // off their SMs) while the other ran the GEMM first (all SMs taken, its all-reduce not yet scheduled), each side would
+    // wait for a kernel the other cannot start. Kernels that wait for peers never overlap each other here.
+    DMLP_CUDA_CHECK(cudaEventRecord(t->ev_rs_comm, t->s_comm));
+    DMLP_CUDA_CHECK(cudaStreamWaitEvent(A, t->ev_rs_comm, 0));
+    if (!((dead >> t->rank) & 1u)) {  // (a rank marked dead goes silent: the survivors' watchdogs report it)
+      for (int l = last; l >= 0; --l) {
+        if (!t->rs_on[l]) continue;
+        TRY(gemm_plan_run(&t->wgrad[par][l], A));  // (GEMM + reduce-scatter + SGD + all-gather: one kernel)
+        ++nk;
+      }
     }
   }
   if (overlap) {
@@ -611,6 +722,8 @@ extern "C" int dmlp_trainer_destroy(dmlp_trainer_t h) {
   if (t->ev_join) cudaEventDestroy(t->ev_join);
   if (t->ev_fork) cudaEventDestroy(t->ev_fork);
   if (t->ev_aux_done) cudaEventDestroy(t->ev_aux_done);
+  if (t->ev_rs) cudaEventDestroy(t->ev_rs);
+  if (t->ev_rs_comm) cudaEventDestroy(t->ev_rs_comm);
   for (int l = 0; l < kMaxLayers; ++l)
     if (t->ev_dz[l]) cudaEventDestroy(t->ev_dz[l]);
   for (int l = 0; l < kMaxLayers; ++l)
@@ -738,6 +851,7 @@ extern "C" int dmlp_trainer_create(const dmlp_trainer_config_t* cfg, int device,
     // default for the cluster-fused shapes on real multi-GPU communicators; fused == 1 keeps the two-kernel chain.
     int emulated = 0;
     TRYF(dmlp_comm_is_emulated(t->comm, &emulated));
+    t->emulated = emulated != 0;
     t->pdp = t->fused_step && !emulated && (cfg->fused == 4 || cfg->fused == -1);
     for (int r = 0; r < world; ++r) t->pdp = t->pdp && t->peer_grads[0][r] != nullptr;
     t->xchg = t->fused_step && cfg->fused == 3;
@@ -794,6 +908,8 @@ extern "C" int dmlp_trainer_create(const dmlp_trainer_config_t* cfg, int device,
   CUF(cudaEventCreateWithFlags(&t->ev_join, cudaEventDisableTiming));
   CUF(cudaEventCreateWithFlags(&t->ev_fork, cudaEventDisableTiming));
   CUF(cudaEventCreateWithFlags(&t->ev_aux_done, cudaEventDisableTiming));
+  CUF(cudaEventCreateWithFlags(&t->ev_rs, cudaEventDisableTiming));
+  CUF(cudaEventCreateWithFlags(&t->ev_rs_comm, cudaEventDisableTiming));
   for (int l = 0; l < L.L; ++l) CUF(cudaEventCreateWithFlags(&t->ev_dz[l], cudaEventDisableTiming));
   for (int l = 0; l < L.L; ++l) CUF(cudaEventCreateWithFlags(&t->ev_bucket[l], cudaEventDisableTiming));
   if (t->fused_step) {
@@ -874,6 +990,14 @@ extern "C" int dmlp_trainer_state(dmlp_trainer_t h, int* failed, int* mode) {
   DMLP_REQUIRE(t, "null trainer");
   if (failed) *failed = t->failed ? 1 : 0;
   if (mode) *mode = t->gx ? 5 : t->pdp ? 4 : t->xchg ? 3 : (t->fused_step && t->comm) ? 1 : 0;
+  return DMLP_OK;
+}
+
+// Layers whose weight gradient runs through the wgrad -> reduce-scatter -> SGD -> all-gather pipeline (wgrad_rs.cuh).
+extern "C" int dmlp_trainer_pipelined_layers(dmlp_trainer_t h, int* n) {
+  Trainer* t = reinterpret_cast<Trainer*>(h);
+  DMLP_REQUIRE(t && n, "bad arguments");
+  *n = t->rs_layers;
   return DMLP_OK;
 }
 

@@ -103,6 +103,7 @@ def _declare(lib) -> None:
         "dmlp_trainer_buffer": [vp, i32, i32, C.POINTER(vp)],
         "dmlp_trainer_set_fault": [vp, C.c_longlong],
         "dmlp_trainer_state": [vp, C.POINTER(i32), C.POINTER(i32)],
+        "dmlp_trainer_pipelined_layers": [vp, C.POINTER(i32)],
     }
     for name, args in sigs.items():
         fn = getattr(lib, name)
@@ -282,6 +283,14 @@ class Trainer:
 
     def set_lr(self, lr: float) -> None:
         native.check(self.lib.dmlp_trainer_set_lr(self._h, float(lr)))
+
+    @property
+    def pipelined_layers(self) -> int:
+        """Layers whose weight gradient goes through the fused wgrad GEMM -> reduce-scatter -> SGD -> all-gather
+        pipeline (``csrc/wgrad_rs.cuh``) instead of a bucket all-reduce."""
+        n = C.c_int32()
+        native.check(self.lib.dmlp_trainer_pipelined_layers(self._h, C.byref(n)))
+        return n.value
 
     @property
     def kernels_per_step(self) -> int:

@@ -411,6 +411,9 @@ int dmlp_trainer_launches_last_run(dmlp_trainer_t t, long long* n);
  * gpu_coordinator_server.go:281-285); mode = data-parallel variant in use (5 = global-batch mode). */
 int dmlp_trainer_set_fault(dmlp_trainer_t trainer, long long step);
 int dmlp_trainer_state(dmlp_trainer_t trainer, int* failed, int* mode);
+/* Layers whose weight gradient is exchanged by the GEMM's reduce-scatter epilogue and its consumer kernel (multi-GPU,
+ * overlap on, big layers; DMLP_WGRAD_RS=0 disables, DMLP_WGRAD_RS_MIN_KB sets the size threshold, default 8192). */
+int dmlp_trainer_pipelined_layers(dmlp_trainer_t trainer, int* n);
 int dmlp_trainer_run(dmlp_trainer_t t, const float* x_host, const int32_t* y_host, size_t num_batches,
                      size_t first_batch, size_t batch_stride, int steps, const float* lr_schedule,
                      float* metrics_out, int use_graph, void* start_event, void* stop_event);

@@ -66,7 +66,7 @@ def test_graft_entry_build_is_importable_and_links():
     for sym in ("dmlp_gemm", "dmlp_allreduce", "dmlp_allreduce_nvls", "dmlp_mlp_fused_steps", "dmlp_trainer_run",
                 "dmlp_allreduce_sum_f32_noalloc", "dmlp_comm_is_emulated", "dmlp_gemm_prof_read",
                 "dmlp_allreduce_noalloc_status", "dmlp_mlp_fused_steps_gx", "dmlp_mlp_fused_set_fault", "dmlp_input_exchange",
-                "dmlp_trainer_set_fault", "dmlp_trainer_state", "dmlp_allreduce_pick_algo_ex"):
+                "dmlp_trainer_set_fault", "dmlp_trainer_state", "dmlp_allreduce_pick_algo_ex", "dmlp_trainer_pipelined_layers"):
         assert hasattr(lib, sym), sym
 
 

@@ -84,6 +84,17 @@ def test_torchrun_global_batch_mode_oracle_soak_and_rank_failure():
 
 
 @needs2
+def test_torchrun_wgrad_reduce_scatter_pipeline():
+    """wgrad GEMM with the reduce-scatter epilogue + its consumer kernel against the unfused GEMM + bucket all-reduce,
+    both precisions, graph and eager; then a rank that dies mid-run."""
+    n = min(_ngpu(), 8)
+    cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", f"--nproc-per-node={n}",
+           "--master-addr", "127.0.0.1", "--master-port", "29623", os.path.join(ROOT, "tests", "mp_rs_worker.py")]
+    r = subprocess.run(cmd, capture_output=True, text=True, timeout=600, cwd=ROOT)
+    assert r.returncode == 0 and "MP_RS_OK" in r.stdout, r.stdout[-3000:] + r.stderr[-3000:]
+
+
+@needs2
 def test_single_process_nvls_allreduce():
     """In-switch reduction through the multicast address (skipped when the fabric has no multicast)."""
     from dmlp_b200.runtime import native
