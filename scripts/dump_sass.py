@@ -9,10 +9,11 @@ SO = os.path.join(ROOT, "distributed-machine-learning-pipeline_b200", "_native",
 OUT = os.path.join(ROOT, "profiles", "sass")
 
 PICK = {  # listing name -> regex on the mangled kernel name
-    "gemm_tcgen05_tf32_fwd.sass": r"gemm_tcgen05_kernelILi4ELb0ELb1ELb0ELb0E",
-    "gemm_tcgen05_bf16_wgrad.sass": r"gemm_tcgen05_kernelILi2ELb1ELb1ELb0ELb0E",
-    "gemm_tcgen05_bf16_fwd_cta_pair.sass": r"gemm_tcgen05_kernelILi2ELb0ELb1ELb1ELb0E",
-    "gemm_tcgen05_bf16_fwd_cta_pair_tma_store.sass": r"gemm_tcgen05_kernelILi2ELb0ELb1ELb1ELb1E",
+    "gemm_tcgen05_tf32_fwd.sass": r"gemm_tcgen05_kernelILi4ELb0ELb1ELb0ELi0E",
+    "gemm_tcgen05_bf16_wgrad.sass": r"gemm_tcgen05_kernelILi2ELb1ELb1ELb0ELi0E",
+    "gemm_tcgen05_bf16_fwd_cta_pair.sass": r"gemm_tcgen05_kernelILi2ELb0ELb1ELb1ELi0E",
+    "gemm_tcgen05_bf16_fwd_cta_pair_tma_store.sass": r"gemm_tcgen05_kernelILi2ELb0ELb1ELb1ELi1E",
+    "gemm_tcgen05_bf16_wgrad_cta_pair_reduce_scatter.sass": r"gemm_tcgen05_kernelILi2ELb1ELb1ELb1ELi2E",
     "mlp_fused_step_16_8.sass": r"mlp_fused_step_kernelILi16ELi8ELb0E",
     "mlp_fused_step_16_8_global_batch.sass": r"mlp_fused_step_kernelILi16ELi8ELb1E",
     "input_exchange.sass": r"input_exchange_kernel",
