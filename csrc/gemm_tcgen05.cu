@@ -1044,8 +1044,7 @@ bool dmlp::gemm_plan_rs_eligible(const GemmPlan* plan, int world) {
   const GemmParams& p = plan->p;
   const int tm = (plan->key & 8) ? 256 : 128;
   return world >= 2 && world <= 8 && p.epi2 && (plan->key & 3) == 3 && p.out_f32 != nullptr && p.out_bf16 == nullptr && p.M % tm == 0 &&
-         p.N % p.block_n == 0 && (p.block_n / 2) % 32 == 0 && plan->total_tiles % world == 0 &&
-         plan->total_tiles >= plan->grid_x / ((plan->key & 8) ? 2 : 1);
+         p.N % p.block_n == 0 && (p.block_n / 2) % 32 == 0 && plan->total_tiles % world == 0;
 }
 
 int dmlp::gemm_plan_enable_rs(GemmPlan* plan, int world, int rank, float* const* slots, uint32_t* const* counts,

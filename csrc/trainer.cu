@@ -126,8 +126,6 @@ struct Trainer {
   bool emulated = false;
   bool rs_on[kMaxLayers] = {};
   int rs_layers = 0;
-  RsReduceParams rs[2][kMaxLayers];
-  int rs_grid[kMaxLayers] = {};
   cudaEvent_t ev_rs = nullptr, ev_rs_comm = nullptr;
   int kernels_per_step = 0;
   long long launches_last_run = 0;  // kernel launches of the most recent run (fused path: a launch may cover several steps)
@@ -181,7 +179,7 @@ static int setup_wgrad_rs(Trainer* t) {
       }
       GemmRsGeometry g;
       TRY(gemm_plan_enable_rs(&t->wgrad[par][l], t->world, t->rank, slots, counts, &g));
-      RsReduceParams& a = t->rs[par][l];
+      RsReduceParams a;
       memset(&a, 0, sizeof(a));
       a.world = t->world; a.rank = t->rank;
       a.ld = L.out_pad[l];
@@ -483,7 +481,7 @@ static int enqueue_step(Trainer* t, int par, bool count_kernels) {
     }
   }
   if (overlap && t->rs_layers > 0) {
-    // Pipelined layers: wgrad GEMM with the reduce-scatter epilogue, then its consumer, after every dgrad of this step
+    // Pipelined layers: wgrad GEMM with the reduce-scatter epilogue and its consumer warps, after every dgrad of this step
     // (a pushed tile tells the peers that this rank no longer reads the layer's weights). The GEMMs of one step run one
     // after the other anyway (each fills the GPU); putting the big weight gradient last lets its whole exchange hide
     // behind its own tensor-core time.

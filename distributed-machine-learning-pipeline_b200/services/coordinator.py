@@ -547,6 +547,8 @@ class GPUCoordinatorService:
         Returns the offset, or None when the heap is full (the caller falls back to the unicast kernels)."""
         key = tuple(addr_of[d.rank] for d in devices)
         slot = comm.heap_slots.get(key)
+        # (a buffer may be longer than the part this collective covers: the whole buffer moves)
+        nbytes = max([nbytes] + [d.local.backend.size(addr_of[d.rank]) for d in devices])
         if slot is None or slot[1] < nbytes:
             cap = max(4096, (nbytes + 4095) // 4096 * 4096)
             try:

@@ -277,3 +277,61 @@ def test_grpc_client_trains_data_parallel_over_the_contract(cluster):
         assert np.abs(w - rw).max() < 1e-5 and np.abs(b - rb).max() < 1e-5
     assert all(np.isfinite(s["loss"]) for s in stats) and 0.0 <= stats[-1]["accuracy"] <= 1.0
     t.close()
+
+
+def test_symmetric_heap_placement_logic():
+    """Host logic of the multicast heap behind AllReduceRing (`_heap_place` / `_allreduce_switch`) against stand-ins for
+    the arena and the CUDA backends: one slot per address tuple at the same offset on every device, sized for the
+    longest buffer, a new slot after growth, None when the heap is full, NVLS only for f32 SUM."""
+    from types import SimpleNamespace
+    from dmlp_b200.runtime.comm import ArenaAllocator
+    from dmlp_b200.services import coordinator as co
+
+    class FakeBackend:
+        def __init__(self, size):
+            self.sizes, self.placed = {0x1000: size}, {}
+
+        def size(self, addr):
+            return self.sizes[addr]
+
+        def adopt(self, addr, ptr, cap):
+            assert self.sizes[addr] <= cap
+            self.placed[addr] = (ptr, cap)
+
+    class FakeHeap:
+        def __init__(self, nbytes):
+            self.uc = {0: 0x10000000, 1: 0x20000000}
+            self.alloc = ArenaAllocator(nbytes)
+            self.calls = []
+
+        def allreduce(self, comm, li, off_in, off_out, count, dev, **kw):
+            self.calls.append((li, off_in, off_out, count, dev, kw))
+
+    bes = [FakeBackend(300_000), FakeBackend(100_000)]
+    devices = [SimpleNamespace(rank=r, local=SimpleNamespace(backend=b)) for r, b in enumerate(bes)]
+    svc = co.GPUCoordinatorService(start_monitor=False)
+    comm = co.Communicator(7, devices)
+    comm.native = SimpleNamespace(local_devs=[0, 1], emulated=False, pick_algo=lambda nbytes, nvls: 4 if nbytes >= 65536 else 1)
+    comm.heap = heap = FakeHeap(1 << 20)
+    addrs = {0: 0x1000, 1: 0x1000}
+    off = svc._heap_place(comm, heap, devices, addrs, 100_000)
+    assert off == 0 and comm.heap_slots[(0x1000, 0x1000)][1] >= 300_000  # the longest buffer decides
+    assert bes[0].placed[0x1000][0] - heap.uc[0] == bes[1].placed[0x1000][0] - heap.uc[1] == off
+    assert svc._heap_place(comm, heap, devices, addrs, 100_000) == off  # same slot again
+    bes[1].sizes[0x1000] = 500_000  # rewritten with more data: a new slot
+    off2 = svc._heap_place(comm, heap, devices, addrs, 100_000)
+    assert off2 > off and comm.heap_slots[(0x1000, 0x1000)][1] >= 500_000
+    bes[0].sizes[0x1000] = 2 << 20
+    assert svc._heap_place(comm, heap, devices, addrs, 100_000) is None  # heap exhausted: caller takes the unicast kernels
+    bes[0].sizes[0x1000], bes[1].sizes[0x1000] = 300_000, 300_000
+    from dmlp_b200.runtime import native
+    # dispatch: f32 SUM + table says NVLS -> one launch per local device on the heap, in place
+    assert svc._allreduce_switch(comm, devices, addrs, 100_000, "f32", pb.SUM, "auto", {}, native, None, None)
+    assert [c[0] for c in heap.calls] == [0, 1] and all(c[1] == c[2] and c[3] == 25_000 for c in heap.calls)
+    assert not svc._allreduce_switch(comm, devices, addrs, 1024, "f32", pb.SUM, "auto", {}, native, None, None)  # table: unicast
+    assert not svc._allreduce_switch(comm, devices, addrs, 100_000, "i32", pb.SUM, "nvls", {}, native, None, None)
+    assert not svc._allreduce_switch(comm, devices, addrs, 100_000, "f32", pb.MAX, "nvls", {}, native, None, None)
+    comm.heap = False
+    with pytest.raises(RuntimeError):
+        svc._allreduce_switch(comm, devices, addrs, 100_000, "f32", pb.SUM, "nvls", {}, native, None, None)
+    assert not svc._allreduce_switch(comm, devices, addrs, 100_000, "f32", pb.SUM, "auto", {}, native, None, None)
