@@ -26,9 +26,12 @@
 #include <stdlib.h>
 #include <string.h>
 
+#include <stdio.h>
+
 #include <mutex>
 #include <new>
 #include <type_traits>
+#include <vector>
 
 namespace dmlp {
 
@@ -851,10 +854,86 @@ static const AlgoRow kAlgoTable[] = {
                                               // NVLS 178 vs 201 us at 64 MiB, 588 vs 761 us at 256 MiB
 };
 
+// The table in force: the built-in rows, overridden per world size by DMLP_ALLREDUCE_TABLE (read once) and by
+// dmlp_allreduce_set_table. Spec: "world:oneshot_max:nvls_min[,world:...]" with byte counts that take a K / M / G
+// suffix (binary) and "never" for "do not pick NVLS", e.g. "8:256K:32M,2:1M:never".
+static std::mutex g_table_mu;
+static std::vector<AlgoRow> g_table;
+static bool g_table_ready = false;
+
+static bool parse_bytes(const char* s, const char* end, size_t* out) {
+  if (end - s == 5 && strncmp(s, "never", 5) == 0) { *out = ~static_cast<size_t>(0); return true; }
+  if (s == end) return false;
+  size_t v = 0;
+  const char* p = s;
+  for (; p < end && *p >= '0' && *p <= '9'; ++p) v = v * 10 + static_cast<size_t>(*p - '0');
+  if (p == s) return false;
+  if (p < end) {
+    const char c = *p++;
+    if (c == 'K' || c == 'k') v <<= 10; else if (c == 'M' || c == 'm') v <<= 20; else if (c == 'G' || c == 'g') v <<= 30; else return false;
+  }
+  if (p != end) return false;
+  *out = v;
+  return true;
+}
+
+// Applies a spec on top of `rows` (kept sorted by world). Returns false on a malformed spec (rows untouched).
+static bool apply_table_spec(const char* spec, std::vector<AlgoRow>* rows) {
+  std::vector<AlgoRow> out = *rows;
+  const char* p = spec;
+  while (*p) {
+    const char* e = strchr(p, ',');
+    if (!e) e = p + strlen(p);
+    const char* c1 = static_cast<const char*>(memchr(p, ':', e - p));
+    const char* c2 = c1 ? static_cast<const char*>(memchr(c1 + 1, ':', e - c1 - 1)) : nullptr;
+    size_t w = 0, one = 0, nv = 0;
+    if (!c1 || !c2 || !parse_bytes(p, c1, &w) || !parse_bytes(c1 + 1, c2, &one) || !parse_bytes(c2 + 1, e, &nv)) return false;
+    if (w < 2 || w > static_cast<size_t>(kMaxRanks)) return false;
+    AlgoRow r{static_cast<int>(w), one, nv};
+    bool found = false;
+    for (AlgoRow& x : out)
+      if (x.world == r.world) { x = r; found = true; }
+    if (!found) {
+      size_t i = 0;
+      while (i < out.size() && out[i].world < r.world) ++i;
+      out.insert(out.begin() + i, r);
+    }
+    p = *e ? e + 1 : e;
+  }
+  *rows = out;
+  return true;
+}
+
+static void table_init_locked() {
+  if (g_table_ready) return;
+  g_table.assign(kAlgoTable, kAlgoTable + sizeof(kAlgoTable) / sizeof(kAlgoTable[0]));
+  const char* e = getenv("DMLP_ALLREDUCE_TABLE");
+  if (e && *e && !apply_table_spec(e, &g_table))
+    fprintf(stderr, "dmlp: ignoring malformed DMLP_ALLREDUCE_TABLE=%s (want world:oneshot_max:nvls_min[,...])\n", e);
+  g_table_ready = true;
+}
+
+// Overrides rows of the dispatcher table for this process (spec as above); NULL or "" restores the built-in table
+// (+ DMLP_ALLREDUCE_TABLE). The thresholds come from sweeps on one box: a different fabric can re-tune without a rebuild.
+extern "C" int dmlp_allreduce_set_table(const char* spec) {
+  std::lock_guard<std::mutex> lk(g_table_mu);
+  if (!spec || !*spec) {
+    g_table_ready = false;
+    table_init_locked();
+    return DMLP_OK;
+  }
+  table_init_locked();
+  if (!apply_table_spec(spec, &g_table))
+    return set_error(DMLP_ERR_INVALID, "dmlp_allreduce_set_table: malformed spec '%s' (want world:oneshot_max:nvls_min[,...])", spec);
+  return DMLP_OK;
+}
+
 extern "C" int dmlp_allreduce_pick_algo_ex(int world, size_t bytes, int nvls_available) {
   if (world <= 1) return DMLP_ALGO_ONESHOT;
-  const AlgoRow* row = &kAlgoTable[0];
-  for (const AlgoRow& r : kAlgoTable)
+  std::lock_guard<std::mutex> lk(g_table_mu);
+  table_init_locked();
+  const AlgoRow* row = &g_table[0];
+  for (const AlgoRow& r : g_table)
     if (r.world <= world) row = &r;  // the largest tabulated world not above this one
   if (nvls_available && bytes >= row->nvls_min) return DMLP_ALGO_NVLS;
   return bytes <= row->oneshot_max ? DMLP_ALGO_ONESHOT : DMLP_ALGO_TWOSHOT;
@@ -865,6 +944,7 @@ extern "C" int dmlp_allreduce_pick_algo(int world, size_t bytes) { return dmlp_a
 extern "C" int dmlp_allreduce(dmlp_comm_t h, int local_idx, const dmlp_allreduce_desc_t* d, void* stream) {
   Comm* c = reinterpret_cast<Comm*>(h);
   DMLP_REQUIRE(c && d, "dmlp_allreduce: null argument");
+  NvtxRange nvtx_ar("dmlp.allreduce");
   DMLP_REQUIRE(d->dtype == DMLP_F32 || d->dtype == DMLP_BF16 || d->dtype == DMLP_U8 || d->dtype == DMLP_I32,
                "dmlp_allreduce: unsupported dtype %d", d->dtype);
   DMLP_REQUIRE(d->op >= DMLP_SUM && d->op <= DMLP_AVG, "dmlp_allreduce: unsupported op %d", d->op);

@@ -1,8 +1,10 @@
 // Host-side helpers shared by all translation units: error plumbing for the C ABI.
 #pragma once
 #include <cuda_runtime.h>
+#include <nvtx3/nvToolsExt.h>
 #include <stdarg.h>
 #include <stdio.h>
+#include <stdlib.h>
 
 #include "../include/dmlp_b200.h"
 
@@ -25,6 +27,20 @@ int set_error(int code, const char* fmt, ...) __attribute__((format(printf, 2, 3
   } while (0)
 
 inline cudaStream_t as_stream(void* s) { return reinterpret_cast<cudaStream_t>(s); }
+
+// NVTX ranges around the host-side phases (trainer runs, graph capture, collective launches), for timelines taken with
+// Nsight Systems / ncu --nvtx. Off unless DMLP_NVTX=1: the reference has no tracing at all.
+inline bool nvtx_enabled() {
+  static const bool on = [] { const char* e = getenv("DMLP_NVTX"); return e && atoi(e) > 0; }();
+  return on;
+}
+struct NvtxRange {
+  bool on;
+  explicit NvtxRange(const char* name) : on(nvtx_enabled()) { if (on) nvtxRangePushA(name); }
+  ~NvtxRange() { if (on) nvtxRangePop(); }
+  NvtxRange(const NvtxRange&) = delete;
+  NvtxRange& operator=(const NvtxRange&) = delete;
+};
 
 // Selects a device for the current scope and restores the caller's device afterwards, so the
 // library never changes the current device behind PyTorch's back.

@@ -458,6 +458,7 @@ extern "C" int dmlp_comm_internal_view(dmlp_comm_t comm, int local_idx, uint32_t
 
 extern "C" int dmlp_allreduce_nvls(dmlp_comm_t comm, int local_idx, const dmlp_nvls_allreduce_desc_t* d, void* stream) {
   DMLP_REQUIRE(comm && d, "dmlp_allreduce_nvls: null argument");
+  NvtxRange nvtx_ar("dmlp.allreduce_nvls");
   DMLP_REQUIRE(d->mc_in && d->mc_out, "dmlp_allreduce_nvls: multicast addresses are required");
   DMLP_REQUIRE(((reinterpret_cast<uintptr_t>(d->mc_in) | reinterpret_cast<uintptr_t>(d->mc_out) |
                  reinterpret_cast<uintptr_t>(d->uc_out) | reinterpret_cast<uintptr_t>(d->mc_out_bf16)) & 15) == 0,

@@ -523,6 +523,7 @@ static int enqueue_step(Trainer* t, int par, bool count_kernels) {
 }
 
 static int capture_graphs(Trainer* t) {
+  NvtxRange nvtx_cap("dmlp.capture_graphs");
   for (int par = 0; par < 2; ++par) {
     DMLP_CUDA_CHECK(cudaStreamBeginCapture(t->s_main, cudaStreamCaptureModeRelaxed));
     int rc = enqueue_step(t, par, false);
@@ -1025,6 +1026,7 @@ extern "C" int dmlp_trainer_run(dmlp_trainer_t h, const float* x_host, const int
                                 float* metrics_out, int use_graph, void* start_event, void* stop_event) {
   Trainer* t = reinterpret_cast<Trainer*>(h);
   DMLP_REQUIRE(t && x_host && y_host && num_batches > 0 && steps >= 0, "dmlp_trainer_run: bad arguments");
+  NvtxRange nvtx_run("dmlp.trainer_run");
   if (t->failed)
     return set_error(DMLP_ERR_ABORTED, "the trainer's communicator is FAILED (a collective watchdog fired earlier); create a new one");
   DeviceGuard g(t->dev);
@@ -1148,6 +1150,7 @@ extern "C" int dmlp_trainer_eval(dmlp_trainer_t h, const float* x_host, const in
                                  double* loss_sum, long long* correct) {
   Trainer* t = reinterpret_cast<Trainer*>(h);
   DMLP_REQUIRE(t && x_host && y_host, "bad arguments");
+  NvtxRange nvtx_eval("dmlp.trainer_eval");
   DeviceGuard g(t->dev);
   const ParamLayout& L = t->lay;
   const int B = t->cfg.batch;

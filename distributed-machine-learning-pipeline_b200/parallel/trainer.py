@@ -23,6 +23,7 @@ import numpy as np
 from ..models.layout import ParamLayout
 from ..runtime import native
 from ..runtime.comm import Communicator
+from ..utils.tracing import traced
 from . import schedule as sched
 
 log = logging.getLogger("dmlp.trainer")
@@ -320,6 +321,7 @@ class Trainer:
         yp = y.ptr if isinstance(y, PinnedArray) else ya.ctypes.data
         return xp, yp, xa.shape[0]
 
+    @traced("dmlp.Trainer.fit")
     def fit(self, x, y, steps: int, first_batch: Optional[int] = None, lr_schedule: Optional[sched.Schedule] = None,
             return_metrics: bool = True, device_timing: bool = False,
             batch_stride: Optional[int] = None) -> Dict[str, float]:
@@ -394,6 +396,7 @@ class Trainer:
             log.info("Training complete.")
         return hist
 
+    @traced("dmlp.Trainer.evaluate")
     def evaluate(self, x, y, label: str = "Final Test Accuracy") -> Dict[str, float]:
         """Forward-only pass over all full batches (reference ``testModel``, client.go:462-502)."""
         xp, yp, n = self._host_ptrs(x, y)

@@ -71,6 +71,18 @@ def peer_matrix(devs: Sequence[int]) -> Dict[str, List[List[int]]]:
     return {"access": sq(acc), "atomics": sq(atom), "perf_rank": sq(perf)}
 
 
+def set_allreduce_table(spec: Optional[str]) -> None:
+    """Overrides rows of the ``algo=auto`` dispatcher table for this process: ``"world:oneshot_max:nvls_min[,...]"`` with
+    K / M / G suffixes and ``never`` (e.g. ``"8:256K:32M,2:1M:never"``); ``None`` / ``""`` restores the built-in table plus
+    ``DMLP_ALLREDUCE_TABLE``. The built-in thresholds come from sweeps on one NVSwitch box (profiles/r2_allreduce_sweep_*)."""
+    native.check(native.lib().dmlp_allreduce_set_table(spec.encode() if spec else None))
+
+
+def pick_algo(world: int, nbytes: int, nvls_available: bool = False) -> int:
+    """``algo=auto`` for ``world`` ranks and a message of ``nbytes`` (no communicator needed)."""
+    return native.lib().dmlp_allreduce_pick_algo_ex(world, nbytes, int(nvls_available))
+
+
 class ArenaAllocator:
     """Bump allocator over the symmetric arena: every rank performs the same sequence of
     allocations, so an offset names the same logical buffer on every rank."""

@@ -147,6 +147,7 @@ def _declare(lib) -> None:
         "dmlp_allreduce": [vp, i32, C.POINTER(AllReduceDesc), vp],
         "dmlp_allreduce_pick_algo": [i32, sz],
         "dmlp_allreduce_pick_algo_ex": [i32, sz, i32],
+        "dmlp_allreduce_set_table": [C.c_char_p],
         "dmlp_p2p_copy": [i32, vp, vp, sz, vp],
         "dmlp_reduce_n": [i32, vp, C.POINTER(vp), i32, sz, i32, i32, vp],
     }

@@ -40,6 +40,7 @@ import numpy as np
 
 from ..proto import gpu_sim as pb
 from ..proto import rpc
+from ..utils.tracing import traced
 from .device import GPUDeviceService
 
 log = logging.getLogger("dmlp.coordinator")
@@ -260,6 +261,7 @@ class GPUCoordinatorService:
             return {}
 
     # ------------------------------------------------------------------ CommInit (:121-192)
+    @traced("dmlp.rpc.coordinator.CommInit")
     def CommInit(self, request, context):
         with self.mu:
             comm_id = self.next_comm_id
@@ -323,6 +325,7 @@ class GPUCoordinatorService:
             comm.native = None
 
     # ------------------------------------------------------------------ Memcpy (:194-240)
+    @traced("dmlp.rpc.coordinator.Memcpy")
     def Memcpy(self, request, context):
         which = request.WhichOneof("either")
         if which == "hostToDevice":
@@ -401,6 +404,7 @@ class GPUCoordinatorService:
             comm.group_active = True
         return pb.GroupStartResponse(success=True)
 
+    @traced("dmlp.rpc.coordinator.GroupEnd")
     def GroupEnd(self, request, context):
         """Ops issued since GroupStart were queued; they are launched back to back here (one fused
         submission), the way ncclGroupEnd flushes a group. The reference only flips a flag."""
@@ -430,6 +434,7 @@ class GPUCoordinatorService:
         return pb.GroupEndResponse(success=True)
 
     # ------------------------------------------------------------------ AllReduceRing (:272-376)
+    @traced("dmlp.rpc.coordinator.AllReduceRing")
     def AllReduceRing(self, request, context):
         comm = self._get(request.commId, context)
         with comm.mu:
@@ -728,6 +733,7 @@ class GPUCoordinatorService:
         return pb.CommFinalizeResponse(success=True)
 
     # ------------------------------------------------------------------ NaiveAllReduce (:611-717)
+    @traced("dmlp.rpc.coordinator.NaiveAllReduce")
     def NaiveAllReduce(self, request, context):
         comm = self._get(request.commId, context)
         with comm.mu:

@@ -27,6 +27,7 @@ from typing import Callable, Dict, Iterable, Optional
 import grpc
 
 from ..proto import gpu_sim as pb
+from ..utils.tracing import traced
 from .backend import AddressError, DeviceBackend, MissingBufferError
 
 log = logging.getLogger("dmlp.device")
@@ -107,6 +108,7 @@ class GPUDeviceService:
             st.recv_addr, st.src_rank, st.initiated_recv = addr, request.srcRank.value, True
         return pb.BeginReceiveResponse(initiated=True)
 
+    @traced("dmlp.rpc.device.StreamSend")
     def StreamSend(self, request_iterator: Iterable, context):
         self._guard_alive(context)
         it = iter(request_iterator)
@@ -183,6 +185,7 @@ class GPUDeviceService:
                     st.status, st.poll = pb.FAILED, None
             return pb.GetStreamStatusResponse(status=st.status)
 
+    @traced("dmlp.rpc.device.Memcpy")
     def Memcpy(self, request, context):
         self._guard_alive(context)
         which = request.WhichOneof("either")
@@ -212,6 +215,7 @@ class GPUDeviceService:
     # The reference's stale stubs declare these and no server implements them. Here they run the MLP on the
     # device that holds the buffers (semantics: services/compute.py); a backend without compute hooks
     # answers UNIMPLEMENTED like the reference.
+    @traced("dmlp.rpc.device.RunForward")
     def RunForward(self, request, context):
         hook = getattr(self.backend, "run_forward", None)
         if hook is None:
@@ -220,6 +224,7 @@ class GPUDeviceService:
         self._run_compute(context, "RunForward", hook, request.inputAddr, request.outputAddr)
         return pb.RunForwardResponse(success=True)
 
+    @traced("dmlp.rpc.device.RunBackward")
     def RunBackward(self, request, context):
         hook = getattr(self.backend, "run_backward", None)
         if hook is None:

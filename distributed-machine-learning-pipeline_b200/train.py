@@ -57,6 +57,9 @@ def main(argv=None) -> int:
     if rank == 0:
         log.info("Loaded %d test samples", xte.shape[0])
 
+    if cfg.allreduce_table:
+        from .runtime.comm import set_allreduce_table
+        set_allreduce_table(cfg.allreduce_table)
     tcfg = TrainerConfig(dims=cfg.dims, batch=cfg.batch, lr=cfg.lr, precision=cfg.precision, allreduce=cfg.allreduce,
                          overlap=cfg.overlap, seed=cfg.seed, watchdog_ms=cfg.watchdog_ms)
     trainer = Trainer(tcfg, device=local, process_group=world > 1)

@@ -34,6 +34,7 @@ class Config:
     allreduce: str = "auto"             # auto | oneshot | twoshot | ring
     overlap: bool = False
     watchdog_ms: int = 10000
+    allreduce_table: str = ""           # rows of the auto dispatcher: "world:oneshot_max:nvls_min,..." (K/M/G, never)
     # services (cmd/*/main.go, gpu_coordinator_server.go:57,103)
     backend: str = "cuda"               # cuda | sim
     coordinator_addr: str = "127.0.0.1:50051"

@@ -222,6 +222,10 @@ int dmlp_allreduce_pick_algo(int world, size_t bytes);
 /* Same with NVLS in the table: nvls_available = both buffers live in multicast-bound memory (dmlp_nvls_*), then
  * DMLP_ALGO_NVLS is returned from the size on at which the in-switch reduction wins (run it with dmlp_allreduce_nvls). */
 int dmlp_allreduce_pick_algo_ex(int world, size_t bytes, int nvls_available);
+/* Overrides rows of that table for this process: "world:oneshot_max:nvls_min[,world:...]", byte counts with an optional
+ * K / M / G suffix, "never" = NVLS is not picked; NULL or "" restores the built-in table (+ the DMLP_ALLREDUCE_TABLE
+ * environment variable, same syntax, read at first use). */
+int dmlp_allreduce_set_table(const char* spec);
 
 /* P2P push copy kernel (StreamSend on real GPUs, gpu_device_server.go:112-181): launched on
  * src_dev, dst may be peer memory. */

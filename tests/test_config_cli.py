@@ -66,7 +66,8 @@ def test_graft_entry_build_is_importable_and_links():
     for sym in ("dmlp_gemm", "dmlp_allreduce", "dmlp_allreduce_nvls", "dmlp_mlp_fused_steps", "dmlp_trainer_run",
                 "dmlp_allreduce_sum_f32_noalloc", "dmlp_comm_is_emulated", "dmlp_gemm_prof_read",
                 "dmlp_allreduce_noalloc_status", "dmlp_mlp_fused_steps_gx", "dmlp_mlp_fused_set_fault", "dmlp_input_exchange",
-                "dmlp_trainer_set_fault", "dmlp_trainer_state", "dmlp_allreduce_pick_algo_ex", "dmlp_trainer_pipelined_layers"):
+                "dmlp_trainer_set_fault", "dmlp_trainer_state", "dmlp_allreduce_pick_algo_ex", "dmlp_trainer_pipelined_layers", "dmlp_allreduce_set_table",
+                "dmlp_wgrad_rs_prof_read"):
         assert hasattr(lib, sym), sym
 
 
@@ -91,3 +92,29 @@ def test_allreduce_dispatcher_table():
     assert pick(8, 512 << 10, 0) == one and pick(8, 1 << 20, 0) == two
     assert pick(8, 16 << 20, 1) == two and pick(8, 64 << 20, 1) == nvls and pick(8, 64 << 20, 0) == two
     assert pick(4, 64 << 20, 1) == nvls and pick(2, 1 << 30, 1) == two  # (no multicast win on two ranks)
+
+
+def test_allreduce_dispatcher_table_can_be_overridden():
+    """Thresholds are data, not code: rows can be replaced per process (`set_allreduce_table`, Config.allreduce_table,
+    DMLP_ALLREDUCE_TABLE) and the built-in table comes back with an empty spec."""
+    import pytest
+    from dmlp_b200.runtime import native
+    if not native.available():
+        pytest.skip("native library not built yet")
+    from dmlp_b200.runtime.comm import pick_algo, set_allreduce_table
+    one, two, nvls = (native.ALGO_BY_NAME[k] for k in ("oneshot", "twoshot", "nvls"))
+    try:
+        set_allreduce_table("8:256K:32M,2:1M:never,5:64K:1G")
+        assert pick_algo(8, 256 << 10) == one and pick_algo(8, (256 << 10) + 4) == two
+        assert pick_algo(8, 32 << 20, True) == nvls and pick_algo(8, (32 << 20) - 4, True) == two
+        assert pick_algo(2, 1 << 20) == one and pick_algo(2, 2 << 20) == two and pick_algo(2, 1 << 30, True) == two
+        assert pick_algo(5, 64 << 10) == one and pick_algo(5, 128 << 10) == two  # a new row between 4 and 6
+        assert pick_algo(4, 1 << 20) == one  # untouched rows keep the built-in values
+        assert pick_algo(7, 512 << 10) == one and pick_algo(7, 1 << 20) == two  # 7 ranks read the row of 6
+        for bad in ("8:256K", "x:1:2", "8:1Q:2", "1:1K:1K", "9:1K:1K", "8:1K:1K,,"):
+            with pytest.raises(native.NativeError):
+                set_allreduce_table(bad)
+        assert pick_algo(8, 256 << 10) == one and pick_algo(8, (256 << 10) + 4) == two  # a bad spec changes nothing
+    finally:
+        set_allreduce_table(None)
+    assert pick_algo(8, 512 << 10) == one and pick_algo(8, 1 << 20) == two and pick_algo(8, 64 << 20, True) == nvls

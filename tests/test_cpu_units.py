@@ -231,3 +231,35 @@ def test_fault_spec_parsing():
     for bad in ("dead-rank:3", "rank:1@step:2", "dead-rank:x@step:2", "dead-rank:1@epoch:2"):
         with pytest.raises(ValueError):
             parse_fault(bad)
+
+
+def test_nvtx_tracing_is_a_no_op_without_a_gpu(monkeypatch):
+    """utils/tracing.py: ranges and the decorator work with DMLP_NVTX on or off, with or without CUDA (here: without)."""
+    from dmlp_b200.utils import tracing
+    calls = []
+
+    @tracing.traced("dmlp.test")
+    def f(a, b=2):
+        calls.append((a, b))
+        return a + b
+
+    monkeypatch.delenv("DMLP_NVTX", raising=False)
+    assert not tracing.enabled() and f(1) == 3
+    monkeypatch.setenv("DMLP_NVTX", "1")
+    assert tracing.enabled() and f(2, b=5) == 7 and f.__name__ == "f"
+    with tracing.nvtx_range("dmlp.block"):
+        calls.append("inside")
+    assert calls == [(1, 2), (2, 5), "inside"]
+    # with a tracer bound, push / pop bracket the call even when it raises
+    pushed = []
+    monkeypatch.setattr(tracing, "_PUSH", lambda n: pushed.append(("push", n)))
+    monkeypatch.setattr(tracing, "_POP", lambda: pushed.append(("pop",)))
+
+    @tracing.traced("dmlp.boom")
+    def boom():
+        raise ValueError("x")
+
+    import pytest
+    with pytest.raises(ValueError):
+        boom()
+    assert pushed == [("push", "dmlp.boom"), ("pop",)]
