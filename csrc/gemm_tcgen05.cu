@@ -1042,9 +1042,15 @@ int dmlp::gemm_plan_create(const dmlp_gemm_desc_t* d, GemmPlan* plan) {
 
 bool dmlp::gemm_plan_rs_eligible(const GemmPlan* plan, int world) {
   const GemmParams& p = plan->p;
-  const int tm = (plan->key & 8) ? 256 : 128;
-  return world >= 2 && world <= 8 && p.epi2 && (plan->key & 3) == 3 && p.out_f32 != nullptr && p.out_bf16 == nullptr && p.M % tm == 0 &&
-         p.N % p.block_n == 0 && (p.block_n / 2) % 32 == 0 && plan->total_tiles % world == 0;
+  const bool two = (plan->key & 8) != 0;
+  const int tm = two ? 256 : 128;
+  // Validated on hardware for CTA-pair plans with 256-column tiles (2 and 8 GPUs, bf16 and tf32); the single-CTA / narrower
+  // tile instantiations follow the same index arithmetic but stay opt-in (DMLP_WGRAD_RS_ANY=1) until they have been run.
+  static int any_env = -1;
+  if (any_env < 0) { const char* e = getenv("DMLP_WGRAD_RS_ANY"); any_env = (e && atoi(e) > 0) ? 1 : 0; }
+  if (!any_env && !(two && p.block_n == 256)) return false;
+  return world >= 2 && world <= 8 && p.epi2 && (plan->key & 3) == 3 && p.out_f32 != nullptr && p.out_bf16 == nullptr &&
+         p.M % tm == 0 && p.N % p.block_n == 0 && (p.block_n / 2) % 32 == 0 && plan->total_tiles % world == 0;
 }
 
 int dmlp::gemm_plan_enable_rs(GemmPlan* plan, int world, int rank, float* const* slots, uint32_t* const* counts,

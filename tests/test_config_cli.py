@@ -118,3 +118,21 @@ def test_allreduce_dispatcher_table_can_be_overridden():
     finally:
         set_allreduce_table(None)
     assert pick_algo(8, 512 << 10) == one and pick_algo(8, 1 << 20) == two and pick_algo(8, 64 << 20, True) == nvls
+
+
+def test_tsan_run_of_the_host_runtime():
+    """ThreadSanitizer over the native runtime's shared host state (dispatcher table, per-thread error slot): opt-in
+    (DMLP_RUN_TSAN=1, ~2 min of nvcc), the recorded run is profiles/r2_tsan_host.txt."""
+    import os
+    import shutil
+    import subprocess
+    import pytest
+    if os.environ.get("DMLP_RUN_TSAN", "0") in ("", "0"):
+        pytest.skip("set DMLP_RUN_TSAN=1 to rebuild the host runtime with -fsanitize=thread and run the driver")
+    if not (shutil.which("nvcc") or os.path.exists("/usr/local/cuda/bin/nvcc")):
+        pytest.skip("no nvcc")
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    r = subprocess.run(["bash", os.path.join(root, "scripts", "tsan_host_runtime.sh")], capture_output=True, text=True, timeout=1200)
+    out = r.stdout + r.stderr
+    assert r.returncode == 0 and "0 inconsistencies, table restored: yes" in out, out[-3000:]
+    assert "WARNING: ThreadSanitizer" not in out, out[-3000:]
