@@ -537,13 +537,13 @@ class GPUCoordinatorService:
         """The communicator's symmetric heap, created on first use (``DMLP_SERVICE_HEAP_MB`` per device, default 64;
         0 disables). ``False`` when the device set cannot have one (emulated ranks, no multicast support)."""
         if comm.heap is None:
-            from ..runtime.nvls import NvlsArena, NvlsUnavailable
+            from ..runtime.nvls import NvlsArena
             mb = int(os.environ.get("DMLP_SERVICE_HEAP_MB", "64"))
             comm.heap = False
             if mb > 0 and not comm.native.emulated:
                 try:
                     comm.heap = NvlsArena.local(list(comm.native.local_devs), mb << 20)
-                except (NvlsUnavailable, Exception) as e:
+                except Exception as e:  # NvlsUnavailable (no multicast on this box) or any driver refusal: not fatal
                     log.info("communicator %d: no symmetric heap (%s); collectives stay on unicast peer memory", comm.id, e)
         return comm.heap
 
