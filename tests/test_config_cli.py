@@ -136,3 +136,23 @@ def test_tsan_run_of_the_host_runtime():
     out = r.stdout + r.stderr
     assert r.returncode == 0 and "0 inconsistencies, table restored: yes" in out, out[-3000:]
     assert "WARNING: ThreadSanitizer" not in out, out[-3000:]
+
+
+def test_pip_install_into_a_target_directory(tmp_path):
+    """setup.py: the hyphenated source directory installs as the import package `dmlp_b200` (sub-packages, console
+    scripts, the in-tree native library as package data). Python side only here (DMLP_SKIP_NATIVE_BUILD=1)."""
+    import os
+    import subprocess
+    import sys
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    target = os.path.join(root, "build", "pipcheck")
+    env = dict(os.environ, DMLP_SKIP_NATIVE_BUILD="1")
+    r = subprocess.run([sys.executable, "-m", "pip", "install", "--no-index", "--no-build-isolation", "--no-deps", "--upgrade",
+                        "--target", target, root], capture_output=True, text=True, env=env, timeout=600)
+    assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-2000:]
+    code = ("import dmlp_b200, dmlp_b200.services.coordinator, dmlp_b200.proto.gpu_sim, dmlp_b200.parallel.schedule;"
+            "print(dmlp_b200.__file__)")
+    r = subprocess.run([sys.executable, "-c", code], capture_output=True, text=True, cwd=str(tmp_path),
+                       env=dict(os.environ, PYTHONPATH=target), timeout=300)
+    assert r.returncode == 0 and os.path.join("pipcheck", "dmlp_b200") in r.stdout, r.stdout + r.stderr
+    assert os.path.exists(os.path.join(target, "bin", "dmlp-train"))
