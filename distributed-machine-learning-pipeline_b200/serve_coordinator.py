@@ -25,14 +25,28 @@ def main(argv=None) -> int:
     ap.add_argument("--device-ids", default=",".join(map(str, srv.DEFAULT_DEVICE_IDS)))
     ap.add_argument("--mem-size", default=hex(srv.DEFAULT_MEM_SIZE))
     ap.add_argument("--cuda-devices", default="")
+    ap.add_argument("--metrics-port", type=int, default=0,
+                    help="serve Prometheus metrics (RPC counts / latencies, communicator states) on this port; 0 = off")
     a = ap.parse_args(argv)
     logging.basicConfig(level=logging.INFO, format="%(asctime)s %(message)s")
+    dev_icpt = coord_icpt = registry = None
+    if a.metrics_port:
+        from .services import observability as obs
+        registry = obs.new_registry()
+        coord_icpt = [obs.MetricsInterceptor("GPUCoordinator", registry)]
+        dev_icpt = [obs.MetricsInterceptor("GPUDevice", registry)]
     devs = []
     if a.with_devices:
         devs = srv.start_devices(a.backend, srv.parse_int_list(a.device_ports), srv.parse_int_list(a.device_ids),
-                                 int(a.mem_size, 0), srv.parse_int_list(a.cuda_devices) or None, a.host)
+                                 int(a.mem_size, 0), srv.parse_int_list(a.cuda_devices) or None, a.host,
+                                 interceptors=dev_icpt)
     coord = srv.start_coordinator_server(f"{a.host}:{a.port}", health_interval=a.health_interval,
-                                         probe_timeout=a.probe_timeout, watchdog_ms=a.watchdog_ms)
+                                         probe_timeout=a.probe_timeout, watchdog_ms=a.watchdog_ms,
+                                         interceptors=coord_icpt)
+    if a.metrics_port:
+        obs.watch_communicators(registry, coord.service)
+        obs.start_http_exporter(registry, a.metrics_port, a.host)
+        logging.getLogger("dmlp.server").info("metrics on http://%s:%d/metrics", a.host, a.metrics_port)
     stop = threading.Event()
     for sig in (signal.SIGINT, signal.SIGTERM):
         signal.signal(sig, lambda *_: stop.set())

@@ -20,11 +20,18 @@ def main(argv=None) -> int:
     ap.add_argument("--mem-size", default=hex(srv.DEFAULT_MEM_SIZE))
     ap.add_argument("--cuda-devices", default="", help="CUDA ordinal per server (default 0,1,2,...)")
     ap.add_argument("--host", default="127.0.0.1")
+    ap.add_argument("--metrics-port", type=int, default=0, help="serve Prometheus metrics (RPC counts / latencies); 0 = off")
     a = ap.parse_args(argv)
     logging.basicConfig(level=logging.INFO, format="%(asctime)s %(message)s")
     ports, ids = srv.parse_int_list(a.ports), srv.parse_int_list(a.device_ids)
     ordinals = srv.parse_int_list(a.cuda_devices) or None
-    devs = srv.start_devices(a.backend, ports, ids, int(a.mem_size, 0), ordinals, a.host)
+    icpt = None
+    if a.metrics_port:
+        from .services import observability as obs
+        registry = obs.new_registry()
+        icpt = [obs.MetricsInterceptor("GPUDevice", registry)]
+        obs.start_http_exporter(registry, a.metrics_port, a.host)
+    devs = srv.start_devices(a.backend, ports, ids, int(a.mem_size, 0), ordinals, a.host, interceptors=icpt)
     stop = threading.Event()
     for sig in (signal.SIGINT, signal.SIGTERM):
         signal.signal(sig, lambda *_: stop.set())

@@ -50,9 +50,9 @@ class RunningCoordinator:
 
 
 def start_device_server(backend: DeviceBackend, addr: str = "127.0.0.1:0", register_local: bool = True,
-                        max_workers: int = 8) -> RunningDevice:
+                        max_workers: int = 8, interceptors: Optional[list] = None) -> RunningDevice:
     svc = GPUDeviceService(backend)
-    server = rpc.make_server(max_workers=max_workers)
+    server = rpc.make_server(max_workers=max_workers, interceptors=interceptors)
     rpc.add_service(server, "GPUDevice", svc)
     host = addr.rsplit(":", 1)[0]
     port = server.add_insecure_port(addr)
@@ -67,9 +67,10 @@ def start_device_server(backend: DeviceBackend, addr: str = "127.0.0.1:0", regis
 
 
 def start_coordinator_server(addr: str = "127.0.0.1:0", service: Optional[GPUCoordinatorService] = None,
-                             max_workers: int = 16, **service_kwargs) -> RunningCoordinator:
+                             max_workers: int = 16, interceptors: Optional[list] = None,
+                             **service_kwargs) -> RunningCoordinator:
     svc = service or GPUCoordinatorService(**service_kwargs)
-    server = rpc.make_server(max_workers=max_workers)
+    server = rpc.make_server(max_workers=max_workers, interceptors=interceptors)
     rpc.add_service(server, "GPUCoordinator", svc)
     host = addr.rsplit(":", 1)[0]
     port = server.add_insecure_port(addr)
@@ -81,13 +82,15 @@ def start_coordinator_server(addr: str = "127.0.0.1:0", service: Optional[GPUCoo
 
 
 def start_devices(backend: str, ports: Sequence[int], device_ids: Sequence[int], mem_size: int,
-                  cuda_ordinals: Optional[Sequence[int]] = None, host: str = "127.0.0.1") -> List[RunningDevice]:
+                  cuda_ordinals: Optional[Sequence[int]] = None, host: str = "127.0.0.1",
+                  interceptors: Optional[list] = None) -> List[RunningDevice]:
     out = []
     for i, (port, did) in enumerate(zip(ports, device_ids)):
         ordinal = None
         if backend == "cuda":
             ordinal = cuda_ordinals[i] if cuda_ordinals else i
-        out.append(start_device_server(make_backend(backend, did, mem_size, ordinal), f"{host}:{port}"))
+        out.append(start_device_server(make_backend(backend, did, mem_size, ordinal), f"{host}:{port}",
+                                       interceptors=interceptors))
     return out
 
 
