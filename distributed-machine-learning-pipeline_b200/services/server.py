@@ -12,7 +12,7 @@ from typing import List, Optional, Sequence, Tuple
 
 import grpc
 
-from ..proto import rpc
+from ..proto import health, rpc
 from .backend import DeviceBackend, make_backend
 from .coordinator import GPUCoordinatorService, register_local_device, unregister_local_device
 from .device import GPUDeviceService
@@ -54,6 +54,8 @@ def start_device_server(backend: DeviceBackend, addr: str = "127.0.0.1:0", regis
     svc = GPUDeviceService(backend)
     server = rpc.make_server(max_workers=max_workers, interceptors=interceptors)
     rpc.add_service(server, "GPUDevice", svc)
+    # standard health protocol: a device that was marked dead (fault injection / lost GPU) reports NOT_SERVING
+    health.add_health_service(server, ["gpu_sim.GPUDevice"], lambda name: not svc.backend.dead)
     host = addr.rsplit(":", 1)[0]
     port = server.add_insecure_port(addr)
     if port == 0:
@@ -72,6 +74,7 @@ def start_coordinator_server(addr: str = "127.0.0.1:0", service: Optional[GPUCoo
     svc = service or GPUCoordinatorService(**service_kwargs)
     server = rpc.make_server(max_workers=max_workers, interceptors=interceptors)
     rpc.add_service(server, "GPUCoordinator", svc)
+    health.add_health_service(server, ["gpu_sim.GPUCoordinator"], lambda name: not svc._stop.is_set())
     host = addr.rsplit(":", 1)[0]
     port = server.add_insecure_port(addr)
     if port == 0:

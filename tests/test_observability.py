@@ -52,3 +52,29 @@ def test_rpc_metrics_and_communicator_states_are_exported():
         coord.stop()
         for d in devs:
             d.stop()
+
+
+def test_standard_grpc_health_protocol():
+    """grpc.health.v1.Health/Check on both servers: SERVING while alive, NOT_SERVING for a device marked dead, NOT_FOUND
+    for a service the server does not host, UNAVAILABLE once the server is gone."""
+    from dmlp_b200.proto import health
+    dev = srv.start_device_server(make_backend("sim", 1, 0x2000, 0))
+    coord = srv.start_coordinator_server(start_monitor=False)
+    try:
+        dch, cch = rpc.insecure_channel(dev.addr), rpc.insecure_channel(coord.addr)
+        assert health.check(dch) == health.SERVING and health.check(dch, "gpu_sim.GPUDevice") == health.SERVING
+        assert health.check(cch) == health.SERVING and health.check(cch, "gpu_sim.GPUCoordinator") == health.SERVING
+        with pytest.raises(grpc.RpcError) as e:
+            health.check(cch, "gpu_sim.GPUDevice")
+        assert e.value.code() == grpc.StatusCode.NOT_FOUND
+        dev.service.backend.dead = True
+        assert health.check(dch) == health.NOT_SERVING
+        dev.service.backend.dead = False
+        # the contract's own RPCs are untouched by the extra service
+        assert rpc.DeviceStub(dch).GetDeviceMetadata(pb.GetDeviceMetadataRequest()).metadata.deviceId.value == 1
+    finally:
+        coord.stop()
+        dev.stop()
+    with pytest.raises(grpc.RpcError) as e:
+        health.check(rpc.insecure_channel(dev.addr), timeout=1.0)
+    assert e.value.code() in (grpc.StatusCode.UNAVAILABLE, grpc.StatusCode.DEADLINE_EXCEEDED)
