@@ -145,6 +145,9 @@ static int dev_alloc(Trainer* t, size_t bytes, void** out) {
     if (_rc) return _rc; \
   } while (0)
 
+static_assert(dmlp::kPadXDone + DMLP_MAX_RANKS <= dmlp::kPadRsBase && (dmlp::kPadRsBase + dmlp::kPadRsWords) * 4 <= 64 * 1024,
+              "the reduce-scatter counters must sit behind the other users of the signal pad and inside its 64 KiB");
+
 // Picks the layers whose weight gradient goes through the fused wgrad -> reduce-scatter -> SGD -> all-gather pipeline
 // (layer-by-layer overlap on a real multi-GPU communicator, big layers whose tiles divide among the ranks) and rewires
 // their wgrad plans. DMLP_WGRAD_RS=0 turns it off, DMLP_WGRAD_RS_MIN_KB moves the size threshold (default 8 MiB).
